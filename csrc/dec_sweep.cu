@@ -1,0 +1,622 @@
+// Decoder sweeps for ProdLDA-type models on sm_100a (tcgen05 + TMEM + TMA).
+//
+// The decoder of the reference (src/models/base/pytorchavitm/avitm_network/decoder_network.py:121-126,
+// loss in avitm.py:203-229) is  softmax_V( BatchNorm_V( theta . beta ) )  followed by the BoW
+// negative log-likelihood.  The [B,V] logits never exist in HBM here: every sweep recomputes a
+// 128x128 logits tile with one short tcgen05.mma K-loop (K = n_components) into TMEM and consumes
+// it in the epilogue warps.
+//
+// One kernel skeleton, two operand families:
+//   ROW family: stationary A = 128 documents of theta_c [B,Kp]  (K-major),
+//               streamed  B = 128-word tiles of beta [Kp,V]      (MN-major for MMA1).
+//               TMEM lane = document  -> per-document reductions are thread-local.
+//   COL family: stationary A = 128-word slab of beta [Kp,V]      (MN-major),
+//               streamed  B = 128-document tiles of theta_c      (K-major for MMA1).
+//               TMEM lane = word      -> per-word (BatchNorm) reductions are thread-local.
+// Modes with a second MMA write the epilogue result P (bf16, 128x128) to shared memory and
+// accumulate   D2 += P . (streamed tile)   in a persistent TMEM accumulator; the streamed tile's
+// shared-memory image is reused by MMA2 with the other major-ness, so beta and theta_c each live
+// in ONE global layout:
+//   ROW_GRAD : D2[doc, topic]  = dLogit . beta^T      (d theta)
+//   COL_GRAD : D2[word, topic] = dLogit^T . theta_c   (d beta, transposed)
+//
+// Warp roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
+// warps 4..7 = epilogue (warp w owns TMEM lanes 32*(w-4)..+31).
+#include "ptx.cuh"
+#include "tmap.h"
+#include "../include/gfedntm_kernels.h"
+
+namespace gf {
+
+enum : int {
+  ROW_LOGITS = 0,  // out[b,v] = theta_c[b].beta[:,v]                      (debug / inference)
+  ROW_LSE = 1,     // per (doc, chunk) online log-sum-exp partials of BN'd logits
+  ROW_GRAD = 2,    // d theta (dense part)
+  COL_STATS = 3,   // per-word second moment over the batch -> BatchNorm rstd, running stats
+  COL_GRAD = 4,    // pass 1: BN-backward column sums; pass 2: d beta (dense part)
+  COL_LOGITS = 5   // out[b,v] via the COL family                          (debug)
+};
+
+constexpr int kTile = 128;
+constexpr int kThreads = 256;
+constexpr int kMaxStages = 4;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+struct SweepParams {
+  int mode;
+  int B, V, K, Kp;
+  int n_stat, n_stream, n_chunks, n_pass, stages;
+  const float4* sb_stream;  // side band per streamed index (padded to a multiple of 128)
+  // generic
+  float* out;               // LOGITS modes: [B,V] fp32
+  // ROW_LSE
+  float2* lse_part;         // [B, n_chunks] (max in log2 units, sum)
+  // ROW_GRAD
+  const float2* doc_const;  // [B] {lse*log2e, S*ln2}
+  float* dtheta;            // [B, Kp] fp32 (atomicAdd)
+  // COL_*
+  float4* colc;             // [Vpad] {rstd*log2e, bias, alpha, gamma}: written by COL_STATS / COL_GRAD
+  const float* theta_mean;  // [K] batch mean of theta (COL_STATS, for running_mean)
+  const __nv_bfloat16* beta_bf;  // [Kp, ldb] bf16 shadow (COL_STATS mean, epilogue reads)
+  int ldb;
+  float* running_mean;      // [V] (may be null)
+  float* running_var;       // [V]
+  float bn_eps, bn_momentum;
+  int use_running;          // eval mode: normalise with running stats (COL_STATS only)
+  const float* asp;         // [V] sparse part of sum_b dy
+  const float* csp;         // [V] sparse part of sum_b dy*y
+  float* dbeta;             // [K, ldg] fp32 gradient (COL_GRAD output)
+  int ldg;
+  const float* corr;        // [V, Kp] sparse correction to d beta^T (may be null)
+  const int* colptr;        // [V+1] CSC pointer of the batch (with corr)
+};
+
+struct Smem {
+  uint8_t* a;
+  uint8_t* b[kMaxStages];
+  float4* sb[kMaxStages];
+  uint8_t* p;
+  uint64_t* a_full;
+  uint64_t* a_empty;
+  uint64_t* b_full;   // [stages]
+  uint64_t* b_empty;  // [stages]
+  uint64_t* d1_full;  // [2]
+  uint64_t* d1_empty; // [2]
+  uint64_t* p_full;
+  uint64_t* p_empty;
+  uint64_t* d2_full;
+  uint64_t* d2_empty;
+  uint32_t* tmem_ptr;
+};
+
+template <int kKChunks, bool kRow, bool kHasMMA2>
+__global__ void __launch_bounds__(kThreads, 1)
+sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant__ CUtensorMap tm_beta,
+             const SweepParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr uint32_t kOperandBytes = kKChunks * 16384u;  // both A and a B stage
+  constexpr uint32_t kSbBytes = kTile * sizeof(float4);
+  const int stages = p.stages;
+  const int Kp = p.Kp;
+
+  Smem s;
+  s.a = base;
+  uint8_t* cur = base + kOperandBytes;
+  for (int i = 0; i < kMaxStages; ++i) {
+    s.b[i] = cur;
+    s.sb[i] = reinterpret_cast<float4*>(cur + kOperandBytes);
+    if (i < stages) cur += kOperandBytes + kSbBytes;
+  }
+  s.p = cur;
+  if (kHasMMA2) cur += 32768;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(cur);
+  s.a_full = bars + 0;
+  s.a_empty = bars + 1;
+  s.b_full = bars + 2;
+  s.b_empty = bars + 2 + kMaxStages;
+  s.d1_full = bars + 2 + 2 * kMaxStages;
+  s.d1_empty = s.d1_full + 2;
+  s.p_full = s.d1_empty + 2;
+  s.p_empty = s.p_full + 1;
+  s.d2_full = s.p_empty + 1;
+  s.d2_empty = s.d2_full + 1;
+  s.tmem_ptr = reinterpret_cast<uint32_t*>(s.d2_empty + 1);
+
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_theta);
+    tma_prefetch_desc(&tm_beta);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(s.a_full, 1);
+    mbar_init(s.a_empty, 1);
+    for (int i = 0; i < kMaxStages; ++i) {
+      mbar_init(&s.b_full[i], 1);
+      mbar_init(&s.b_empty[i], 1 + 128);  // MMA commit + every epilogue thread
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s.d1_full[i], 1);
+      mbar_init(&s.d1_empty[i], 128);
+    }
+    mbar_init(s.p_full, 128);
+    mbar_init(s.p_empty, 1);
+    mbar_init(s.d2_full, 1);
+    mbar_init(s.d2_empty, 128);
+    mbar_fence_init();
+  }
+  constexpr uint32_t kTmemCols = kHasMMA2 ? 512 : 256;
+  if (warp == 2) tmem_alloc<kTmemCols>(s.tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *s.tmem_ptr;
+
+  const int total_work = p.n_stat * p.n_chunks;
+  const int n_ksteps = Kp >> 4;
+  // bytes landed per stationary / streamed tile
+  const uint32_t theta_tile_bytes = kKChunks * 16384u;      // kKChunks boxes {64 x 128 rows}
+  const uint32_t beta_tile_bytes = 2u * (uint32_t)Kp * 128u;  // 2 boxes {64 words x Kp rows}
+  const uint32_t a_bytes = kRow ? theta_tile_bytes : beta_tile_bytes;
+  const uint32_t b_bytes = (kRow ? beta_tile_bytes : theta_tile_bytes) + kSbBytes;
+
+  if (warp == 0) {
+    // ============================ TMA producer ============================
+    if (lane == 0) {
+      uint32_t a_it = 0, b_it = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int stat = w / p.n_chunks, chunk = w - stat * p.n_chunks;
+        const int t0 = (int)(((long long)chunk * p.n_stream) / p.n_chunks);
+        const int t1 = (int)(((long long)(chunk + 1) * p.n_stream) / p.n_chunks);
+        mbar_wait(s.a_empty, (a_it & 1) ^ 1);
+        mbar_arrive_expect_tx(s.a_full, a_bytes);
+        if (kRow) {
+          for (int kc = 0; kc < kKChunks; ++kc)
+            tma_load_2d(s.a + kc * 16384, &tm_theta, s.a_full, kc * 64, stat * kTile);
+        } else {
+          for (int nb = 0; nb < 2; ++nb)
+            tma_load_2d(s.a + nb * Kp * 128, &tm_beta, s.a_full, stat * kTile + nb * 64, 0);
+        }
+        ++a_it;
+        for (int pass = 0; pass < p.n_pass; ++pass) {
+          for (int t = t0; t < t1; ++t) {
+            const int st = b_it % stages;
+            mbar_wait(&s.b_empty[st], ((b_it / stages) & 1) ^ 1);
+            mbar_arrive_expect_tx(&s.b_full[st], b_bytes);
+            if (kRow) {
+              for (int nb = 0; nb < 2; ++nb)
+                tma_load_2d(s.b[st] + nb * Kp * 128, &tm_beta, &s.b_full[st], t * kTile + nb * 64, 0);
+            } else {
+              for (int kc = 0; kc < kKChunks; ++kc)
+                tma_load_2d(s.b[st] + kc * 16384, &tm_theta, &s.b_full[st], kc * 64, t * kTile);
+            }
+            // side band: 128 float4 = 2 KB, plain bulk copy onto the same barrier
+            asm volatile(
+                "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::
+                    "r"(smem_u32(s.sb[st])),
+                "l"(reinterpret_cast<uint64_t>(p.sb_stream + (size_t)t * kTile)), "r"(kSbBytes),
+                "r"(smem_u32(&s.b_full[st]))
+                : "memory");
+            ++b_it;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================ MMA issuer ============================
+    if (lane == 0) {
+      const uint32_t idesc1 = umma_idesc_bf16(128, 128, kRow ? 0u : 1u, kRow ? 1u : 0u);
+      const uint32_t idesc2 = umma_idesc_bf16(128, (uint32_t)Kp, 0u, kRow ? 0u : 1u);
+      const uint32_t a_base = smem_u32(s.a);
+      const uint32_t p_base = smem_u32(s.p);
+      const uint32_t mn_lbo = (uint32_t)Kp * 128u;  // distance between 64-word blocks of a beta tile
+      uint32_t a_it = 0, b_it = 0, d1_it = 0, p_it = 0, d2_it = 0;
+
+      auto issue_mma2 = [&](int st, bool first) {
+        mbar_wait(s.p_full, p_it & 1);
+        tc_fence_after();
+        const uint32_t b_base = smem_u32(s.b[st]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {  // 128-wide contraction = 8 k-steps of 16
+          const uint64_t da = umma_smem_desc(p_base + (j >> 2) * 16384u + (j & 3) * 32u, 16, 1024);
+          uint64_t db;
+          if (kRow)  // beta tile as K-major B: rows = topics, contraction over words
+            db = umma_smem_desc(b_base + (j >> 2) * mn_lbo + (j & 3) * 32u, 16, 1024);
+          else       // theta tile as MN-major B: rows = documents (contraction), 64-topic blocks
+            db = umma_smem_desc(b_base + j * 2048u, 16384, 1024);
+          umma_f16(tmem + 256, da, db, idesc2, (first && j == 0) ? 0u : 1u);
+        }
+        umma_commit(s.p_empty);
+        umma_commit(&s.b_empty[st]);
+        ++p_it;
+      };
+
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int stat = w / p.n_chunks, chunk = w - stat * p.n_chunks;
+        const int t0 = (int)(((long long)chunk * p.n_stream) / p.n_chunks);
+        const int t1 = (int)(((long long)(chunk + 1) * p.n_stream) / p.n_chunks);
+        mbar_wait(s.a_full, a_it & 1);
+        for (int pass = 0; pass < p.n_pass; ++pass) {
+          const bool m2 = kHasMMA2 && (pass == p.n_pass - 1);
+          int pending = -1;
+          bool first2 = true;
+          if (m2) mbar_wait(s.d2_empty, (d2_it & 1) ^ 1);
+          for (int t = t0; t < t1; ++t) {
+            const int st = b_it % stages;
+            mbar_wait(&s.b_full[st], (b_it / stages) & 1);
+            const uint32_t buf = d1_it & 1;
+            mbar_wait(&s.d1_empty[buf], ((d1_it >> 1) & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t b_base = smem_u32(s.b[st]);
+            for (int j = 0; j < n_ksteps; ++j) {
+              uint64_t da, db;
+              if (kRow) {
+                da = umma_smem_desc(a_base + (j >> 2) * 16384u + (j & 3) * 32u, 16, 1024);
+                db = umma_smem_desc(b_base + j * 2048u, mn_lbo, 1024);
+              } else {
+                da = umma_smem_desc(a_base + j * 2048u, mn_lbo, 1024);
+                db = umma_smem_desc(b_base + (j >> 2) * 16384u + (j & 3) * 32u, 16, 1024);
+              }
+              umma_f16(tmem + buf * 128, da, db, idesc1, j > 0 ? 1u : 0u);
+            }
+            umma_commit(&s.d1_full[buf]);
+            ++d1_it;
+            if (m2) {
+              if (pending >= 0) {
+                issue_mma2(pending, first2);
+                first2 = false;
+              }
+              pending = st;
+            } else {
+              umma_commit(&s.b_empty[st]);
+            }
+            ++b_it;
+          }
+          if (m2) {
+            if (pending >= 0) issue_mma2(pending, first2);
+            umma_commit(s.d2_full);
+            ++d2_it;
+          }
+        }
+        umma_commit(s.a_empty);
+        ++a_it;
+      }
+    }
+  } else if (warp >= 4) {
+    // ============================ epilogue ============================
+    const uint32_t q = warp - 4;
+    const uint32_t row = q * 32 + lane;  // TMEM lane == tile row
+    const uint32_t lane_addr = tmem + ((q * 32) << 16);
+    uint32_t b_it = 0, d1_it = 0, p_it = 0, d2_it = 0;
+    const int mode = p.mode;
+
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      const int stat = w / p.n_chunks, chunk = w - stat * p.n_chunks;
+      const int t0 = (int)(((long long)chunk * p.n_stream) / p.n_chunks);
+      const int t1 = (int)(((long long)(chunk + 1) * p.n_stream) / p.n_chunks);
+      const int grow = stat * kTile + (int)row;  // global doc (ROW) or word (COL) index
+
+      // ---- per-work-item thread state
+      float acc0 = 0.f, acc1 = 0.f;   // ROW_LSE: (max2, sum); COL: (a, c') / sumsq
+      float c_r2 = 0.f, c_alpha = 0.f, c_gamma = 0.f, c_rstd = 0.f, c_bias = 0.f;
+      float d_lse2 = 0.f, d_sp = 0.f;
+      if (mode == ROW_LSE) acc0 = -INFINITY;
+      if (mode == ROW_GRAD && grow < p.B) {
+        const float2 dc = p.doc_const[grow];
+        d_lse2 = dc.x;
+        d_sp = dc.y;
+      }
+      if (mode == COL_GRAD && grow < p.V) {
+        const float4 cc = p.colc[grow];
+        c_r2 = cc.x;
+        c_bias = cc.y;
+        c_rstd = cc.x * kLn2;
+      }
+
+      for (int pass = 0; pass < p.n_pass; ++pass) {
+        const bool m2 = kHasMMA2 && (pass == p.n_pass - 1);
+        for (int t = t0; t < t1; ++t) {
+          const int st = b_it % stages;
+          const uint32_t buf = d1_it & 1;
+          mbar_wait(&s.d1_full[buf], (d1_it >> 1) & 1);
+          tc_fence_after();
+          if (m2) mbar_wait(s.p_empty, (p_it & 1) ^ 1);
+          const float4* sb = s.sb[st];
+#pragma unroll 1
+          for (int c = 0; c < 4; ++c) {
+            float v[32];
+            tmem_ld32(lane_addr + buf * 128 + c * 32, v);
+            tmem_ld_wait();
+            const int col0 = t * kTile + c * 32;  // global streamed index of v[0]
+            if (mode == ROW_LOGITS) {
+              if (grow < p.B) {
+                float* o = p.out + (size_t)grow * p.V + col0;
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (col0 + i < p.V) o[i] = v[i];
+              }
+            } else if (mode == COL_LOGITS) {
+              if (grow < p.V) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (col0 + i < p.B) p.out[(size_t)(col0 + i) * p.V + grow] = v[i];
+              }
+            } else if (mode == ROW_LSE) {
+              float cmax = -INFINITY;
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const float4 cc = sb[c * 32 + i];
+                v[i] = fmaf(v[i], cc.x, cc.y);
+                cmax = fmaxf(cmax, v[i]);
+              }
+              const float nm = fmaxf(acc0, cmax);
+              if (nm > -INFINITY) {
+                float sum = acc1 * ex2_approx(acc0 - nm);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) sum += ex2_approx(v[i] - nm);
+                acc1 = sum;
+                acc0 = nm;
+              }
+            } else if (mode == ROW_GRAD) {
+              // dl = rstd*S*p - alpha - gamma*yc ; p = 2^(yc*r2 + bias - lse2)
+              uint32_t pk[16];
+#pragma unroll
+              for (int i = 0; i < 32; i += 2) {
+                const float4 c0 = sb[c * 32 + i];
+                const float4 c1 = sb[c * 32 + i + 1];
+                const float p0 = ex2_approx(fmaf(v[i], c0.x, c0.y) - d_lse2);
+                const float p1 = ex2_approx(fmaf(v[i + 1], c1.x, c1.y) - d_lse2);
+                const float g0 = fmaf(-c0.w, v[i], fmaf(c0.x * d_sp, p0, -c0.z));
+                const float g1 = fmaf(-c1.w, v[i + 1], fmaf(c1.x * d_sp, p1, -c1.z));
+                pk[i >> 1] = pack_bf16(g0, g1);
+              }
+              // P tile, K-major SW128: chunk = (c>>1), slots (c&1)*4 .. +3 of row `row`
+              uint8_t* prow = s.p + (c >> 1) * 16384 + row * 128;
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                const uint32_t slot = ((c & 1) * 4 + g) ^ (row & 7);
+                *reinterpret_cast<uint4*>(prow + slot * 16) =
+                    make_uint4(pk[g * 4], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
+              }
+            } else if (mode == COL_STATS) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) acc0 = fmaf(v[i], v[i], acc0);
+            } else if (mode == COL_GRAD) {
+              if (!m2) {
+                // pass 1: a += S*p ; c' += S*p*yc
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                  const float4 dc = sb[c * 32 + i];  // {lse2_b, S_b, -, -}
+                  const float d = dc.y * ex2_approx(fmaf(v[i], c_r2, c_bias - dc.x));
+                  acc0 += d;
+                  acc1 = fmaf(d, v[i], acc1);
+                }
+              } else {
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {
+                  const float4 d0 = sb[c * 32 + i];
+                  const float4 d1 = sb[c * 32 + i + 1];
+                  const float p0 = ex2_approx(fmaf(v[i], c_r2, c_bias - d0.x));
+                  const float p1 = ex2_approx(fmaf(v[i + 1], c_r2, c_bias - d1.x));
+                  const float g0 = fmaf(-c_gamma, v[i], fmaf(c_rstd * d0.y, p0, -c_alpha));
+                  const float g1 = fmaf(-c_gamma, v[i + 1], fmaf(c_rstd * d1.y, p1, -c_alpha));
+                  pk[i >> 1] = pack_bf16(g0, g1);
+                }
+                uint8_t* prow = s.p + (c >> 1) * 16384 + row * 128;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                  const uint32_t slot = ((c & 1) * 4 + g) ^ (row & 7);
+                  *reinterpret_cast<uint4*>(prow + slot * 16) =
+                      make_uint4(pk[g * 4], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
+                }
+              }
+            }
+          }
+          tc_fence_before();
+          mbar_arrive(&s.d1_empty[buf]);
+          mbar_arrive(&s.b_empty[st]);  // side band of this stage fully consumed
+          ++d1_it;
+          ++b_it;
+          if (m2) {
+            fence_proxy_async_smem();
+            mbar_arrive(s.p_full);
+            ++p_it;
+          }
+        }
+
+        // ---- end of a pass
+        if (mode == COL_GRAD && !m2) {
+          // finalise BN-backward column means, publish the per-word constants
+          if (grow < p.V) {
+            const float invB = 1.0f / (float)p.B;
+            const float abar = (acc0 - p.asp[grow]) * invB;
+            const float cbar = (c_rstd * acc1 - p.csp[grow]) * invB;
+            c_alpha = c_rstd * abar;
+            c_gamma = c_rstd * c_rstd * cbar;
+            p.colc[grow] = make_float4(c_r2, c_bias, c_alpha, c_gamma);
+          }
+        }
+        if (m2) {
+          mbar_wait(s.d2_full, d2_it & 1);
+          tc_fence_after();
+          const bool has_corr = (mode == COL_GRAD) && p.corr != nullptr && grow < p.V &&
+                                (p.colptr[grow + 1] > p.colptr[grow]);
+          for (int c = 0; c * 32 < Kp; ++c) {
+            float v[32];
+            tmem_ld32(lane_addr + 256 + c * 32, v);
+            tmem_ld_wait();
+            if (mode == ROW_GRAD) {
+              if (grow < p.B) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (c * 32 + i < Kp) atomicAdd(&p.dtheta[(size_t)grow * Kp + c * 32 + i], v[i]);
+              }
+            } else {  // COL_GRAD: d beta[k, word]
+              if (grow < p.V) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                  const int k = c * 32 + i;
+                  if (k < p.K) {
+                    float g = v[i];
+                    if (has_corr) g -= p.corr[(size_t)grow * Kp + k];
+                    p.dbeta[(size_t)k * p.ldg + grow] = g;
+                  }
+                }
+              }
+            }
+          }
+          tc_fence_before();
+          mbar_arrive(s.d2_empty);
+          ++d2_it;
+        }
+      }
+
+      // ---- end of work item
+      if (mode == ROW_LSE) {
+        if (grow < p.B) p.lse_part[(size_t)grow * p.n_chunks + chunk] = make_float2(acc0, acc1);
+      } else if (mode == COL_STATS) {
+        if (grow < p.V) {
+          float mean = 0.f;
+          if (p.theta_mean != nullptr) {
+            for (int k = 0; k < p.K; ++k)
+              mean = fmaf(p.theta_mean[k], __bfloat162float(p.beta_bf[(size_t)k * p.ldb + grow]), mean);
+          }
+          const float var = acc0 / (float)p.B;  // biased batch variance of the centred logits
+          float rstd, bias;
+          if (p.use_running) {
+            rstd = rsqrtf(p.running_var[grow] + p.bn_eps);
+            bias = -p.running_mean[grow] * rstd * kLog2e;
+          } else {
+            rstd = rsqrtf(var + p.bn_eps);
+            bias = 0.f;
+            if (p.running_mean != nullptr) {
+              const float mom = p.bn_momentum;
+              const float unb = p.B > 1 ? var * (float)p.B / (float)(p.B - 1) : var;
+              p.running_mean[grow] = (1.f - mom) * p.running_mean[grow] + mom * mean;
+              p.running_var[grow] = (1.f - mom) * p.running_var[grow] + mom * unb;
+            }
+          }
+          p.colc[grow] = make_float4(rstd * kLog2e, bias, 0.f, 0.f);
+        } else if (grow < p.n_stat * kTile) {
+          p.colc[grow] = make_float4(0.f, -INFINITY, 0.f, 0.f);  // padded words never contribute
+        }
+      }
+    }
+  }
+
+  // ---- teardown
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<kTmemCols>(tmem);
+}
+
+template <int kKChunks, bool kRow, bool kHasMMA2>
+static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, SweepParams& p,
+                        cudaStream_t stream) {
+  const size_t operand = (size_t)kKChunks * 16384;
+  const size_t fixed = 1024 + operand + (kHasMMA2 ? 32768 : 0) + 512;
+  const size_t per_stage = operand + kTile * sizeof(float4);
+  int max_smem = 0, dev = 0;
+  GF_CUDA_CHECK(cudaGetDevice(&dev));
+  GF_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  int stages = (int)(((size_t)max_smem - fixed) / per_stage);
+  if (stages > kMaxStages) stages = kMaxStages;
+  GF_ARG_CHECK(stages >= 2, "n_components too large for the fused decoder sweeps (need Kp <= 240)");
+  p.stages = stages;
+  size_t smem = fixed + (size_t)stages * per_stage;
+  if (kHasMMA2 && smem < 120 * 1024) smem = 120 * 1024;  // 512 TMEM columns => one CTA per SM
+  auto kern = sweep_kernel<kKChunks, kRow, kHasMMA2>;
+  GF_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int total = p.n_stat * p.n_chunks;
+  const int occ = kHasMMA2 ? 1 : ((smem <= 110 * 1024) ? 2 : 1);
+  int grid = num_sms() * occ;
+  if (grid > total) grid = total;
+  if (grid < 1) grid = 1;
+  kern<<<grid, kThreads, smem, stream>>>(tm_theta, tm_beta, p);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+static int dispatch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, SweepParams& p,
+                          cudaStream_t stream) {
+  const int kc = (p.Kp + 63) / 64;
+  const bool row = (p.mode == ROW_LOGITS || p.mode == ROW_LSE || p.mode == ROW_GRAD);
+  const bool m2 = (p.mode == ROW_GRAD || p.mode == COL_GRAD);
+#define GF_CASE(KC)                                                                   \
+  case KC:                                                                            \
+    if (row) {                                                                        \
+      if (m2) return launch_sweep<KC, true, true>(tm_theta, tm_beta, p, stream);      \
+      return launch_sweep<KC, true, false>(tm_theta, tm_beta, p, stream);             \
+    } else {                                                                          \
+      if (m2) return launch_sweep<KC, false, true>(tm_theta, tm_beta, p, stream);     \
+      return launch_sweep<KC, false, false>(tm_theta, tm_beta, p, stream);            \
+    }
+  switch (kc) {
+    GF_CASE(1)
+    GF_CASE(2)
+    GF_CASE(3)
+    GF_CASE(4)
+    default:
+      break;
+  }
+#undef GF_CASE
+  fprintf(stderr, "[gfedntm] dec sweep: unsupported Kp=%d\n", p.Kp);
+  return GF_ERR_ARG;
+}
+
+}  // namespace gf
+
+using namespace gf;
+
+extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(a != nullptr, "null args");
+  GF_ARG_CHECK(a->Kp % 16 == 0 && a->Kp >= 16 && a->Kp <= 240, "Kp must be a multiple of 16 in [16,240]");
+  GF_ARG_CHECK(a->K <= a->Kp && a->K > 0, "K");
+  GF_ARG_CHECK(a->ld_theta % 8 == 0 && a->ld_beta % 8 == 0, "bf16 leading dims must be multiples of 8");
+  GF_ARG_CHECK(a->ld_theta >= a->Kp && a->ld_beta >= a->V, "leading dims too small");
+  GF_ARG_CHECK(a->mode >= 0 && a->mode <= 5, "mode");
+  CUtensorMap tm_theta, tm_beta;
+  // theta_c [B, ld_theta] bf16: box = 64 topics x 128 documents
+  int rc = make_tmap_bf16_2d(&tm_theta, a->theta_bf, (uint64_t)a->Kp, (uint64_t)a->B,
+                             (uint64_t)a->ld_theta * 2, 64, 128);
+  if (rc) return rc;
+  // beta [Kp, ld_beta] bf16: box = 64 words x Kp topics; words beyond V read as zero
+  rc = make_tmap_bf16_2d(&tm_beta, a->beta_bf, (uint64_t)a->V, (uint64_t)a->Kp,
+                         (uint64_t)a->ld_beta * 2, 64, (uint32_t)a->Kp);
+  if (rc) return rc;
+
+  SweepParams p{};
+  p.mode = a->mode;
+  p.B = a->B; p.V = a->V; p.K = a->K; p.Kp = a->Kp;
+  const bool row = (a->mode == ROW_LOGITS || a->mode == ROW_LSE || a->mode == ROW_GRAD);
+  const int doc_tiles = (a->B + kTile - 1) / kTile, word_tiles = (a->V + kTile - 1) / kTile;
+  p.n_stat = row ? doc_tiles : word_tiles;
+  p.n_stream = row ? word_tiles : doc_tiles;
+  p.n_chunks = row ? a->n_chunks : 1;
+  GF_ARG_CHECK(p.n_chunks >= 1 && p.n_chunks <= p.n_stream, "n_chunks");
+  p.n_pass = (a->mode == COL_GRAD) ? 2 : 1;
+  p.sb_stream = reinterpret_cast<const float4*>(a->sb_stream);
+  GF_ARG_CHECK(p.sb_stream != nullptr, "sb_stream (padded side band) is required");
+  p.out = a->out;
+  p.lse_part = reinterpret_cast<float2*>(a->lse_part);
+  p.doc_const = reinterpret_cast<const float2*>(a->doc_const);
+  p.dtheta = a->dtheta;
+  p.colc = reinterpret_cast<float4*>(a->colc);
+  p.theta_mean = a->theta_mean;
+  p.beta_bf = reinterpret_cast<const __nv_bfloat16*>(a->beta_bf);
+  p.ldb = a->ld_beta;
+  p.running_mean = a->running_mean;
+  p.running_var = a->running_var;
+  p.bn_eps = a->bn_eps;
+  p.bn_momentum = a->bn_momentum;
+  p.use_running = a->use_running;
+  p.asp = a->asp; p.csp = a->csp;
+  p.dbeta = a->dbeta; p.ldg = a->ld_dbeta;
+  p.corr = a->corr; p.colptr = a->colptr;
+  return dispatch_sweep(tm_theta, tm_beta, p, stream);
+}

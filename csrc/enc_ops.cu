@@ -1,0 +1,573 @@
+// Encoder-side kernels (inference network + latent layer), forward and backward.
+//
+// Ref forward: src/models/base/pytorchavitm/avitm_network/inference_network.py:76-85 and
+// decoder_network.py:102-118; CTM variants contextualized_topic_models/ctm_network/
+// inference_network.py:79-94,160-193.  Ref KL: avitm_network/avitm.py:207-220.
+//
+// The bag-of-words input is consumed as CSR (never densified): the first layer is a sparse
+// row-gather over W1^T [V,H0]; everything after it is [B,H]/[B,K]-sized and runs in one block
+// per 8 documents.  Batch-coupled steps (BatchNorm over the batch) split the work into
+// kernels at the points where a batch-wide reduction must be complete.
+#include "ptx.cuh"
+#include "tmap.h"
+#include "../include/gfedntm_kernels.h"
+
+namespace gf {
+
+constexpr int kMaxH = 256;      // widest supported hidden layer / topic count
+constexpr int kDocsPerBlock = 8;
+
+enum { ACT_SOFTPLUS = 0, ACT_RELU, ACT_SIGMOID, ACT_TANH, ACT_LEAKYRELU, ACT_RRELU, ACT_ELU, ACT_SELU };
+
+__device__ __forceinline__ float act_fwd(int act, float x, float slope) {
+  switch (act) {
+    case ACT_SOFTPLUS: return x > 20.f ? x : log1pf(__expf(x));
+    case ACT_RELU: return fmaxf(x, 0.f);
+    case ACT_SIGMOID: return 1.f / (1.f + __expf(-x));
+    case ACT_TANH: return tanhf(x);
+    case ACT_LEAKYRELU: return x > 0.f ? x : 0.01f * x;
+    case ACT_RRELU: return x >= 0.f ? x : slope * x;
+    case ACT_ELU: return x > 0.f ? x : (__expf(x) - 1.f);
+    case ACT_SELU: return 1.0507009873554805f * (x > 0.f ? x : 1.6732632423543772f * (__expf(x) - 1.f));
+  }
+  return x;
+}
+__device__ __forceinline__ float act_bwd(int act, float x, float slope) {  // d act / d x at pre-activation x
+  switch (act) {
+    case ACT_SOFTPLUS: return x > 20.f ? 1.f : 1.f / (1.f + __expf(-x));
+    case ACT_RELU: return x > 0.f ? 1.f : 0.f;
+    case ACT_SIGMOID: { float s = 1.f / (1.f + __expf(-x)); return s * (1.f - s); }
+    case ACT_TANH: { float t = tanhf(x); return 1.f - t * t; }
+    case ACT_LEAKYRELU: return x > 0.f ? 1.f : 0.01f;
+    case ACT_RRELU: return x >= 0.f ? 1.f : slope;
+    case ACT_ELU: return x > 0.f ? 1.f : __expf(x);
+    case ACT_SELU: return 1.0507009873554805f * (x > 0.f ? 1.f : 1.6732632423543772f * __expf(x));
+  }
+  return 1.f;
+}
+// RReLU slope: U(1/8, 1/3) in training (regenerated identically in backward), mean in eval.
+__device__ __forceinline__ float rrelu_slope(int act, int training, uint64_t seed, uint64_t layer, uint64_t idx) {
+  if (act != ACT_RRELU) return 0.f;
+  if (!training) return 0.5f * (0.125f + 1.f / 3.f);
+  Philox ph(seed);
+  uint4 r = ph(idx, 0x52520000ull + layer);
+  return 0.125f + (1.f / 3.f - 0.125f) * u32_to_unit(r.x);
+}
+
+// ---------------------------------------------------------------------------------------------
+// enc_fwd: CSR gather + optional dense input + hidden layers + enc-dropout + mu/sigma heads.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kDocsPerBlock * 32)
+enc_fwd_kernel(const GfEncArgs a) {
+  __shared__ float hbuf[2][kDocsPerBlock][kMaxH];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b0 = blockIdx.x * kDocsPerBlock;
+  const int b = b0 + warp;
+  const int H0 = a.H[0];
+
+  // ---- layer 0: sparse gather (+ dense part)
+  if (b < a.B) {
+    float acc[kMaxH / 32];
+#pragma unroll
+    for (int c = 0; c < kMaxH / 32; ++c) {
+      const int j = c * 32 + lane;
+      acc[c] = (j < H0) ? a.b1[j] : 0.f;
+    }
+    if (a.indptr != nullptr) {
+      const int e0 = a.indptr[b], e1 = a.indptr[b + 1];
+      for (int e = e0; e < e1; ++e) {
+        const int v = a.indices[e];
+        const float x = a.counts[e];
+        const float* wr = a.W1T + (size_t)v * H0;
+#pragma unroll
+        for (int c = 0; c < kMaxH / 32; ++c) {
+          const int j = c * 32 + lane;
+          if (j < H0) acc[c] = fmaf(x, __ldg(wr + j), acc[c]);
+        }
+      }
+    }
+    if (a.xdense != nullptr) {
+      const float* xr = a.xdense + (size_t)b * a.C;
+      for (int c0 = 0; c0 < a.C; ++c0) {
+        const float x = __ldg(xr + c0);
+        const float* wr = a.WdT + (size_t)c0 * H0;
+#pragma unroll
+        for (int c = 0; c < kMaxH / 32; ++c) {
+          const int j = c * 32 + lane;
+          if (j < H0) acc[c] = fmaf(x, __ldg(wr + j), acc[c]);
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < kMaxH / 32; ++c) {
+      const int j = c * 32 + lane;
+      if (j < H0) {
+        a.pre[0][(size_t)b * H0 + j] = acc[c];
+        const float sl = rrelu_slope(a.act, a.training, a.seed, 0, (uint64_t)b * H0 + j);
+        hbuf[0][warp][j] = act_fwd(a.act, acc[c], sl);
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- hidden layers 1..L-1 (all threads, outputs strided)
+  int cur = 0;
+  for (int l = 1; l < a.L; ++l) {
+    const int M = a.H[l - 1], N = a.H[l];
+    const float* W = a.Wh[l - 1];
+    const float* bias = a.bh[l - 1];
+    for (int idx = threadIdx.x; idx < kDocsPerBlock * N; idx += blockDim.x) {
+      const int r = idx / N, n = idx - r * N;
+      if (b0 + r >= a.B) continue;
+      float s = bias[n];
+      const float* wr = W + (size_t)n * M;
+      for (int m = 0; m < M; ++m) s = fmaf(__ldg(wr + m), hbuf[cur][r][m], s);
+      a.pre[l][(size_t)(b0 + r) * N + n] = s;
+      const float sl = rrelu_slope(a.act, a.training, a.seed, l, (uint64_t)(b0 + r) * N + n);
+      hbuf[cur ^ 1][r][n] = act_fwd(a.act, s, sl);
+    }
+    __syncthreads();
+    cur ^= 1;
+  }
+
+  // ---- encoder dropout on the last hidden activation
+  const int HL = a.H[a.L - 1];
+  for (int idx = threadIdx.x; idx < kDocsPerBlock * HL; idx += blockDim.x) {
+    const int r = idx / HL, n = idx - r * HL;
+    const int bb = b0 + r;
+    if (bb >= a.B) continue;
+    float m = 1.f;
+    if (a.training && a.enc_drop_p > 0.f) {
+      if (a.mask_enc_in != nullptr) {
+        m = a.mask_enc_in[(size_t)bb * HL + n];
+      } else {
+        Philox ph(a.seed);
+        const uint4 rr = ph((uint64_t)bb * HL + n, 0x454e4300ull);
+        m = (u32_to_unit(rr.x) > a.enc_drop_p) ? 1.f / (1.f - a.enc_drop_p) : 0.f;
+      }
+    }
+    if (a.mask_enc != nullptr) a.mask_enc[(size_t)bb * HL + n] = m;
+    hbuf[cur][r][n] *= m;
+  }
+  __syncthreads();
+
+  // ---- heads: mu_pre / ls_pre, plus BatchNorm partial sums
+  const int K = a.K;
+  for (int idx = threadIdx.x; idx < kDocsPerBlock * 2 * K; idx += blockDim.x) {
+    const int r = idx / (2 * K), n2 = idx - r * 2 * K;
+    const int bb = b0 + r;
+    if (bb >= a.B) continue;
+    const bool is_sig = n2 >= K;
+    const int n = is_sig ? n2 - K : n2;
+    const float* wr = (is_sig ? a.Wsig : a.Wmu) + (size_t)n * HL;
+    float s = (is_sig ? a.bsig : a.bmu)[n];
+    for (int m = 0; m < HL; ++m) s = fmaf(__ldg(wr + m), hbuf[cur][r][m], s);
+    (is_sig ? a.ls_pre : a.mu_pre)[(size_t)bb * K + n] = s;
+    if (a.bn_sums != nullptr) {
+      atomicAdd(&a.bn_sums[(is_sig ? 2 * K : 0) + n], (double)s);
+      atomicAdd(&a.bn_sums[(is_sig ? 3 * K : K) + n], (double)s * (double)s);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// latent_fwd: BatchNorm(mu), BatchNorm(log sigma^2), reparameterise, softmax, theta dropout, KL.
+// One warp per document; lanes stride over topics.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 8 + warp;
+  const int K = a.K;
+  const double invB = 1.0 / (double)a.B;
+
+  // running statistics (one block, after the sums are final because this kernel follows enc_fwd)
+  if (a.training && blockIdx.x == 0 && a.mu_rm != nullptr) {
+    for (int k = threadIdx.x; k < 2 * K; k += blockDim.x) {
+      const bool sg = k >= K;
+      const int kk = sg ? k - K : k;
+      const double mean = a.bn_sums[(sg ? 2 * K : 0) + kk] * invB;
+      double var = a.bn_sums[(sg ? 3 * K : K) + kk] * invB - mean * mean;
+      if (var < 0) var = 0;
+      const double unb = a.B > 1 ? var * (double)a.B / (double)(a.B - 1) : var;
+      float* rm = sg ? a.ls_rm : a.mu_rm;
+      float* rv = sg ? a.ls_rv : a.mu_rv;
+      rm[kk] = (1.f - a.bn_momentum) * rm[kk] + a.bn_momentum * (float)mean;
+      rv[kk] = (1.f - a.bn_momentum) * rv[kk] + a.bn_momentum * (float)unb;
+    }
+  }
+  if (b >= a.B) return;
+
+  float z[kMaxH / 32], mu[kMaxH / 32], lv[kMaxH / 32], ep[kMaxH / 32];
+  float zmax = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < kMaxH / 32; ++c) {
+    const int k = c * 32 + lane;
+    z[c] = -INFINITY; mu[c] = 0.f; lv[c] = 0.f; ep[c] = 0.f;
+    if (k < K) {
+      float mmean, mrstd, smean, srstd;
+      if (a.training) {
+        const double m1 = a.bn_sums[k] * invB;
+        double v1 = a.bn_sums[K + k] * invB - m1 * m1;
+        const double m2 = a.bn_sums[2 * K + k] * invB;
+        double v2 = a.bn_sums[3 * K + k] * invB - m2 * m2;
+        if (v1 < 0) v1 = 0;
+        if (v2 < 0) v2 = 0;
+        mmean = (float)m1; mrstd = rsqrtf((float)v1 + a.bn_eps);
+        smean = (float)m2; srstd = rsqrtf((float)v2 + a.bn_eps);
+      } else {
+        mmean = a.mu_rm[k]; mrstd = rsqrtf(a.mu_rv[k] + a.bn_eps);
+        smean = a.ls_rm[k]; srstd = rsqrtf(a.ls_rv[k] + a.bn_eps);
+      }
+      mu[c] = (a.mu_pre[(size_t)b * K + k] - mmean) * mrstd;
+      lv[c] = (a.ls_pre[(size_t)b * K + k] - smean) * srstd;
+      float e;
+      if (a.eps_in != nullptr) {
+        e = a.eps_in[(size_t)b * K + k];
+      } else if (a.sample) {
+        Philox ph(a.seed);
+        const uint4 rr = ph((uint64_t)b * K + k, 0x45505300ull);
+        e = box_muller(rr.x, rr.y).x;
+      } else {
+        e = 0.f;
+      }
+      ep[c] = e;
+      z[c] = mu[c] + e * __expf(0.5f * lv[c]);
+      zmax = fmaxf(zmax, z[c]);
+    }
+  }
+  zmax = warp_max(zmax);
+  float zs = 0.f;
+#pragma unroll
+  for (int c = 0; c < kMaxH / 32; ++c) {
+    const int k = c * 32 + lane;
+    if (k < K) { z[c] = __expf(z[c] - zmax); zs += z[c]; }
+  }
+  zs = warp_sum(zs);
+  const float inv = 1.f / zs;
+  float kl = 0.f;
+#pragma unroll
+  for (int c = 0; c < kMaxH / 32; ++c) {
+    const int k = c * 32 + lane;
+    if (k < K) {
+      const float th = z[c] * inv;
+      float m = 1.f;
+      if (a.training && a.theta_drop_p > 0.f) {
+        if (a.mask_theta_in != nullptr) {
+          m = a.mask_theta_in[(size_t)b * K + k];
+        } else {
+          Philox ph(a.seed);
+          const uint4 rr = ph((uint64_t)b * K + k, 0x54484500ull);
+          m = (u32_to_unit(rr.x) > a.theta_drop_p) ? 1.f / (1.f - a.theta_drop_p) : 0.f;
+        }
+      }
+      const size_t o = (size_t)b * K + k;
+      a.mu[o] = mu[c];
+      a.logvar[o] = lv[c];
+      a.eps[o] = ep[c];
+      a.theta_s[o] = th;
+      a.mask_theta[o] = m;
+      const float thd = th * m;
+      a.theta[o] = thd;
+      if (a.theta_colsum != nullptr) atomicAdd(&a.theta_colsum[k], thd);
+      const float pv = a.prior_var[k], pm = a.prior_mean[k];
+      const float var = __expf(lv[c]);
+      const float d = pm - mu[c];
+      kl += var / pv + d * d / pv - 1.f + __logf(pv) - lv[c];
+    }
+  }
+  kl = 0.5f * warp_sum(kl);
+  if (lane == 0) {
+    a.kl[b] = kl;
+    if (a.loss != nullptr) atomicAdd(a.loss, (double)(kl * a.kl_weight));
+  }
+}
+
+// theta_c (bf16) = theta - column mean (training) or theta (eval); zero padding to ld columns.
+__global__ void theta_center_kernel(const float* __restrict__ theta, const float* __restrict__ colsum,
+                                    __nv_bfloat16* __restrict__ out, float* __restrict__ mean_out,
+                                    int B, int K, int ld, int center) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * ld) return;
+  const int b = idx / ld, k = idx - b * ld;
+  float v = 0.f;
+  if (k < K) {
+    const float m = center ? colsum[k] / (float)B : 0.f;
+    v = theta[(size_t)b * K + k] - m;
+    if (b == 0 && mean_out != nullptr) mean_out[k] = m;
+  }
+  out[idx] = __float2bfloat16(v);
+}
+
+// ---------------------------------------------------------------------------------------------
+// latent_bwd: d theta -> (dropout, softmax, reparameterisation, KL) -> d mu_bn, d logvar_bn,
+// prior gradients and the BatchNorm-backward batch sums.  One warp per document.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) latent_bwd_kernel(const GfLatentBwdArgs a) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 8 + warp;
+  if (b >= a.B) return;
+  const int K = a.K;
+  float g[kMaxH / 32], ths[kMaxH / 32];
+  float dot = 0.f;
+#pragma unroll
+  for (int c = 0; c < kMaxH / 32; ++c) {
+    const int k = c * 32 + lane;
+    g[c] = 0.f; ths[c] = 0.f;
+    if (k < K) {
+      const size_t o = (size_t)b * K + k;
+      g[c] = a.dtheta[(size_t)b * a.ld_dtheta + k] * a.mask_theta[o];
+      ths[c] = a.theta_s[o];
+      dot = fmaf(g[c], ths[c], dot);
+    }
+  }
+  dot = warp_sum(dot);
+#pragma unroll
+  for (int c = 0; c < kMaxH / 32; ++c) {
+    const int k = c * 32 + lane;
+    if (k < K) {
+      const size_t o = (size_t)b * K + k;
+      const float dz = ths[c] * (g[c] - dot);
+      const float mu = a.mu[o], lv = a.logvar[o], ep = a.eps[o];
+      const float pv = a.prior_var[k], pm = a.prior_mean[k];
+      const float var = __expf(lv), sd = __expf(0.5f * lv);
+      const float w = a.kl_weight * a.gscale;
+      const float dmu = dz + w * (mu - pm) / pv;
+      const float dlv = dz * 0.5f * ep * sd + w * 0.5f * (var / pv - 1.f);
+      a.dmu[o] = dmu;
+      a.dlv[o] = dlv;
+      // BatchNorm backward needs sum_b d and sum_b d*xhat per topic
+      atomicAdd(&a.bn_bsums[k], dmu);
+      atomicAdd(&a.bn_bsums[K + k], dmu * mu);
+      atomicAdd(&a.bn_bsums[2 * K + k], dlv);
+      atomicAdd(&a.bn_bsums[3 * K + k], dlv * lv);
+      if (a.d_prior_mean != nullptr) {
+        const float d = pm - mu;
+        atomicAdd(&a.d_prior_mean[k], w * d / pv);
+        atomicAdd(&a.d_prior_var[k], w * 0.5f * (-var / (pv * pv) - d * d / (pv * pv) + 1.f / pv));
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// enc_bwd: BatchNorm backward for both heads, head / hidden-layer weight gradients, and the
+// gradient w.r.t. the first-layer pre-activation (consumed by the CSC scatter kernel).
+// Weight gradients are accumulated per block in registers/shared memory, then added with atomics.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kDocsPerBlock * 32)
+enc_bwd_kernel(const GfEncBwdArgs a) {
+  __shared__ float hact[kDocsPerBlock][kMaxH];   // forward activation of the layer below
+  __shared__ float dcur[kDocsPerBlock][kMaxH];   // gradient w.r.t. current layer output
+  __shared__ float dhead[kDocsPerBlock][2 * kMaxH];  // d mu_pre | d ls_pre
+  const int b0 = blockIdx.x * kDocsPerBlock;
+  const int K = a.K, L = a.L;
+  const int HL = a.H[L - 1];
+  const float invB = 1.f / (float)a.B;
+
+  // ---- BN backward on the heads: dpre = rstd * (d - mean(d) - xhat * mean(d*xhat))
+  for (int idx = threadIdx.x; idx < kDocsPerBlock * 2 * K; idx += blockDim.x) {
+    const int r = idx / (2 * K), n2 = idx - r * 2 * K;
+    const int bb = b0 + r;
+    float v = 0.f;
+    if (bb < a.B) {
+      const bool sg = n2 >= K;
+      const int k = sg ? n2 - K : n2;
+      const size_t o = (size_t)bb * K + k;
+      const float d = (sg ? a.dlv : a.dmu)[o];
+      const float xh = (sg ? a.logvar : a.mu)[o];
+      const double m1 = a.bn_sums[(sg ? 2 * K : 0) + k] / (double)a.B;
+      double var = a.bn_sums[(sg ? 3 * K : K) + k] / (double)a.B - m1 * m1;
+      if (var < 0) var = 0;
+      const float rstd = rsqrtf((float)var + a.bn_eps);
+      const float s1 = a.bn_bsums[(sg ? 2 * K : 0) + k] * invB;
+      const float s2 = a.bn_bsums[(sg ? 3 * K : K) + k] * invB;
+      v = rstd * (d - s1 - xh * s2);
+    }
+    dhead[r][n2] = v;
+  }
+  // ---- forward activation of the last hidden layer (post act, post dropout)
+  for (int idx = threadIdx.x; idx < kDocsPerBlock * HL; idx += blockDim.x) {
+    const int r = idx / HL, n = idx - r * HL;
+    const int bb = b0 + r;
+    float h = 0.f;
+    if (bb < a.B) {
+      const size_t o = (size_t)bb * HL + n;
+      const float sl = rrelu_slope(a.act, 1, a.seed, L - 1, o);
+      h = act_fwd(a.act, a.pre[L - 1][o], sl) * a.mask_enc[o];
+    }
+    hact[r][n] = h;
+  }
+  __syncthreads();
+
+  // ---- head weight / bias gradients
+  for (int idx = threadIdx.x; idx < 2 * K * HL; idx += blockDim.x) {
+    const int n2 = idx / HL, m = idx - n2 * HL;
+    float s = 0.f;
+#pragma unroll
+    for (int r = 0; r < kDocsPerBlock; ++r) s = fmaf(dhead[r][n2], hact[r][m], s);
+    const bool sg = n2 >= K;
+    atomicAdd(&(sg ? a.dWsig : a.dWmu)[(size_t)(sg ? n2 - K : n2) * HL + m], s);
+  }
+  for (int n2 = threadIdx.x; n2 < 2 * K; n2 += blockDim.x) {
+    float s = 0.f;
+#pragma unroll
+    for (int r = 0; r < kDocsPerBlock; ++r) s += dhead[r][n2];
+    const bool sg = n2 >= K;
+    atomicAdd(&(sg ? a.dbsig : a.dbmu)[sg ? n2 - K : n2], s);
+  }
+  // ---- d h_last = Wmu^T dmu_pre + Wsig^T dls_pre, then dropout mask
+  for (int idx = threadIdx.x; idx < kDocsPerBlock * HL; idx += blockDim.x) {
+    const int r = idx / HL, m = idx - r * HL;
+    const int bb = b0 + r;
+    float s = 0.f;
+    if (bb < a.B) {
+      for (int k = 0; k < K; ++k) {
+        s = fmaf(__ldg(a.Wmu + (size_t)k * HL + m), dhead[r][k], s);
+        s = fmaf(__ldg(a.Wsig + (size_t)k * HL + m), dhead[r][K + k], s);
+      }
+      s *= a.mask_enc[(size_t)bb * HL + m];
+    }
+    dcur[r][m] = s;
+  }
+  __syncthreads();
+
+  // ---- hidden layers, top down
+  for (int l = L - 1; l >= 1; --l) {
+    const int N = a.H[l], M = a.H[l - 1];
+    // dpre_l = dcur * act'(pre_l)   (in place)
+    for (int idx = threadIdx.x; idx < kDocsPerBlock * N; idx += blockDim.x) {
+      const int r = idx / N, n = idx - r * N;
+      const int bb = b0 + r;
+      float v = 0.f;
+      if (bb < a.B) {
+        const size_t o = (size_t)bb * N + n;
+        const float sl = rrelu_slope(a.act, 1, a.seed, l, o);
+        v = dcur[r][n] * act_bwd(a.act, a.pre[l][o], sl);
+      }
+      dcur[r][n] = v;
+    }
+    // activation of layer l-1
+    for (int idx = threadIdx.x; idx < kDocsPerBlock * M; idx += blockDim.x) {
+      const int r = idx / M, m = idx - r * M;
+      const int bb = b0 + r;
+      float h = 0.f;
+      if (bb < a.B) {
+        const size_t o = (size_t)bb * M + m;
+        const float sl = rrelu_slope(a.act, 1, a.seed, l - 1, o);
+        h = act_fwd(a.act, a.pre[l - 1][o], sl);
+      }
+      hact[r][m] = h;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < N * M; idx += blockDim.x) {
+      const int n = idx / M, m = idx - n * M;
+      float s = 0.f;
+#pragma unroll
+      for (int r = 0; r < kDocsPerBlock; ++r) s = fmaf(dcur[r][n], hact[r][m], s);
+      atomicAdd(&a.dWh[l - 1][idx], s);
+    }
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+      float s = 0.f;
+#pragma unroll
+      for (int r = 0; r < kDocsPerBlock; ++r) s += dcur[r][n];
+      atomicAdd(&a.dbh[l - 1][n], s);
+    }
+    // d h_{l-1} = W_l^T dpre_l  -> stage in dhead (reused as scratch), then copy to dcur
+    for (int idx = threadIdx.x; idx < kDocsPerBlock * M; idx += blockDim.x) {
+      const int r = idx / M, m = idx - r * M;
+      float s = 0.f;
+      for (int n = 0; n < N; ++n) s = fmaf(__ldg(a.Wh[l - 1] + (size_t)n * M + m), dcur[r][n], s);
+      dhead[r][m] = s;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < kDocsPerBlock * M; idx += blockDim.x) {
+      const int r = idx / M, m = idx - r * M;
+      dcur[r][m] = dhead[r][m];
+    }
+    __syncthreads();
+  }
+
+  // ---- layer 0: d pre_0 = dcur * act'(pre_0); bias gradient; write for the scatter kernels
+  const int H0 = a.H[0];
+  for (int idx = threadIdx.x; idx < kDocsPerBlock * H0; idx += blockDim.x) {
+    const int r = idx / H0, n = idx - r * H0;
+    const int bb = b0 + r;
+    float v = 0.f;
+    if (bb < a.B) {
+      const size_t o = (size_t)bb * H0 + n;
+      const float sl = rrelu_slope(a.act, 1, a.seed, 0, o);
+      v = dcur[r][n] * act_bwd(a.act, a.pre[0][o], sl);
+      a.dpre0[o] = v;
+    }
+    dcur[r][n] = v;
+  }
+  __syncthreads();
+  for (int n = threadIdx.x; n < H0; n += blockDim.x) {
+    float s = 0.f;
+#pragma unroll
+    for (int r = 0; r < kDocsPerBlock; ++r) s += dcur[r][n];
+    atomicAdd(&a.db1[n], s);
+  }
+  // dense first-layer input (CTM): d WdT[c, j] += sum_b x[b,c] * dpre0[b,j]
+  if (a.xdense != nullptr && a.dWdT != nullptr) {
+    for (int idx = threadIdx.x; idx < a.C * H0; idx += blockDim.x) {
+      const int c = idx / H0, j = idx - c * H0;
+      float s = 0.f;
+#pragma unroll
+      for (int r = 0; r < kDocsPerBlock; ++r)
+        if (b0 + r < a.B) s = fmaf(__ldg(a.xdense + (size_t)(b0 + r) * a.C + c), dcur[r][j], s);
+      atomicAdd(&a.dWdT[idx], s);
+    }
+  }
+}
+
+}  // namespace gf
+
+using namespace gf;
+
+extern "C" int gf_enc_fwd(const GfEncArgs* a, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(a->L >= 1 && a->L <= GF_MAX_HIDDEN, "number of hidden layers");
+  for (int l = 0; l < a->L; ++l) GF_ARG_CHECK(a->H[l] >= 1 && a->H[l] <= kMaxH, "hidden size must be <= 256");
+  GF_ARG_CHECK(a->K >= 1 && a->K <= kMaxH, "n_components must be <= 256");
+  const int grid = (a->B + kDocsPerBlock - 1) / kDocsPerBlock;
+  enc_fwd_kernel<<<grid, kDocsPerBlock * 32, 0, st>>>(*a);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_latent_fwd(const GfLatentArgs* a, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(a->K >= 1 && a->K <= kMaxH, "n_components must be <= 256");
+  GF_ARG_CHECK(!a->training || a->B >= 2, "training-mode BatchNorm needs at least 2 documents");
+  const int grid = (a->B + 7) / 8;
+  latent_fwd_kernel<<<grid, 256, 0, st>>>(*a);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_theta_center(const float* theta, const float* colsum, void* out_bf16, float* mean_out,
+                               int B, int K, int ld, int center, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  const int n = B * ld;
+  theta_center_kernel<<<(n + 255) / 256, 256, 0, st>>>(theta, colsum, reinterpret_cast<__nv_bfloat16*>(out_bf16),
+                                                       mean_out, B, K, ld, center);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_latent_bwd(const GfLatentBwdArgs* a, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  const int grid = (a->B + 7) / 8;
+  latent_bwd_kernel<<<grid, 256, 0, st>>>(*a);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_enc_bwd(const GfEncBwdArgs* a, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  const int grid = (a->B + kDocsPerBlock - 1) / kDocsPerBlock;
+  enc_bwd_kernel<<<grid, kDocsPerBlock * 32, 0, st>>>(*a);
+  GF_LAUNCHED();
+  return GF_OK;
+}

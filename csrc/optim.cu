@@ -1,0 +1,119 @@
+// Fused optimiser kernels.  Ref: optimizer.step() in federated_avitm.py:78 / avitm.py:141-143
+// (torch.optim.Adam, betas=(momentum, 0.99)), plus the bf16 operand shadows the tensor-core
+// decoder sweeps read (beta [Kp,ldb] and beta^T [V,Kp]).
+#include "ptx.cuh"
+#include "tmap.h"
+#include "../include/gfedntm_kernels.h"
+
+namespace gf {
+
+struct AdamH {
+  float lr, b1, b2, eps, bc1, bc2_sqrt, wd;  // bc1 = 1-b1^t, bc2_sqrt = sqrt(1-b2^t)
+};
+
+__device__ __forceinline__ float adam_one(float p, float g, float& m, float& v, const AdamH& h) {
+  if (h.wd != 0.f) g = fmaf(h.wd, p, g);
+  m = fmaf(h.b1, m, (1.f - h.b1) * g);
+  v = fmaf(h.b2, v, (1.f - h.b2) * g * g);
+  const float denom = sqrtf(v) / h.bc2_sqrt + h.eps;
+  return p - (h.lr / h.bc1) * (m / denom);
+}
+
+__global__ void __launch_bounds__(256) adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                        float* __restrict__ m, float* __restrict__ v, long long n,
+                                                        AdamH h, float gscale) {
+  const long long i0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i0 + 3 < n && ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
+                      reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0) {
+    float4 pp = *reinterpret_cast<float4*>(p + i0);
+    const float4 gg = *reinterpret_cast<const float4*>(g + i0);
+    float4 mm = *reinterpret_cast<float4*>(m + i0);
+    float4 vv = *reinterpret_cast<float4*>(v + i0);
+    pp.x = adam_one(pp.x, gg.x * gscale, mm.x, vv.x, h);
+    pp.y = adam_one(pp.y, gg.y * gscale, mm.y, vv.y, h);
+    pp.z = adam_one(pp.z, gg.z * gscale, mm.z, vv.z, h);
+    pp.w = adam_one(pp.w, gg.w * gscale, mm.w, vv.w, h);
+    *reinterpret_cast<float4*>(p + i0) = pp;
+    *reinterpret_cast<float4*>(m + i0) = mm;
+    *reinterpret_cast<float4*>(v + i0) = vv;
+  } else {
+    for (long long i = i0; i < i0 + 4 && i < n; ++i) {
+      float mm = m[i], vv = v[i];
+      p[i] = adam_one(p[i], g[i] * gscale, mm, vv, h);
+      m[i] = mm;
+      v[i] = vv;
+    }
+  }
+}
+
+// beta [K, ldp] fp32 (+ Adam) -> beta_bf [Kp, ldb] bf16 and betaT_bf [V, Kp] bf16.
+// 32x32 tiles; the transposed shadow goes through shared memory so both writes are coalesced.
+__global__ void __launch_bounds__(256) adam_beta_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                        float* __restrict__ m, float* __restrict__ v, int K, int V,
+                                                        int ldp, int ldg, __nv_bfloat16* __restrict__ beta_bf, int ldb,
+                                                        __nv_bfloat16* __restrict__ betaT_bf, int Kp, AdamH h,
+                                                        float gscale, int do_update) {
+  __shared__ float tile[32][33];
+  const int v0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int k = k0 + ty + r * 8, vv = v0 + tx;
+    float val = 0.f;
+    if (k < K && vv < V) {
+      const size_t ip = (size_t)k * ldp + vv;
+      val = p[ip];
+      if (do_update) {
+        float mm = m[ip], v2 = v[ip];
+        val = adam_one(val, g[(size_t)k * ldg + vv] * gscale, mm, v2, h);
+        p[ip] = val;
+        m[ip] = mm;
+        v[ip] = v2;
+      }
+      beta_bf[(size_t)k * ldb + vv] = __float2bfloat16(val);
+    }
+    tile[ty + r * 8][tx] = val;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int vv = v0 + ty + r * 8, k = k0 + tx;
+    if (vv < V && k < K) betaT_bf[(size_t)vv * Kp + k] = __float2bfloat16(tile[tx][ty + r * 8]);
+  }
+}
+
+}  // namespace gf
+
+using namespace gf;
+
+static AdamH make_h(float lr, float b1, float b2, float eps, float wd, int step) {
+  AdamH h;
+  h.lr = lr; h.b1 = b1; h.b2 = b2; h.eps = eps; h.wd = wd;
+  h.bc1 = 1.f - powf(b1, (float)step);
+  h.bc2_sqrt = sqrtf(1.f - powf(b2, (float)step));
+  return h;
+}
+
+extern "C" int gf_adam_flat(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
+                            float eps, float wd, int step, float gscale, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  if (n <= 0) return GF_OK;
+  GF_ARG_CHECK(step >= 1, "Adam step must be >= 1");
+  const long long thr = (n + 3) / 4;
+  adam_flat_kernel<<<(unsigned)((thr + 255) / 256), 256, 0, st>>>(p, g, m, v, n, make_h(lr, b1, b2, eps, wd, step), gscale);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_adam_beta(float* p, const float* g, float* m, float* v, int K, int V, int ldp, int ldg,
+                            void* beta_bf, int ldb, void* betaT_bf, int Kp, float lr, float b1, float b2, float eps,
+                            float wd, int step, float gscale, int do_update, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(!do_update || step >= 1, "Adam step must be >= 1");
+  dim3 grid((V + 31) / 32, (K + 31) / 32);
+  adam_beta_kernel<<<grid, 256, 0, st>>>(p, g, m, v, K, V, ldp, ldg, reinterpret_cast<__nv_bfloat16*>(beta_bf), ldb,
+                                         reinterpret_cast<__nv_bfloat16*>(betaT_bf), Kp,
+                                         make_h(lr, b1, b2, eps, wd, do_update ? step : 1), gscale, do_update);
+  GF_LAUNCHED();
+  return GF_OK;
+}

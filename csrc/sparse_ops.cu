@@ -1,0 +1,520 @@
+// Sparse (bag-of-words) side of the decoder and of the first encoder layer, the per-step
+// CSR->CSC transpose of the minibatch, and the NeuralLDA (model_type='LDA') decoder which is
+// sparse end to end.
+//
+// Ref: avitm_network/avitm.py:225 (RL = -sum x log(p+1e-10)), decoder_network.py:121-132,
+// and the autograd of those ops.
+#include "ptx.cuh"
+#include "tmap.h"
+#include "../include/gfedntm_kernels.h"
+
+namespace gf {
+
+constexpr float kLog2e_s = 1.4426950408889634f;
+constexpr float kLn2_s = 0.6931471805599453f;
+constexpr int kMaxKp = 256;
+
+// ---------------------------------------------------------------------------------------------
+// CSR -> CSC of one minibatch (counting sort by word id; order inside a column is arbitrary).
+// ---------------------------------------------------------------------------------------------
+__global__ void csc_hist_kernel(const int* __restrict__ indices, int nnz, int* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nnz) atomicAdd(&count[indices[i] + 1], 1);
+}
+// exclusive scan of count[0..n] in place (count[0] == 0 on entry => colptr), single block.
+__global__ void __launch_bounds__(1024) scan_kernel(int* __restrict__ data, int n) {
+  __shared__ int warp_tot[32];
+  __shared__ int carry_s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  for (int base = 0; base < n; base += 1024 * 4) {
+    int v[4], s = 0;
+    const int i0 = base + tid * 4;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[j] = (i0 + j < n) ? data[i0 + j] : 0;
+      s += v[j];
+    }
+    int inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      int w = warp_tot[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += t;
+      }
+      warp_tot[lane] = w;
+    }
+    __syncthreads();
+    const int carry = carry_s;
+    int run = carry + (warp > 0 ? warp_tot[warp - 1] : 0) + inc - s;  // exclusive prefix of this thread
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      run += v[j];
+      if (i0 + j < n) data[i0 + j] = run;  // inclusive => data[i] = sum_{<=i}; with data[0]=0 this is colptr
+    }
+    __syncthreads();
+    if (tid == 1023) carry_s = run;
+    __syncthreads();
+  }
+}
+__global__ void csc_scatter_kernel(const int* __restrict__ indptr, const int* __restrict__ indices, int B,
+                                   const int* __restrict__ colptr, int* __restrict__ cursor,
+                                   int* __restrict__ csc_row, int* __restrict__ csc_src) {
+  // one warp per document
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= B) return;
+  const int e0 = indptr[warp], e1 = indptr[warp + 1];
+  for (int e = e0 + lane; e < e1; e += 32) {
+    const int v = indices[e];
+    const int pos = colptr[v] + atomicAdd(&cursor[v], 1);
+    csc_row[pos] = warp;
+    csc_src[pos] = e;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// ProdLDA decoder, sparse part (one warp per document):
+//   lse_b from the ROW_LSE partials, then for every non-zero (b,v,x):
+//     y = BN'd logit, p = softmax prob, RL -= x log(p+1e-10), t = g*x*p/(p+1e-10)
+//   S_b = sum t; asp[v] += t; csp[v] += t*y; tnnz[e] = rstd_v * t;
+//   dtheta[b,:] = -sum rstd_v t beta[:,v]   (plain store: initialises the d theta buffer)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) dec_sparse_doc_kernel(const GfDecSparseArgs a) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int b = warp;
+  if (b >= a.B) return;
+  const int Kp = a.Kp;
+  const float2* lse_part = reinterpret_cast<const float2*>(a.lse_part);
+  const __nv_bfloat16* theta_bf = reinterpret_cast<const __nv_bfloat16*>(a.theta_bf);
+  const __nv_bfloat16* betaT_bf = reinterpret_cast<const __nv_bfloat16*>(a.betaT_bf);
+  const float4* colc = reinterpret_cast<const float4*>(a.colc);
+  float2* doc_const = reinterpret_cast<float2*>(a.doc_const);
+  float4* sb_doc = reinterpret_cast<float4*>(a.sb_doc);
+  // combine log-sum-exp partials
+  float m = -INFINITY;
+  for (int c = lane; c < a.n_chunks; c += 32) m = fmaxf(m, lse_part[(size_t)b * a.n_chunks + c].x);
+  m = warp_max(m);
+  float ssum = 0.f;
+  for (int c = lane; c < a.n_chunks; c += 32) {
+    const float2 pr = lse_part[(size_t)b * a.n_chunks + c];
+    if (pr.x > -INFINITY) ssum += pr.y * exp2f(pr.x - m);
+  }
+  ssum = warp_sum(ssum);
+  const float lse2 = m + log2f(ssum);
+
+  float th[kMaxKp / 32], dth[kMaxKp / 32];
+#pragma unroll
+  for (int c = 0; c < kMaxKp / 32; ++c) {
+    const int k = c * 32 + lane;
+    th[c] = (k < Kp) ? __bfloat162float(theta_bf[(size_t)b * a.ld_theta + k]) : 0.f;
+    dth[c] = 0.f;
+  }
+  float rl = 0.f, S = 0.f;
+  const int e0 = a.indptr[b], e1 = a.indptr[b + 1];
+  for (int e = e0; e < e1; ++e) {
+    const int v = a.indices[e];
+    const float x = a.counts[e];
+    const __nv_bfloat16* br = betaT_bf + (size_t)v * Kp;
+    float bv[kMaxKp / 32];
+    float dot = 0.f;
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) {
+      const int k = c * 32 + lane;
+      bv[c] = (k < Kp) ? __bfloat162float(br[k]) : 0.f;
+      dot = fmaf(th[c], bv[c], dot);
+    }
+    dot = warp_sum(dot);
+    const float4 cc = colc[v];
+    const float t2 = fmaf(dot, cc.x, cc.y);
+    const float p = exp2f(t2 - lse2);
+    const float y = t2 * kLn2_s;
+    const float rstd = cc.x * kLn2_s;
+    rl -= x * __logf(p + 1e-10f);
+    const float t = a.gscale * x * p / (p + 1e-10f);
+    S += t;
+    if (lane == 0 && a.asp != nullptr) {
+      atomicAdd(&a.asp[v], t);
+      atomicAdd(&a.csp[v], t * y);
+      a.tnnz[e] = rstd * t;
+    }
+    const float w = rstd * t;
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) dth[c] = fmaf(-w, bv[c], dth[c]);
+  }
+  if (a.dtheta != nullptr) {
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) {
+      const int k = c * 32 + lane;
+      if (k < Kp) a.dtheta[(size_t)b * Kp + k] = dth[c];
+    }
+  }
+  if (lane == 0) {
+    a.rl[b] = rl;
+    if (a.loss != nullptr) atomicAdd(a.loss, (double)rl);
+    if (doc_const != nullptr) doc_const[b] = make_float2(lse2, S * kLn2_s);
+    if (sb_doc != nullptr) sb_doc[b] = make_float4(lse2, S, 0.f, 0.f);
+  }
+}
+
+// corr[v, :] = sum over the column's entries of tnnz[e] * theta_c[b, :]   (one warp per word)
+__global__ void __launch_bounds__(256) csc_corr_kernel(const int* __restrict__ colptr, const int* __restrict__ csc_row,
+                                                       const int* __restrict__ csc_src, const float* __restrict__ tnnz,
+                                                       const __nv_bfloat16* __restrict__ theta_bf, int ld_theta,
+                                                       float* __restrict__ corr, int V, int Kp) {
+  const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (v >= V) return;
+  const int e0 = colptr[v], e1 = colptr[v + 1];
+  if (e0 == e1) return;
+  float acc[kMaxKp / 32];
+#pragma unroll
+  for (int c = 0; c < kMaxKp / 32; ++c) acc[c] = 0.f;
+  for (int e = e0; e < e1; ++e) {
+    const int b = csc_row[e];
+    const float w = tnnz[csc_src[e]];
+    const __nv_bfloat16* tr = theta_bf + (size_t)b * ld_theta;
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) {
+      const int k = c * 32 + lane;
+      if (k < Kp) acc[c] = fmaf(w, __bfloat162float(tr[k]), acc[c]);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < kMaxKp / 32; ++c) {
+    const int k = c * 32 + lane;
+    if (k < Kp) corr[(size_t)v * Kp + k] = acc[c];
+  }
+}
+
+// out[v, :] (+)= scale * sum over the column's entries of val[e] * dense[b, :]  (one warp per word).
+// Used for d W1^T (val = counts, dense = d pre_0) and by the NeuralLDA decoder.
+__global__ void __launch_bounds__(256) csc_spmm_kernel(const int* __restrict__ colptr, const int* __restrict__ csc_row,
+                                                       const int* __restrict__ csc_src, const float* __restrict__ val,
+                                                       const float* __restrict__ dense, int ldd,
+                                                       float* __restrict__ out, int ldo, int V, int N, int accumulate) {
+  const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (v >= V) return;
+  const int e0 = colptr[v], e1 = colptr[v + 1];
+  float acc[kMaxKp / 32];
+#pragma unroll
+  for (int c = 0; c < kMaxKp / 32; ++c) acc[c] = 0.f;
+  for (int e = e0; e < e1; ++e) {
+    const int b = csc_row[e];
+    const float w = val[csc_src[e]];
+    const float* dr = dense + (size_t)b * ldd;
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) {
+      const int j = c * 32 + lane;
+      if (j < N) acc[c] = fmaf(w, __ldg(dr + j), acc[c]);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < kMaxKp / 32; ++c) {
+    const int j = c * 32 + lane;
+    if (j < N) {
+      float* o = out + (size_t)v * ldo + j;
+      *o = accumulate ? (*o + acc[c]) : acc[c];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// NeuralLDA ('LDA') decoder:  beta' = softmax_V(BN_K(beta)),  word_dist = theta . beta'.
+// Only the non-zero words of each document are ever needed.
+// ---------------------------------------------------------------------------------------------
+// Stage 1 (one thread per word): BatchNorm over the K topic rows of beta for this word column.
+__global__ void lda_beta_bn_kernel(const float* __restrict__ beta, int ldb, int K, int V, float eps, float momentum,
+                                   int training, float* __restrict__ running_mean, float* __restrict__ running_var,
+                                   float* __restrict__ xhat /*[K,V]*/, float* __restrict__ col_rstd /*[V]*/) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= V) return;
+  float mean, var;
+  if (training) {
+    float s = 0.f;
+    for (int k = 0; k < K; ++k) s += beta[(size_t)k * ldb + v];
+    mean = s / K;
+    float q = 0.f;
+    for (int k = 0; k < K; ++k) { const float d = beta[(size_t)k * ldb + v] - mean; q = fmaf(d, d, q); }
+    var = q / K;
+    if (running_mean != nullptr) {
+      const float unb = K > 1 ? var * K / (float)(K - 1) : var;
+      running_mean[v] = (1.f - momentum) * running_mean[v] + momentum * mean;
+      running_var[v] = (1.f - momentum) * running_var[v] + momentum * unb;
+    }
+  } else {
+    mean = running_mean[v];
+    var = running_var[v];
+  }
+  const float rstd = rsqrtf(var + eps);
+  col_rstd[v] = rstd;
+  for (int k = 0; k < K; ++k) xhat[(size_t)k * V + v] = (beta[(size_t)k * ldb + v] - mean) * rstd;
+}
+// Stage 2 (one block per topic row): row soft-max over the vocabulary -> beta'.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float r = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : 0.f;
+  r = warp_sum(r);
+  __syncthreads();
+  if (threadIdx.x == 0) red[0] = r;
+  __syncthreads();
+  r = red[0];
+  __syncthreads();
+  return r;
+}
+__device__ __forceinline__ float block_max(float v, float* red) {
+  v = warp_max(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float r = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : -INFINITY;
+  r = warp_max(r);
+  __syncthreads();
+  if (threadIdx.x == 0) red[0] = r;
+  __syncthreads();
+  r = red[0];
+  __syncthreads();
+  return r;
+}
+__global__ void __launch_bounds__(1024) lda_row_softmax_kernel(const float* __restrict__ xhat, float* __restrict__ bp,
+                                                               int V) {
+  __shared__ float red[32];
+  const int k = blockIdx.x;
+  const float* x = xhat + (size_t)k * V;
+  float m = -INFINITY;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) m = fmaxf(m, x[v]);
+  m = block_max(m, red);
+  float s = 0.f;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) s += __expf(x[v] - m);
+  s = block_sum(s, red);
+  const float inv = 1.f / s;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) bp[(size_t)k * V + v] = __expf(x[v] - m) * inv;
+}
+// Stage 3 (one warp per document): wd = theta . beta'[:,v] at the non-zeros; RL; d theta;
+// g[e] = -gscale * x / (wd + 1e-10) kept for the d beta' scatter.
+__global__ void __launch_bounds__(256) lda_doc_kernel(const int* __restrict__ indptr, const int* __restrict__ indices,
+                                                      const float* __restrict__ counts, const float* __restrict__ theta,
+                                                      const float* __restrict__ bp /*[K,V]*/, int B, int K, int V,
+                                                      float gscale, float* __restrict__ rl, double* __restrict__ loss,
+                                                      float* __restrict__ dtheta, int ld_dtheta,
+                                                      float* __restrict__ gnnz) {
+  const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (b >= B) return;
+  float th[kMaxKp / 32], dth[kMaxKp / 32];
+#pragma unroll
+  for (int c = 0; c < kMaxKp / 32; ++c) {
+    const int k = c * 32 + lane;
+    th[c] = (k < K) ? theta[(size_t)b * K + k] : 0.f;
+    dth[c] = 0.f;
+  }
+  float r = 0.f;
+  for (int e = indptr[b]; e < indptr[b + 1]; ++e) {
+    const int v = indices[e];
+    const float x = counts[e];
+    float bv[kMaxKp / 32], dot = 0.f;
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) {
+      const int k = c * 32 + lane;
+      bv[c] = (k < K) ? __ldg(bp + (size_t)k * V + v) : 0.f;
+      dot = fmaf(th[c], bv[c], dot);
+    }
+    dot = warp_sum(dot);
+    r -= x * __logf(dot + 1e-10f);
+    const float g = -gscale * x / (dot + 1e-10f);
+    if (lane == 0 && gnnz != nullptr) gnnz[e] = g;
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) dth[c] = fmaf(g, bv[c], dth[c]);
+  }
+  if (dtheta != nullptr) {
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) {
+      const int k = c * 32 + lane;
+      if (k < ld_dtheta) dtheta[(size_t)b * ld_dtheta + k] = (k < K) ? dth[c] : 0.f;
+    }
+  }
+  if (lane == 0) {
+    rl[b] = r;
+    if (loss != nullptr) atomicAdd(loss, (double)r);
+  }
+}
+// Stage 4 (one block per topic row): soft-max backward along V given d beta' (sparse, scattered
+// through the CSC of the batch into dbp [V,K] beforehand):  dxhat = bp * (dbp - sum_v dbp*bp).
+__global__ void __launch_bounds__(1024) lda_row_softmax_bwd_kernel(const float* __restrict__ bp, const float* __restrict__ dbpT,
+                                                                   int ldt, float* __restrict__ dxhat, int K, int V) {
+  __shared__ float red[32];
+  const int k = blockIdx.x;
+  float s = 0.f;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) s = fmaf(dbpT[(size_t)v * ldt + k], bp[(size_t)k * V + v], s);
+  const float dot = block_sum(s, red);
+  for (int v = threadIdx.x; v < V; v += blockDim.x) {
+    const float p = bp[(size_t)k * V + v];
+    dxhat[(size_t)k * V + v] = p * (dbpT[(size_t)v * ldt + k] - dot);
+  }
+}
+// Stage 5 (one thread per word): BatchNorm-over-K backward -> d beta[:, v].
+__global__ void lda_beta_bn_bwd_kernel(const float* __restrict__ dxhat, const float* __restrict__ xhat,
+                                       const float* __restrict__ col_rstd, float* __restrict__ dbeta, int ldg, int K,
+                                       int V, int training) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= V) return;
+  const float rstd = col_rstd[v];
+  float s1 = 0.f, s2 = 0.f;
+  if (training) {
+    for (int k = 0; k < K; ++k) {
+      const float d = dxhat[(size_t)k * V + v];
+      s1 += d;
+      s2 = fmaf(d, xhat[(size_t)k * V + v], s2);
+    }
+    s1 /= K;
+    s2 /= K;
+  }
+  for (int k = 0; k < K; ++k) {
+    const float d = dxhat[(size_t)k * V + v];
+    dbeta[(size_t)k * ldg + v] = rstd * (d - s1 - xhat[(size_t)k * V + v] * s2);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Row top-k of a [K,V] matrix (k <= 32), one block per row.  Ref: avitm.py:574 (torch.topk).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) row_topk_kernel(const float* __restrict__ mat, int ld, int V, int topk,
+                                                       int* __restrict__ out_idx, float* __restrict__ out_val) {
+  __shared__ float sval[256];
+  __shared__ int sidx[256];
+  __shared__ int chosen[32];
+  const int row = blockIdx.x;
+  const float* x = mat + (size_t)row * ld;
+  for (int t = 0; t < topk; ++t) {
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+      bool used = false;
+      for (int j = 0; j < t; ++j) used |= (chosen[j] == v);
+      const float val = x[v];
+      if (!used && (val > best || (val == best && v < bi))) { best = val; bi = v; }
+    }
+    sval[threadIdx.x] = best;
+    sidx[threadIdx.x] = bi;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (threadIdx.x < o) {
+        const float ov = sval[threadIdx.x + o];
+        const int oi = sidx[threadIdx.x + o];
+        if (ov > sval[threadIdx.x] || (ov == sval[threadIdx.x] && oi < sidx[threadIdx.x])) {
+          sval[threadIdx.x] = ov;
+          sidx[threadIdx.x] = oi;
+        }
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      chosen[t] = sidx[0];
+      out_idx[row * topk + t] = sidx[0];
+      if (out_val != nullptr) out_val[row * topk + t] = sval[0];
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace gf
+
+using namespace gf;
+
+extern "C" int gf_csr_to_csc(const int* indptr, const int* indices, int B, int V, int nnz, int* colptr,
+                             int* cursor_scratch, int* csc_row, int* csc_src, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(B >= 0 && V > 0 && nnz >= 0, "sizes");
+  GF_CUDA_CHECK(cudaMemsetAsync(colptr, 0, sizeof(int) * (size_t)(V + 1), st));
+  GF_CUDA_CHECK(cudaMemsetAsync(cursor_scratch, 0, sizeof(int) * (size_t)V, st));
+  if (nnz > 0) {
+    csc_hist_kernel<<<(nnz + 255) / 256, 256, 0, st>>>(indices, nnz, colptr);
+    GF_LAUNCHED();
+  }
+  scan_kernel<<<1, 1024, 0, st>>>(colptr, V + 1);
+  GF_LAUNCHED();
+  if (nnz > 0) {
+    csc_scatter_kernel<<<(B * 32 + 255) / 256, 256, 0, st>>>(indptr, indices, B, colptr, cursor_scratch, csc_row, csc_src);
+    GF_LAUNCHED();
+  }
+  return GF_OK;
+}
+
+extern "C" int gf_dec_sparse_doc(const GfDecSparseArgs* a, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(a->Kp <= kMaxKp && a->Kp % 16 == 0, "Kp");
+  dec_sparse_doc_kernel<<<(a->B * 32 + 255) / 256, 256, 0, st>>>(*a);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_csc_corr(const int* colptr, const int* csc_row, const int* csc_src, const float* tnnz,
+                           const void* theta_bf, int ld_theta, float* corr, int V, int Kp, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(Kp <= kMaxKp, "Kp");
+  csc_corr_kernel<<<((size_t)V * 32 + 255) / 256, 256, 0, st>>>(colptr, csc_row, csc_src, tnnz,
+                                                                reinterpret_cast<const __nv_bfloat16*>(theta_bf), ld_theta,
+                                                                corr, V, Kp);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_csc_spmm(const int* colptr, const int* csc_row, const int* csc_src, const float* val,
+                           const float* dense, int ldd, float* out, int ldo, int V, int N, int accumulate,
+                           void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(N <= kMaxKp, "N must be <= 256");
+  csc_spmm_kernel<<<((size_t)V * 32 + 255) / 256, 256, 0, st>>>(colptr, csc_row, csc_src, val, dense, ldd, out, ldo, V,
+                                                                N, accumulate);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_lda_beta_fwd(const float* beta, int ldb, int K, int V, float eps, float momentum, int training,
+                               float* running_mean, float* running_var, float* xhat, float* col_rstd, float* bp,
+                               void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  lda_beta_bn_kernel<<<(V + 255) / 256, 256, 0, st>>>(beta, ldb, K, V, eps, momentum, training, running_mean,
+                                                      running_var, xhat, col_rstd);
+  GF_LAUNCHED();
+  lda_row_softmax_kernel<<<K, 1024, 0, st>>>(xhat, bp, V);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_lda_doc(const int* indptr, const int* indices, const float* counts, const float* theta,
+                          const float* bp, int B, int K, int V, float gscale, float* rl, double* loss, float* dtheta,
+                          int ld_dtheta, float* gnnz, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(K <= kMaxKp && ld_dtheta <= kMaxKp, "K");
+  lda_doc_kernel<<<(B * 32 + 255) / 256, 256, 0, st>>>(indptr, indices, counts, theta, bp, B, K, V, gscale, rl, loss,
+                                                       dtheta, ld_dtheta, gnnz);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_lda_beta_bwd(const float* bp, const float* dbpT, int ldt, const float* xhat, const float* col_rstd,
+                               float* dxhat, float* dbeta, int ldg, int K, int V, int training, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  lda_row_softmax_bwd_kernel<<<K, 1024, 0, st>>>(bp, dbpT, ldt, dxhat, K, V);
+  GF_LAUNCHED();
+  lda_beta_bn_bwd_kernel<<<(V + 255) / 256, 256, 0, st>>>(dxhat, xhat, col_rstd, dbeta, ldg, K, V, training);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_row_topk(const float* mat, int ld, int rows, int V, int topk, int* out_idx, float* out_val,
+                           void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(topk >= 1 && topk <= 32 && topk <= V, "topk must be in [1,32]");
+  row_topk_kernel<<<rows, 256, 0, st>>>(mat, ld, V, topk, out_idx, out_val);
+  GF_LAUNCHED();
+  return GF_OK;
+}

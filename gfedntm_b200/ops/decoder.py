@@ -1,0 +1,148 @@
+"""ProdLDA decoder (theta.beta -> BatchNorm(V) -> softmax(V) -> BoW NLL) forward + backward,
+composed from the sm_100a kernels.  Nothing of size [B,V] is ever materialised.
+
+Ref: avitm_network/decoder_network.py:121-126, avitm.py:225 and their autograd
+(`loss.backward()` in federated_avitm.py:75).
+
+Kernel sequence of one training step (see csrc/dec_sweep.cu for the operand families):
+
+  theta_center     theta_c = bf16(theta - mean_b theta)
+  COL_STATS        per-word batch variance of the centred logits -> rstd, running stats
+  ROW_LSE          per-document log-sum-exp partials over vocabulary chunks
+  dec_sparse_doc   non-zeros: RL, S_b, sparse d theta, sparse BN-backward sums
+  csc_corr         sparse correction of d beta (through the CSC of the minibatch)
+  COL_GRAD         pass 1: BN-backward column means; pass 2: d beta
+  ROW_GRAD         d theta (dense part, atomically added to the sparse part)
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import kernels as K_
+from .kernels import TILE, padded_topics, round_up
+
+
+@dataclass
+class CsrBatch:
+    """A minibatch of bag-of-words rows in CSR form on the device."""
+    indptr: torch.Tensor   # int32 [B+1]
+    indices: torch.Tensor  # int32 [nnz]
+    counts: torch.Tensor   # float32 [nnz]
+    B: int
+    V: int
+
+    @property
+    def nnz(self) -> int:
+        return self.indices.numel()
+
+    @staticmethod
+    def from_dense(x: torch.Tensor) -> "CsrBatch":
+        """Helper for tests / dense-input API calls."""
+        B, V = x.shape
+        sp = x.to_sparse_csr()
+        return CsrBatch(sp.crow_indices().to(torch.int32), sp.col_indices().to(torch.int32),
+                        sp.values().to(torch.float32), B, V)
+
+    def to_dense(self) -> torch.Tensor:
+        return torch.sparse_csr_tensor(self.indptr.long(), self.indices.long(), self.counts,
+                                       size=(self.B, self.V)).to_dense()
+
+
+class CscWorkspace:
+    """Per-step transpose of the minibatch (colptr / row ids / source positions)."""
+
+    def __init__(self, V: int, max_nnz: int, device) -> None:
+        self.V = V
+        self.colptr = torch.zeros(V + 1, dtype=torch.int32, device=device)
+        self.cursor = torch.zeros(V, dtype=torch.int32, device=device)
+        self.row = torch.zeros(max(max_nnz, 1), dtype=torch.int32, device=device)
+        self.src = torch.zeros(max(max_nnz, 1), dtype=torch.int32, device=device)
+
+    def build(self, batch: CsrBatch) -> None:
+        assert batch.nnz <= self.row.numel(), "CSC workspace too small for this minibatch"
+        K_.csr_to_csc(batch.indptr, batch.indices, B=batch.B, V=self.V, nnz=batch.nnz,
+                      colptr=self.colptr, cursor=self.cursor, csc_row=self.row, csc_src=self.src)
+
+
+class ProdLDADecoder:
+    """Workspace + launcher for the fused ProdLDA decoder at fixed (max B, V, K)."""
+
+    def __init__(self, max_B: int, V: int, K: int, max_nnz: int, device, bn_eps: float = 1e-5,
+                 bn_momentum: float = 0.1) -> None:
+        self.max_B, self.V, self.K = max_B, V, K
+        self.Kp = padded_topics(K)
+        if self.Kp > 240:
+            raise ValueError("the fused decoder supports n_components <= 240")
+        self.bn_eps, self.bn_momentum = bn_eps, bn_momentum
+        dev = device
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.Bpad = round_up(max_B, TILE)
+        self.Vpad = round_up(V, TILE)
+        self.theta_bf = torch.zeros(max_B, self.Kp, dtype=torch.bfloat16, device=dev)
+        self.theta_mean = torch.zeros(K, **f32)
+        self.colc = torch.zeros(self.Vpad, 4, **f32)
+        self.sb_doc = torch.zeros(self.Bpad, 4, **f32)
+        self.doc_const = torch.zeros(max_B, 2, **f32)
+        self.max_chunks = (V + TILE - 1) // TILE
+        self.lse_part = torch.zeros(max_B * self.max_chunks, 2, **f32)
+        self.rl = torch.zeros(max_B, **f32)
+        self.asp_csp = torch.zeros(2, V, **f32)
+        self.tnnz = torch.zeros(max(max_nnz, 1), **f32)
+        self.corr = torch.zeros(V, self.Kp, **f32)
+        self.dtheta = torch.zeros(max_B, self.Kp, **f32)
+
+    # -- forward statistics + per-document reconstruction loss (+ everything backward needs)
+    def forward_backward(self, theta: torch.Tensor, theta_colsum: torch.Tensor, beta_bf: torch.Tensor,
+                         betaT_bf: torch.Tensor, batch: CsrBatch, csc: Optional[CscWorkspace], *,
+                         training: bool, running_mean: Optional[torch.Tensor],
+                         running_var: Optional[torch.Tensor], dbeta: Optional[torch.Tensor],
+                         loss: Optional[torch.Tensor], gscale: float = 1.0, need_grad: bool = True):
+        """Runs the sweeps.  Returns (rl[B], dtheta[B,Kp] or None).  ``dbeta`` [K,ld] is overwritten."""
+        B, V, Kt = batch.B, self.V, self.K
+        assert B <= self.max_B
+        K_.theta_center(theta, theta_colsum, self.theta_bf, self.theta_mean, B=B, K=Kt, center=training)
+        K_.dec_sweep(K_.COL_STATS, B=B, V=V, K=Kt, theta_bf=self.theta_bf, beta_bf=beta_bf,
+                     sb_stream=self.sb_doc, colc=self.colc,
+                     theta_mean=self.theta_mean if training else None,
+                     running_mean=running_mean, running_var=running_var, bn_eps=self.bn_eps,
+                     bn_momentum=self.bn_momentum, use_running=not training)
+        n_chunks = K_.default_row_chunks(B, V)
+        K_.dec_sweep(K_.ROW_LSE, B=B, V=V, K=Kt, theta_bf=self.theta_bf, beta_bf=beta_bf,
+                     sb_stream=self.colc, n_chunks=n_chunks, lse_part=self.lse_part)
+        grad = need_grad and training
+        if grad:
+            self.asp_csp.zero_()
+        K_.dec_sparse_doc(B=B, n_chunks=n_chunks, indptr=batch.indptr, indices=batch.indices,
+                          counts=batch.counts, theta_bf=self.theta_bf, betaT_bf=betaT_bf, colc=self.colc,
+                          lse_part=self.lse_part, gscale=gscale, rl=self.rl, loss=loss,
+                          asp=self.asp_csp[0] if grad else None, csp=self.asp_csp[1] if grad else None,
+                          tnnz=self.tnnz if grad else None, dtheta=self.dtheta if grad else None,
+                          doc_const=self.doc_const if grad else None, sb_doc=self.sb_doc if grad else None)
+        if not grad:
+            return self.rl[:B], None
+        assert csc is not None and dbeta is not None
+        K_.csc_corr(csc.colptr, csc.row, csc.src, self.tnnz, self.theta_bf, self.corr, V=V)
+        K_.dec_sweep(K_.COL_GRAD, B=B, V=V, K=Kt, theta_bf=self.theta_bf, beta_bf=beta_bf,
+                     sb_stream=self.sb_doc, colc=self.colc, asp=self.asp_csp[0], csp=self.asp_csp[1],
+                     dbeta=dbeta, corr=self.corr, colptr=csc.colptr)
+        n_chunks_g = K_.default_row_chunks(B, V, second_mma=True)
+        K_.dec_sweep(K_.ROW_GRAD, B=B, V=V, K=Kt, theta_bf=self.theta_bf, beta_bf=beta_bf,
+                     sb_stream=self.colc, n_chunks=n_chunks_g, doc_const=self.doc_const,
+                     dtheta=self.dtheta)
+        return self.rl[:B], self.dtheta[:B]
+
+
+def make_beta_shadows(K: int, V: int, device):
+    """bf16 operand shadows of beta: [Kp, ldb] (rows >= K zero) and beta^T [V, Kp]."""
+    Kp = padded_topics(K)
+    beta_bf = torch.zeros(Kp, round_up(V, 8), dtype=torch.bfloat16, device=device)
+    betaT_bf = torch.zeros(V, Kp, dtype=torch.bfloat16, device=device)
+    return beta_bf, betaT_bf
+
+
+def refresh_beta_shadows(beta: torch.Tensor, beta_bf: torch.Tensor, betaT_bf: torch.Tensor) -> None:
+    K, V = beta.shape
+    K_.adam_beta(beta, None, None, None, beta_bf, betaT_bf, K=K, V=V, do_update=False)

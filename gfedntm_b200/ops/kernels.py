@@ -1,0 +1,271 @@
+"""Torch-tensor front end of the C-ABI kernels.
+
+Every function takes CUDA tensors, checks shapes/dtypes, fills the argument struct and launches
+on the current CUDA stream.  There is no CPU or PyTorch fallback in this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import (GF_MAX_HIDDEN, GfDecSparseArgs, GfEncArgs, GfEncBwdArgs, GfLatentArgs,
+                   GfLatentBwdArgs, GfSweepArgs, check)
+
+ROW_LOGITS, ROW_LSE, ROW_GRAD, COL_STATS, COL_GRAD, COL_LOGITS = range(6)
+TILE = 128
+LOG2E = 1.4426950408889634
+LN2 = 0.6931471805599453
+
+ACTIVATIONS = {"softplus": 0, "relu": 1, "sigmoid": 2, "tanh": 3, "leakyrelu": 4, "rrelu": 5,
+               "elu": 6, "selu": 7}
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    if t is None:
+        return None
+    assert t.is_cuda, "kernel arguments must be CUDA tensors"
+    return t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def padded_topics(k: int) -> int:
+    """Topics padded to the UMMA K granularity (16)."""
+    return round_up(k, 16)
+
+
+def default_row_chunks(B: int, V: int, second_mma: bool = False) -> int:
+    """Vocabulary split of the ROW sweeps so that (doc tiles x chunks) fills the SMs ~2x."""
+    props = torch.cuda.get_device_properties(torch.cuda.current_device())
+    sms = props.multi_processor_count
+    doc_tiles = (B + TILE - 1) // TILE
+    word_tiles = (V + TILE - 1) // TILE
+    waves = 1 if second_mma else 2
+    target = max(1, (sms * waves + doc_tiles - 1) // doc_tiles)
+    return max(1, min(word_tiles, target))
+
+
+# ----------------------------------------------------------------------------------------------
+# decoder sweeps
+# ----------------------------------------------------------------------------------------------
+def dec_sweep(mode: int, *, B: int, V: int, K: int, theta_bf: torch.Tensor, beta_bf: torch.Tensor,
+              sb_stream: torch.Tensor, n_chunks: int = 1, out=None, lse_part=None, doc_const=None,
+              dtheta=None, colc=None, theta_mean=None, running_mean=None, running_var=None,
+              bn_eps: float = 1e-5, bn_momentum: float = 0.1, use_running: bool = False, asp=None,
+              csp=None, dbeta=None, corr=None, colptr=None) -> None:
+    lib = _lib.load()
+    Kp = beta_bf.shape[0]
+    assert theta_bf.dtype == torch.bfloat16 and beta_bf.dtype == torch.bfloat16
+    assert theta_bf.shape[0] >= B and theta_bf.stride(1) == 1 and beta_bf.stride(1) == 1
+    a = GfSweepArgs()
+    a.mode, a.B, a.V, a.K, a.Kp, a.n_chunks = mode, B, V, K, Kp, n_chunks
+    a.theta_bf, a.ld_theta = _ptr(theta_bf), theta_bf.stride(0)
+    a.beta_bf, a.ld_beta = _ptr(beta_bf), beta_bf.stride(0)
+    a.sb_stream = _ptr(sb_stream)
+    a.out, a.lse_part, a.doc_const, a.dtheta = _ptr(out), _ptr(lse_part), _ptr(doc_const), _ptr(dtheta)
+    a.colc, a.theta_mean = _ptr(colc), _ptr(theta_mean)
+    a.running_mean, a.running_var = _ptr(running_mean), _ptr(running_var)
+    a.bn_eps, a.bn_momentum, a.use_running = bn_eps, bn_momentum, int(use_running)
+    a.asp, a.csp = _ptr(asp), _ptr(csp)
+    a.dbeta, a.ld_dbeta = _ptr(dbeta), (dbeta.stride(0) if dbeta is not None else 0)
+    a.corr, a.colptr = _ptr(corr), _ptr(colptr)
+    check(lib.gf_dec_sweep(C.byref(a), _stream()), "gf_dec_sweep")
+
+
+# ----------------------------------------------------------------------------------------------
+# encoder / latent
+# ----------------------------------------------------------------------------------------------
+def _fill_ptr_array(arr, tensors: Sequence[Optional[torch.Tensor]]) -> None:
+    for i, t in enumerate(tensors):
+        arr[i] = _ptr(t)
+
+
+def enc_fwd(*, B: int, V: int, K: int, hidden: Sequence[int], act: int, training: bool,
+            indptr, indices, counts, W1T, b1, xdense, WdT, Wh, bh, Wmu, bmu, Wsig, bsig, pre,
+            enc_drop_p: float, mask_enc_in, mask_enc, mu_pre, ls_pre, bn_sums, seed: int) -> None:
+    lib = _lib.load()
+    a = GfEncArgs()
+    a.B, a.V, a.K, a.L = B, V, K, len(hidden)
+    for i, h in enumerate(hidden):
+        a.H[i] = h
+    a.act, a.training = act, int(training)
+    a.indptr, a.indices, a.counts = _ptr(indptr), _ptr(indices), _ptr(counts)
+    a.W1T, a.b1 = _ptr(W1T), _ptr(b1)
+    a.xdense, a.C, a.WdT = _ptr(xdense), (xdense.shape[1] if xdense is not None else 0), _ptr(WdT)
+    _fill_ptr_array(a.Wh, Wh)
+    _fill_ptr_array(a.bh, bh)
+    a.Wmu, a.bmu, a.Wsig, a.bsig = _ptr(Wmu), _ptr(bmu), _ptr(Wsig), _ptr(bsig)
+    _fill_ptr_array(a.pre, pre)
+    a.enc_drop_p = enc_drop_p
+    a.mask_enc_in, a.mask_enc = _ptr(mask_enc_in), _ptr(mask_enc)
+    a.mu_pre, a.ls_pre, a.bn_sums = _ptr(mu_pre), _ptr(ls_pre), _ptr(bn_sums)
+    a.seed = seed & 0xFFFFFFFFFFFFFFFF
+    check(lib.gf_enc_fwd(C.byref(a), _stream()), "gf_enc_fwd")
+
+
+def latent_fwd(*, B: int, K: int, training: bool, sample: bool, mu_pre, ls_pre, bn_sums, mu_rm,
+               mu_rv, ls_rm, ls_rv, bn_eps: float, bn_momentum: float, prior_mean, prior_var, eps_in,
+               mask_theta_in, theta_drop_p: float, mu, logvar, eps, theta_s, mask_theta, theta,
+               theta_colsum, kl, loss, kl_weight: float, seed: int) -> None:
+    lib = _lib.load()
+    a = GfLatentArgs()
+    a.B, a.K, a.training, a.sample = B, K, int(training), int(sample)
+    a.mu_pre, a.ls_pre, a.bn_sums = _ptr(mu_pre), _ptr(ls_pre), _ptr(bn_sums)
+    a.mu_rm, a.mu_rv, a.ls_rm, a.ls_rv = _ptr(mu_rm), _ptr(mu_rv), _ptr(ls_rm), _ptr(ls_rv)
+    a.bn_eps, a.bn_momentum = bn_eps, bn_momentum
+    a.prior_mean, a.prior_var = _ptr(prior_mean), _ptr(prior_var)
+    a.eps_in, a.mask_theta_in, a.theta_drop_p = _ptr(eps_in), _ptr(mask_theta_in), theta_drop_p
+    a.mu, a.logvar, a.eps, a.theta_s = _ptr(mu), _ptr(logvar), _ptr(eps), _ptr(theta_s)
+    a.mask_theta, a.theta = _ptr(mask_theta), _ptr(theta)
+    a.theta_colsum, a.kl, a.loss, a.kl_weight = _ptr(theta_colsum), _ptr(kl), _ptr(loss), kl_weight
+    a.seed = seed & 0xFFFFFFFFFFFFFFFF
+    check(lib.gf_latent_fwd(C.byref(a), _stream()), "gf_latent_fwd")
+
+
+def theta_center(theta, colsum, out_bf16, mean_out, *, B: int, K: int, center: bool) -> None:
+    lib = _lib.load()
+    check(lib.gf_theta_center(_ptr(theta), _ptr(colsum), _ptr(out_bf16), _ptr(mean_out), B, K,
+                              out_bf16.stride(0), int(center), _stream()), "gf_theta_center")
+
+
+def latent_bwd(*, B: int, K: int, dtheta, mask_theta, theta_s, mu, logvar, eps, prior_mean,
+               prior_var, kl_weight: float, gscale: float, dmu, dlv, bn_bsums, d_prior_mean,
+               d_prior_var) -> None:
+    lib = _lib.load()
+    a = GfLatentBwdArgs()
+    a.B, a.K = B, K
+    a.dtheta, a.ld_dtheta = _ptr(dtheta), dtheta.stride(0)
+    a.mask_theta, a.theta_s, a.mu, a.logvar, a.eps = (_ptr(mask_theta), _ptr(theta_s), _ptr(mu),
+                                                       _ptr(logvar), _ptr(eps))
+    a.prior_mean, a.prior_var = _ptr(prior_mean), _ptr(prior_var)
+    a.kl_weight, a.gscale = kl_weight, gscale
+    a.dmu, a.dlv, a.bn_bsums = _ptr(dmu), _ptr(dlv), _ptr(bn_bsums)
+    a.d_prior_mean, a.d_prior_var = _ptr(d_prior_mean), _ptr(d_prior_var)
+    check(lib.gf_latent_bwd(C.byref(a), _stream()), "gf_latent_bwd")
+
+
+def enc_bwd(*, B: int, V: int, K: int, hidden: Sequence[int], act: int, dmu, dlv, mu, logvar,
+            bn_sums, bn_bsums, bn_eps: float, pre, mask_enc, Wh, Wmu, Wsig, dWh, dbh, dWmu, dbmu,
+            dWsig, dbsig, db1, dpre0, xdense, dWdT, seed: int) -> None:
+    lib = _lib.load()
+    a = GfEncBwdArgs()
+    a.B, a.V, a.K, a.L = B, V, K, len(hidden)
+    for i, h in enumerate(hidden):
+        a.H[i] = h
+    a.act = act
+    a.dmu, a.dlv, a.mu, a.logvar = _ptr(dmu), _ptr(dlv), _ptr(mu), _ptr(logvar)
+    a.bn_sums, a.bn_bsums, a.bn_eps = _ptr(bn_sums), _ptr(bn_bsums), bn_eps
+    _fill_ptr_array(a.pre, pre)
+    a.mask_enc = _ptr(mask_enc)
+    _fill_ptr_array(a.Wh, Wh)
+    a.Wmu, a.Wsig = _ptr(Wmu), _ptr(Wsig)
+    _fill_ptr_array(a.dWh, dWh)
+    _fill_ptr_array(a.dbh, dbh)
+    a.dWmu, a.dbmu, a.dWsig, a.dbsig, a.db1 = _ptr(dWmu), _ptr(dbmu), _ptr(dWsig), _ptr(dbsig), _ptr(db1)
+    a.dpre0 = _ptr(dpre0)
+    a.xdense, a.C, a.dWdT = _ptr(xdense), (xdense.shape[1] if xdense is not None else 0), _ptr(dWdT)
+    a.seed = seed & 0xFFFFFFFFFFFFFFFF
+    check(lib.gf_enc_bwd(C.byref(a), _stream()), "gf_enc_bwd")
+
+
+# ----------------------------------------------------------------------------------------------
+# sparse side
+# ----------------------------------------------------------------------------------------------
+def csr_to_csc(indptr, indices, *, B: int, V: int, nnz: int, colptr, cursor, csc_row, csc_src) -> None:
+    lib = _lib.load()
+    check(lib.gf_csr_to_csc(_ptr(indptr), _ptr(indices), B, V, nnz, _ptr(colptr), _ptr(cursor),
+                            _ptr(csc_row), _ptr(csc_src), _stream()), "gf_csr_to_csc")
+
+
+def dec_sparse_doc(*, B: int, n_chunks: int, indptr, indices, counts, theta_bf, betaT_bf, colc,
+                   lse_part, gscale: float, rl, loss, asp, csp, tnnz, dtheta, doc_const, sb_doc) -> None:
+    lib = _lib.load()
+    a = GfDecSparseArgs()
+    a.B, a.Kp, a.n_chunks = B, betaT_bf.shape[1], n_chunks
+    a.indptr, a.indices, a.counts = _ptr(indptr), _ptr(indices), _ptr(counts)
+    a.theta_bf, a.ld_theta = _ptr(theta_bf), theta_bf.stride(0)
+    a.betaT_bf, a.colc, a.lse_part = _ptr(betaT_bf), _ptr(colc), _ptr(lse_part)
+    a.gscale = gscale
+    a.rl, a.loss, a.asp, a.csp, a.tnnz = _ptr(rl), _ptr(loss), _ptr(asp), _ptr(csp), _ptr(tnnz)
+    a.dtheta, a.doc_const, a.sb_doc = _ptr(dtheta), _ptr(doc_const), _ptr(sb_doc)
+    check(lib.gf_dec_sparse_doc(C.byref(a), _stream()), "gf_dec_sparse_doc")
+
+
+def csc_corr(colptr, csc_row, csc_src, tnnz, theta_bf, corr, *, V: int) -> None:
+    lib = _lib.load()
+    check(lib.gf_csc_corr(_ptr(colptr), _ptr(csc_row), _ptr(csc_src), _ptr(tnnz), _ptr(theta_bf),
+                          theta_bf.stride(0), _ptr(corr), V, corr.shape[1], _stream()), "gf_csc_corr")
+
+
+def csc_spmm(colptr, csc_row, csc_src, val, dense, out, *, V: int, N: int, accumulate: bool = False) -> None:
+    lib = _lib.load()
+    check(lib.gf_csc_spmm(_ptr(colptr), _ptr(csc_row), _ptr(csc_src), _ptr(val), _ptr(dense),
+                          dense.stride(0), _ptr(out), out.stride(0), V, N, int(accumulate), _stream()),
+          "gf_csc_spmm")
+
+
+def lda_beta_fwd(beta, *, K: int, V: int, eps: float, momentum: float, training: bool, running_mean,
+                 running_var, xhat, col_rstd, bp) -> None:
+    lib = _lib.load()
+    check(lib.gf_lda_beta_fwd(_ptr(beta), beta.stride(0), K, V, eps, momentum, int(training),
+                              _ptr(running_mean), _ptr(running_var), _ptr(xhat), _ptr(col_rstd), _ptr(bp),
+                              _stream()), "gf_lda_beta_fwd")
+
+
+def lda_doc(indptr, indices, counts, theta, bp, *, B: int, K: int, V: int, gscale: float, rl, loss,
+            dtheta, gnnz) -> None:
+    lib = _lib.load()
+    check(lib.gf_lda_doc(_ptr(indptr), _ptr(indices), _ptr(counts), _ptr(theta), _ptr(bp), B, K, V, gscale,
+                         _ptr(rl), _ptr(loss), _ptr(dtheta), (dtheta.stride(0) if dtheta is not None else 0),
+                         _ptr(gnnz), _stream()), "gf_lda_doc")
+
+
+def lda_beta_bwd(bp, dbpT, xhat, col_rstd, dxhat, dbeta, *, K: int, V: int, training: bool) -> None:
+    lib = _lib.load()
+    check(lib.gf_lda_beta_bwd(_ptr(bp), _ptr(dbpT), dbpT.stride(0), _ptr(xhat), _ptr(col_rstd), _ptr(dxhat),
+                              _ptr(dbeta), dbeta.stride(0), K, V, int(training), _stream()), "gf_lda_beta_bwd")
+
+
+def row_topk(mat: torch.Tensor, k: int):
+    """Indices and values of the k largest entries of every row (k <= 32), sorted descending."""
+    lib = _lib.load()
+    rows, V = mat.shape
+    idx = torch.empty(rows, k, dtype=torch.int32, device=mat.device)
+    val = torch.empty(rows, k, dtype=torch.float32, device=mat.device)
+    mat = mat.float()
+    if mat.stride(1) != 1:
+        mat = mat.contiguous()
+    check(lib.gf_row_topk(_ptr(mat), mat.stride(0), rows, V, k, _ptr(idx), _ptr(val), _stream()), "gf_row_topk")
+    return val, idx.long()
+
+
+# ----------------------------------------------------------------------------------------------
+# optimiser
+# ----------------------------------------------------------------------------------------------
+def adam_flat(p, g, m, v, *, lr: float, b1: float, b2: float, eps: float, wd: float, step: int,
+              gscale: float = 1.0) -> None:
+    lib = _lib.load()
+    n = p.numel()
+    assert g.numel() == n and m.numel() == n and v.numel() == n
+    check(lib.gf_adam_flat(_ptr(p), _ptr(g), _ptr(m), _ptr(v), n, lr, b1, b2, eps, wd, step, gscale,
+                           _stream()), "gf_adam_flat")
+
+
+def adam_beta(p, g, m, v, beta_bf, betaT_bf, *, K: int, V: int, lr: float = 0.0, b1: float = 0.9,
+              b2: float = 0.999, eps: float = 1e-8, wd: float = 0.0, step: int = 1, gscale: float = 1.0,
+              do_update: bool = True) -> None:
+    lib = _lib.load()
+    check(lib.gf_adam_beta(_ptr(p), _ptr(g), _ptr(m), _ptr(v), K, V, p.stride(0),
+                           (g.stride(0) if g is not None else 0), _ptr(beta_bf), beta_bf.stride(0),
+                           _ptr(betaT_bf), betaT_bf.shape[1], lr, b1, b2, eps, wd, step, gscale,
+                           int(do_update), _stream()), "gf_adam_beta")

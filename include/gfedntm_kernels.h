@@ -1,0 +1,219 @@
+/* gfedntm_b200 — C ABI of the sm_100a kernel library (libgfedntm_kernels.so).
+ *
+ * Every entry point takes raw device pointers plus a cudaStream_t (passed as void*) and returns
+ * 0 on success, non-zero on error (a message is printed to stderr).  Nothing here allocates
+ * device memory unless stated; callers (gfedntm_b200.ops) own all buffers.
+ *
+ * "Ref" comments cite the reference op each kernel replaces (paths relative to the reference
+ * repository root).
+ */
+#ifndef GFEDNTM_KERNELS_H_
+#define GFEDNTM_KERNELS_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------
+ * Library info
+ * ---------------------------------------------------------------------------------------- */
+/* Returns the ABI version of the loaded library. */
+int gf_abi_version(void);
+/* Number of kernel launches issued through this library since load (all entry points). */
+long long gf_launch_count(void);
+/* sizeof() of argument struct number `which` (order of declaration in this header), -1 if unknown. */
+int gf_sizeof(int which);
+
+/* ------------------------------------------------------------------------------------------
+ * Decoder sweeps (tcgen05 / TMEM / TMA).
+ * Ref: src/models/base/pytorchavitm/avitm_network/decoder_network.py:121-126 (theta.beta ->
+ *      BatchNorm1d(V) -> softmax over V) and avitm.py:225 (BoW NLL), plus their autograd.
+ * ---------------------------------------------------------------------------------------- */
+enum GfSweepMode {
+  GF_ROW_LOGITS = 0, /* out[b,v] = theta_bf[b,:].beta_bf[:,v] (fp32)                           */
+  GF_ROW_LSE = 1,    /* lse_part[b,chunk] = online (max2,sum) of 2^(logit*colc.x + colc.y)     */
+  GF_ROW_GRAD = 2,   /* dtheta[b,:] += sum_v dlogit[b,v] * beta[:,v]      (dense part)         */
+  GF_COL_STATS = 3,  /* colc[v] = {rstd*log2e, bias, 0, 0}; running stats update               */
+  GF_COL_GRAD = 4,   /* colc[v].zw = BN-backward constants; dbeta[:,v] = sum_b dlogit*theta_c  */
+  GF_COL_LOGITS = 5  /* same result as GF_ROW_LOGITS through the word-major operand family     */
+};
+
+typedef struct GfSweepArgs {
+  int mode;              /* GfSweepMode */
+  int B, V, K, Kp;       /* documents, vocabulary, topics, topics padded to a multiple of 16  */
+  int n_chunks;          /* ROW modes: vocabulary split per document tile (>=1)                */
+  const void* theta_bf;  /* [B, ld_theta] bf16, columns >= K zero                               */
+  int ld_theta;
+  const void* beta_bf;   /* [Kp, ld_beta] bf16, rows >= K zero                                  */
+  int ld_beta;
+  const void* sb_stream; /* float4 side band of the streamed axis, padded to a multiple of 128:
+                            ROW modes: colc (per word); COL modes: {lse*log2e, S, 0, 0} per doc.
+                            Padding entries must be finite zeros.                               */
+  float* out;            /* LOGITS modes: [B,V] fp32                                            */
+  void* lse_part;        /* ROW_LSE: float2 [B, n_chunks]                                       */
+  const void* doc_const; /* ROW_GRAD: float2 [B] {lse*log2e, S*ln2}                             */
+  float* dtheta;         /* ROW_GRAD: [B, Kp] fp32, accumulated with atomics                    */
+  void* colc;            /* float4 [ceil(V/128)*128]                                            */
+  const float* theta_mean; /* COL_STATS: [K] batch mean of theta (for running_mean), may be 0  */
+  float* running_mean;   /* [V] or null                                                         */
+  float* running_var;    /* [V] or null                                                         */
+  float bn_eps, bn_momentum;
+  int use_running;       /* COL_STATS: 1 = eval mode (normalise with running statistics)        */
+  const float* asp;      /* COL_GRAD: [V] sparse part of sum_b dy                               */
+  const float* csp;      /* COL_GRAD: [V] sparse part of sum_b dy*y                             */
+  float* dbeta;          /* COL_GRAD: [K, ld_dbeta] fp32                                        */
+  int ld_dbeta;
+  const float* corr;     /* COL_GRAD: [V, Kp] sparse correction (subtracted), may be null       */
+  const int* colptr;     /* COL_GRAD: [V+1] CSC pointer of the batch (required with corr)       */
+} GfSweepArgs;
+
+int gf_dec_sweep(const GfSweepArgs* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Encoder / latent layer (CUDA-core kernels on [B,H] / [B,K] data; the BoW input is CSR).
+ * Ref: avitm_network/inference_network.py:76-85, decoder_network.py:102-118, avitm.py:207-220;
+ *      ctm_network/inference_network.py:79-94,160-193.
+ * ---------------------------------------------------------------------------------------- */
+#define GF_MAX_HIDDEN 8
+
+enum GfActivation {
+  GF_ACT_SOFTPLUS = 0, GF_ACT_RELU, GF_ACT_SIGMOID, GF_ACT_TANH,
+  GF_ACT_LEAKYRELU, GF_ACT_RRELU, GF_ACT_ELU, GF_ACT_SELU
+};
+
+typedef struct GfEncArgs {
+  int B, V, K, L;            /* L = number of hidden layers, H[l] their widths (<= 256)       */
+  int H[GF_MAX_HIDDEN];
+  int act, training;
+  /* sparse first-layer input (may be null for ZeroShotTM): CSR of the minibatch             */
+  const int* indptr; const int* indices; const float* counts;
+  const float* W1T;          /* [V, H0]  input_layer.weight[:, :V] transposed                 */
+  const float* b1;           /* [H0]                                                          */
+  /* dense first-layer input (CTM): xdense [B,C], WdT [C,H0]                                  */
+  const float* xdense; int C; const float* WdT;
+  const float* Wh[GF_MAX_HIDDEN]; const float* bh[GF_MAX_HIDDEN]; /* hidden l: [H[l],H[l-1]]  */
+  const float* Wmu; const float* bmu; const float* Wsig; const float* bsig; /* [K, H_last]    */
+  float* pre[GF_MAX_HIDDEN]; /* out: pre-activations [B, H[l]]                                */
+  float enc_drop_p;
+  const float* mask_enc_in;  /* optional injected dropout multipliers [B, H_last]             */
+  float* mask_enc;           /* out: multipliers used                                         */
+  float* mu_pre; float* ls_pre; /* out: [B,K] head outputs before BatchNorm                   */
+  double* bn_sums;           /* out (+=): [4K] sum mu, sum mu^2, sum ls, sum ls^2 (zeroed by caller) */
+  unsigned long long seed;
+} GfEncArgs;
+int gf_enc_fwd(const GfEncArgs* args, void* stream);
+
+typedef struct GfLatentArgs {
+  int B, K, training, sample;   /* sample: draw eps ~ N(0,1) (else eps = 0 unless eps_in)     */
+  const float* mu_pre; const float* ls_pre;
+  const double* bn_sums;        /* [4K] from gf_enc_fwd (training)                            */
+  float* mu_rm; float* mu_rv; float* ls_rm; float* ls_rv; /* running stats [K]                */
+  float bn_eps, bn_momentum;
+  const float* prior_mean; const float* prior_var;
+  const float* eps_in; const float* mask_theta_in; /* optional injected noise / multipliers   */
+  float theta_drop_p;
+  float* mu; float* logvar; float* eps; float* theta_s; float* mask_theta; float* theta; /* [B,K] */
+  float* theta_colsum;          /* (+=) [K], zeroed by caller; may be null                    */
+  float* kl;                    /* [B]                                                        */
+  double* loss;                 /* (+=) scalar, may be null                                   */
+  float kl_weight;
+  unsigned long long seed;
+} GfLatentArgs;
+int gf_latent_fwd(const GfLatentArgs* args, void* stream);
+
+/* theta_c (bf16, [B, ld]) = theta - colsum/B (center=1) or theta (center=0); zero padded.     */
+int gf_theta_center(const float* theta, const float* colsum, void* out_bf16, float* mean_out,
+                    int B, int K, int ld, int center, void* stream);
+
+typedef struct GfLatentBwdArgs {
+  int B, K;
+  const float* dtheta; int ld_dtheta;  /* gradient w.r.t. theta (post dropout)                */
+  const float* mask_theta; const float* theta_s; const float* mu; const float* logvar; const float* eps;
+  const float* prior_mean; const float* prior_var;
+  float kl_weight, gscale;
+  float* dmu; float* dlv;              /* out: gradient w.r.t. BatchNorm outputs [B,K]        */
+  float* bn_bsums;                     /* (+=) [4K] sum d, sum d*xhat for mu then logvar      */
+  float* d_prior_mean; float* d_prior_var; /* (+=) [K], may be null                           */
+} GfLatentBwdArgs;
+int gf_latent_bwd(const GfLatentBwdArgs* args, void* stream);
+
+typedef struct GfEncBwdArgs {
+  int B, V, K, L;
+  int H[GF_MAX_HIDDEN];
+  int act;
+  const float* dmu; const float* dlv; const float* mu; const float* logvar;
+  const double* bn_sums; const float* bn_bsums; float bn_eps;
+  const float* pre[GF_MAX_HIDDEN]; const float* mask_enc;
+  const float* Wh[GF_MAX_HIDDEN]; const float* Wmu; const float* Wsig;
+  float* dWh[GF_MAX_HIDDEN]; float* dbh[GF_MAX_HIDDEN]; /* (+=)                                */
+  float* dWmu; float* dbmu; float* dWsig; float* dbsig; float* db1; /* (+=)                   */
+  float* dpre0;              /* out: [B,H0] gradient w.r.t. first pre-activation              */
+  const float* xdense; int C; float* dWdT; /* CTM dense input: (+=) [C,H0]                     */
+  unsigned long long seed;
+} GfEncBwdArgs;
+int gf_enc_bwd(const GfEncBwdArgs* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Sparse side: minibatch transpose, decoder non-zeros, scatter kernels, NeuralLDA decoder.
+ * ---------------------------------------------------------------------------------------- */
+/* CSR -> CSC of a minibatch.  colptr [V+1], csc_row/csc_src [nnz]; cursor_scratch is V ints of
+ * scratch owned by the caller.  Ref: client.py:461-462 builds a dense [n_docs,V] array instead. */
+int gf_csr_to_csc(const int* indptr, const int* indices, int B, int V, int nnz, int* colptr,
+                  int* cursor_scratch, int* csc_row, int* csc_src, void* stream);
+
+typedef struct GfDecSparseArgs {
+  int B, Kp, n_chunks;
+  const int* indptr; const int* indices; const float* counts;
+  const void* theta_bf; int ld_theta;   /* bf16 [B, ld_theta]                                  */
+  const void* betaT_bf;                 /* bf16 [V, Kp]                                        */
+  const void* colc;                     /* float4 [Vpad]                                       */
+  const void* lse_part;                 /* float2 [B, n_chunks]                                */
+  float gscale;                         /* upstream gradient scale (federated client weight)   */
+  float* rl;                            /* out [B] reconstruction loss                         */
+  double* loss;                         /* (+=) scalar, may be null                            */
+  float* asp; float* csp;               /* (+=) [V], zeroed by caller; null => forward only    */
+  float* tnnz;                          /* out [nnz]                                           */
+  float* dtheta;                        /* out [B,Kp] sparse part (plain store); may be null   */
+  void* doc_const;                      /* out float2 [B]                                      */
+  void* sb_doc;                         /* out float4 [Bpad]                                   */
+} GfDecSparseArgs;
+int gf_dec_sparse_doc(const GfDecSparseArgs* args, void* stream);
+
+int gf_csc_corr(const int* colptr, const int* csc_row, const int* csc_src, const float* tnnz,
+                const void* theta_bf, int ld_theta, float* corr, int V, int Kp, void* stream);
+/* out[v,:N] (+)= sum_{entries of column v} val[src] * dense[row,:N]                          */
+int gf_csc_spmm(const int* colptr, const int* csc_row, const int* csc_src, const float* val,
+                const float* dense, int ldd, float* out, int ldo, int V, int N, int accumulate,
+                void* stream);
+
+/* NeuralLDA decoder.  Ref: decoder_network.py:127-132.                                        */
+int gf_lda_beta_fwd(const float* beta, int ldb, int K, int V, float eps, float momentum, int training,
+                    float* running_mean, float* running_var, float* xhat, float* col_rstd, float* bp,
+                    void* stream);
+int gf_lda_doc(const int* indptr, const int* indices, const float* counts, const float* theta,
+               const float* bp, int B, int K, int V, float gscale, float* rl, double* loss, float* dtheta,
+               int ld_dtheta, float* gnnz, void* stream);
+int gf_lda_beta_bwd(const float* bp, const float* dbpT, int ldt, const float* xhat, const float* col_rstd,
+                    float* dxhat, float* dbeta, int ldg, int K, int V, int training, void* stream);
+
+/* Row top-k (k <= 32) of a [rows, V] matrix.  Ref: avitm.py:574.                               */
+int gf_row_topk(const float* mat, int ld, int rows, int V, int topk, int* out_idx, float* out_val,
+                void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Optimiser.  Ref: torch.optim.Adam in avitm.py:141-143 / federated_avitm.py:78.
+ * ---------------------------------------------------------------------------------------- */
+int gf_adam_flat(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
+                 float eps, float wd, int step, float gscale, void* stream);
+/* Adam on beta [K,ldp] plus the bf16 operand shadows beta_bf [Kp,ldb] and betaT_bf [V,Kp];
+ * do_update = 0 only refreshes the shadows.                                                  */
+int gf_adam_beta(float* p, const float* g, float* m, float* v, int K, int V, int ldp, int ldg,
+                 void* beta_bf, int ldb, void* betaT_bf, int Kp, float lr, float b1, float b2, float eps,
+                 float wd, int step, float gscale, int do_update, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GFEDNTM_KERNELS_H_ */

@@ -1,0 +1,109 @@
+"""GPU numerics of the tcgen05 decoder sweeps against plain PyTorch fp32 references."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk(B, V, K, seed=0, nnz_per_doc=40):
+    from gfedntm_b200.ops import kernels as Kx
+    from gfedntm_b200.ops.decoder import CsrBatch, make_beta_shadows, refresh_beta_shadows
+
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    dev = "cuda"
+    theta = torch.softmax(torch.randn(B, K, device=dev, generator=g) * 1.5, dim=1)
+    beta = (torch.rand(K, V, device=dev, generator=g) - 0.5) * 0.6
+    x = torch.zeros(B, V, device=dev)
+    idx = torch.randint(0, V, (B, nnz_per_doc), device=dev, generator=g)
+    x.scatter_add_(1, idx, torch.ones(B, nnz_per_doc, device=dev))
+    beta_bf, betaT_bf = make_beta_shadows(K, V, dev)
+    refresh_beta_shadows(beta, beta_bf, betaT_bf)
+    return theta, beta, x, beta_bf, betaT_bf, CsrBatch.from_dense(x), Kx
+
+
+@pytest.mark.parametrize("B,V,K", [(64, 1000, 10), (200, 5000, 50), (300, 2000, 100), (130, 3000, 200)])
+@pytest.mark.parametrize("mode", ["row", "col"])
+def test_logits_gemm(B, V, K, mode):
+    theta, beta, x, beta_bf, betaT_bf, batch, Kx = _mk(B, V, K)
+    Kp = beta_bf.shape[0]
+    th_bf = torch.zeros(B, Kp, dtype=torch.bfloat16, device="cuda")
+    th_bf[:, :K] = theta.to(torch.bfloat16)
+    out = torch.full((B, V), float("nan"), device="cuda")
+    Vpad = Kx.round_up(V, 128)
+    Bpad = Kx.round_up(B, 128)
+    sb = torch.zeros(max(Vpad, Bpad), 4, device="cuda")
+    Kx.dec_sweep(Kx.ROW_LOGITS if mode == "row" else Kx.COL_LOGITS, B=B, V=V, K=K, theta_bf=th_bf,
+                 beta_bf=beta_bf, sb_stream=sb, n_chunks=min(3, (V + 127) // 128), out=out)
+    torch.cuda.synchronize()
+    ref = th_bf[:, :K].float() @ beta_bf[:K, :V].float()
+    assert torch.isfinite(out).all()
+    torch.testing.assert_close(out, ref, rtol=1e-3, atol=1e-4)
+    # the bf16 transposed shadow must agree with the row-major one
+    torch.testing.assert_close(betaT_bf[:, :K].float(), beta_bf[:K, :V].float().t())
+
+
+def _reference(theta, beta_bf, x, K, V, eps=1e-5):
+    thc = (theta - theta.mean(0, keepdim=True)).to(torch.bfloat16).float().requires_grad_(True)
+    bb = beta_bf[:K, :V].float().clone().requires_grad_(True)
+    logits = thc @ bb
+    y = F.batch_norm(logits, None, None, training=True, eps=eps)
+    p = torch.softmax(y, dim=1)
+    rl = -(x * torch.log(p + 1e-10)).sum(1)
+    rl.sum().backward()
+    var = logits.detach().var(0, unbiased=False)
+    return rl.detach(), thc.grad, bb.grad, var
+
+
+@pytest.mark.parametrize("B,V,K", [(64, 1000, 10), (200, 5000, 50), (257, 2100, 100), (130, 3000, 200)])
+def test_prodlda_decoder_fwd_bwd(B, V, K):
+    from gfedntm_b200.ops.decoder import CscWorkspace, ProdLDADecoder
+
+    theta, beta, x, beta_bf, betaT_bf, batch, Kx = _mk(B, V, K, seed=1)
+    dec = ProdLDADecoder(B, V, K, batch.nnz, "cuda")
+    csc = CscWorkspace(V, batch.nnz, "cuda")
+    csc.build(batch)
+    dbeta = torch.zeros(K, V, device="cuda")
+    loss = torch.zeros(1, dtype=torch.float64, device="cuda")
+    rm = torch.zeros(V, device="cuda")
+    rv = torch.ones(V, device="cuda")
+    rl, dtheta = dec.forward_backward(theta, theta.sum(0), beta_bf, betaT_bf, batch, csc, training=True,
+                                      running_mean=rm, running_var=rv, dbeta=dbeta, loss=loss)
+    torch.cuda.synchronize()
+    rl_ref, dth_ref, db_ref, var_ref = _reference(theta, beta_bf, x, K, V)
+    # BatchNorm statistics
+    rstd = dec.colc[:V, 0] * 0.6931471805599453
+    torch.testing.assert_close(rstd, torch.rsqrt(var_ref + 1e-5), rtol=2e-3, atol=1e-6)
+    torch.testing.assert_close(rl, rl_ref, rtol=2e-3, atol=1e-2)
+    assert abs(loss.item() - rl_ref.sum().item()) <= 2e-3 * abs(rl_ref.sum().item())
+    scale_t = dth_ref.abs().max().item()
+    scale_b = db_ref.abs().max().item()
+    err_t = (dtheta[:, :K] - dth_ref).abs().max().item()
+    err_b = (dbeta - db_ref).abs().max().item()
+    assert err_t <= 2e-2 * scale_t, (err_t, scale_t)
+    assert err_b <= 2e-2 * scale_b, (err_b, scale_b)
+    # running statistics (momentum 0.1, unbiased variance)
+    mean_ref = (theta.mean(0, keepdim=True) @ beta_bf[:K, :V].float()).squeeze(0)
+    torch.testing.assert_close(rm, 0.1 * mean_ref, rtol=1e-2, atol=1e-4)
+    torch.testing.assert_close(rv, 0.9 + 0.1 * var_ref * B / (B - 1), rtol=1e-2, atol=1e-6)
+
+
+def test_csr_to_csc_roundtrip():
+    theta, beta, x, beta_bf, betaT_bf, batch, Kx = _mk(77, 999, 10, seed=3)
+    from gfedntm_b200.ops.decoder import CscWorkspace
+
+    csc = CscWorkspace(999, batch.nnz, "cuda")
+    csc.build(batch)
+    torch.cuda.synchronize()
+    colptr = csc.colptr.cpu()
+    assert colptr[0] == 0 and colptr[-1] == batch.nnz
+    counts_per_col = (x > 0).sum(0).cpu()
+    assert torch.equal(colptr[1:] - colptr[:-1], counts_per_col.to(torch.int32))
+    # every CSC entry points back at a CSR entry of the right column / row
+    src = csc.src[: batch.nnz].long()
+    assert torch.equal(torch.sort(src).values.cpu(), torch.arange(batch.nnz))
+    cols = torch.repeat_interleave(torch.arange(999), (colptr[1:] - colptr[:-1]).long()).cuda()
+    assert torch.equal(batch.indices.long()[src], cols)
+    rows_of_src = torch.repeat_interleave(torch.arange(77, device="cuda"),
+                                          (batch.indptr[1:] - batch.indptr[:-1]).long())
+    assert torch.equal(rows_of_src[src], csc.row[: batch.nnz].long())
