@@ -96,18 +96,20 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
              const SweepParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  constexpr uint32_t kOperandBytes = kKChunks * 16384u;  // both A and a B stage
   constexpr uint32_t kSbBytes = kTile * sizeof(float4);
   const int stages = p.stages;
   const int Kp = p.Kp;
+  // theta tile: kKChunks boxes of 64 topics x 128 docs; beta tile: 2 boxes of 64 words x Kp topics
+  const uint32_t a_alloc = kRow ? kKChunks * 16384u : (uint32_t)Kp * 256u;
+  const uint32_t b_alloc = kRow ? (uint32_t)Kp * 256u : kKChunks * 16384u;
 
   Smem s;
   s.a = base;
-  uint8_t* cur = base + kOperandBytes;
+  uint8_t* cur = base + a_alloc;
   for (int i = 0; i < kMaxStages; ++i) {
     s.b[i] = cur;
-    s.sb[i] = reinterpret_cast<float4*>(cur + kOperandBytes);
-    if (i < stages) cur += kOperandBytes + kSbBytes;
+    s.sb[i] = reinterpret_cast<float4*>(cur + b_alloc);
+    if (i < stages) cur += b_alloc + kSbBytes;
   }
   s.p = cur;
   if (kHasMMA2) cur += 32768;
@@ -517,9 +519,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
 template <int kKChunks, bool kRow, bool kHasMMA2>
 static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, SweepParams& p,
                         cudaStream_t stream) {
-  const size_t operand = (size_t)kKChunks * 16384;
-  const size_t fixed = 1024 + operand + (kHasMMA2 ? 32768 : 0) + 512;
-  const size_t per_stage = operand + kTile * sizeof(float4);
+  const size_t theta_tile = (size_t)kKChunks * 16384, beta_tile = (size_t)p.Kp * 256;
+  const size_t fixed = 1024 + (kRow ? theta_tile : beta_tile) + (kHasMMA2 ? 32768 : 0) + 512;
+  const size_t per_stage = (kRow ? beta_tile : theta_tile) + kTile * sizeof(float4);
   int max_smem = 0, dev = 0;
   GF_CUDA_CHECK(cudaGetDevice(&dev));
   GF_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));

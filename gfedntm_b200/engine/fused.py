@@ -1,0 +1,387 @@
+"""Fused sm_100a training / inference engine for the VAE topic models.
+
+The engine owns flat fp32 buffers for parameters, gradients and Adam moments, re-homes the
+``nn.Module`` parameters into them (so ``state_dict()`` / ``load_state_dict()`` keep working on
+the live storage) and runs one minibatch step as a fixed sequence of hand-written kernels:
+
+  csr_to_csc -> enc_fwd -> latent_fwd -> [ProdLDA decoder sweeps | NeuralLDA sparse decoder]
+  -> latent_bwd -> enc_bwd -> csc_spmm (d W1^T) -> fused Adam (+ bf16 operand shadows)
+
+Ref: the per-minibatch body of ``FederatedAVITM.train_mb_delta`` (federated_avitm.py:51-83) /
+``AVITM._train_epoch`` (avitm.py:231-277) and their CTM counterparts.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from ..models.networks import ENCODER_DROPOUT, DecoderNetwork
+from ..ops import kernels as K_
+from ..ops.decoder import (CscWorkspace, CsrBatch, ProdLDADecoder, make_beta_shadows,
+                           refresh_beta_shadows)
+
+BN_EPS = 1e-5
+BN_MOMENTUM = 0.1
+
+
+@dataclass
+class Segment:
+    name: str
+    offset: int
+    numel: int
+    shape: Tuple[int, ...]
+    transposed: bool  # stored as [in, out] (transposed w.r.t. the nn.Linear weight)
+
+
+class FlatParams:
+    """Flat fp32 parameter / gradient / Adam-moment buffers with named segments.
+
+    Order: every small tensor first (one contiguous ``small`` range), then the first-layer weight
+    stored transposed ``[fan_in, H0]`` (row gather for the sparse BoW input), then
+    ``adapt_bert.weight`` (CombinedTM), and ``beta`` last.
+    """
+
+    BIG = ("inf_net.input_layer.weight", "inf_net.adapt_bert.weight", "beta")
+
+    def __init__(self, model: DecoderNetwork, device) -> None:
+        named = [(n, p) for n, p in model.named_parameters()]
+        small = [(n, p) for n, p in named if n not in self.BIG]
+        big = [(n, p) for n in self.BIG for (m, p) in named if m == n]
+        self.segments: Dict[str, Segment] = {}
+        off = 0
+        for n, p in small + big:
+            off = (off + 3) // 4 * 4  # 16-byte alignment of every segment
+            self.segments[n] = Segment(n, off, p.numel(), tuple(p.shape), n == "inf_net.input_layer.weight")
+            off += p.numel()
+        self.total = (off + 3) // 4 * 4
+        first_big = big[0][0]
+        self.small_end = self.segments[first_big].offset
+        self.beta_off = self.segments["beta"].offset
+        f32 = dict(dtype=torch.float32, device=device)
+        self.P = torch.zeros(self.total, **f32)
+        self.G = torch.zeros(self.total, **f32)
+        self.M = torch.zeros(self.total, **f32)
+        self.V2 = torch.zeros(self.total, **f32)
+        self._params = dict(named)
+        with torch.no_grad():
+            for n, p in named:
+                view = self.view(self.P, n)
+                view.copy_(p.detach().to(device))
+                p.data = view
+                p.grad = self.view(self.G, n)
+
+    def view(self, flat: torch.Tensor, name: str) -> torch.Tensor:
+        s = self.segments[name]
+        raw = flat[s.offset:s.offset + s.numel]
+        if s.transposed:
+            out_f, in_f = s.shape
+            return raw.view(in_f, out_f).t()
+        return raw.view(s.shape)
+
+    def storage_view(self, flat: torch.Tensor, name: str) -> torch.Tensor:
+        """The segment in its *storage* layout (first layer: [fan_in, H0])."""
+        s = self.segments[name]
+        raw = flat[s.offset:s.offset + s.numel]
+        if s.transposed:
+            out_f, in_f = s.shape
+            return raw.view(in_f, out_f)
+        return raw.view(s.shape)
+
+
+class FusedEngine:
+    """One model replica on one GPU, trained step-at-a-time through the kernel library."""
+
+    def __init__(self, model: DecoderNetwork, *, max_batch: int, max_nnz: int, lr: float = 2e-3,
+                 betas: Tuple[float, float] = (0.99, 0.99), adam_eps: float = 1e-8,
+                 weight_decay: float = 0.0, kl_weight: float = 1.0, seed: int = 0, device=None) -> None:
+        if not torch.cuda.is_available():
+            raise RuntimeError("FusedEngine needs a CUDA device (sm_100a); use the eager backend on CPU")
+        if model.label_size:
+            raise NotImplementedError("label_size > 0 runs on the eager backend")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.model = model.to(self.device)
+        self.kind = model.infnet
+        self.is_prod = model.model_type.lower() == "prodlda"
+        self.V, self.K = model.input_size, model.n_components
+        self.hidden = tuple(model.hidden_sizes)
+        self.C = model.contextual_size
+        self.act = K_.ACTIVATIONS[model.activation]
+        self.theta_drop = float(model.dropout)
+        self.enc_drop = float(model.inf_net.dropout)
+        self.kl_weight = float(kl_weight)
+        self.lr, self.betas, self.adam_eps, self.weight_decay = lr, betas, adam_eps, weight_decay
+        self.seed = int(seed)
+        self.step_count = 0       # optimiser steps taken
+        self.rng_calls = 0        # forward passes (advances the Philox seed)
+        self.max_batch, self.max_nnz = max_batch, max_nnz
+
+        self.flat = FlatParams(self.model, self.device)
+        dev = self.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        B, K, V = max_batch, self.K, self.V
+        HL = self.hidden[-1]
+        self.Kp = K_.padded_topics(K)
+
+        # forward/backward workspace
+        self.pre = [torch.zeros(B, h, **f32) for h in self.hidden]
+        self.mask_enc = torch.ones(B, HL, **f32)
+        self.mu_pre = torch.zeros(B, K, **f32)
+        self.ls_pre = torch.zeros(B, K, **f32)
+        self.mu = torch.zeros(B, K, **f32)
+        self.logvar = torch.zeros(B, K, **f32)
+        self.eps = torch.zeros(B, K, **f32)
+        self.theta_s = torch.zeros(B, K, **f32)
+        self.mask_theta = torch.ones(B, K, **f32)
+        self.theta = torch.zeros(B, K, **f32)
+        self.kl = torch.zeros(B, **f32)
+        self.dmu = torch.zeros(B, K, **f32)
+        self.dlv = torch.zeros(B, K, **f32)
+        self.dpre0 = torch.zeros(B, self.hidden[0], **f32)
+        # buffers that must start at zero every step, zeroed with one memset each
+        self.zpool = torch.zeros(4 * K + K, **f32)
+        self.bn_bsums = self.zpool[:4 * K]
+        self.theta_colsum = self.zpool[4 * K:5 * K]
+        self.dpool = torch.zeros(4 * K + 1, dtype=torch.float64, device=dev)
+        self.bn_sums = self.dpool[:4 * K]
+        self.loss = self.dpool[4 * K:]
+
+        self.csc = CscWorkspace(V, max_nnz, dev)
+        if self.is_prod:
+            self.decoder = ProdLDADecoder(B, V, K, max_nnz, dev, BN_EPS, BN_MOMENTUM)
+            self.beta_bf, self.betaT_bf = make_beta_shadows(K, V, dev)
+        else:
+            self.xhat = torch.zeros(K, V, **f32)
+            self.bp = torch.zeros(K, V, **f32)
+            self.dxhat = torch.zeros(K, V, **f32)
+            self.col_rstd = torch.zeros(V, **f32)
+            self.dbpT = torch.zeros(V, K, **f32)
+            self.gnnz = torch.zeros(max(max_nnz, 1), **f32)
+            self.rl = torch.zeros(B, **f32)
+            self.dtheta_lda = torch.zeros(B, self.Kp, **f32)
+        self._nbt_pending = 0
+        self.model.register_state_dict_pre_hook(lambda *a, **k: self.flush_counters())
+        self.sync_shadows()
+
+    def flush_counters(self) -> None:
+        """Apply the pending ``num_batches_tracked`` increments of the three BatchNorm layers."""
+        if self._nbt_pending:
+            for bn in (self.model.inf_net.f_mu_batchnorm, self.model.inf_net.f_sigma_batchnorm,
+                       self.model.beta_batchnorm):
+                bn.num_batches_tracked += self._nbt_pending
+            self._nbt_pending = 0
+
+    # ------------------------------------------------------------------------------------------
+    # parameter access helpers
+    # ------------------------------------------------------------------------------------------
+    def _p(self, name: str) -> torch.Tensor:
+        return self.flat.view(self.flat.P, name)
+
+    def _g(self, name: str) -> torch.Tensor:
+        return self.flat.view(self.flat.G, name)
+
+    def sync_shadows(self) -> None:
+        """Rebuild the bf16 operand shadows after parameters were written from outside
+        (load_state_dict, federated parameter averaging)."""
+        if self.is_prod:
+            refresh_beta_shadows(self._p("beta"), self.beta_bf, self.betaT_bf)
+
+    def _hidden_params(self, flat: torch.Tensor):
+        Wh, bh = [], []
+        for i in range(len(self.hidden) - 1):
+            Wh.append(self.flat.view(flat, f"inf_net.hiddens.l_{i}.0.weight"))
+            bh.append(self.flat.view(flat, f"inf_net.hiddens.l_{i}.0.bias"))
+        pad = K_.GF_MAX_HIDDEN - len(Wh)
+        return Wh + [None] * pad, bh + [None] * pad
+
+    def _bn(self, which: str):
+        bn = getattr(self.model.inf_net, which)
+        return bn.running_mean, bn.running_var, bn.num_batches_tracked
+
+    # ------------------------------------------------------------------------------------------
+    # forward (+ backward) of one minibatch
+    # ------------------------------------------------------------------------------------------
+    def _first_layer(self, x_ctx: Optional[torch.Tensor]):
+        """Returns (W1T or None, b1, xdense, WdT) for enc_fwd according to the encoder kind."""
+        st = self.flat.storage_view(self.flat.P, "inf_net.input_layer.weight")  # [fan_in, H0]
+        b1 = self._p("inf_net.input_layer.bias")
+        if self.kind == "bow":
+            return st, b1, None, None
+        if self.kind == "zeroshot":
+            return None, b1, x_ctx, st
+        # combined: collapse adapt_bert into the first layer, M^T = A^T W1b^T  ([C,V] x [V,H0])
+        V = self.V
+        A = self._p("inf_net.adapt_bert.weight")      # [V, C]
+        ab = self._p("inf_net.adapt_bert.bias")       # [V]
+        W1bT = st[V:2 * V]                            # [V, H0]
+        self._MT = A.t() @ W1bT                       # plain library GEMM (cuBLAS), see DESIGN.md
+        self._b1_eff = b1 + ab @ W1bT
+        return st[:V], self._b1_eff, x_ctx, self._MT
+
+    def forward_backward(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *,
+                         training: bool = True, sample: bool = True, gscale: float = 1.0,
+                         need_grad: bool = True, eps_in=None, mask_enc_in=None, mask_theta_in=None):
+        """Runs forward (and backward when ``need_grad``); returns the device scalar
+        ``loss = sum_b (kl_weight*KL_b + RL_b)`` (float64, shape [1])."""
+        B, K, V = batch.B, self.K, self.V
+        if B > self.max_batch or batch.nnz > self.max_nnz:
+            raise ValueError("minibatch exceeds the engine workspace (max_batch / max_nnz)")
+        grad = need_grad and training
+        seed = (self.seed * 0x9E3779B97F4A7C15 + self.rng_calls * 0xD1B54A32D192ED03 + 1) & ((1 << 64) - 1)
+        self.rng_calls += 1
+        self.zpool.zero_()
+        self.dpool.zero_()
+        if grad:
+            self.flat.G[:self.flat.small_end].zero_()
+            self.csc.build(batch)
+
+        W1T, b1, xdense, WdT = self._first_layer(x_ctx)
+        Wh, bh = self._hidden_params(self.flat.P)
+        use_bow = self.kind in ("bow", "combined")
+        pad = [None] * (K_.GF_MAX_HIDDEN - len(self.hidden))
+        K_.enc_fwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, training=training,
+                   indptr=batch.indptr if use_bow else None, indices=batch.indices if use_bow else None,
+                   counts=batch.counts if use_bow else None, W1T=W1T, b1=b1, xdense=xdense, WdT=WdT,
+                   Wh=Wh, bh=bh, Wmu=self._p("inf_net.f_mu.weight"), bmu=self._p("inf_net.f_mu.bias"),
+                   Wsig=self._p("inf_net.f_sigma.weight"), bsig=self._p("inf_net.f_sigma.bias"),
+                   pre=self.pre + pad, enc_drop_p=self.enc_drop, mask_enc_in=mask_enc_in,
+                   mask_enc=self.mask_enc, mu_pre=self.mu_pre, ls_pre=self.ls_pre,
+                   bn_sums=self.bn_sums if training else None, seed=seed)
+        mu_rm, mu_rv, mu_nbt = self._bn("f_mu_batchnorm")
+        ls_rm, ls_rv, ls_nbt = self._bn("f_sigma_batchnorm")
+        K_.latent_fwd(B=B, K=K, training=training, sample=sample, mu_pre=self.mu_pre, ls_pre=self.ls_pre,
+                      bn_sums=self.bn_sums, mu_rm=mu_rm, mu_rv=mu_rv, ls_rm=ls_rm, ls_rv=ls_rv,
+                      bn_eps=BN_EPS, bn_momentum=BN_MOMENTUM, prior_mean=self.model.prior_mean,
+                      prior_var=self.model.prior_variance, eps_in=eps_in, mask_theta_in=mask_theta_in,
+                      theta_drop_p=self.theta_drop, mu=self.mu, logvar=self.logvar, eps=self.eps,
+                      theta_s=self.theta_s, mask_theta=self.mask_theta, theta=self.theta,
+                      theta_colsum=self.theta_colsum, kl=self.kl, loss=self.loss,
+                      kl_weight=self.kl_weight, seed=seed)
+        bbn = self.model.beta_batchnorm
+        if training:
+            self._nbt_pending += 1  # BatchNorm step counters are flushed lazily (state_dict hook)
+
+        if self.is_prod:
+            _, dtheta = self.decoder.forward_backward(
+                self.theta, self.theta_colsum, self.beta_bf, self.betaT_bf, batch, self.csc,
+                training=training, running_mean=bbn.running_mean, running_var=bbn.running_var,
+                dbeta=self._g("beta") if grad else None, loss=self.loss, gscale=gscale, need_grad=grad)
+        else:
+            beta = self._p("beta")
+            K_.lda_beta_fwd(beta, K=K, V=V, eps=BN_EPS, momentum=BN_MOMENTUM, training=training,
+                            running_mean=bbn.running_mean, running_var=bbn.running_var, xhat=self.xhat,
+                            col_rstd=self.col_rstd, bp=self.bp)
+            K_.lda_doc(batch.indptr, batch.indices, batch.counts, self.theta, self.bp, B=B, K=K, V=V,
+                       gscale=gscale, rl=self.rl, loss=self.loss,
+                       dtheta=self.dtheta_lda if grad else None, gnnz=self.gnnz if grad else None)
+            dtheta = self.dtheta_lda[:B] if grad else None
+            if grad:
+                K_.csc_spmm(self.csc.colptr, self.csc.row, self.csc.src, self.gnnz, self.theta, self.dbpT,
+                            V=V, N=K)
+                K_.lda_beta_bwd(self.bp, self.dbpT, self.xhat, self.col_rstd, self.dxhat, self._g("beta"),
+                                K=K, V=V, training=training)
+        if not grad:
+            return self.loss
+
+        learn = self.model.learn_priors
+        K_.latent_bwd(B=B, K=K, dtheta=dtheta, mask_theta=self.mask_theta, theta_s=self.theta_s, mu=self.mu,
+                      logvar=self.logvar, eps=self.eps, prior_mean=self.model.prior_mean,
+                      prior_var=self.model.prior_variance, kl_weight=self.kl_weight, gscale=gscale,
+                      dmu=self.dmu, dlv=self.dlv, bn_bsums=self.bn_bsums,
+                      d_prior_mean=self._g("prior_mean") if learn else None,
+                      d_prior_var=self._g("prior_variance") if learn else None)
+        dWh, dbh = self._hidden_params(self.flat.G)
+        gst = self.flat.storage_view(self.flat.G, "inf_net.input_layer.weight")
+        if self.kind == "zeroshot":
+            gst.zero_()
+            dWdT = gst
+        elif self.kind == "combined":
+            self._dMT = torch.zeros_like(self._MT)
+            dWdT = self._dMT
+        else:
+            dWdT = None
+        K_.enc_bwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, dmu=self.dmu, dlv=self.dlv, mu=self.mu,
+                   logvar=self.logvar, bn_sums=self.bn_sums, bn_bsums=self.bn_bsums, bn_eps=BN_EPS,
+                   pre=self.pre + pad, mask_enc=self.mask_enc, Wh=Wh, Wmu=self._p("inf_net.f_mu.weight"),
+                   Wsig=self._p("inf_net.f_sigma.weight"), dWh=dWh, dbh=dbh,
+                   dWmu=self._g("inf_net.f_mu.weight"), dbmu=self._g("inf_net.f_mu.bias"),
+                   dWsig=self._g("inf_net.f_sigma.weight"), dbsig=self._g("inf_net.f_sigma.bias"),
+                   db1=self._g("inf_net.input_layer.bias"), dpre0=self.dpre0, xdense=xdense, dWdT=dWdT,
+                   seed=seed)
+        if use_bow:
+            # d W1a^T[v,:] = sum_b x[b,v] * dpre0[b,:]  (all V rows written, zeros for unused words)
+            K_.csc_spmm(self.csc.colptr, self.csc.row, self.csc.src, batch.counts, self.dpre0, gst[:V],
+                        V=V, N=self.hidden[0])
+        if self.kind == "combined":
+            st = self.flat.storage_view(self.flat.P, "inf_net.input_layer.weight")
+            A = self._p("inf_net.adapt_bert.weight")
+            ab = self._p("inf_net.adapt_bert.bias")
+            W1bT = st[V:2 * V]
+            dsum = self._g("inf_net.input_layer.bias")        # = sum_b dpre0
+            torch.matmul(W1bT, self._dMT.t(), out=self._g("inf_net.adapt_bert.weight"))
+            torch.addmm(torch.outer(ab, dsum), A, self._dMT, out=gst[V:2 * V])
+            torch.mv(W1bT, dsum, out=self._g("inf_net.adapt_bert.bias"))
+        return self.loss
+
+    # ------------------------------------------------------------------------------------------
+    # optimiser
+    # ------------------------------------------------------------------------------------------
+    def optimizer_step(self, gscale: float = 1.0) -> None:
+        """Fused Adam over the flat buffers; refreshes the bf16 shadows of beta."""
+        self.step_count += 1
+        fl = self.flat
+        b1, b2 = self.betas
+        end = fl.beta_off
+        K_.adam_flat(fl.P[:end], fl.G[:end], fl.M[:end], fl.V2[:end], lr=self.lr, b1=b1, b2=b2,
+                     eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale)
+        K, V = self.K, self.V
+        if self.is_prod:
+            K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"),
+                         fl.view(fl.V2, "beta"), self.beta_bf, self.betaT_bf, K=K, V=V, lr=self.lr, b1=b1,
+                         b2=b2, eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale)
+        else:
+            s = fl.segments["beta"]
+            sl = slice(s.offset, s.offset + s.numel)
+            K_.adam_flat(fl.P[sl], fl.G[sl], fl.M[sl], fl.V2[sl], lr=self.lr, b1=b1, b2=b2,
+                         eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale)
+
+    def train_step(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, **kw) -> torch.Tensor:
+        loss = self.forward_backward(batch, x_ctx, training=True, **kw)
+        self.optimizer_step()
+        return loss
+
+    # ------------------------------------------------------------------------------------------
+    # inference
+    # ------------------------------------------------------------------------------------------
+    def sample_theta(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, n_samples: int = 1
+                     ) -> torch.Tensor:
+        """Mean of ``n_samples`` stochastic draws of theta in eval mode (running BN statistics, no
+        dropout).  Ref: avitm.py:470-523 (get_doc_topic_distribution)."""
+        B, K, V = batch.B, self.K, self.V
+        acc = torch.zeros(B, K, dtype=torch.float32, device=self.device)
+        W1T, b1, xdense, WdT = self._first_layer(x_ctx)
+        Wh, bh = self._hidden_params(self.flat.P)
+        use_bow = self.kind in ("bow", "combined")
+        pad = [None] * (K_.GF_MAX_HIDDEN - len(self.hidden))
+        K_.enc_fwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, training=False,
+                   indptr=batch.indptr if use_bow else None, indices=batch.indices if use_bow else None,
+                   counts=batch.counts if use_bow else None, W1T=W1T, b1=b1, xdense=xdense, WdT=WdT,
+                   Wh=Wh, bh=bh, Wmu=self._p("inf_net.f_mu.weight"), bmu=self._p("inf_net.f_mu.bias"),
+                   Wsig=self._p("inf_net.f_sigma.weight"), bsig=self._p("inf_net.f_sigma.bias"),
+                   pre=self.pre + pad, enc_drop_p=0.0, mask_enc_in=None, mask_enc=None,
+                   mu_pre=self.mu_pre, ls_pre=self.ls_pre, bn_sums=None, seed=0)
+        mu_rm, mu_rv, _ = self._bn("f_mu_batchnorm")
+        ls_rm, ls_rv, _ = self._bn("f_sigma_batchnorm")
+        for _ in range(n_samples):
+            seed = (self.seed * 0x9E3779B97F4A7C15 + self.rng_calls * 0xD1B54A32D192ED03 + 7) & ((1 << 64) - 1)
+            self.rng_calls += 1
+            K_.latent_fwd(B=B, K=K, training=False, sample=True, mu_pre=self.mu_pre, ls_pre=self.ls_pre,
+                          bn_sums=self.bn_sums, mu_rm=mu_rm, mu_rv=mu_rv, ls_rm=ls_rm, ls_rv=ls_rv,
+                          bn_eps=BN_EPS, bn_momentum=BN_MOMENTUM, prior_mean=self.model.prior_mean,
+                          prior_var=self.model.prior_variance, eps_in=None, mask_theta_in=None,
+                          theta_drop_p=0.0, mu=self.mu, logvar=self.logvar, eps=self.eps,
+                          theta_s=self.theta_s, mask_theta=self.mask_theta, theta=self.theta,
+                          theta_colsum=None, kl=self.kl, loss=None, kl_weight=self.kl_weight, seed=seed)
+            acc += self.theta[:B]
+        return acc / float(n_samples)

@@ -1,0 +1,134 @@
+"""Fused engine (all kernels of one training step) against eager PyTorch autograd on the same
+parameters, noise and dropout masks."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle(model, x, x_ctx, eps, mask_enc, mask_theta, kl_weight=1.0):
+    """Eager forward with injected noise/masks; returns loss (sum over batch)."""
+    from gfedntm_b200.models.networks import elbo_terms
+
+    inf = model.inf_net
+    h = inf.activation(inf.input_layer(inf.first_layer_input(x, x_ctx, None)))
+    h = inf.hiddens(h)
+    h = h * mask_enc
+    mu = inf.f_mu_batchnorm(inf.f_mu(h))
+    logvar = inf.f_sigma_batchnorm(inf.f_sigma(h))
+    theta = F.softmax(mu + eps * torch.exp(0.5 * logvar), dim=1) * mask_theta
+    wd = model.decode(theta)
+    kl, rl = elbo_terms(x, wd, model.prior_mean, model.prior_variance, mu, torch.exp(logvar), logvar)
+    return (kl_weight * kl + rl).sum(), theta
+
+
+def _masks(B, H, K, p_enc, p_theta, g):
+    me = (torch.rand(B, H, device="cuda", generator=g) > p_enc).float() / (1 - p_enc)
+    mt = (torch.rand(B, K, device="cuda", generator=g) > p_theta).float() / (1 - p_theta)
+    return me, mt
+
+
+@pytest.mark.parametrize("kind,model_type,act,hidden", [
+    ("bow", "prodLDA", "softplus", (50, 50)),
+    ("bow", "prodLDA", "relu", (64,)),
+    ("bow", "LDA", "softplus", (50, 50)),
+    ("combined", "prodLDA", "softplus", (50, 50)),
+    ("zeroshot", "prodLDA", "tanh", (40, 30, 20)),
+])
+def test_engine_step_matches_autograd(kind, model_type, act, hidden):
+    from gfedntm_b200.engine.fused import FusedEngine
+    from gfedntm_b200.models.networks import DecoderNetwork
+    from gfedntm_b200.ops.decoder import CsrBatch
+
+    torch.manual_seed(0)
+    B, V, K, C = 96, 1500, 20, 48
+    g = torch.Generator(device="cuda").manual_seed(5)
+    model = DecoderNetwork(V, K, model_type, hidden, act, 0.2, True, infnet=kind, contextual_size=C if kind != "bow" else 0)
+    # bigger beta than xavier so the decoder is not dominated by the BN epsilon
+    with torch.no_grad():
+        model.beta.mul_(20.0)
+    ref = copy.deepcopy(model).cuda().train()
+    x = torch.zeros(B, V, device="cuda")
+    idx = torch.randint(0, V, (B, 60), device="cuda", generator=g)
+    x.scatter_add_(1, idx, torch.ones(B, 60, device="cuda"))
+    x_ctx = torch.randn(B, C, device="cuda", generator=g) if kind != "bow" else None
+    eps = torch.randn(B, K, device="cuda", generator=g)
+    me, mt = _masks(B, hidden[-1], K, 0.2, 0.2, g)
+
+    eng = FusedEngine(model, max_batch=B, max_nnz=B * 60, lr=2e-3, seed=1)
+    batch = CsrBatch.from_dense(x)
+    loss = eng.forward_backward(batch, x_ctx, training=True, eps_in=eps, mask_enc_in=me, mask_theta_in=mt)
+    torch.cuda.synchronize()
+
+    ref_loss, ref_theta = _oracle(ref, x, x_ctx, eps, me, mt)
+    ref_loss.backward()
+    assert abs(loss.item() - ref_loss.item()) <= 3e-3 * abs(ref_loss.item()), (loss.item(), ref_loss.item())
+    torch.testing.assert_close(eng.theta[:B], ref_theta, rtol=1e-3, atol=1e-5)
+    for name, p in ref.named_parameters():
+        got = eng.flat.view(eng.flat.G, name)
+        scale = p.grad.abs().max().item() + 1e-12
+        err = (got - p.grad).abs().max().item()
+        assert err <= 3e-2 * scale, f"{name}: err {err:.3e} scale {scale:.3e}"
+    # running statistics of the two encoder BatchNorms follow PyTorch's update rule
+    torch.testing.assert_close(model.inf_net.f_mu_batchnorm.running_mean, ref.inf_net.f_mu_batchnorm.running_mean,
+                               rtol=1e-3, atol=1e-5)
+    torch.testing.assert_close(model.inf_net.f_sigma_batchnorm.running_var, ref.inf_net.f_sigma_batchnorm.running_var,
+                               rtol=1e-3, atol=1e-5)
+    sd = model.state_dict()
+    assert int(sd["beta_batchnorm.num_batches_tracked"]) == 1
+
+
+def test_engine_adam_matches_torch():
+    from gfedntm_b200.engine.fused import FusedEngine
+    from gfedntm_b200.models.networks import DecoderNetwork
+    from gfedntm_b200.ops.decoder import CsrBatch
+
+    torch.manual_seed(1)
+    B, V, K = 64, 800, 10
+    model = DecoderNetwork(V, K, "prodLDA", (32, 32), "softplus", 0.2, True)
+    eng = FusedEngine(model, max_batch=B, max_nnz=B * 30, lr=2e-3, betas=(0.99, 0.99), seed=3)
+    x = torch.zeros(B, V, device="cuda")
+    x.scatter_add_(1, torch.randint(0, V, (B, 30), device="cuda"), torch.ones(B, 30, device="cuda"))
+    batch = CsrBatch.from_dense(x)
+    params = {n: p.detach().clone().requires_grad_(True) for n, p in model.named_parameters()}
+    opt = torch.optim.Adam(list(params.values()), lr=2e-3, betas=(0.99, 0.99))
+    for _ in range(3):
+        eng.forward_backward(batch, training=True)
+        for n, p in params.items():
+            p.grad = eng.flat.view(eng.flat.G, n).detach().clone()
+        eng.optimizer_step()
+        opt.step()
+    torch.cuda.synchronize()
+    for n, p in params.items():
+        torch.testing.assert_close(eng.flat.view(eng.flat.P, n), p.detach(), rtol=1e-4, atol=1e-6)
+    # bf16 shadows track the fp32 master copy of beta
+    torch.testing.assert_close(eng.beta_bf[:K, :V].float(), model.beta.detach().to(torch.bfloat16).float())
+    torch.testing.assert_close(eng.betaT_bf[:, :K].float(), model.beta.detach().t().to(torch.bfloat16).float())
+
+
+def test_engine_loss_decreases_and_theta_inference():
+    from gfedntm_b200.engine.fused import FusedEngine
+    from gfedntm_b200.models.networks import DecoderNetwork
+    from gfedntm_b200.ops.decoder import CsrBatch
+
+    torch.manual_seed(2)
+    B, V, K = 128, 1000, 8
+    # documents drawn from 8 disjoint word blocks -> learnable structure
+    x = torch.zeros(B, V, device="cuda")
+    for b in range(B):
+        blk = b % K
+        idx = torch.randint(blk * (V // K), (blk + 1) * (V // K), (80,), device="cuda")
+        x[b].scatter_add_(0, idx, torch.ones(80, device="cuda"))
+    model = DecoderNetwork(V, K, "prodLDA", (50, 50), "softplus", 0.2, True)
+    eng = FusedEngine(model, max_batch=B, max_nnz=int((x > 0).sum().item()), lr=2e-3, seed=0)
+    batch = CsrBatch.from_dense(x)
+    losses = [eng.train_step(batch).item() for _ in range(150)]
+    assert all(l == l for l in losses)
+    assert losses[-1] < 0.9 * losses[0], (losses[0], losses[-1])
+    theta = eng.sample_theta(batch, n_samples=5)
+    torch.testing.assert_close(theta.sum(1), torch.ones(B, device="cuda"), rtol=1e-4, atol=1e-4)
+    val = eng.forward_backward(batch, training=False, sample=True, need_grad=False)
+    assert torch.isfinite(val).all()
