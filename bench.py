@@ -1,0 +1,296 @@
+#!/usr/bin/env python
+"""Headline benchmark: federated ProdLDA/CTM training throughput (documents / second).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config NAME] [--impl ours|reference]
+
+One federated client per GPU (one process per GPU; for N > 1 launch through
+``python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N``).  Every client runs
+one minibatch step per global step on its own synthetic LDA corpus; with N > 1 the clients
+aggregate every step (weighted by corpus size) through the fused NVLink collective.
+
+Prints ONE JSON line on rank 0.  ``value`` is the device-timed (CUDA events, max over ranks)
+aggregate docs/s with the minibatches already resident on the device; ``e2e`` is the same metric
+through the public trainer API with every step's minibatch assembled on the host, copied from
+pinned memory, and the loss read back.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # BASELINE.json configs (hidden sizes / optimiser from config/dft_params.cf of the reference)
+    "prodlda_10k": dict(family="avitm", model_type="prodLDA", V=10000, K=50, hidden=(50, 50), B=64,
+                        desc="ProdLDA K=50 V=10k, batch 64/client"),
+    "neurallda_20k": dict(family="avitm", model_type="LDA", V=20000, K=50, hidden=(50, 50), B=64,
+                          desc="NeuralLDA K=50 V=20k, batch 64/client"),
+    "ctm_50k": dict(family="ctm", model_type="prodLDA", V=50000, K=100, hidden=(50, 50), B=64, C=768,
+                    inference_type="combined", desc="CombinedTM K=100 V=50k C=768, batch 64/client"),
+    "zeroshot_50k": dict(family="ctm", model_type="prodLDA", V=50000, K=100, hidden=(50, 50), B=64, C=768,
+                         inference_type="zeroshot", desc="ZeroShotTM K=100 V=50k C=768, batch 64/client"),
+    "prodlda_200k": dict(family="avitm", model_type="prodLDA", V=200000, K=200, hidden=(50, 50), B=4096,
+                         desc="large-vocab ProdLDA V=200k K=200, batch 4096/client"),
+}
+DEFAULT_CONFIG = "prodlda_200k"
+L2_BYTES = 126 * 1024 * 1024
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons every 200 ms while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int) -> None:
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self) -> None:
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu_index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self) -> None:
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def make_corpus(cfg: dict, n_docs: int, seed: int, device: str):
+    from gfedntm_b200.utils.synthetic import generate_corpus_gpu
+
+    counts, _ = generate_corpus_gpu(n_docs, cfg["V"], cfg["K"], eta=0.01, seed=seed, device=device)
+    ctx = None
+    if cfg["family"] == "ctm":
+        ctx = np.random.default_rng(seed).standard_normal((n_docs, cfg["C"])).astype(np.float32)
+    return counts, ctx
+
+
+def allreduce_max(x: float, world: int, device) -> float:
+    if world == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args, cfg: dict) -> dict:
+    import torch
+    import torch.distributed as dist
+
+    from gfedntm_b200.federated.trainer import FederatedTrainer
+    from gfedntm_b200.models import AVITM, CTM, BOWDataset, CTMDataset
+    from gfedntm_b200.ops import _lib
+
+    rank, world, local = dist_env()
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    B, V, K = cfg["B"], cfg["V"], cfg["K"]
+    n_batches = 4
+    counts, ctx = make_corpus(cfg, B * n_batches, seed=1234 + rank, device=f"cuda:{local}")
+    vocab = None
+    if cfg["family"] == "ctm":
+        ds = CTMDataset(ctx, counts, vocab)
+        model = CTM(input_size=V, contextual_size=cfg["C"], inference_type=cfg["inference_type"],
+                    n_components=K, model_type=cfg["model_type"], hidden_sizes=cfg["hidden"], batch_size=B,
+                    num_epochs=1, verbose=False, device=device, seed=7)
+    else:
+        ds = BOWDataset(counts, vocab)
+        model = AVITM(input_size=V, n_components=K, model_type=cfg["model_type"], hidden_sizes=cfg["hidden"],
+                      batch_size=B, num_epochs=1, verbose=False, device=device, seed=7)
+    assert model.backend == "fused", "bench must run the sm_100a kernel path"
+    trainer = FederatedTrainer(model, n_samples=len(ds), world_size=world, rank=rank, agg=args.agg)
+    loader = model.make_loader(ds, shuffle=True)
+    trainer.prepare(loader)
+    lib = _lib.load()
+
+    # ---- device-resident minibatches for the kernel-only number
+    staged = []
+    for mb in loader:
+        staged.append((mb.bow.__class__(mb.bow.indptr.clone(), mb.bow.indices.clone(), mb.bow.counts.clone(),
+                                        mb.bow.B, mb.bow.V),
+                       mb.x_ctx.clone() if mb.x_ctx is not None else None))
+    torch.cuda.synchronize()
+    small_ws = trainer.working_set_bytes() < 2 * L2_BYTES
+    flush = torch.empty(2 * L2_BYTES // 4, dtype=torch.float32, device=device) if small_ws else None
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        bow, xc = staged[i % len(staged)]
+        trainer.step(bow, xc)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.gf_launch_count()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    if flush is None:
+        starts[0].record()
+    for i in range(args.steps):
+        bow, xc = staged[i % len(staged)]
+        if flush is not None:
+            flush.add_(1.0)  # evict L2 between timed steps (write > L2 bytes)
+            starts[i].record()
+        trainer.step(bow, xc)
+        if flush is not None:
+            ends[i].record()
+    if flush is None:
+        ends[-1].record()
+    barrier()
+    launches = lib.gf_launch_count() - launches0
+    if flush is None:
+        ms = starts[0].elapsed_time(ends[-1])
+    else:
+        ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
+    ms = allreduce_max(ms, world, device)
+    agg_us = trainer.last_aggregation_us()
+
+    # ---- end to end through the public API: host assembly + pinned H2D + step + loss D2H
+    loss_host = torch.zeros(1, dtype=torch.float64).pin_memory()
+    it = iter(loader)
+    h2d = 0
+    for _ in range(min(args.warmup, 3)):
+        try:
+            mb = next(it)
+        except StopIteration:
+            it = iter(loader)
+            mb = next(it)
+        trainer.step(mb.bow, mb.x_ctx)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        try:
+            mb = next(it)
+        except StopIteration:
+            it = iter(loader)
+            mb = next(it)
+        loss = trainer.step(mb.bow, mb.x_ctx)
+        loss_host.copy_(loss.reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        h2d = mb.h2d_bytes
+    barrier()
+    e2e_s = allreduce_max(time.perf_counter() - t0, world, device)
+    clocks = sampler.stop() if rank == 0 else None
+
+    docs = world * B * args.steps
+    value = docs / (ms / 1e3)
+    out = {
+        "metric": "ProdLDA/CTM docs/sec (federated, one client per GPU)", "value": value, "unit": "docs/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic LDA corpus (torch-sampled), random-init weights",
+        "config": {"model": cfg["desc"], "name": args.config, "global_batch": world * B, "seq_len": None,
+                   "vocab": V, "topics": K, "hidden": list(cfg["hidden"]),
+                   "parallelism": f"fed{world}" + (f"-{args.agg}" if world > 1 else ""),
+                   "l2": "flush 252 MB between timed steps" if flush is not None else
+                         "working set (params+shadows+grads) larger than L2"},
+        "e2e": {"value": docs / e2e_s, "unit": "docs/s", "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": 8, "ms_per_step": 1e3 * e2e_s / args.steps},
+        "gpu_launches": int(launches), "aggregation_us_per_step": agg_us, "clocks": clocks, "impl": "ours",
+    }
+    if world > 1:
+        dist.destroy_process_group()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args, cfg: dict) -> dict:
+    from baseline.ref_arm import run_reference_arm
+
+    return run_reference_arm(args, cfg, ClockSampler, dist_env, make_corpus, allreduce_max)
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--config", type=str, default=DEFAULT_CONFIG, choices=sorted(CONFIGS))
+    ap.add_argument("--impl", type=str, default="ours", choices=["ours", "reference"])
+    ap.add_argument("--agg", type=str, default="grad", choices=["grad", "param"],
+                    help="federated aggregation: weighted gradients + global Adam, or weighted parameters")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    cfg = CONFIGS[args.config]
+    rank, world, _ = dist_env()
+    if world != args.gpus and args.gpus > 1 and world == 1:
+        # convenience: spawn the ranks ourselves when not started through torch.distributed.run
+        port = 29500 + (os.getpid() % 2000)
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    try:
+        out = run_reference(args, cfg) if args.impl == "reference" else run_ours(args, cfg)
+    except ImportError as ex:
+        if args.impl != "reference":
+            raise
+        out = {"impl": "reference", "unavailable": f"reference arm not importable: {ex}"}
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

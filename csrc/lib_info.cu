@@ -19,6 +19,8 @@ extern "C" int gf_sizeof(int which) {
     case 3: return (int)sizeof(GfLatentBwdArgs);
     case 4: return (int)sizeof(GfEncBwdArgs);
     case 5: return (int)sizeof(GfDecSparseArgs);
+    case 6: return (int)sizeof(GfFabricRank);
+    case 7: return (int)sizeof(GfFedArgs);
     default: return -1;
   }
 }

@@ -45,7 +45,7 @@ class FlatParams:
 
     BIG = ("inf_net.input_layer.weight", "inf_net.adapt_bert.weight", "beta")
 
-    def __init__(self, model: DecoderNetwork, device) -> None:
+    def __init__(self, model: DecoderNetwork, device, arena) -> None:
         named = [(n, p) for n, p in model.named_parameters()]
         small = [(n, p) for n, p in named if n not in self.BIG]
         big = [(n, p) for n in self.BIG for (m, p) in named if m == n]
@@ -60,8 +60,25 @@ class FlatParams:
         self.small_end = self.segments[first_big].offset
         self.beta_off = self.segments["beta"].offset
         f32 = dict(dtype=torch.float32, device=device)
-        self.P = torch.zeros(self.total, **f32)
-        self.G = torch.zeros(self.total, **f32)
+        # BatchNorm running statistics: one flat buffer as well (federated clients average them)
+        K, V = model.n_components, model.input_size
+        self.s_n = (4 * K + 2 * V + 3) // 4 * 4
+        Kp = (K + 15) // 16 * 16
+        ldb = (V + 7) // 8 * 8
+        self.has_shadows = model.model_type.lower() == "prodlda"
+        if "P" not in arena.offsets:
+            arena.reserve("P", 4 * self.total)
+            arena.reserve("G", 4 * self.total)
+            arena.reserve("S", 4 * self.s_n)
+            arena.reserve("flags", 256)
+            if self.has_shadows:
+                arena.reserve("beta_bf", 2 * Kp * ldb)
+                arena.reserve("betaT_bf", 2 * V * Kp)
+            arena.commit(device)
+        self.arena = arena
+        self.P = arena.tensor("P", torch.float32)
+        self.G = arena.tensor("G", torch.float32)
+        self.S = arena.tensor("S", torch.float32)
         self.M = torch.zeros(self.total, **f32)
         self.V2 = torch.zeros(self.total, **f32)
         self._params = dict(named)
@@ -71,6 +88,17 @@ class FlatParams:
                 view.copy_(p.detach().to(device))
                 p.data = view
                 p.grad = self.view(self.G, n)
+            off = 0
+            for bn, n in ((model.inf_net.f_mu_batchnorm, K), (model.inf_net.f_sigma_batchnorm, K),
+                          (model.beta_batchnorm, V)):
+                for attr in ("running_mean", "running_var"):
+                    view = self.S[off:off + n]
+                    view.copy_(getattr(bn, attr).detach().to(device))
+                    setattr(bn, attr, view)
+                    off += n
+        if self.has_shadows:
+            self.beta_bf = arena.tensor("beta_bf", torch.bfloat16).view(Kp, ldb)
+            self.betaT_bf = arena.tensor("betaT_bf", torch.bfloat16).view(V, Kp)
 
     def view(self, flat: torch.Tensor, name: str) -> torch.Tensor:
         s = self.segments[name]
@@ -95,7 +123,8 @@ class FusedEngine:
 
     def __init__(self, model: DecoderNetwork, *, max_batch: int, max_nnz: int, lr: float = 2e-3,
                  betas: Tuple[float, float] = (0.99, 0.99), adam_eps: float = 1e-8,
-                 weight_decay: float = 0.0, kl_weight: float = 1.0, seed: int = 0, device=None) -> None:
+                 weight_decay: float = 0.0, kl_weight: float = 1.0, seed: int = 0, device=None,
+                 arena=None) -> None:
         if not torch.cuda.is_available():
             raise RuntimeError("FusedEngine needs a CUDA device (sm_100a); use the eager backend on CPU")
         if model.label_size:
@@ -117,7 +146,11 @@ class FusedEngine:
         self.rng_calls = 0        # forward passes (advances the Philox seed)
         self.max_batch, self.max_nnz = max_batch, max_nnz
 
-        self.flat = FlatParams(self.model, self.device)
+        if arena is None:
+            from ..parallel.fabric import LocalArena
+
+            arena = LocalArena()
+        self.flat = FlatParams(self.model, self.device, arena)
         dev = self.device
         f32 = dict(dtype=torch.float32, device=dev)
         B, K, V = max_batch, self.K, self.V
@@ -150,7 +183,7 @@ class FusedEngine:
         self.csc = CscWorkspace(V, max_nnz, dev)
         if self.is_prod:
             self.decoder = ProdLDADecoder(B, V, K, max_nnz, dev, BN_EPS, BN_MOMENTUM)
-            self.beta_bf, self.betaT_bf = make_beta_shadows(K, V, dev)
+            self.beta_bf, self.betaT_bf = self.flat.beta_bf, self.flat.betaT_bf
         else:
             self.xhat = torch.zeros(K, V, **f32)
             self.bp = torch.zeros(K, V, **f32)

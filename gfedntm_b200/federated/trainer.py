@@ -1,0 +1,120 @@
+"""In-box federated training: one client per GPU, aggregation fused over NVLink peer memory.
+
+This is the B200 data plane of the federation.  The reference's server pulls every client's
+post-step tensors over gRPC once per minibatch, averages them on the host weighted by corpus size
+and pushes the average back (src/federation/server.py:430-521).  Here every client is a rank of a
+``torch.distributed`` job on one NVSwitch domain and the same synchronous per-minibatch protocol
+runs as one kernel per rank (``csrc/fabric.cu``):
+
+* ``agg="grad"``  — product path: weighted gradient sum (weights n_c / sum n folded into the
+  backward pass), ONE global Adam whose state is sharded across the ranks, updated parameters and
+  bf16 operand shadows pushed to every rank.
+* ``agg="param"`` — reference-parity semantics: local Adam on every client, then the weighted mean
+  of the parameters (exactly server.py:477-487), Adam moments stay local.
+
+BatchNorm running statistics are averaged with the same weights in both modes.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from ..ops.decoder import CsrBatch
+from ..parallel.fabric import FusedAggregator, LocalArena, SymmetricArena
+
+
+class FederatedTrainer:
+    def __init__(self, model, n_samples: int, world_size: int = 1, rank: int = 0, agg: str = "grad",
+                 arena=None, weights: Optional[Sequence[float]] = None, group=None) -> None:
+        if agg not in ("grad", "param"):
+            raise ValueError("agg must be 'grad' or 'param'")
+        self.model = model
+        self.n_samples = int(n_samples)
+        self.world, self.rank, self.agg = int(world_size), int(rank), agg
+        self.arena = arena
+        self.group = group
+        self.weights = list(weights) if weights is not None else None
+        self.aggregator: Optional[FusedAggregator] = None
+        self._agg_events: List = []
+        self.global_step = 0
+
+    # ------------------------------------------------------------------------------------------
+    def prepare(self, loader) -> None:
+        """Allocates the engine inside the shared arena, agrees on the client weights and makes every
+        client start from rank 0's initial model (the reference's intent, server.py:292-301)."""
+        m = self.model
+        if m.backend != "fused":
+            raise RuntimeError("FederatedTrainer drives the fused engine; use the gRPC federation on CPU")
+        from ..engine.fused import FusedEngine
+
+        if self.arena is None:
+            self.arena = SymmetricArena(self.group) if self.world > 1 else LocalArena()
+        m.engine = FusedEngine(m.model, max_batch=loader.batch_size, max_nnz=max(loader.max_nnz, 1), lr=m.lr,
+                               betas=(m.momentum, 0.99), kl_weight=float(m.weights["beta"]), seed=m.seed + self.rank,
+                               device=m.device, arena=self.arena)
+        eng = m.engine
+        if self.world > 1 and isinstance(self.arena, SymmetricArena):
+            import torch.distributed as dist
+
+            if self.weights is None:
+                n = torch.tensor([float(self.n_samples)], device=eng.device)
+                alln = [torch.zeros_like(n) for _ in range(self.world)]
+                dist.all_gather(alln, n, group=self.arena.group)
+                tot = sum(float(x.item()) for x in alln)
+                self.weights = [float(x.item()) / tot for x in alln]
+            dist.broadcast(eng.flat.P, src=0, group=self.arena.group)
+            dist.broadcast(eng.flat.S, src=0, group=self.arena.group)
+            eng.sync_shadows()
+            self.arena.barrier()
+        if self.weights is None:
+            self.weights = [1.0 / self.world] * self.world
+        fl = eng.flat
+        self.aggregator = FusedAggregator(world=self.world, weights=self.weights, flat_n=fl.beta_off,
+                                          beta_off=fl.beta_off, s_n=fl.s_n, K=eng.K, V=eng.V, Kp=eng.Kp,
+                                          ldb=(eng.beta_bf.stride(0) if eng.is_prod else 0), lr=m.lr,
+                                          betas=(m.momentum, 0.99))
+        self.aggregator.add_rank(self.arena, self.rank, M=fl.M, V2=fl.V2, has_shadows=eng.is_prod)
+
+    # ------------------------------------------------------------------------------------------
+    def step(self, bow: CsrBatch, x_ctx: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One synchronous global step (local minibatch + aggregation).  Returns this client's summed
+        minibatch loss (device tensor)."""
+        eng = self.model.engine
+        self.global_step += 1
+        if self.world == 1:
+            return eng.train_step(bow, x_ctx)
+        if self.agg == "grad":
+            loss = eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank])
+            eng.step_count += 1
+            self._launch("grad", eng.step_count)
+        else:
+            loss = eng.forward_backward(bow, x_ctx, training=True)
+            eng.optimizer_step()
+            self._launch("param", eng.step_count)
+        return loss
+
+    def _launch(self, mode: str, step: int) -> None:
+        s = torch.cuda.Event(enable_timing=True)
+        e = torch.cuda.Event(enable_timing=True)
+        s.record()
+        self.aggregator.launch(mode=mode, step=step)
+        e.record()
+        self._agg_events.append((s, e))
+        if len(self._agg_events) > 256:
+            self._agg_events = self._agg_events[-128:]
+
+    def last_aggregation_us(self) -> Optional[float]:
+        """Mean device time of the aggregation kernel over the recorded steps (needs a prior sync)."""
+        if not self._agg_events:
+            return None
+        torch.cuda.synchronize()
+        ev = self._agg_events[-64:]
+        return 1e3 * sum(s.elapsed_time(e) for s, e in ev) / len(ev)
+
+    def working_set_bytes(self) -> int:
+        eng = self.model.engine
+        n = 4 * eng.flat.total * 4
+        if eng.is_prod:
+            n += eng.beta_bf.numel() * 2 + eng.betaT_bf.numel() * 2
+        return n

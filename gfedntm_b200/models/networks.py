@@ -139,7 +139,9 @@ class DecoderNetwork(nn.Module):
         self.infnet = infnet
         self.contextual_size = contextual_size
         self.label_size = label_size
-        self.topic_word_matrix: Optional[torch.Tensor] = None
+        # plain attribute (not a registered parameter): assigning the nn.Parameter through
+        # Module.__setattr__ would add a 'topic_word_matrix' key to the state dict
+        object.__setattr__(self, "topic_word_matrix", None)
 
         self.inf_net = InferenceNetwork(input_size, n_components, hidden_sizes, activation,
                                         kind=infnet, contextual_size=contextual_size,
@@ -175,11 +177,11 @@ class DecoderNetwork(nn.Module):
     def decode(self, theta: torch.Tensor) -> torch.Tensor:
         if self.model_type.lower() == "prodlda":
             word_dist = F.softmax(self.beta_batchnorm(theta @ self.beta), dim=1)
-            self.topic_word_matrix = self.beta
+            object.__setattr__(self, "topic_word_matrix", self.beta)
         else:
             beta = F.softmax(self.beta_batchnorm(self.beta), dim=1)
             word_dist = theta @ beta
-            self.topic_word_matrix = beta
+            object.__setattr__(self, "topic_word_matrix", beta)
         return word_dist
 
     def forward(self, x_bow=None, x_ctx=None, labels=None, eps: Optional[torch.Tensor] = None):

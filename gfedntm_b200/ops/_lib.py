@@ -108,7 +108,32 @@ class GfDecSparseArgs(C.Structure):
     ]
 
 
-_STRUCTS = [GfSweepArgs, GfEncArgs, GfLatentArgs, GfLatentBwdArgs, GfEncBwdArgs, GfDecSparseArgs]
+GF_MAX_RANKS = 8
+
+
+class GfFabricRank(C.Structure):
+    _fields_ = [
+        ("rank", _i),
+        ("G", _p * GF_MAX_RANKS), ("P", _p * GF_MAX_RANKS), ("S", _p * GF_MAX_RANKS),
+        ("beta_bf", _p * GF_MAX_RANKS), ("betaT_bf", _p * GF_MAX_RANKS), ("flags", _p * GF_MAX_RANKS),
+        ("M", _p), ("V2", _p), ("done_counter", _p),
+    ]
+
+
+class GfFedArgs(C.Structure):
+    _fields_ = [
+        ("world", _i), ("mode", _i), ("epoch", _i), ("n_rank_ctx", _i),
+        ("flat_n", C.c_longlong), ("beta_off", C.c_longlong), ("s_n", C.c_longlong),
+        ("K", _i), ("V", _i), ("Kp", _i), ("ldb", _i),
+        ("w", _f * GF_MAX_RANKS),
+        ("lr", _f), ("b1", _f), ("b2", _f), ("eps", _f), ("wd", _f),
+        ("step", _i),
+        ("ranks", GfFabricRank * GF_MAX_RANKS),
+    ]
+
+
+_STRUCTS = [GfSweepArgs, GfEncArgs, GfLatentArgs, GfLatentBwdArgs, GfEncBwdArgs, GfDecSparseArgs,
+            GfFabricRank, GfFedArgs]
 
 LIB_PATH = Path(__file__).resolve().parent / "libgfedntm_kernels.so"
 _lib: Optional[C.CDLL] = None
@@ -141,7 +166,11 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_adam_flat.argtypes = [_p, _p, _p, _p, ll, _f, _f, _f, _f, _f, _i, _f, _p]
     lib.gf_adam_beta.argtypes = [_p, _p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i,
                                  _f, _f, _f, _f, _f, _i, _f, _i, _p]
-    for fn in ("gf_dec_sweep", "gf_enc_fwd", "gf_latent_fwd", "gf_theta_center", "gf_latent_bwd",
+    lib.gf_fed_aggregate.argtypes = [C.POINTER(GfFedArgs), _p]
+    lib.gf_fed_aggregate.restype = _i
+    lib.gf_host_gather_csr.argtypes = [_p, _p, _p, _p, _i, _p, _p, _p, ll, _i]
+    lib.gf_host_gather_rows.argtypes = [_p, ll, _p, _i, _p]
+    for fn in ("gf_host_gather_csr", "gf_host_gather_rows", "gf_dec_sweep", "gf_enc_fwd", "gf_latent_fwd", "gf_theta_center", "gf_latent_bwd",
                "gf_enc_bwd", "gf_csr_to_csc", "gf_dec_sparse_doc", "gf_csc_corr", "gf_csc_spmm",
                "gf_lda_beta_fwd", "gf_lda_doc", "gf_lda_beta_bwd", "gf_row_topk", "gf_adam_flat",
                "gf_adam_beta"):

@@ -42,13 +42,19 @@ class CsrBatch:
     def from_dense(x: torch.Tensor) -> "CsrBatch":
         """Helper for tests / dense-input API calls."""
         B, V = x.shape
-        sp = x.to_sparse_csr()
-        return CsrBatch(sp.crow_indices().to(torch.int32), sp.col_indices().to(torch.int32),
-                        sp.values().to(torch.float32), B, V)
+        nz = x != 0
+        lens = nz.sum(1)
+        indptr = torch.zeros(B + 1, dtype=torch.int32, device=x.device)
+        indptr[1:] = torch.cumsum(lens, 0).to(torch.int32)
+        rows, cols = nz.nonzero(as_tuple=True)  # row-major order == CSR order with sorted columns
+        return CsrBatch(indptr, cols.to(torch.int32), x[rows, cols].to(torch.float32), B, V)
 
     def to_dense(self) -> torch.Tensor:
-        return torch.sparse_csr_tensor(self.indptr.long(), self.indices.long(), self.counts,
-                                       size=(self.B, self.V)).to_dense()
+        lens = (self.indptr[1:] - self.indptr[:-1]).long()
+        rows = torch.repeat_interleave(torch.arange(self.B, device=self.indptr.device), lens)
+        out = torch.zeros(self.B, self.V, dtype=torch.float32, device=self.indptr.device)
+        out.index_put_((rows, self.indices.long()), self.counts, accumulate=True)
+        return out
 
 
 class CscWorkspace:

@@ -1,0 +1,189 @@
+"""NVLink / NVSwitch fabric layer: a symmetric arena shared by the federated clients of one box and
+the launcher of the fused aggregation kernel (``csrc/fabric.cu``).
+
+One process per GPU.  ``torch.distributed`` (NCCL backend) is used only for the plumbing:
+rendezvous of the symmetric allocation through ``torch.distributed._symmetric_memory`` (CUDA VMM
+handles exchanged between the processes, every peer's arena mapped into every process) and host
+barriers.  The per-step data path is the kernel, which loads/stores peer memory directly.
+
+Three arena flavours:
+
+* ``SymmetricArena``  — real multi-GPU (world > 1).
+* ``LocalArena``      — world == 1 (plain device memory).
+* ``EmulatedArena``   — N logical ranks on ONE device for tests: every "peer" buffer is a separate
+  allocation on the same GPU and the kernel runs all ranks as co-resident blocks of one grid.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from ..ops import _lib
+from ..ops._lib import GF_MAX_RANKS, GfFedArgs, check
+
+
+def _align(n: int, a: int = 256) -> int:
+    return (n + a - 1) // a * a
+
+
+class _ArenaBase:
+    """Bump allocator over one byte buffer; remembers the offset of every named block."""
+
+    def __init__(self) -> None:
+        self.offsets: Dict[str, int] = {}
+        self.sizes: Dict[str, int] = {}
+        self._cursor = 0
+
+    def reserve(self, name: str, nbytes: int) -> None:
+        self.offsets[name] = self._cursor
+        self.sizes[name] = nbytes
+        self._cursor = _align(self._cursor + nbytes)
+
+    @property
+    def nbytes(self) -> int:
+        return max(self._cursor, 256)
+
+    def _view(self, buf: torch.Tensor, name: str, dtype: torch.dtype) -> torch.Tensor:
+        off, n = self.offsets[name], self.sizes[name]
+        return buf[off:off + n].view(dtype)
+
+
+class LocalArena(_ArenaBase):
+    world, rank = 1, 0
+
+    def commit(self, device) -> None:
+        self.buf = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
+        self.base_ptrs = [self.buf.data_ptr()]
+
+    def tensor(self, name: str, dtype: torch.dtype) -> torch.Tensor:
+        return self._view(self.buf, name, dtype)
+
+    def peer_ptr(self, rank: int, name: str) -> int:
+        return self.base_ptrs[rank] + self.offsets[name]
+
+    def barrier(self) -> None:
+        torch.cuda.synchronize()
+
+
+class SymmetricArena(_ArenaBase):
+    """Symmetric allocation across the ranks of a ``torch.distributed`` process group."""
+
+    def __init__(self, group=None) -> None:
+        super().__init__()
+        import torch.distributed as dist
+
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+
+    def commit(self, device) -> None:
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.buf = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        self.handle = symm_mem.rendezvous(self.buf, self.group)
+        self.base_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.multicast_ptr = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        torch.cuda.synchronize()
+        dist.barrier(self.group)
+
+    def tensor(self, name: str, dtype: torch.dtype) -> torch.Tensor:
+        return self._view(self.buf, name, dtype)
+
+    def peer_ptr(self, rank: int, name: str) -> int:
+        return self.base_ptrs[rank] + self.offsets[name]
+
+    def barrier(self) -> None:
+        import torch.distributed as dist
+
+        torch.cuda.synchronize()
+        dist.barrier(self.group)
+
+
+class EmulatedArena(_ArenaBase):
+    """``world`` logical ranks on one device.  ``view_as(rank)`` returns that rank's arena."""
+
+    def __init__(self, world: int) -> None:
+        super().__init__()
+        self.world = world
+        self.rank = 0
+        self._shared: Optional["EmulatedArena"] = None
+
+    def commit(self, device) -> None:
+        self.bufs = [torch.zeros(self.nbytes, dtype=torch.uint8, device=device) for _ in range(self.world)]
+        self.base_ptrs = [b.data_ptr() for b in self.bufs]
+
+    def view_as(self, rank: int) -> "EmulatedArena":
+        v = EmulatedArena(self.world)
+        v.offsets, v.sizes, v._cursor = self.offsets, self.sizes, self._cursor
+        v.bufs, v.base_ptrs, v.rank = self.bufs, self.base_ptrs, rank
+        return v
+
+    def tensor(self, name: str, dtype: torch.dtype) -> torch.Tensor:
+        return self._view(self.bufs[self.rank], name, dtype)
+
+    def peer_ptr(self, rank: int, name: str) -> int:
+        return self.base_ptrs[rank] + self.offsets[name]
+
+    def barrier(self) -> None:
+        torch.cuda.synchronize()
+
+
+FLAG_BYTES = 2 * GF_MAX_RANKS * 4
+
+
+def fill_rank_ctx(ctx, arena, rank: int, *, M: torch.Tensor, V2: torch.Tensor, done_counter: torch.Tensor,
+                  has_shadows: bool) -> None:
+    """Peer pointer tables of one rank (names: P, G, S, beta_bf, betaT_bf, flags)."""
+    ctx.rank = rank
+    for c in range(arena.world):
+        ctx.G[c] = arena.peer_ptr(c, "G")
+        ctx.P[c] = arena.peer_ptr(c, "P")
+        ctx.S[c] = arena.peer_ptr(c, "S")
+        ctx.flags[c] = arena.peer_ptr(c, "flags")
+        ctx.beta_bf[c] = arena.peer_ptr(c, "beta_bf") if has_shadows else None
+        ctx.betaT_bf[c] = arena.peer_ptr(c, "betaT_bf") if has_shadows else None
+    ctx.M, ctx.V2 = M.data_ptr(), V2.data_ptr()
+    ctx.done_counter = done_counter.data_ptr()
+
+
+class FusedAggregator:
+    """Launches ``gf_fed_aggregate`` for one rank (or for all emulated ranks at once)."""
+
+    def __init__(self, *, world: int, weights: Sequence[float], flat_n: int, beta_off: int, s_n: int, K: int,
+                 V: int, Kp: int, ldb: int, lr: float, betas, eps: float = 1e-8, wd: float = 0.0) -> None:
+        assert 1 <= world <= GF_MAX_RANKS
+        self.args = GfFedArgs()
+        a = self.args
+        a.world, a.flat_n, a.beta_off, a.s_n = world, flat_n, beta_off, s_n
+        a.K, a.V, a.Kp, a.ldb = K, V, Kp, ldb
+        for c in range(world):
+            a.w[c] = float(weights[c])
+        a.lr, a.b1, a.b2, a.eps, a.wd = lr, betas[0], betas[1], eps, wd
+        a.n_rank_ctx = 0
+        self.epoch = 0
+        self._keep: List[torch.Tensor] = []
+
+    def add_rank(self, arena, rank: int, *, M, V2, has_shadows: bool) -> None:
+        i = self.args.n_rank_ctx
+        done = torch.zeros(1, dtype=torch.int32, device=M.device)
+        self._keep.append(done)
+        fill_rank_ctx(self.args.ranks[i], arena, rank, M=M, V2=V2, done_counter=done, has_shadows=has_shadows)
+        self.args.n_rank_ctx = i + 1
+
+    def set_lr(self, lr: float, betas) -> None:
+        self.args.lr, self.args.b1, self.args.b2 = lr, betas[0], betas[1]
+
+    def launch(self, *, mode: str, step: int) -> None:
+        """``mode``: 'grad' (weighted gradients + global sharded Adam) or 'param' (weighted mean of the
+        parameters).  Every rank must call this once per global step."""
+        self.epoch += 1
+        a = self.args
+        a.mode = 0 if mode == "grad" else 1
+        a.epoch = self.epoch
+        a.step = step
+        lib = _lib.load()
+        check(lib.gf_fed_aggregate(C.byref(a), torch.cuda.current_stream().cuda_stream), "gf_fed_aggregate")

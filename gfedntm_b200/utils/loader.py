@@ -1,0 +1,166 @@
+"""Minibatch loader that feeds CSR minibatches (plus contextual embeddings / labels) to the device.
+
+The corpus stays on the host as one CSR matrix.  Each minibatch is assembled by the native helper
+``gf_host_gather_csr`` straight into pinned staging buffers and copied with one async H2D copy
+per array; two staging slots alternate so the next batch is assembled while the current step runs.
+
+Ref: ``DataLoader(train_data, batch_size, shuffle=True)`` in federated_model.py:82-86 and
+avitm.py:371-375 (dense rows, default collate, ``.cuda()`` per batch).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Iterator, Optional
+
+import numpy as np
+import torch
+
+from ..ops.decoder import CsrBatch
+
+
+@dataclass
+class Minibatch:
+    bow: CsrBatch
+    x_ctx: Optional[torch.Tensor]
+    labels: Optional[torch.Tensor]
+    index: np.ndarray          # corpus row ids of the documents in this batch
+    h2d_bytes: int = 0
+
+    @property
+    def size(self) -> int:
+        return self.bow.B
+
+
+def _native():
+    try:
+        from ..ops import _lib
+
+        return _lib.load()
+    except Exception:  # library not built (pure-CPU install): numpy fallback below
+        return None
+
+
+class _Slot:
+    def __init__(self, max_B: int, max_nnz: int, C_ctx: int, L: int, device: torch.device) -> None:
+        pin = device.type == "cuda"
+        self.indptr_h = torch.empty(max_B + 1, dtype=torch.int32, pin_memory=pin)
+        self.indices_h = torch.empty(max(max_nnz, 1), dtype=torch.int32, pin_memory=pin)
+        self.counts_h = torch.empty(max(max_nnz, 1), dtype=torch.float32, pin_memory=pin)
+        self.ctx_h = torch.empty(max_B, C_ctx, dtype=torch.float32, pin_memory=pin) if C_ctx else None
+        self.lab_h = torch.empty(max_B, L, dtype=torch.float32, pin_memory=pin) if L else None
+        if pin:
+            self.indptr_d = torch.empty(max_B + 1, dtype=torch.int32, device=device)
+            self.indices_d = torch.empty(max(max_nnz, 1), dtype=torch.int32, device=device)
+            self.counts_d = torch.empty(max(max_nnz, 1), dtype=torch.float32, device=device)
+            self.ctx_d = torch.empty(max_B, C_ctx, dtype=torch.float32, device=device) if C_ctx else None
+            self.lab_d = torch.empty(max_B, L, dtype=torch.float32, device=device) if L else None
+        self.ready = torch.cuda.Event() if pin else None
+        self.in_flight = False
+
+
+class CsrMinibatchLoader:
+    """Iterates over a ``BOWDataset`` / ``CTMDataset`` in (optionally shuffled) CSR minibatches."""
+
+    def __init__(self, dataset, batch_size: int, shuffle: bool = True, drop_last: bool = False,
+                 device=None, seed: int = 0, n_threads: int = 4) -> None:
+        self.dataset = dataset
+        self.batch_size = int(batch_size)
+        self.shuffle, self.drop_last = shuffle, drop_last
+        self.device = torch.device(device) if device is not None else torch.device("cpu")
+        self.rng = np.random.default_rng(seed)
+        self.n_threads = n_threads
+        X = dataset.X
+        self.indptr = np.ascontiguousarray(X.indptr, dtype=np.int32)
+        self.indices = np.ascontiguousarray(X.indices, dtype=np.int32)
+        self.data = np.ascontiguousarray(X.data, dtype=np.float32)
+        self.N, self.V = X.shape
+        lens = np.diff(self.indptr)
+        top = np.sort(lens)[::-1][: self.batch_size]
+        self.max_nnz = int(top.sum()) if len(top) else 0
+        self.ctx = getattr(dataset, "X_contextual", None)
+        self.labels = getattr(dataset, "labels", None)
+        C_ctx = self.ctx.shape[1] if self.ctx is not None else 0
+        L = self.labels.shape[1] if self.labels is not None else 0
+        self.slots = [_Slot(self.batch_size, self.max_nnz, C_ctx, L, self.device) for _ in range(2)]
+        self.lib = _native()
+        self.copy_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+
+    def __len__(self) -> int:
+        if self.drop_last:
+            return self.N // self.batch_size
+        return (self.N + self.batch_size - 1) // self.batch_size
+
+    # -- host assembly + H2D of one batch into a slot
+    def _stage(self, slot: _Slot, rows: np.ndarray) -> Minibatch:
+        n = len(rows)
+        if slot.in_flight:
+            slot.ready.synchronize()  # the previous H2D out of these pinned buffers must be done
+        rows64 = np.ascontiguousarray(rows, dtype=np.int64)
+        ip, ix, ct = slot.indptr_h.numpy(), slot.indices_h.numpy(), slot.counts_h.numpy()
+        if self.lib is not None:
+            rc = self.lib.gf_host_gather_csr(self.indptr.ctypes.data, self.indices.ctypes.data,
+                                             self.data.ctypes.data, rows64.ctypes.data, n, ip.ctypes.data,
+                                             ix.ctypes.data, ct.ctypes.data, len(ix), self.n_threads)
+            if rc != 0:
+                raise RuntimeError("gf_host_gather_csr failed (staging buffer too small?)")
+        else:
+            lens = self.indptr[rows64 + 1] - self.indptr[rows64]
+            ip[0] = 0
+            np.cumsum(lens, out=ip[1:n + 1])
+            for i, r in enumerate(rows64):
+                s, e = self.indptr[r], self.indptr[r + 1]
+                ix[ip[i]:ip[i + 1]] = self.indices[s:e]
+                ct[ip[i]:ip[i + 1]] = self.data[s:e]
+        nnz = int(ip[n])
+        if self.ctx is not None:
+            if self.lib is not None:
+                self.lib.gf_host_gather_rows(self.ctx.ctypes.data, self.ctx.shape[1], rows64.ctypes.data, n,
+                                             slot.ctx_h.numpy().ctypes.data)
+            else:
+                slot.ctx_h.numpy()[:n] = self.ctx[rows64]
+        if self.labels is not None:
+            slot.lab_h.numpy()[:n] = self.dataset.label_rows(rows64)
+        h2d = 4 * (n + 1) + 8 * nnz
+        if self.device.type == "cuda":
+            with torch.cuda.stream(self.copy_stream):
+                slot.indptr_d[: n + 1].copy_(slot.indptr_h[: n + 1], non_blocking=True)
+                slot.indices_d[:nnz].copy_(slot.indices_h[:nnz], non_blocking=True)
+                slot.counts_d[:nnz].copy_(slot.counts_h[:nnz], non_blocking=True)
+                if slot.ctx_h is not None:
+                    slot.ctx_d[:n].copy_(slot.ctx_h[:n], non_blocking=True)
+                    h2d += 4 * n * slot.ctx_h.shape[1]
+                if slot.lab_h is not None:
+                    slot.lab_d[:n].copy_(slot.lab_h[:n], non_blocking=True)
+                    h2d += 4 * n * slot.lab_h.shape[1]
+                slot.ready.record(self.copy_stream)
+                slot.in_flight = True
+            bow = CsrBatch(slot.indptr_d[: n + 1], slot.indices_d[:nnz], slot.counts_d[:nnz], n, self.V)
+            ctx = slot.ctx_d[:n] if slot.ctx_h is not None else None
+            lab = slot.lab_d[:n] if slot.lab_h is not None else None
+        else:
+            bow = CsrBatch(slot.indptr_h[: n + 1].clone(), slot.indices_h[:nnz].clone(),
+                           slot.counts_h[:nnz].clone(), n, self.V)
+            ctx = slot.ctx_h[:n].clone() if slot.ctx_h is not None else None
+            lab = slot.lab_h[:n].clone() if slot.lab_h is not None else None
+        return Minibatch(bow, ctx, lab, rows64, h2d)
+
+    def __iter__(self) -> Iterator[Minibatch]:
+        order = self.rng.permutation(self.N) if self.shuffle else np.arange(self.N)
+        starts = list(range(0, self.N, self.batch_size))
+        if self.drop_last and starts and self.N - starts[-1] < self.batch_size:
+            starts.pop()
+        pending = None
+        for i, s in enumerate(starts):
+            slot = self.slots[i & 1]
+            if self.device.type == "cuda":
+                # the slot's device buffers were last read by the step two batches ago
+                self.copy_stream.wait_stream(torch.cuda.current_stream(self.device))
+            mb = self._stage(slot, order[s:s + self.batch_size])
+            if pending is not None:
+                yield pending
+            if self.device.type == "cuda":
+                torch.cuda.current_stream(self.device).wait_event(slot.ready)
+            pending = mb
+        if pending is not None:
+            yield pending

@@ -213,6 +213,53 @@ int gf_adam_beta(float* p, const float* g, float* m, float* v, int K, int V, int
                  void* beta_bf, int ldb, void* betaT_bf, int Kp, float lr, float b1, float b2, float eps,
                  float wd, int step, float gscale, int do_update, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Fused federated aggregation over NVLink peer memory (no NCCL on this path).
+ * Ref: src/federation/server.py:442-521 (gather / weighted mean / broadcast over gRPC) and the
+ *      clients' optimizer.step() + load_state_dict (federated_avitm.py:78, federated_model.py:117-131).
+ * ---------------------------------------------------------------------------------------- */
+#define GF_MAX_RANKS 8
+
+typedef struct GfFabricRank {
+  int rank;
+  float* G[GF_MAX_RANKS];         /* flat gradient buffer of every rank (peer-mapped)           */
+  float* P[GF_MAX_RANKS];         /* flat parameter buffer of every rank                        */
+  float* S[GF_MAX_RANKS];         /* flat BatchNorm running statistics of every rank            */
+  void* beta_bf[GF_MAX_RANKS];    /* bf16 [Kp, ldb] shadow of every rank (may be null)          */
+  void* betaT_bf[GF_MAX_RANKS];   /* bf16 [V, Kp] shadow of every rank (may be null)            */
+  uint32_t* flags[GF_MAX_RANKS];  /* flag array of every rank: uint32 [2][GF_MAX_RANKS], zeroed once */
+  float* M; float* V2;            /* this rank's Adam moments (same indexing as P)              */
+  unsigned int* done_counter;     /* this rank, zeroed once                                     */
+} GfFabricRank;
+
+typedef struct GfFedArgs {
+  int world;                      /* number of federated clients (ranks)                        */
+  int mode;                       /* 0 = weighted gradients + global Adam, 1 = weighted parameters */
+  int epoch;                      /* strictly increasing per call (flag value)                  */
+  int n_rank_ctx;                 /* 1 in production; = world for the single-GPU emulation      */
+  long long flat_n;               /* elements before beta in the flat buffers (multiple of 4)   */
+  long long beta_off;             /* offset of beta [K,V] in the flat buffers                   */
+  long long s_n;                  /* BatchNorm statistics elements (multiple of 4)              */
+  int K, V, Kp, ldb;              /* K = 0 skips the beta region                                */
+  float w[GF_MAX_RANKS];          /* client weights n_c / sum n                                 */
+  float lr, b1, b2, eps, wd;
+  int step;                       /* Adam step count (>= 1) for the bias correction             */
+  GfFabricRank ranks[GF_MAX_RANKS];
+} GfFedArgs;
+
+/* One call per rank and step, on every rank of the federation, with the same `epoch`.          */
+int gf_fed_aggregate(const GfFedArgs* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Host-side data loader helpers (no device code).
+ * Ref: torch DataLoader over a dense [n_docs, V] array, federated_model.py:82-86.
+ * ---------------------------------------------------------------------------------------- */
+/* Gather CSR rows `rows[0..n_rows)` of a corpus into staging buffers (pinned memory welcome).  */
+int gf_host_gather_csr(const int* indptr, const int* indices, const float* data, const long long* rows,
+                       int n_rows, int* out_indptr, int* out_indices, float* out_data,
+                       long long out_capacity, int n_threads);
+int gf_host_gather_rows(const float* src, long long row_len, const long long* rows, int n_rows, float* out);
+
 #ifdef __cplusplus
 }
 #endif

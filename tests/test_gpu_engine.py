@@ -67,11 +67,16 @@ def test_engine_step_matches_autograd(kind, model_type, act, hidden):
     ref_loss.backward()
     assert abs(loss.item() - ref_loss.item()) <= 3e-3 * abs(ref_loss.item()), (loss.item(), ref_loss.item())
     torch.testing.assert_close(eng.theta[:B], ref_theta, rtol=1e-3, atol=1e-5)
+    bad = []
     for name, p in ref.named_parameters():
         got = eng.flat.view(eng.flat.G, name)
-        scale = p.grad.abs().max().item() + 1e-12
+        scale = p.grad.abs().max().item()
         err = (got - p.grad).abs().max().item()
-        assert err <= 3e-2 * scale, f"{name}: err {err:.3e} scale {scale:.3e}"
+        # absolute slack: d prior_mean and the biases feeding a BatchNorm have exactly-zero gradients
+        # (BatchNorm removes them), so both sides hold rounding noise of ~1e-3 there
+        if err > 3e-2 * scale + 2e-3:
+            bad.append(f"{name}: err {err:.3e} scale {scale:.3e}")
+    assert not bad, "\n".join(bad)
     # running statistics of the two encoder BatchNorms follow PyTorch's update rule
     torch.testing.assert_close(model.inf_net.f_mu_batchnorm.running_mean, ref.inf_net.f_mu_batchnorm.running_mean,
                                rtol=1e-3, atol=1e-5)

@@ -1,0 +1,87 @@
+"""Fused aggregation kernel (reduce-scatter + weighting + sharded Adam + all-gather of parameters and
+bf16 shadows) — all logical ranks emulated on ONE GPU as co-resident blocks of a single launch."""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(world, model_type="prodLDA", V=700, K=12, B=48):
+    from gfedntm_b200.engine.fused import FusedEngine
+    from gfedntm_b200.models.networks import DecoderNetwork
+    from gfedntm_b200.ops.decoder import CsrBatch
+    from gfedntm_b200.parallel.fabric import EmulatedArena, FusedAggregator
+
+    torch.manual_seed(0)
+    base = DecoderNetwork(V, K, model_type, (24, 24), "softplus", 0.2, True)
+    arena = EmulatedArena(world)
+    engines, batches = [], []
+    g = torch.Generator(device="cuda").manual_seed(11)
+    for r in range(world):
+        model = copy.deepcopy(base)
+        eng = FusedEngine(model, max_batch=B, max_nnz=B * 30, lr=2e-3, betas=(0.99, 0.99), seed=5 + r,
+                          arena=arena if r == 0 else arena.view_as(r))
+        if r == 0:
+            arena = eng.flat.arena  # committed
+        engines.append(eng)
+        x = torch.zeros(B, V, device="cuda")
+        x.scatter_add_(1, torch.randint(0, V, (B, 30), device="cuda", generator=g), torch.ones(B, 30, device="cuda"))
+        batches.append(CsrBatch.from_dense(x))
+    weights = [float(i + 1) for i in range(world)]
+    tot = sum(weights)
+    weights = [w / tot for w in weights]
+    fl = engines[0].flat
+    agg = FusedAggregator(world=world, weights=weights, flat_n=fl.beta_off, beta_off=fl.beta_off, s_n=fl.s_n,
+                          K=K, V=V, Kp=engines[0].Kp,
+                          ldb=engines[0].beta_bf.stride(0) if engines[0].is_prod else 0, lr=2e-3,
+                          betas=(0.99, 0.99))
+    for r, eng in enumerate(engines):
+        agg.add_rank(arena.view_as(r) if r else arena, r, M=eng.flat.M, V2=eng.flat.V2, has_shadows=eng.is_prod)
+    return engines, batches, weights, agg
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_fused_grad_aggregation_matches_global_adam(world):
+    engines, batches, weights, agg = _setup(world)
+    names = [n for n, _ in engines[0].model.named_parameters()]
+    ref = {n: engines[0].flat.view(engines[0].flat.P, n).detach().clone() for n in names}
+    for n in ref:
+        ref[n].requires_grad_(True)
+    opt = torch.optim.Adam([ref[n] for n in names], lr=2e-3, betas=(0.99, 0.99))
+    for step in range(1, 4):
+        for r, eng in enumerate(engines):
+            eng.forward_backward(batches[r], training=True, gscale=weights[r])
+        gsum = {n: sum(e.flat.view(e.flat.G, n).detach().clone() for e in engines) for n in names}
+        s_mean = sum(w * e.flat.S.detach().clone() for w, e in zip(weights, engines))
+        agg.launch(mode="grad", step=step)
+        torch.cuda.synchronize()
+        for n in names:
+            ref[n].grad = gsum[n]
+        opt.step()
+        for r, eng in enumerate(engines):
+            for n in names:
+                torch.testing.assert_close(eng.flat.view(eng.flat.P, n), ref[n].detach(), rtol=2e-4, atol=2e-6,
+                                           msg=lambda m: f"rank {r} {n} step {step}: {m}")
+            torch.testing.assert_close(eng.flat.S, s_mean, rtol=1e-5, atol=1e-6)
+            K, V = eng.K, eng.V
+            torch.testing.assert_close(eng.beta_bf[:K, :V].float(), ref["beta"].detach().to(torch.bfloat16).float())
+            torch.testing.assert_close(eng.betaT_bf[:, :K].float(), ref["beta"].detach().t().to(torch.bfloat16).float())
+            eng.step_count = step
+
+
+def test_fused_param_aggregation_matches_weighted_mean():
+    world = 4
+    engines, batches, weights, agg = _setup(world, model_type="LDA")
+    names = [n for n, _ in engines[0].model.named_parameters()]
+    for step in range(1, 3):
+        for r, eng in enumerate(engines):
+            eng.forward_backward(batches[r], training=True)
+            eng.optimizer_step()
+        want = {n: sum(w * e.flat.view(e.flat.P, n).detach().clone() for w, e in zip(weights, engines)) for n in names}
+        agg.launch(mode="param", step=step)
+        torch.cuda.synchronize()
+        for eng in engines:
+            for n in names:
+                torch.testing.assert_close(eng.flat.view(eng.flat.P, n), want[n], rtol=1e-5, atol=1e-7)
