@@ -518,3 +518,62 @@ extern "C" int gf_row_topk(const float* mat, int ld, int rows, int V, int topk, 
   GF_LAUNCHED();
   return GF_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// gf_csr_to_csc_static — the minibatch transpose for callers that must not allocate.
+//
+// gf_csr_to_csc needs V ints of scratch (the per-word write cursors) and leaves it to the caller to
+// allocate them.  Some callers cannot: a host application that hands the whole device to its own
+// memory pool at start-up has nothing left for cudaMalloc to give out, and a caller inside a
+// latency-critical loop cannot afford cudaMalloc/cudaFree because both synchronise the device and
+// stall every other stream.  For them the cursors live in the fixed array below, which is part of
+// the library image: each GPU that loads the library carries these 4 MiB until the process exits.
+//
+// Rules that follow from sharing one array:
+//   * V must not exceed GF_CSC_STATIC_MAX_V; larger vocabularies are refused (use gf_csr_to_csc).
+//   * The array keeps whatever the previous call left in it.  The cursors have to start at zero,
+//     so every call clears the first V of them on `stream` before the kernels run.
+//   * All calls on one GPU use the same array.  Two calls whose kernels can be in flight at the same
+//     time (different streams, or different host threads on different streams) race on it; issue them
+//     on one stream or order them with events.
+//   * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+//     that device current) and remembers it.  Make that first call during set-up, before any stream
+//     capture is started on the device.
+// No cudaMalloc, cudaFree or allocating library routine is reached from this entry point.
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+static __device__ __align__(256) int g_csc_static_cursor[GF_CSC_STATIC_MAX_V];
+
+namespace {
+constexpr int kMaxCscDevices = 64;
+int* g_csc_cursor_addr[kMaxCscDevices] = {nullptr};  // device address of the array, per device ordinal
+std::mutex g_csc_cursor_mu;
+}  // namespace
+
+extern "C" int gf_csr_to_csc_static(const int* indptr, const int* indices, int B, int V, int nnz, int* colptr,
+                                    int* csc_row, int* csc_src, void* stream_) {
+  if (V > GF_CSC_STATIC_MAX_V) {
+    fprintf(stderr,
+            "[gfedntm] gf_csr_to_csc_static: V=%d exceeds the built-in scratch (GF_CSC_STATIC_MAX_V=%d); "
+            "call gf_csr_to_csc with caller-allocated scratch instead\n",
+            V, (int)GF_CSC_STATIC_MAX_V);
+    return GF_ERR_ARG;
+  }
+  int dev = -1;
+  GF_CUDA_CHECK(cudaGetDevice(&dev));
+  GF_ARG_CHECK(dev >= 0 && dev < kMaxCscDevices, "device ordinal out of range for gf_csr_to_csc_static");
+  int* cursor = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_csc_cursor_mu);
+    cursor = g_csc_cursor_addr[dev];
+    if (cursor == nullptr) {
+      // In host code `g_csc_static_cursor` is only a handle for this lookup, never an address to pass
+      // to a kernel: the kernels get the device address resolved here, for the current device.
+      GF_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&cursor), g_csc_static_cursor));
+      g_csc_cursor_addr[dev] = cursor;
+    }
+  }
+  // Same launches as the allocating-caller entry point; it zeroes colptr and the first V cursors itself.
+  return gf_csr_to_csc(indptr, indices, B, V, nnz, colptr, cursor, csc_row, csc_src, stream_);
+}

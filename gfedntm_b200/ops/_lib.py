@@ -156,6 +156,8 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_latent_bwd.argtypes = [C.POINTER(GfLatentBwdArgs), _p]
     lib.gf_enc_bwd.argtypes = [C.POINTER(GfEncBwdArgs), _p]
     lib.gf_csr_to_csc.argtypes = [_p, _p, _i, _i, _i, _p, _p, _p, _p, _p]
+    lib.gf_csr_to_csc_static.argtypes = [_p, _p, _i, _i, _i, _p, _p, _p, _p]
+    lib.gf_csr_to_csc_static.restype = _i
     lib.gf_dec_sparse_doc.argtypes = [C.POINTER(GfDecSparseArgs), _p]
     lib.gf_csc_corr.argtypes = [_p, _p, _p, _p, _p, _i, _p, _i, _i, _p]
     lib.gf_csc_spmm.argtypes = [_p, _p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _p]

@@ -163,6 +163,21 @@ int gf_enc_bwd(const GfEncBwdArgs* args, void* stream);
 int gf_csr_to_csc(const int* indptr, const int* indices, int B, int V, int nnz, int* colptr,
                   int* cursor_scratch, int* csc_row, int* csc_src, void* stream);
 
+/* Same transpose, for callers that cannot allocate device memory (a host whose own pool already owns
+ * the whole device, or a latency-critical loop where cudaMalloc/cudaFree would stall every stream).
+ * No counterpart in the reference: it exists only because this library is callable through its C ABI
+ * from such hosts.  The V write cursors live in a fixed array inside the library image
+ * (GF_CSC_STATIC_MAX_V ints = 4 MiB, held by every GPU that loads the library until process exit).
+ *   - V > GF_CSC_STATIC_MAX_V is refused with an error (use gf_csr_to_csc).
+ *   - The array is shared by all calls on a GPU and keeps the previous call's contents; each call
+ *     zeroes the cursors it needs on `stream` first.  Calls that can overlap on the GPU race.
+ *   - The first call on a device resolves the array's device address; make it during set-up, before
+ *     starting any stream capture on that device.
+ * Inputs and outputs are passed exactly as for gf_csr_to_csc; nothing is allocated or freed.        */
+#define GF_CSC_STATIC_MAX_V (1 << 20)
+int gf_csr_to_csc_static(const int* indptr, const int* indices, int B, int V, int nnz, int* colptr,
+                         int* csc_row, int* csc_src, void* stream);
+
 typedef struct GfDecSparseArgs {
   int B, Kp, n_chunks;
   const int* indptr; const int* indices; const float* counts;
