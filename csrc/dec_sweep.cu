@@ -72,17 +72,21 @@ struct SweepParams {
   const int* colptr;        // [V+1] CSC pointer of the batch (with corr)
 };
 
+constexpr int kSbStages = 4;   // side-band ring depth (2 KB per entry)
+
 struct Smem {
   uint8_t* a;
   uint8_t* b[kMaxStages];
-  float4* sb[kMaxStages];
+  float4* sb[kSbStages];
   uint8_t* p;
   uint64_t* a_full;
   uint64_t* a_empty;
-  uint64_t* b_full;   // [stages]
-  uint64_t* b_empty;  // [stages]
-  uint64_t* d1_full;  // [2]
-  uint64_t* d1_empty; // [2]
+  uint64_t* b_full;    // [kMaxStages]  operand tile landed
+  uint64_t* b_empty;   // [kMaxStages]  operand tile no longer read by any MMA
+  uint64_t* sb_full;   // [kSbStages]   side band landed
+  uint64_t* sb_empty;  // [kSbStages]   side band consumed by the epilogue
+  uint64_t* d1_full;   // [2]
+  uint64_t* d1_empty;  // [2]
   uint64_t* p_full;
   uint64_t* p_empty;
   uint64_t* d2_full;
@@ -90,35 +94,45 @@ struct Smem {
   uint32_t* tmem_ptr;
 };
 
-template <int kKChunks, bool kRow, bool kHasMMA2>
+// Both operands are stored "topics x contiguous axis" in global memory:
+//   theta_T [Kp, B]  (documents contiguous)      beta [Kp, V]  (words contiguous)
+// so a 128-wide tile of either is two TMA boxes of {64 columns x Kp rows} (Kp*128 bytes each,
+// 128B-swizzled rows).  For MMA1 both tiles are MN-major operands (rows = contraction index);
+// for MMA2 the streamed tile's very same bytes are a K-major B operand (rows = N index = topics).
+template <int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant__ CUtensorMap tm_beta,
              const SweepParams p) {
+  constexpr bool kRow = (kMode == ROW_LOGITS || kMode == ROW_LSE || kMode == ROW_GRAD);
+  constexpr bool kHasMMA2 = (kMode == ROW_GRAD || kMode == COL_GRAD);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t kSbBytes = kTile * sizeof(float4);
   const int stages = p.stages;
   const int Kp = p.Kp;
-  // theta tile: kKChunks boxes of 64 topics x 128 docs; beta tile: 2 boxes of 64 words x Kp topics
-  const uint32_t a_alloc = kRow ? kKChunks * 16384u : (uint32_t)Kp * 256u;
-  const uint32_t b_alloc = kRow ? (uint32_t)Kp * 256u : kKChunks * 16384u;
+  const uint32_t tile_bytes = (uint32_t)Kp * 256u;  // 2 boxes of Kp rows x 128 B
 
   Smem s;
   s.a = base;
-  uint8_t* cur = base + a_alloc;
+  uint8_t* cur = base + tile_bytes;
   for (int i = 0; i < kMaxStages; ++i) {
     s.b[i] = cur;
-    s.sb[i] = reinterpret_cast<float4*>(cur + b_alloc);
-    if (i < stages) cur += b_alloc + kSbBytes;
+    if (i < stages) cur += tile_bytes;
   }
   s.p = cur;
   if (kHasMMA2) cur += 32768;
+  for (int i = 0; i < kSbStages; ++i) {
+    s.sb[i] = reinterpret_cast<float4*>(cur);
+    cur += kSbBytes;
+  }
   uint64_t* bars = reinterpret_cast<uint64_t*>(cur);
   s.a_full = bars + 0;
   s.a_empty = bars + 1;
   s.b_full = bars + 2;
-  s.b_empty = bars + 2 + kMaxStages;
-  s.d1_full = bars + 2 + 2 * kMaxStages;
+  s.b_empty = s.b_full + kMaxStages;
+  s.sb_full = s.b_empty + kMaxStages;
+  s.sb_empty = s.sb_full + kSbStages;
+  s.d1_full = s.sb_empty + kSbStages;
   s.d1_empty = s.d1_full + 2;
   s.p_full = s.d1_empty + 2;
   s.p_empty = s.p_full + 1;
@@ -138,7 +152,11 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
     mbar_init(s.a_empty, 1);
     for (int i = 0; i < kMaxStages; ++i) {
       mbar_init(&s.b_full[i], 1);
-      mbar_init(&s.b_empty[i], 1 + 128);  // MMA commit + every epilogue thread
+      mbar_init(&s.b_empty[i], 1);  // tcgen05.commit of the last MMA that reads the tile
+    }
+    for (int i = 0; i < kSbStages; ++i) {
+      mbar_init(&s.sb_full[i], 1);
+      mbar_init(&s.sb_empty[i], 128);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&s.d1_full[i], 1);
@@ -159,11 +177,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
 
   const int total_work = p.n_stat * p.n_chunks;
   const int n_ksteps = Kp >> 4;
-  // bytes landed per stationary / streamed tile
-  const uint32_t theta_tile_bytes = kKChunks * 16384u;      // kKChunks boxes {64 x 128 rows}
-  const uint32_t beta_tile_bytes = 2u * (uint32_t)Kp * 128u;  // 2 boxes {64 words x Kp rows}
-  const uint32_t a_bytes = kRow ? theta_tile_bytes : beta_tile_bytes;
-  const uint32_t b_bytes = (kRow ? beta_tile_bytes : theta_tile_bytes) + kSbBytes;
+  const CUtensorMap* tm_stat = kRow ? &tm_theta : &tm_beta;
+  const CUtensorMap* tm_strm = kRow ? &tm_beta : &tm_theta;
+  const uint32_t blk = (uint32_t)Kp * 128u;  // bytes of one 64-column block
 
   if (warp == 0) {
     // ============================ TMA producer ============================
@@ -174,33 +190,26 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         const int t0 = (int)(((long long)chunk * p.n_stream) / p.n_chunks);
         const int t1 = (int)(((long long)(chunk + 1) * p.n_stream) / p.n_chunks);
         mbar_wait(s.a_empty, (a_it & 1) ^ 1);
-        mbar_arrive_expect_tx(s.a_full, a_bytes);
-        if (kRow) {
-          for (int kc = 0; kc < kKChunks; ++kc)
-            tma_load_2d(s.a + kc * 16384, &tm_theta, s.a_full, kc * 64, stat * kTile);
-        } else {
-          for (int nb = 0; nb < 2; ++nb)
-            tma_load_2d(s.a + nb * Kp * 128, &tm_beta, s.a_full, stat * kTile + nb * 64, 0);
-        }
+        mbar_arrive_expect_tx(s.a_full, tile_bytes);
+        tma_load_2d(s.a, tm_stat, s.a_full, stat * kTile, 0);
+        tma_load_2d(s.a + blk, tm_stat, s.a_full, stat * kTile + 64, 0);
         ++a_it;
         for (int pass = 0; pass < p.n_pass; ++pass) {
           for (int t = t0; t < t1; ++t) {
-            const int st = b_it % stages;
+            const int st = b_it % stages, sbs = b_it % kSbStages;
             mbar_wait(&s.b_empty[st], ((b_it / stages) & 1) ^ 1);
-            mbar_arrive_expect_tx(&s.b_full[st], b_bytes);
-            if (kRow) {
-              for (int nb = 0; nb < 2; ++nb)
-                tma_load_2d(s.b[st] + nb * Kp * 128, &tm_beta, &s.b_full[st], t * kTile + nb * 64, 0);
-            } else {
-              for (int kc = 0; kc < kKChunks; ++kc)
-                tma_load_2d(s.b[st] + kc * 16384, &tm_theta, &s.b_full[st], kc * 64, t * kTile);
-            }
-            // side band: 128 float4 = 2 KB, plain bulk copy onto the same barrier
+            mbar_wait(&s.sb_empty[sbs], ((b_it / kSbStages) & 1) ^ 1);
+            mbar_arrive_expect_tx(&s.b_full[st], tile_bytes);
+            tma_load_2d(s.b[st], tm_strm, &s.b_full[st], t * kTile, 0);
+            tma_load_2d(s.b[st] + blk, tm_strm, &s.b_full[st], t * kTile + 64, 0);
+            // side band: 128 float4 = 2 KB, plain bulk copy with its own full/empty pair (its ring
+            // slot is only reused after the epilogue released it, so the parity can never alias)
+            mbar_arrive_expect_tx(&s.sb_full[sbs], kSbBytes);
             asm volatile(
                 "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::
-                    "r"(smem_u32(s.sb[st])),
+                    "r"(smem_u32(s.sb[sbs])),
                 "l"(reinterpret_cast<uint64_t>(p.sb_stream + (size_t)t * kTile)), "r"(kSbBytes),
-                "r"(smem_u32(&s.b_full[st]))
+                "r"(smem_u32(&s.sb_full[sbs]))
                 : "memory");
             ++b_it;
           }
@@ -210,11 +219,10 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   } else if (warp == 1) {
     // ============================ MMA issuer ============================
     if (lane == 0) {
-      const uint32_t idesc1 = umma_idesc_bf16(128, 128, kRow ? 0u : 1u, kRow ? 1u : 0u);
-      const uint32_t idesc2 = umma_idesc_bf16(128, (uint32_t)Kp, 0u, kRow ? 0u : 1u);
+      const uint32_t idesc1 = umma_idesc_bf16(128, 128, 1u, 1u);
+      const uint32_t idesc2 = umma_idesc_bf16(128, (uint32_t)Kp, 0u, 0u);
       const uint32_t a_base = smem_u32(s.a);
       const uint32_t p_base = smem_u32(s.p);
-      const uint32_t mn_lbo = (uint32_t)Kp * 128u;  // distance between 64-word blocks of a beta tile
       uint32_t a_it = 0, b_it = 0, d1_it = 0, p_it = 0, d2_it = 0;
 
       auto issue_mma2 = [&](int st, bool first) {
@@ -224,11 +232,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
 #pragma unroll
         for (int j = 0; j < 8; ++j) {  // 128-wide contraction = 8 k-steps of 16
           const uint64_t da = umma_smem_desc(p_base + (j >> 2) * 16384u + (j & 3) * 32u, 16, 1024);
-          uint64_t db;
-          if (kRow)  // beta tile as K-major B: rows = topics, contraction over words
-            db = umma_smem_desc(b_base + (j >> 2) * mn_lbo + (j & 3) * 32u, 16, 1024);
-          else       // theta tile as MN-major B: rows = documents (contraction), 64-topic blocks
-            db = umma_smem_desc(b_base + j * 2048u, 16384, 1024);
+          const uint64_t db = umma_smem_desc(b_base + (j >> 2) * blk + (j & 3) * 32u, 16, 1024);
           umma_f16(tmem + 256, da, db, idesc2, (first && j == 0) ? 0u : 1u);
         }
         umma_commit(s.p_empty);
@@ -254,14 +258,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
             tc_fence_after();
             const uint32_t b_base = smem_u32(s.b[st]);
             for (int j = 0; j < n_ksteps; ++j) {
-              uint64_t da, db;
-              if (kRow) {
-                da = umma_smem_desc(a_base + (j >> 2) * 16384u + (j & 3) * 32u, 16, 1024);
-                db = umma_smem_desc(b_base + j * 2048u, mn_lbo, 1024);
-              } else {
-                da = umma_smem_desc(a_base + j * 2048u, mn_lbo, 1024);
-                db = umma_smem_desc(b_base + (j >> 2) * 16384u + (j & 3) * 32u, 16, 1024);
-              }
+              const uint64_t da = umma_smem_desc(a_base + j * 2048u, blk, 1024);
+              const uint64_t db = umma_smem_desc(b_base + j * 2048u, blk, 1024);
               umma_f16(tmem + buf * 128, da, db, idesc1, j > 0 ? 1u : 0u);
             }
             umma_commit(&s.d1_full[buf]);
@@ -273,7 +271,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
               }
               pending = st;
             } else {
-              umma_commit(&s.b_empty[st]);
+              umma_commit(&s.b_empty[st]);  // operand tile is free as soon as MMA1 has read it
             }
             ++b_it;
           }
@@ -293,7 +291,6 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
     const uint32_t row = q * 32 + lane;  // TMEM lane == tile row
     const uint32_t lane_addr = tmem + ((q * 32) << 16);
     uint32_t b_it = 0, d1_it = 0, p_it = 0, d2_it = 0;
-    const int mode = p.mode;
 
     for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
       const int stat = w / p.n_chunks, chunk = w - stat * p.n_chunks;
@@ -305,13 +302,13 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       float acc0 = 0.f, acc1 = 0.f;   // ROW_LSE: (max2, sum); COL: (a, c') / sumsq
       float c_r2 = 0.f, c_alpha = 0.f, c_gamma = 0.f, c_rstd = 0.f, c_bias = 0.f;
       float d_lse2 = 0.f, d_sp = 0.f;
-      if (mode == ROW_LSE) acc0 = -INFINITY;
-      if (mode == ROW_GRAD && grow < p.B) {
+      if (kMode == ROW_LSE) acc0 = -INFINITY;
+      if (kMode == ROW_GRAD && grow < p.B) {
         const float2 dc = p.doc_const[grow];
         d_lse2 = dc.x;
         d_sp = dc.y;
       }
-      if (mode == COL_GRAD && grow < p.V) {
+      if (kMode == COL_GRAD && grow < p.V) {
         const float4 cc = p.colc[grow];
         c_r2 = cc.x;
         c_bias = cc.y;
@@ -321,32 +318,32 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       for (int pass = 0; pass < p.n_pass; ++pass) {
         const bool m2 = kHasMMA2 && (pass == p.n_pass - 1);
         for (int t = t0; t < t1; ++t) {
-          const int st = b_it % stages;
+          const int sbs = b_it % kSbStages;
           const uint32_t buf = d1_it & 1;
+          mbar_wait(&s.sb_full[sbs], (b_it / kSbStages) & 1);
           mbar_wait(&s.d1_full[buf], (d1_it >> 1) & 1);
           tc_fence_after();
           if (m2) mbar_wait(s.p_empty, (p_it & 1) ^ 1);
-          const float4* sb = s.sb[st];
-#pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            float v[32];
-            tmem_ld32(lane_addr + buf * 128 + c * 32, v);
-            tmem_ld_wait();
+          const float4* sb = s.sb[sbs];
+          const uint32_t taddr = lane_addr + buf * 128;
+
+          // consume one 32-column chunk `c` of the accumulator held in v[]
+          auto process = [&](const int c, float (&v)[32]) {
             const int col0 = t * kTile + c * 32;  // global streamed index of v[0]
-            if (mode == ROW_LOGITS) {
+            if (kMode == ROW_LOGITS) {
               if (grow < p.B) {
                 float* o = p.out + (size_t)grow * p.V + col0;
 #pragma unroll
                 for (int i = 0; i < 32; ++i)
                   if (col0 + i < p.V) o[i] = v[i];
               }
-            } else if (mode == COL_LOGITS) {
+            } else if (kMode == COL_LOGITS) {
               if (grow < p.V) {
 #pragma unroll
                 for (int i = 0; i < 32; ++i)
                   if (col0 + i < p.B) p.out[(size_t)(col0 + i) * p.V + grow] = v[i];
               }
-            } else if (mode == ROW_LSE) {
+            } else if (kMode == ROW_LSE) {
               float cmax = -INFINITY;
 #pragma unroll
               for (int i = 0; i < 32; ++i) {
@@ -362,7 +359,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 acc1 = sum;
                 acc0 = nm;
               }
-            } else if (mode == ROW_GRAD) {
+            } else if (kMode == ROW_GRAD) {
               // dl = rstd*S*p - alpha - gamma*yc ; p = 2^(yc*r2 + bias - lse2)
               uint32_t pk[16];
 #pragma unroll
@@ -383,10 +380,10 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 *reinterpret_cast<uint4*>(prow + slot * 16) =
                     make_uint4(pk[g * 4], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
               }
-            } else if (mode == COL_STATS) {
+            } else if (kMode == COL_STATS) {
 #pragma unroll
               for (int i = 0; i < 32; ++i) acc0 = fmaf(v[i], v[i], acc0);
-            } else if (mode == COL_GRAD) {
+            } else if (kMode == COL_GRAD) {
               if (!m2) {
                 // pass 1: a += S*p ; c' += S*p*yc
 #pragma unroll
@@ -417,10 +414,23 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 }
               }
             }
-          }
+          };
+
+          // TMEM -> registers two chunks ahead of their use
+          float va[32], vb[32];
+          tmem_ld32(taddr + 0, va);
+          tmem_ld32(taddr + 32, vb);
+          tmem_ld_wait();
+          process(0, va);
+          tmem_ld32(taddr + 64, va);
+          process(1, vb);
+          tmem_ld32(taddr + 96, vb);
+          tmem_ld_wait();
           tc_fence_before();
-          mbar_arrive(&s.d1_empty[buf]);
-          mbar_arrive(&s.b_empty[st]);  // side band of this stage fully consumed
+          mbar_arrive(&s.d1_empty[buf]);  // accumulator buffer can be overwritten by the next MMA1
+          process(2, va);
+          process(3, vb);
+          mbar_arrive(&s.sb_empty[sbs]);  // side band of this tile fully consumed
           ++d1_it;
           ++b_it;
           if (m2) {
@@ -431,7 +441,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         }
 
         // ---- end of a pass
-        if (mode == COL_GRAD && !m2) {
+        if (kMode == COL_GRAD && !m2) {
           // finalise BN-backward column means, publish the per-word constants
           if (grow < p.V) {
             const float invB = 1.0f / (float)p.B;
@@ -445,13 +455,13 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         if (m2) {
           mbar_wait(s.d2_full, d2_it & 1);
           tc_fence_after();
-          const bool has_corr = (mode == COL_GRAD) && p.corr != nullptr && grow < p.V &&
+          const bool has_corr = (kMode == COL_GRAD) && p.corr != nullptr && grow < p.V &&
                                 (p.colptr[grow + 1] > p.colptr[grow]);
           for (int c = 0; c * 32 < Kp; ++c) {
             float v[32];
             tmem_ld32(lane_addr + 256 + c * 32, v);
             tmem_ld_wait();
-            if (mode == ROW_GRAD) {
+            if (kMode == ROW_GRAD) {
               if (grow < p.B) {
 #pragma unroll
                 for (int i = 0; i < 32; ++i)
@@ -478,9 +488,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       }
 
       // ---- end of work item
-      if (mode == ROW_LSE) {
+      if (kMode == ROW_LSE) {
         if (grow < p.B) p.lse_part[(size_t)grow * p.n_chunks + chunk] = make_float2(acc0, acc1);
-      } else if (mode == COL_STATS) {
+      } else if (kMode == COL_STATS) {
         if (grow < p.V) {
           float mean = 0.f;
           if (p.theta_mean != nullptr) {
@@ -516,22 +526,22 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   if (warp == 2) tmem_dealloc<kTmemCols>(tmem);
 }
 
-template <int kKChunks, bool kRow, bool kHasMMA2>
+template <int kMode>
 static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, SweepParams& p,
                         cudaStream_t stream) {
-  const size_t theta_tile = (size_t)kKChunks * 16384, beta_tile = (size_t)p.Kp * 256;
-  const size_t fixed = 1024 + (kRow ? theta_tile : beta_tile) + (kHasMMA2 ? 32768 : 0) + 512;
-  const size_t per_stage = (kRow ? beta_tile : theta_tile) + kTile * sizeof(float4);
+  constexpr bool kHasMMA2 = (kMode == ROW_GRAD || kMode == COL_GRAD);
+  const size_t tile = (size_t)p.Kp * 256;
+  const size_t fixed = 1024 + tile + (kHasMMA2 ? 32768 : 0) + kSbStages * kTile * sizeof(float4) + 1024;
   int max_smem = 0, dev = 0;
   GF_CUDA_CHECK(cudaGetDevice(&dev));
   GF_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  int stages = (int)(((size_t)max_smem - fixed) / per_stage);
+  int stages = (int)(((size_t)max_smem - fixed) / tile);
   if (stages > kMaxStages) stages = kMaxStages;
   GF_ARG_CHECK(stages >= 2, "n_components too large for the fused decoder sweeps (need Kp <= 240)");
   p.stages = stages;
-  size_t smem = fixed + (size_t)stages * per_stage;
+  size_t smem = fixed + (size_t)stages * tile;
   if (kHasMMA2 && smem < 120 * 1024) smem = 120 * 1024;  // 512 TMEM columns => one CTA per SM
-  auto kern = sweep_kernel<kKChunks, kRow, kHasMMA2>;
+  auto kern = sweep_kernel<kMode>;
   GF_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int total = p.n_stat * p.n_chunks;
   const int occ = kHasMMA2 ? 1 : ((smem <= 110 * 1024) ? 2 : 1);
@@ -545,34 +555,57 @@ static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta,
 
 static int dispatch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, SweepParams& p,
                           cudaStream_t stream) {
-  const int kc = (p.Kp + 63) / 64;
-  const bool row = (p.mode == ROW_LOGITS || p.mode == ROW_LSE || p.mode == ROW_GRAD);
-  const bool m2 = (p.mode == ROW_GRAD || p.mode == COL_GRAD);
-#define GF_CASE(KC)                                                                   \
-  case KC:                                                                            \
-    if (row) {                                                                        \
-      if (m2) return launch_sweep<KC, true, true>(tm_theta, tm_beta, p, stream);      \
-      return launch_sweep<KC, true, false>(tm_theta, tm_beta, p, stream);             \
-    } else {                                                                          \
-      if (m2) return launch_sweep<KC, false, true>(tm_theta, tm_beta, p, stream);     \
-      return launch_sweep<KC, false, false>(tm_theta, tm_beta, p, stream);            \
-    }
-  switch (kc) {
-    GF_CASE(1)
-    GF_CASE(2)
-    GF_CASE(3)
-    GF_CASE(4)
-    default:
-      break;
+  switch (p.mode) {
+    case ROW_LOGITS: return launch_sweep<ROW_LOGITS>(tm_theta, tm_beta, p, stream);
+    case ROW_LSE: return launch_sweep<ROW_LSE>(tm_theta, tm_beta, p, stream);
+    case ROW_GRAD: return launch_sweep<ROW_GRAD>(tm_theta, tm_beta, p, stream);
+    case COL_STATS: return launch_sweep<COL_STATS>(tm_theta, tm_beta, p, stream);
+    case COL_GRAD: return launch_sweep<COL_GRAD>(tm_theta, tm_beta, p, stream);
+    case COL_LOGITS: return launch_sweep<COL_LOGITS>(tm_theta, tm_beta, p, stream);
+    default: break;
   }
-#undef GF_CASE
-  fprintf(stderr, "[gfedntm] dec sweep: unsupported Kp=%d\n", p.Kp);
+  fprintf(stderr, "[gfedntm] dec sweep: unsupported mode %d\n", p.mode);
   return GF_ERR_ARG;
+}
+
+// Number of persistent CTAs the ROW modes of this configuration will run (for chunk planning).
+static int sweep_grid_capacity(int mode, int Kp) {
+  const bool m2 = (mode == ROW_GRAD || mode == COL_GRAD);
+  const size_t tile = (size_t)Kp * 256;
+  const size_t fixed = 1024 + tile + (m2 ? 32768 : 0) + kSbStages * kTile * sizeof(float4) + 1024;
+  int max_smem = 232448;
+  int stages = (int)(((size_t)max_smem - fixed) / tile);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) stages = 2;
+  const size_t smem = fixed + (size_t)stages * tile;
+  const int occ = m2 ? 1 : ((smem <= 110 * 1024) ? 2 : 1);
+  return num_sms() * occ;
 }
 
 }  // namespace gf
 
 using namespace gf;
+
+// Vocabulary split for the ROW modes: the smallest chunk count whose (document tiles x chunks) work
+// items fill the persistent grid in whole waves (>= 95 % wave efficiency), so no SM idles in the tail.
+extern "C" int gf_dec_row_chunks(int mode, int B, int V, int Kp) {
+  const int doc_tiles = (B + kTile - 1) / kTile, word_tiles = (V + kTile - 1) / kTile;
+  const int grid = sweep_grid_capacity(mode, Kp);
+  int best = 1;
+  double best_eff = 0.0;
+  const int cmax = word_tiles < 4 * grid ? word_tiles : 4 * grid;
+  for (int c = 1; c <= cmax; ++c) {
+    const long long w = (long long)doc_tiles * c;
+    const long long waves = (w + grid - 1) / grid;
+    const double eff = (double)w / (double)(waves * grid);
+    if (eff > best_eff + 1e-9) {
+      best_eff = eff;
+      best = c;
+    }
+    if (w >= grid && eff >= 0.95) return c;
+  }
+  return best;
+}
 
 extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
@@ -580,12 +613,12 @@ extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
   GF_ARG_CHECK(a->Kp % 16 == 0 && a->Kp >= 16 && a->Kp <= 240, "Kp must be a multiple of 16 in [16,240]");
   GF_ARG_CHECK(a->K <= a->Kp && a->K > 0, "K");
   GF_ARG_CHECK(a->ld_theta % 8 == 0 && a->ld_beta % 8 == 0, "bf16 leading dims must be multiples of 8");
-  GF_ARG_CHECK(a->ld_theta >= a->Kp && a->ld_beta >= a->V, "leading dims too small");
+  GF_ARG_CHECK(a->ld_theta >= a->B && a->ld_beta >= a->V, "leading dims too small");
   GF_ARG_CHECK(a->mode >= 0 && a->mode <= 5, "mode");
   CUtensorMap tm_theta, tm_beta;
-  // theta_c [B, ld_theta] bf16: box = 64 topics x 128 documents
-  int rc = make_tmap_bf16_2d(&tm_theta, a->theta_bf, (uint64_t)a->Kp, (uint64_t)a->B,
-                             (uint64_t)a->ld_theta * 2, 64, 128);
+  // theta_c^T [Kp, ld_theta] bf16: box = 64 documents x Kp topics; documents beyond B read as zero
+  int rc = make_tmap_bf16_2d(&tm_theta, a->theta_bf, (uint64_t)a->B, (uint64_t)a->Kp,
+                             (uint64_t)a->ld_theta * 2, 64, (uint32_t)a->Kp);
   if (rc) return rc;
   // beta [Kp, ld_beta] bf16: box = 64 words x Kp topics; words beyond V read as zero
   rc = make_tmap_bf16_2d(&tm_beta, a->beta_bf, (uint64_t)a->V, (uint64_t)a->Kp,

@@ -282,20 +282,32 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a) {
   }
 }
 
-// theta_c (bf16) = theta - column mean (training) or theta (eval); zero padding to ld columns.
+// theta_c (bf16) = theta - column mean (training) or theta (eval), written in two layouts:
+// out [B, ld] (zero padded columns) and outT [Kp = ld rows, ldT] (documents contiguous).
 __global__ void theta_center_kernel(const float* __restrict__ theta, const float* __restrict__ colsum,
-                                    __nv_bfloat16* __restrict__ out, float* __restrict__ mean_out,
-                                    int B, int K, int ld, int center) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= B * ld) return;
-  const int b = idx / ld, k = idx - b * ld;
-  float v = 0.f;
-  if (k < K) {
-    const float m = center ? colsum[k] / (float)B : 0.f;
-    v = theta[(size_t)b * K + k] - m;
-    if (b == 0 && mean_out != nullptr) mean_out[k] = m;
+                                    __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ outT,
+                                    float* __restrict__ mean_out, int B, int K, int ld, int ldT, int center) {
+  __shared__ float tile[32][33];
+  const int b0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int b = b0 + ty + r * 8, k = k0 + tx;
+    float v = 0.f;
+    if (b < B && k < K) {
+      const float m = center ? colsum[k] / (float)B : 0.f;
+      v = theta[(size_t)b * K + k] - m;
+      if (b == 0 && mean_out != nullptr) mean_out[k] = m;
+    }
+    if (b < B && k < ld) out[(size_t)b * ld + k] = __float2bfloat16(v);
+    tile[ty + r * 8][tx] = v;
   }
-  out[idx] = __float2bfloat16(v);
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int k = k0 + ty + r * 8, b = b0 + tx;
+    if (k < ld && b < B) outT[(size_t)k * ldT + b] = __float2bfloat16(tile[tx][ty + r * 8]);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -546,12 +558,13 @@ extern "C" int gf_latent_fwd(const GfLatentArgs* a, void* stream_) {
   return GF_OK;
 }
 
-extern "C" int gf_theta_center(const float* theta, const float* colsum, void* out_bf16, float* mean_out,
-                               int B, int K, int ld, int center, void* stream_) {
+extern "C" int gf_theta_center(const float* theta, const float* colsum, void* out_bf16, void* outT_bf16,
+                               float* mean_out, int B, int K, int ld, int ldT, int center, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
-  const int n = B * ld;
-  theta_center_kernel<<<(n + 255) / 256, 256, 0, st>>>(theta, colsum, reinterpret_cast<__nv_bfloat16*>(out_bf16),
-                                                       mean_out, B, K, ld, center);
+  dim3 grid((B + 31) / 32, (ld + 31) / 32);
+  theta_center_kernel<<<grid, 256, 0, st>>>(theta, colsum, reinterpret_cast<__nv_bfloat16*>(out_bf16),
+                                            reinterpret_cast<__nv_bfloat16*>(outT_bf16), mean_out, B, K, ld, ldT,
+                                            center);
   GF_LAUNCHED();
   return GF_OK;
 }

@@ -152,7 +152,9 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_dec_sweep.argtypes = [C.POINTER(GfSweepArgs), _p]
     lib.gf_enc_fwd.argtypes = [C.POINTER(GfEncArgs), _p]
     lib.gf_latent_fwd.argtypes = [C.POINTER(GfLatentArgs), _p]
-    lib.gf_theta_center.argtypes = [_p, _p, _p, _p, _i, _i, _i, _i, _p]
+    lib.gf_theta_center.argtypes = [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]
+    lib.gf_dec_row_chunks.argtypes = [_i, _i, _i, _i]
+    lib.gf_dec_row_chunks.restype = _i
     lib.gf_latent_bwd.argtypes = [C.POINTER(GfLatentBwdArgs), _p]
     lib.gf_enc_bwd.argtypes = [C.POINTER(GfEncBwdArgs), _p]
     lib.gf_csr_to_csc.argtypes = [_p, _p, _i, _i, _i, _p, _p, _p, _p, _p]

@@ -87,12 +87,13 @@ class ProdLDADecoder:
         f32 = dict(dtype=torch.float32, device=dev)
         self.Bpad = round_up(max_B, TILE)
         self.Vpad = round_up(V, TILE)
-        self.theta_bf = torch.zeros(max_B, self.Kp, dtype=torch.bfloat16, device=dev)
+        self.theta_bf = torch.zeros(max_B, self.Kp, dtype=torch.bfloat16, device=dev)        # sparse kernels
+        self.thetaT_bf = torch.zeros(self.Kp, round_up(max_B, 8), dtype=torch.bfloat16, device=dev)  # sweeps
         self.theta_mean = torch.zeros(K, **f32)
         self.colc = torch.zeros(self.Vpad, 4, **f32)
         self.sb_doc = torch.zeros(self.Bpad, 4, **f32)
         self.doc_const = torch.zeros(max_B, 2, **f32)
-        self.max_chunks = (V + TILE - 1) // TILE
+        self.max_chunks = min((V + TILE - 1) // TILE, 2048)
         self.lse_part = torch.zeros(max_B * self.max_chunks, 2, **f32)
         self.rl = torch.zeros(max_B, **f32)
         self.asp_csp = torch.zeros(2, V, **f32)
@@ -109,14 +110,15 @@ class ProdLDADecoder:
         """Runs the sweeps.  Returns (rl[B], dtheta[B,Kp] or None).  ``dbeta`` [K,ld] is overwritten."""
         B, V, Kt = batch.B, self.V, self.K
         assert B <= self.max_B
-        K_.theta_center(theta, theta_colsum, self.theta_bf, self.theta_mean, B=B, K=Kt, center=training)
-        K_.dec_sweep(K_.COL_STATS, B=B, V=V, K=Kt, theta_bf=self.theta_bf, beta_bf=beta_bf,
+        K_.theta_center(theta, theta_colsum, self.theta_bf, self.thetaT_bf, self.theta_mean, B=B, K=Kt,
+                        center=training)
+        K_.dec_sweep(K_.COL_STATS, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=beta_bf,
                      sb_stream=self.sb_doc, colc=self.colc,
                      theta_mean=self.theta_mean if training else None,
                      running_mean=running_mean, running_var=running_var, bn_eps=self.bn_eps,
                      bn_momentum=self.bn_momentum, use_running=not training)
-        n_chunks = K_.default_row_chunks(B, V)
-        K_.dec_sweep(K_.ROW_LSE, B=B, V=V, K=Kt, theta_bf=self.theta_bf, beta_bf=beta_bf,
+        n_chunks = K_.default_row_chunks(B, V, Kp=self.Kp)
+        K_.dec_sweep(K_.ROW_LSE, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=beta_bf,
                      sb_stream=self.colc, n_chunks=n_chunks, lse_part=self.lse_part)
         grad = need_grad and training
         if grad:
@@ -131,11 +133,11 @@ class ProdLDADecoder:
             return self.rl[:B], None
         assert csc is not None and dbeta is not None
         K_.csc_corr(csc.colptr, csc.row, csc.src, self.tnnz, self.theta_bf, self.corr, V=V)
-        K_.dec_sweep(K_.COL_GRAD, B=B, V=V, K=Kt, theta_bf=self.theta_bf, beta_bf=beta_bf,
+        K_.dec_sweep(K_.COL_GRAD, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=beta_bf,
                      sb_stream=self.sb_doc, colc=self.colc, asp=self.asp_csp[0], csp=self.asp_csp[1],
                      dbeta=dbeta, corr=self.corr, colptr=csc.colptr)
-        n_chunks_g = K_.default_row_chunks(B, V, second_mma=True)
-        K_.dec_sweep(K_.ROW_GRAD, B=B, V=V, K=Kt, theta_bf=self.theta_bf, beta_bf=beta_bf,
+        n_chunks_g = K_.default_row_chunks(B, V, second_mma=True, Kp=self.Kp)
+        K_.dec_sweep(K_.ROW_GRAD, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=beta_bf,
                      sb_stream=self.colc, n_chunks=n_chunks_g, doc_const=self.doc_const,
                      dtheta=self.dtheta)
         return self.rl[:B], self.dtheta[:B]

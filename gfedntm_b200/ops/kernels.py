@@ -44,15 +44,11 @@ def padded_topics(k: int) -> int:
     return round_up(k, 16)
 
 
-def default_row_chunks(B: int, V: int, second_mma: bool = False) -> int:
-    """Vocabulary split of the ROW sweeps so that (doc tiles x chunks) fills the SMs ~2x."""
-    props = torch.cuda.get_device_properties(torch.cuda.current_device())
-    sms = props.multi_processor_count
-    doc_tiles = (B + TILE - 1) // TILE
-    word_tiles = (V + TILE - 1) // TILE
-    waves = 1 if second_mma else 2
-    target = max(1, (sms * waves + doc_tiles - 1) // doc_tiles)
-    return max(1, min(word_tiles, target))
+def default_row_chunks(B: int, V: int, second_mma: bool = False, Kp: int = 64) -> int:
+    """Vocabulary split of the ROW sweeps: smallest chunk count that fills the persistent grid in
+    whole waves (computed by the library, which knows the grid each mode launches)."""
+    lib = _lib.load()
+    return int(lib.gf_dec_row_chunks(ROW_GRAD if second_mma else ROW_LSE, B, V, Kp))
 
 
 # ----------------------------------------------------------------------------------------------
@@ -66,7 +62,9 @@ def dec_sweep(mode: int, *, B: int, V: int, K: int, theta_bf: torch.Tensor, beta
     lib = _lib.load()
     Kp = beta_bf.shape[0]
     assert theta_bf.dtype == torch.bfloat16 and beta_bf.dtype == torch.bfloat16
-    assert theta_bf.shape[0] >= B and theta_bf.stride(1) == 1 and beta_bf.stride(1) == 1
+    # theta_bf is the TRANSPOSED centred theta: [Kp, ld >= B], documents contiguous
+    assert theta_bf.shape[0] == Kp and theta_bf.shape[1] >= B and theta_bf.stride(1) == 1
+    assert beta_bf.stride(1) == 1
     a = GfSweepArgs()
     a.mode, a.B, a.V, a.K, a.Kp, a.n_chunks = mode, B, V, K, Kp, n_chunks
     a.theta_bf, a.ld_theta = _ptr(theta_bf), theta_bf.stride(0)
@@ -132,10 +130,11 @@ def latent_fwd(*, B: int, K: int, training: bool, sample: bool, mu_pre, ls_pre, 
     check(lib.gf_latent_fwd(C.byref(a), _stream()), "gf_latent_fwd")
 
 
-def theta_center(theta, colsum, out_bf16, mean_out, *, B: int, K: int, center: bool) -> None:
+def theta_center(theta, colsum, out_bf16, outT_bf16, mean_out, *, B: int, K: int, center: bool) -> None:
+    """theta_c as bf16 in both layouts: out [B, Kp] and outT [Kp, ldT]."""
     lib = _lib.load()
-    check(lib.gf_theta_center(_ptr(theta), _ptr(colsum), _ptr(out_bf16), _ptr(mean_out), B, K,
-                              out_bf16.stride(0), int(center), _stream()), "gf_theta_center")
+    check(lib.gf_theta_center(_ptr(theta), _ptr(colsum), _ptr(out_bf16), _ptr(outT_bf16), _ptr(mean_out), B, K,
+                              out_bf16.stride(0), outT_bf16.stride(0), int(center), _stream()), "gf_theta_center")
 
 
 def latent_bwd(*, B: int, K: int, dtheta, mask_theta, theta_s, mu, logvar, eps, prior_mean,

@@ -44,7 +44,8 @@ typedef struct GfSweepArgs {
   int mode;              /* GfSweepMode */
   int B, V, K, Kp;       /* documents, vocabulary, topics, topics padded to a multiple of 16  */
   int n_chunks;          /* ROW modes: vocabulary split per document tile (>=1)                */
-  const void* theta_bf;  /* [B, ld_theta] bf16, columns >= K zero                               */
+  const void* theta_bf;  /* theta_c TRANSPOSED: [Kp, ld_theta] bf16 (documents contiguous,
+                            ld_theta >= B, multiple of 8), rows >= K zero                       */
   int ld_theta;
   const void* beta_bf;   /* [Kp, ld_beta] bf16, rows >= K zero                                  */
   int ld_beta;
@@ -70,6 +71,8 @@ typedef struct GfSweepArgs {
 } GfSweepArgs;
 
 int gf_dec_sweep(const GfSweepArgs* args, void* stream);
+/* Vocabulary chunk count for the ROW modes that fills the persistent grid in whole waves.       */
+int gf_dec_row_chunks(int mode, int B, int V, int Kp);
 
 /* ------------------------------------------------------------------------------------------
  * Encoder / latent layer (CUDA-core kernels on [B,H] / [B,K] data; the BoW input is CSR).
@@ -123,9 +126,11 @@ typedef struct GfLatentArgs {
 } GfLatentArgs;
 int gf_latent_fwd(const GfLatentArgs* args, void* stream);
 
-/* theta_c (bf16, [B, ld]) = theta - colsum/B (center=1) or theta (center=0); zero padded.     */
-int gf_theta_center(const float* theta, const float* colsum, void* out_bf16, float* mean_out,
-                    int B, int K, int ld, int center, void* stream);
+/* theta_c = theta - colsum/B (center=1) or theta (center=0) as bf16 in two layouts:
+ * out_bf16 [B, ld] (row per document, zero padded to ld columns; sparse kernels) and
+ * outT_bf16 [Kp, ldT] (row per topic, documents contiguous; tensor-core sweeps).               */
+int gf_theta_center(const float* theta, const float* colsum, void* out_bf16, void* outT_bf16,
+                    float* mean_out, int B, int K, int ld, int ldT, int center, void* stream);
 
 typedef struct GfLatentBwdArgs {
   int B, K;

@@ -29,11 +29,13 @@ def test_logits_gemm(B, V, K, mode):
     Kp = beta_bf.shape[0]
     th_bf = torch.zeros(B, Kp, dtype=torch.bfloat16, device="cuda")
     th_bf[:, :K] = theta.to(torch.bfloat16)
+    thT_bf = torch.zeros(Kp, Kx.round_up(B, 8), dtype=torch.bfloat16, device="cuda")
+    thT_bf[:, :B] = th_bf.t()
     out = torch.full((B, V), float("nan"), device="cuda")
     Vpad = Kx.round_up(V, 128)
     Bpad = Kx.round_up(B, 128)
     sb = torch.zeros(max(Vpad, Bpad), 4, device="cuda")
-    Kx.dec_sweep(Kx.ROW_LOGITS if mode == "row" else Kx.COL_LOGITS, B=B, V=V, K=K, theta_bf=th_bf,
+    Kx.dec_sweep(Kx.ROW_LOGITS if mode == "row" else Kx.COL_LOGITS, B=B, V=V, K=K, theta_bf=thT_bf,
                  beta_bf=beta_bf, sb_stream=sb, n_chunks=min(3, (V + 127) // 128), out=out)
     torch.cuda.synchronize()
     ref = th_bf[:, :K].float() @ beta_bf[:K, :V].float()
