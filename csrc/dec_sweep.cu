@@ -47,6 +47,7 @@ struct SweepParams {
   int mode;
   int B, V, K, Kp;
   int n_stat, n_stream, n_chunks, n_pass, stages;
+  int p_bufs;               // 1 or 2 shared-memory P tiles (gradient modes)
   const float4* sb_stream;  // side band per streamed index (padded to a multiple of 128)
   // generic
   float* out;               // LOGITS modes: [B,V] fp32
@@ -72,13 +73,13 @@ struct SweepParams {
   const int* colptr;        // [V+1] CSC pointer of the batch (with corr)
 };
 
-constexpr int kSbStages = 4;   // side-band ring depth (2 KB per entry)
+constexpr int kSbStagesMax = 4;  // side-band ring depth (2 KB per entry); 2 in the gradient modes
 
 struct Smem {
   uint8_t* a;
   uint8_t* b[kMaxStages];
-  float4* sb[kSbStages];
-  uint8_t* p;
+  float4* sb[kSbStagesMax];
+  uint8_t* p[2];
   uint64_t* a_full;
   uint64_t* a_empty;
   uint64_t* b_full;    // [kMaxStages]  operand tile landed
@@ -87,8 +88,8 @@ struct Smem {
   uint64_t* sb_empty;  // [kSbStages]   side band consumed by the epilogue
   uint64_t* d1_full;   // [2]
   uint64_t* d1_empty;  // [2]
-  uint64_t* p_full;
-  uint64_t* p_empty;
+  uint64_t* p_full;    // [2]
+  uint64_t* p_empty;   // [2]
   uint64_t* d2_full;
   uint64_t* d2_empty;
   uint32_t* tmem_ptr;
@@ -105,6 +106,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
              const SweepParams p) {
   constexpr bool kRow = (kMode == ROW_LOGITS || kMode == ROW_LSE || kMode == ROW_GRAD);
   constexpr bool kHasMMA2 = (kMode == ROW_GRAD || kMode == COL_GRAD);
+  constexpr int kSbStages = kHasMMA2 ? 2 : kSbStagesMax;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t kSbBytes = kTile * sizeof(float4);
@@ -119,11 +121,12 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
     s.b[i] = cur;
     if (i < stages) cur += tile_bytes;
   }
-  s.p = cur;
-  if (kHasMMA2) cur += 32768;
-  for (int i = 0; i < kSbStages; ++i) {
+  s.p[0] = cur;
+  s.p[1] = cur + 32768;
+  if (kHasMMA2) cur += 32768u * p.p_bufs;  // double-buffered when it fits: epilogue(t+1) overlaps MMA2(t)
+  for (int i = 0; i < kSbStagesMax; ++i) {
     s.sb[i] = reinterpret_cast<float4*>(cur);
-    cur += kSbBytes;
+    if (i < kSbStages) cur += kSbBytes;
   }
   uint64_t* bars = reinterpret_cast<uint64_t*>(cur);
   s.a_full = bars + 0;
@@ -131,12 +134,12 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   s.b_full = bars + 2;
   s.b_empty = s.b_full + kMaxStages;
   s.sb_full = s.b_empty + kMaxStages;
-  s.sb_empty = s.sb_full + kSbStages;
-  s.d1_full = s.sb_empty + kSbStages;
+  s.sb_empty = s.sb_full + kSbStagesMax;
+  s.d1_full = s.sb_empty + kSbStagesMax;
   s.d1_empty = s.d1_full + 2;
   s.p_full = s.d1_empty + 2;
-  s.p_empty = s.p_full + 1;
-  s.d2_full = s.p_empty + 1;
+  s.p_empty = s.p_full + 2;
+  s.d2_full = s.p_empty + 2;
   s.d2_empty = s.d2_full + 1;
   s.tmem_ptr = reinterpret_cast<uint32_t*>(s.d2_empty + 1);
 
@@ -162,8 +165,10 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       mbar_init(&s.d1_full[i], 1);
       mbar_init(&s.d1_empty[i], 128);
     }
-    mbar_init(s.p_full, 128);
-    mbar_init(s.p_empty, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s.p_full[i], 128);
+      mbar_init(&s.p_empty[i], 1);
+    }
     mbar_init(s.d2_full, 1);
     mbar_init(s.d2_empty, 128);
     mbar_fence_init();
@@ -222,12 +227,13 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       const uint32_t idesc1 = umma_idesc_bf16(128, 128, 1u, 1u);
       const uint32_t idesc2 = umma_idesc_bf16(128, (uint32_t)Kp, 0u, 0u);
       const uint32_t a_base = smem_u32(s.a);
-      const uint32_t p_base = smem_u32(s.p);
       uint32_t a_it = 0, b_it = 0, d1_it = 0, p_it = 0, d2_it = 0;
 
       auto issue_mma2 = [&](int st, bool first) {
-        mbar_wait(s.p_full, p_it & 1);
+        const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;
+        mbar_wait(&s.p_full[pb], ((p.p_bufs == 2) ? (p_it >> 1) : p_it) & 1);
         tc_fence_after();
+        const uint32_t p_base = smem_u32(s.p[pb]);
         const uint32_t b_base = smem_u32(s.b[st]);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {  // 128-wide contraction = 8 k-steps of 16
@@ -235,7 +241,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           const uint64_t db = umma_smem_desc(b_base + (j >> 2) * blk + (j & 3) * 32u, 16, 1024);
           umma_f16(tmem + 256, da, db, idesc2, (first && j == 0) ? 0u : 1u);
         }
-        umma_commit(s.p_empty);
+        umma_commit(&s.p_empty[pb]);
         umma_commit(&s.b_empty[st]);
         ++p_it;
       };
@@ -323,7 +329,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           mbar_wait(&s.sb_full[sbs], (b_it / kSbStages) & 1);
           mbar_wait(&s.d1_full[buf], (d1_it >> 1) & 1);
           tc_fence_after();
-          if (m2) mbar_wait(s.p_empty, (p_it & 1) ^ 1);
+          const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;
+          uint8_t* const pbuf = s.p[pb];
+          if (m2) mbar_wait(&s.p_empty[pb], (((p.p_bufs == 2) ? (p_it >> 1) : p_it) & 1) ^ 1);
           const float4* sb = s.sb[sbs];
           const uint32_t taddr = lane_addr + buf * 128;
 
@@ -373,7 +381,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 pk[i >> 1] = pack_bf16(g0, g1);
               }
               // P tile, K-major SW128: chunk = (c>>1), slots (c&1)*4 .. +3 of row `row`
-              uint8_t* prow = s.p + (c >> 1) * 16384 + row * 128;
+              uint8_t* prow = pbuf + (c >> 1) * 16384 + row * 128;
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
                 const uint32_t slot = ((c & 1) * 4 + g) ^ (row & 7);
@@ -405,7 +413,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                   const float g1 = fmaf(-c_gamma, v[i + 1], fmaf(c_rstd * d1.y, p1, -c_alpha));
                   pk[i >> 1] = pack_bf16(g0, g1);
                 }
-                uint8_t* prow = s.p + (c >> 1) * 16384 + row * 128;
+                uint8_t* prow = pbuf + (c >> 1) * 16384 + row * 128;
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
                   const uint32_t slot = ((c & 1) * 4 + g) ^ (row & 7);
@@ -435,7 +443,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           ++b_it;
           if (m2) {
             fence_proxy_async_smem();
-            mbar_arrive(s.p_full);
+            mbar_arrive(&s.p_full[pb]);
             ++p_it;
           }
         }
@@ -531,10 +539,13 @@ static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta,
                         cudaStream_t stream) {
   constexpr bool kHasMMA2 = (kMode == ROW_GRAD || kMode == COL_GRAD);
   const size_t tile = (size_t)p.Kp * 256;
-  const size_t fixed = 1024 + tile + (kHasMMA2 ? 32768 : 0) + kSbStages * kTile * sizeof(float4) + 1024;
   int max_smem = 0, dev = 0;
   GF_CUDA_CHECK(cudaGetDevice(&dev));
   GF_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  const size_t base_fixed = 1024 + tile + (kHasMMA2 ? 2 : kSbStagesMax) * kTile * sizeof(float4) + 1024;
+  p.p_bufs = kHasMMA2 ? 2 : 0;
+  if (kHasMMA2 && (size_t)max_smem < base_fixed + 65536 + 2 * tile) p.p_bufs = 1;  // large Kp: single P tile
+  const size_t fixed = base_fixed + 32768 * (size_t)p.p_bufs;
   int stages = (int)(((size_t)max_smem - fixed) / tile);
   if (stages > kMaxStages) stages = kMaxStages;
   GF_ARG_CHECK(stages >= 2, "n_components too large for the fused decoder sweeps (need Kp <= 240)");
@@ -572,8 +583,10 @@ static int dispatch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_bet
 static int sweep_grid_capacity(int mode, int Kp) {
   const bool m2 = (mode == ROW_GRAD || mode == COL_GRAD);
   const size_t tile = (size_t)Kp * 256;
-  const size_t fixed = 1024 + tile + (m2 ? 32768 : 0) + kSbStages * kTile * sizeof(float4) + 1024;
   int max_smem = 232448;
+  const size_t base_fixed = 1024 + tile + (m2 ? 2 : kSbStagesMax) * kTile * sizeof(float4) + 1024;
+  const int p_bufs = m2 ? (((size_t)max_smem < base_fixed + 65536 + 2 * tile) ? 1 : 2) : 0;
+  const size_t fixed = base_fixed + 32768 * (size_t)p_bufs;
   int stages = (int)(((size_t)max_smem - fixed) / tile);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) stages = 2;
