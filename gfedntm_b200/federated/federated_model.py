@@ -87,8 +87,8 @@ class FederatedModel:
         sd = self.model.state_dict()
         named = dict(self.model.named_parameters())
         for key in self._shared_keys():
-            if self.share == "grad" and key in named and named[key].grad is not None:
-                params[key] = named[key].grad.detach()
+            if self.share == "grad" and key in named and key in getattr(self, "_grad_payload", {}):
+                params[key] = self._grad_payload[key]
             else:
                 params[key] = sd[key]
         return params
@@ -115,12 +115,21 @@ class FederatedModel:
         return self.get_gradients()
 
     def gradient_minibatch(self, mb) -> torch.Tensor:
-        """Forward + backward only (no optimiser step): ``share='grad'`` clients."""
+        """``share='grad'`` clients: forward + backward, gradients stay available for the payload, then a
+        local optimiser step.  The step only matters for tensors that are NOT shared (they keep training
+        locally); shared tensors are overwritten by the server's result in ``deltaUpdateFit``."""
         if self.backend == "fused":
-            return self.engine.forward_backward(mb.bow, mb.x_ctx, training=True).clone()
+            loss = self.engine.forward_backward(mb.bow, mb.x_ctx, training=True).clone()
+            self._grad_payload = {n: p.grad.detach().clone() for n, p in self.model.named_parameters()
+                                  if n in self.grads_to_share}
+            self.engine.optimizer_step()
+            return loss
         self.model.zero_grad()
         loss = self._eager_forward_loss(mb)
         loss.backward()
+        self._grad_payload = {n: p.grad.detach().clone() for n, p in self.model.named_parameters()
+                              if n in self.grads_to_share and p.grad is not None}
+        self.optimizer.step()
         return loss.detach()
 
     def _epoch_end(self, save_dir: Optional[str]) -> None:

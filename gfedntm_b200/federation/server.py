@@ -118,24 +118,32 @@ class FederatedServer(federated_pb2_grpc.FederationServicer):
     # ------------------------------------------------------------------------------------------
     # bookkeeping
     # ------------------------------------------------------------------------------------------
+    @staticmethod
+    def _key(client_id: int) -> str:
+        """Registry key of a client.  The reference keys on ``context.peer()``; two clients of one host
+        process can share a TCP connection (gRPC pools sub-channels per target), and a reconnecting
+        client gets a new peer string, so the numeric client id is the stable identity here."""
+        return f"client:{int(client_id)}"
+
     def record_client_consensus(self, context, nr_samples: int, client_id: int) -> None:
-        peer = context.peer()
-        self._federation.connect_consensus(peer)
+        key = self._key(client_id)
+        self._federation.connect_consensus(key)
         with self._federation.federation_lock:
-            pos = federation_client.FederationClient.get_pos_by_key(peer, self._federation.federation_clients)
+            pos = federation_client.FederationClient.get_pos_by_key(key, self._federation.federation_clients)
             c = self._federation.federation_clients[pos]
             c.vocab_sent, c.nr_samples, c.client_id = True, int(nr_samples), int(client_id)
+            c.peer = context.peer()
             c.last_seen = time.time()
-            self._federation.merge_duplicate_ids()
-        context.add_callback(lambda: self._federation.disconnect(peer))
+        context.add_callback(lambda: self._federation.disconnect(key))
 
     def record_client_waiting_or_consensus(self, context, waiting: bool) -> None:
+        """A client blocks in ``sendGlobalDicAndInitialNN`` (``waiting=False``) or in
+        ``trainFederatedModel`` (``waiting=True``); nothing to add to the roster, only liveness."""
         peer = context.peer()
         with self._federation.federation_lock:
-            known = federation_client.FederationClient.get_pos_by_key(peer, self._federation.federation_clients) >= 0
-            if known:
-                self._federation.connect_waiting_or_consensus(peer, waiting)
-                context.add_callback(lambda: self._federation.disconnect(peer))
+            for c in self._federation.federation_clients:
+                if getattr(c, "peer", None) == peer:
+                    c.last_seen = time.time()
 
     def can_send_aggragated_vocab(self) -> bool:
         cl = self._federation.federation_clients
@@ -223,9 +231,6 @@ class FederatedServer(federated_pb2_grpc.FederationServicer):
         cid = self._client_id_from_header(request.header)
         with self._federation.federation_lock:
             pos = federation_client.FederationClient.get_pos_by_id(cid, self._federation.federation_clients)
-            if pos < 0:
-                pos = federation_client.FederationClient.get_pos_by_key(context.peer(),
-                                                                        self._federation.federation_clients)
             if pos >= 0:
                 self._federation.federation_clients[pos].ready_for_training = True
         self._notify()
