@@ -35,7 +35,7 @@ def main():
     tr.prepare(loader)
     eng = model.engine
     names = [n for n, _ in model.model.named_parameters()]
-    ref = {n: eng.flat.view(eng.flat.P, n).detach().clone().requires_grad_(True) for n in names}
+    ref = {n: eng.flat.view(eng.flat.P, n).detach().clone().contiguous().requires_grad_(True) for n in names}
     opt = torch.optim.Adam([ref[n] for n in names], lr=model.lr, betas=(model.momentum, 0.99))
     wsum = sum(tr.weights)
     assert abs(wsum - 1.0) < 1e-6 and len(set(round(w, 6) for w in tr.weights)) == world
@@ -43,11 +43,15 @@ def main():
     it = iter(loader)
     losses = []
     for step in range(6):
-        mb = next(it)
+        try:
+            mb = next(it)
+        except StopIteration:
+            it = iter(loader)
+            mb = next(it)
         if agg == "grad":
             # replicate what trainer.step does, but keep the gradients for the oracle
             loss = eng.forward_backward(mb.bow, None, training=True, gscale=tr.weights[rank])
-            g = {n: eng.flat.view(eng.flat.G, n).detach().clone() for n in names}
+            g = {n: eng.flat.view(eng.flat.G, n).detach().clone().contiguous() for n in names}
             s_local = eng.flat.S.detach().clone() * tr.weights[rank]
             eng.step_count += 1
             tr._launch("grad", eng.step_count)
@@ -76,7 +80,7 @@ def main():
         if not torch.equal(mine, root):
             print(f"[rank {rank}] step {step}: parameters differ from rank 0")
             ok = False
-        sh = eng.beta_bf.detach().clone().view(torch.int16)
+        sh = eng.beta_bf.detach().clone().contiguous().view(torch.int32)
         sh0 = sh.clone()
         dist.broadcast(sh0, src=0)
         if not torch.equal(sh, sh0):
