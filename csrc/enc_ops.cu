@@ -57,8 +57,15 @@ __device__ __forceinline__ float rrelu_slope(int act, int training, uint64_t see
 // ---------------------------------------------------------------------------------------------
 // enc_fwd: CSR gather + optional dense input + hidden layers + enc-dropout + mu/sigma heads.
 // ---------------------------------------------------------------------------------------------
+// seed of this step: host seed advanced by the device-side step counter (graph-replay safe)
+__device__ __forceinline__ unsigned long long step_seed(unsigned long long seed, const long long* ctr) {
+  return ctr != nullptr ? seed + (unsigned long long)ctr[0] * 0x9E3779B97F4A7C15ull : seed;
+}
+
 __global__ void __launch_bounds__(kDocsPerBlock * 32)
-enc_fwd_kernel(const GfEncArgs a) {
+enc_fwd_kernel(const GfEncArgs a_) {
+  GfEncArgs a = a_;
+  a.seed = step_seed(a_.seed, a_.step_ctr);
   __shared__ float hbuf[2][kDocsPerBlock][kMaxH];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b0 = blockIdx.x * kDocsPerBlock;
@@ -174,7 +181,9 @@ enc_fwd_kernel(const GfEncArgs a) {
 // latent_fwd: BatchNorm(mu), BatchNorm(log sigma^2), reparameterise, softmax, theta dropout, KL.
 // One warp per document; lanes stride over topics.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a) {
+__global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) {
+  GfLatentArgs a = a_;
+  a.seed = step_seed(a_.seed, a_.step_ctr);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * 8 + warp;
   const int K = a.K;
@@ -367,7 +376,9 @@ __global__ void __launch_bounds__(256) latent_bwd_kernel(const GfLatentBwdArgs a
 // Weight gradients are accumulated per block in registers/shared memory, then added with atomics.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kDocsPerBlock * 32)
-enc_bwd_kernel(const GfEncBwdArgs a) {
+enc_bwd_kernel(const GfEncBwdArgs a_) {
+  GfEncBwdArgs a = a_;
+  a.seed = step_seed(a_.seed, a_.step_ctr);
   __shared__ float hact[kDocsPerBlock][kMaxH];   // forward activation of the layer below
   __shared__ float dcur[kDocsPerBlock][kMaxH];   // gradient w.r.t. current layer output
   __shared__ float dhead[kDocsPerBlock][2 * kMaxH];  // d mu_pre | d ls_pre
@@ -533,9 +544,24 @@ enc_bwd_kernel(const GfEncBwdArgs a) {
   }
 }
 
+// ctr[0] += inc_rng (every forward pass), ctr[1] += inc_opt (every optimiser step)
+__global__ void step_begin_kernel(long long* ctr, int inc_rng, int inc_opt) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    ctr[0] += inc_rng;
+    ctr[1] += inc_opt;
+  }
+}
+
 }  // namespace gf
 
 using namespace gf;
+
+extern "C" int gf_step_begin(long long* ctr, int inc_rng, int inc_opt, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  gf::step_begin_kernel<<<1, 32, 0, st>>>(ctr, inc_rng, inc_opt);
+  GF_LAUNCHED();
+  return GF_OK;
+}
 
 extern "C" int gf_enc_fwd(const GfEncArgs* a, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);

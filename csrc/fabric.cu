@@ -81,7 +81,13 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
   __shared__ int is_last;
   const GfFabricRank& me = a.ranks[blockIdx.y];
   const int world = a.world, rank = me.rank;
-  const uint32_t epoch = (uint32_t)a.epoch;
+  uint32_t epoch = (uint32_t)a.epoch;
+  if (a.step_ctr != nullptr) {  // graph replay: epoch and Adam step come from the device counters
+    const long long t = a.step_ctr[1];
+    epoch = (uint32_t)t;
+    h.bc1 = 1.f - powf(h.b1, (float)t);
+    h.bc2_sqrt = sqrtf(1.f - powf(h.b2, (float)t));
+  }
 
   // ---------------- phase A: publish "gradients ready", wait for everyone
   if (blockIdx.x == 0 && threadIdx.x < (unsigned)world) {
@@ -230,7 +236,7 @@ extern "C" int gf_fed_aggregate(const GfFedArgs* a, void* stream_) {
   GF_ARG_CHECK(a->mode == 0 || a->mode == 1, "mode");
   GF_ARG_CHECK(a->flat_n % 4 == 0 && a->beta_off % 4 == 0 && a->s_n % 4 == 0,
                "flat_n, beta_off and s_n must be multiples of 4 (16-byte vectors)");
-  GF_ARG_CHECK(a->mode == 1 || a->step >= 1, "Adam step must be >= 1");
+  GF_ARG_CHECK(a->mode == 1 || a->step >= 1 || a->step_ctr != nullptr, "Adam step must be >= 1");
   AdamF h;
   h.lr = a->lr; h.b1 = a->b1; h.b2 = a->b2; h.eps = a->eps; h.wd = a->wd;
   const int step = a->step >= 1 ? a->step : 1;

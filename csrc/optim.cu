@@ -9,7 +9,16 @@ namespace gf {
 
 struct AdamH {
   float lr, b1, b2, eps, bc1, bc2_sqrt, wd;  // bc1 = 1-b1^t, bc2_sqrt = sqrt(1-b2^t)
+  const long long* step_ctr;                // optional: t = step_ctr[1] read on the device
 };
+__device__ __forceinline__ AdamH resolve_step(AdamH h) {
+  if (h.step_ctr != nullptr) {
+    const float t = (float)h.step_ctr[1];
+    h.bc1 = 1.f - powf(h.b1, t);
+    h.bc2_sqrt = sqrtf(1.f - powf(h.b2, t));
+  }
+  return h;
+}
 
 __device__ __forceinline__ float adam_one(float p, float g, float& m, float& v, const AdamH& h) {
   if (h.wd != 0.f) g = fmaf(h.wd, p, g);
@@ -21,7 +30,8 @@ __device__ __forceinline__ float adam_one(float p, float g, float& m, float& v, 
 
 __global__ void __launch_bounds__(256) adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                         float* __restrict__ m, float* __restrict__ v, long long n,
-                                                        AdamH h, float gscale) {
+                                                        AdamH h_, float gscale) {
+  const AdamH h = resolve_step(h_);
   const long long i0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i0 + 3 < n && ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
                       reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0) {
@@ -51,8 +61,9 @@ __global__ void __launch_bounds__(256) adam_flat_kernel(float* __restrict__ p, c
 __global__ void __launch_bounds__(256) adam_beta_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                         float* __restrict__ m, float* __restrict__ v, int K, int V,
                                                         int ldp, int ldg, __nv_bfloat16* __restrict__ beta_bf, int ldb,
-                                                        __nv_bfloat16* __restrict__ betaT_bf, int Kp, AdamH h,
+                                                        __nv_bfloat16* __restrict__ betaT_bf, int Kp, AdamH h_,
                                                         float gscale, int do_update) {
+  const AdamH h = resolve_step(h_);
   __shared__ float tile[32][33];
   const int v0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
@@ -86,34 +97,38 @@ __global__ void __launch_bounds__(256) adam_beta_kernel(float* __restrict__ p, c
 
 using namespace gf;
 
-static AdamH make_h(float lr, float b1, float b2, float eps, float wd, int step) {
+static AdamH make_h(float lr, float b1, float b2, float eps, float wd, int step, const long long* step_ctr) {
   AdamH h;
-  h.lr = lr; h.b1 = b1; h.b2 = b2; h.eps = eps; h.wd = wd;
+  h.lr = lr; h.b1 = b1; h.b2 = b2; h.eps = eps; h.wd = wd; h.step_ctr = step_ctr;
   h.bc1 = 1.f - powf(b1, (float)step);
   h.bc2_sqrt = sqrtf(1.f - powf(b2, (float)step));
   return h;
 }
 
 extern "C" int gf_adam_flat(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
-                            float eps, float wd, int step, float gscale, void* stream_) {
+                            float eps, float wd, int step, float gscale, const long long* step_ctr, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   if (n <= 0) return GF_OK;
-  GF_ARG_CHECK(step >= 1, "Adam step must be >= 1");
+  GF_ARG_CHECK(step >= 1 || step_ctr != nullptr, "Adam step must be >= 1");
+  if (step < 1) step = 1;
   const long long thr = (n + 3) / 4;
-  adam_flat_kernel<<<(unsigned)((thr + 255) / 256), 256, 0, st>>>(p, g, m, v, n, make_h(lr, b1, b2, eps, wd, step), gscale);
+  adam_flat_kernel<<<(unsigned)((thr + 255) / 256), 256, 0, st>>>(p, g, m, v, n, make_h(lr, b1, b2, eps, wd, step, step_ctr), gscale);
   GF_LAUNCHED();
   return GF_OK;
 }
 
 extern "C" int gf_adam_beta(float* p, const float* g, float* m, float* v, int K, int V, int ldp, int ldg,
                             void* beta_bf, int ldb, void* betaT_bf, int Kp, float lr, float b1, float b2, float eps,
-                            float wd, int step, float gscale, int do_update, void* stream_) {
+                            float wd, int step, float gscale, int do_update, const long long* step_ctr,
+                            void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
-  GF_ARG_CHECK(!do_update || step >= 1, "Adam step must be >= 1");
+  GF_ARG_CHECK(!do_update || step >= 1 || step_ctr != nullptr, "Adam step must be >= 1");
+  if (step < 1) step = 1;
   dim3 grid((V + 31) / 32, (K + 31) / 32);
   adam_beta_kernel<<<grid, 256, 0, st>>>(p, g, m, v, K, V, ldp, ldg, reinterpret_cast<__nv_bfloat16*>(beta_bf), ldb,
                                          reinterpret_cast<__nv_bfloat16*>(betaT_bf), Kp,
-                                         make_h(lr, b1, b2, eps, wd, do_update ? step : 1), gscale, do_update);
+                                         make_h(lr, b1, b2, eps, wd, do_update ? step : 1, do_update ? step_ctr : nullptr), gscale,
+                                         do_update);
   GF_LAUNCHED();
   return GF_OK;
 }

@@ -447,6 +447,33 @@ extern "C" int gf_csr_to_csc(const int* indptr, const int* indices, int B, int V
   return GF_OK;
 }
 
+namespace gf {
+__global__ void csc_hist_dyn_kernel(const int* __restrict__ indptr, int B, const int* __restrict__ indices,
+                                    int* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < indptr[B]) atomicAdd(&count[indices[i] + 1], 1);
+}
+}  // namespace gf
+
+extern "C" int gf_csr_to_csc_dyn(const int* indptr, const int* indices, int B, int V, int nnz_capacity, int* colptr,
+                                 int* cursor_scratch, int* csc_row, int* csc_src, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(B >= 0 && V > 0 && nnz_capacity >= 0, "sizes");
+  GF_CUDA_CHECK(cudaMemsetAsync(colptr, 0, sizeof(int) * (size_t)(V + 1), st));
+  GF_CUDA_CHECK(cudaMemsetAsync(cursor_scratch, 0, sizeof(int) * (size_t)V, st));
+  if (nnz_capacity > 0) {
+    gf::csc_hist_dyn_kernel<<<(nnz_capacity + 255) / 256, 256, 0, st>>>(indptr, B, indices, colptr);
+    GF_LAUNCHED();
+  }
+  scan_kernel<<<1, 1024, 0, st>>>(colptr, V + 1);
+  GF_LAUNCHED();
+  if (nnz_capacity > 0) {
+    csc_scatter_kernel<<<(B * 32 + 255) / 256, 256, 0, st>>>(indptr, indices, B, colptr, cursor_scratch, csc_row, csc_src);
+    GF_LAUNCHED();
+  }
+  return GF_OK;
+}
+
 extern "C" int gf_dec_sparse_doc(const GfDecSparseArgs* a, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(a->Kp <= kMaxKp && a->Kp % 16 == 0, "Kp");

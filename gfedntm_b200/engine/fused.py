@@ -193,6 +193,12 @@ class FusedEngine:
             self.gnnz = torch.zeros(max(max_nnz, 1), **f32)
             self.rl = torch.zeros(B, **f32)
             self.dtheta_lda = torch.zeros(B, self.Kp, **f32)
+        # device-side counters (forward passes, optimiser steps): seeds / Adam bias correction / the
+        # federated epoch flag are derived from them on the device, so a captured step can be replayed
+        self.ctr = torch.zeros(2, dtype=torch.int64, device=dev)
+        self._graphs = {}
+        self._warm = set()
+        self.use_graphs = True
         self._nbt_pending = 0
         self.model.register_state_dict_pre_hook(lambda *a, **k: self.flush_counters())
         self.sync_shadows()
@@ -204,6 +210,11 @@ class FusedEngine:
                        self.model.beta_batchnorm):
                 bn.num_batches_tracked += self._nbt_pending
             self._nbt_pending = 0
+
+    def set_step_count(self, n: int) -> None:
+        """Optimiser step counter (host mirror + device counter used by the Adam kernels)."""
+        self.step_count = int(n)
+        self.ctr[1] = int(n)
 
     # ------------------------------------------------------------------------------------------
     # parameter access helpers
@@ -261,13 +272,13 @@ class FusedEngine:
         if B > self.max_batch or batch.nnz > self.max_nnz:
             raise ValueError("minibatch exceeds the engine workspace (max_batch / max_nnz)")
         grad = need_grad and training
-        seed = (self.seed * 0x9E3779B97F4A7C15 + self.rng_calls * 0xD1B54A32D192ED03 + 1) & ((1 << 64) - 1)
-        self.rng_calls += 1
+        seed = (self.seed * 0x9E3779B97F4A7C15 + 1) & ((1 << 64) - 1)
+        K_.step_begin(self.ctr, 1, 0)
         self.zpool.zero_()
         self.dpool.zero_()
         if grad:
             self.flat.G[:self.flat.small_end].zero_()
-            self.csc.build(batch)
+            self.csc.build(batch, dynamic_nnz=True)
 
         W1T, b1, xdense, WdT = self._first_layer(x_ctx)
         Wh, bh = self._hidden_params(self.flat.P)
@@ -280,7 +291,7 @@ class FusedEngine:
                    Wsig=self._p("inf_net.f_sigma.weight"), bsig=self._p("inf_net.f_sigma.bias"),
                    pre=self.pre + pad, enc_drop_p=self.enc_drop, mask_enc_in=mask_enc_in,
                    mask_enc=self.mask_enc, mu_pre=self.mu_pre, ls_pre=self.ls_pre,
-                   bn_sums=self.bn_sums if training else None, seed=seed)
+                   bn_sums=self.bn_sums if training else None, seed=seed, step_ctr=self.ctr)
         mu_rm, mu_rv, mu_nbt = self._bn("f_mu_batchnorm")
         ls_rm, ls_rv, ls_nbt = self._bn("f_sigma_batchnorm")
         K_.latent_fwd(B=B, K=K, training=training, sample=sample, mu_pre=self.mu_pre, ls_pre=self.ls_pre,
@@ -290,9 +301,9 @@ class FusedEngine:
                       theta_drop_p=self.theta_drop, mu=self.mu, logvar=self.logvar, eps=self.eps,
                       theta_s=self.theta_s, mask_theta=self.mask_theta, theta=self.theta,
                       theta_colsum=self.theta_colsum, kl=self.kl, loss=self.loss,
-                      kl_weight=self.kl_weight, seed=seed)
+                      kl_weight=self.kl_weight, seed=seed, step_ctr=self.ctr)
         bbn = self.model.beta_batchnorm
-        if training:
+        if training and not torch.cuda.is_current_stream_capturing():
             self._nbt_pending += 1  # BatchNorm step counters are flushed lazily (state_dict hook)
 
         if self.is_prod:
@@ -341,7 +352,7 @@ class FusedEngine:
                    dWmu=self._g("inf_net.f_mu.weight"), dbmu=self._g("inf_net.f_mu.bias"),
                    dWsig=self._g("inf_net.f_sigma.weight"), dbsig=self._g("inf_net.f_sigma.bias"),
                    db1=self._g("inf_net.input_layer.bias"), dpre0=self.dpre0, xdense=xdense, dWdT=dWdT,
-                   seed=seed)
+                   seed=seed, step_ctr=self.ctr)
         if use_bow:
             # d W1a^T[v,:] = sum_b x[b,v] * dpre0[b,:]  (all V rows written, zeros for unused words)
             K_.csc_spmm(self.csc.colptr, self.csc.row, self.csc.src, batch.counts, self.dpre0, gst[:V],
@@ -362,27 +373,59 @@ class FusedEngine:
     # ------------------------------------------------------------------------------------------
     def optimizer_step(self, gscale: float = 1.0) -> None:
         """Fused Adam over the flat buffers; refreshes the bf16 shadows of beta."""
-        self.step_count += 1
+        if not torch.cuda.is_current_stream_capturing():
+            self.step_count += 1
+        K_.step_begin(self.ctr, 0, 1)
         fl = self.flat
         b1, b2 = self.betas
         end = fl.beta_off
         K_.adam_flat(fl.P[:end], fl.G[:end], fl.M[:end], fl.V2[:end], lr=self.lr, b1=b1, b2=b2,
-                     eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale)
+                     eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
+                     step_ctr=self.ctr)
         K, V = self.K, self.V
         if self.is_prod:
             K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"),
                          fl.view(fl.V2, "beta"), self.beta_bf, self.betaT_bf, K=K, V=V, lr=self.lr, b1=b1,
-                         b2=b2, eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale)
+                         b2=b2, eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
+                         step_ctr=self.ctr)
         else:
             s = fl.segments["beta"]
             sl = slice(s.offset, s.offset + s.numel)
             K_.adam_flat(fl.P[sl], fl.G[sl], fl.M[sl], fl.V2[sl], lr=self.lr, b1=b1, b2=b2,
-                         eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale)
+                         eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
+                         step_ctr=self.ctr)
 
     def train_step(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, **kw) -> torch.Tensor:
-        loss = self.forward_backward(batch, x_ctx, training=True, **kw)
-        self.optimizer_step()
-        return loss
+        """Forward + backward + Adam on one minibatch.  The kernel sequence is captured into a CUDA
+        graph per (input buffers, batch size) and replayed: the first call on a new key runs eagerly
+        (warm-up), the second captures, later ones replay.  Injected noise/masks force the eager path."""
+        def body():
+            self.forward_backward(batch, x_ctx, training=True, **kw)
+            self.optimizer_step()
+
+        if kw or not self.use_graphs:
+            body()
+            return self.loss
+        return self.run_graphed(("train", batch.indptr.data_ptr(), batch.indices.data_ptr(), batch.B,
+                                 x_ctx.data_ptr() if x_ctx is not None else 0), body)
+
+    def run_graphed(self, key, body, n_opt_steps: int = 1) -> torch.Tensor:
+        """Runs ``body`` (a pure sequence of launches on static buffers) through a cached CUDA graph."""
+        graph = self._graphs.get(key)
+        if graph is None:
+            if key not in self._warm:
+                self._warm.add(key)
+                body()          # eager warm-up (this is a real step; host counters advance inside)
+                return self.loss
+            graph = torch.cuda.CUDAGraph()
+            torch.cuda.synchronize()
+            with torch.cuda.graph(graph):
+                body()          # capture only: nothing executes, host counters are left alone
+            self._graphs[key] = graph
+        graph.replay()
+        self.step_count += n_opt_steps
+        self._nbt_pending += 1
+        return self.loss
 
     # ------------------------------------------------------------------------------------------
     # inference

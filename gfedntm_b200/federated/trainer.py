@@ -84,25 +84,44 @@ class FederatedTrainer:
         self.global_step += 1
         if self.world == 1:
             return eng.train_step(bow, x_ctx)
-        if self.agg == "grad":
-            loss = eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank])
-            eng.step_count += 1
-            self._launch("grad", eng.step_count)
-        else:
-            loss = eng.forward_backward(bow, x_ctx, training=True)
-            eng.optimizer_step()
-            self._launch("param", eng.step_count)
+        from ..ops import kernels as K_
+
+        def body():
+            if self.agg == "grad":
+                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank])
+                K_.step_begin(eng.ctr, 0, 1)
+                self._launch("grad", eng.step_count + 1)
+            else:
+                eng.forward_backward(bow, x_ctx, training=True)
+                eng.optimizer_step()
+                self._launch("param", eng.step_count)
+
+        if not eng.use_graphs:
+            body()
+            if self.agg == "grad":
+                eng.step_count += 1
+            return eng.loss
+        key = ("fed", self.agg, bow.indptr.data_ptr(), bow.indices.data_ptr(), bow.B,
+               x_ctx.data_ptr() if x_ctx is not None else 0)
+        eager_warmup = key not in eng._warm
+        loss = eng.run_graphed(key, body, n_opt_steps=1)
+        if eager_warmup and self.agg == "grad":
+            eng.step_count += 1  # (agg="param": optimizer_step() advanced the host mirror itself)
         return loss
 
     def _launch(self, mode: str, step: int) -> None:
-        s = torch.cuda.Event(enable_timing=True)
-        e = torch.cuda.Event(enable_timing=True)
-        s.record()
-        self.aggregator.launch(mode=mode, step=step)
-        e.record()
-        self._agg_events.append((s, e))
-        if len(self._agg_events) > 256:
-            self._agg_events = self._agg_events[-128:]
+        eng = self.model.engine
+        capturing = torch.cuda.is_current_stream_capturing()
+        if not capturing:
+            s = torch.cuda.Event(enable_timing=True)
+            e = torch.cuda.Event(enable_timing=True)
+            s.record()
+        self.aggregator.launch(mode=mode, step=step, step_ctr=eng.ctr)
+        if not capturing:
+            e.record()
+            self._agg_events.append((s, e))
+            if len(self._agg_events) > 256:
+                self._agg_events = self._agg_events[-128:]
 
     def last_aggregation_us(self) -> Optional[float]:
         """Mean device time of the aggregation kernel over the recorded steps (needs a prior sync)."""

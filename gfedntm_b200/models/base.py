@@ -205,7 +205,8 @@ class NeuralTopicModel:
         if old is not None:  # keep optimiser state across a workspace re-allocation
             self.engine.flat.M.copy_(old.flat.M)
             self.engine.flat.V2.copy_(old.flat.V2)
-            self.engine.step_count = old.step_count
+            self.engine.set_step_count(old.step_count)
+            self.engine.ctr[0] = old.ctr[0]
             self.engine.rng_calls = old.rng_calls
         self._apply_pending_opt_state()
 
@@ -220,7 +221,7 @@ class NeuralTopicModel:
             eng.flat.view(eng.flat.M, name).copy_(torch.as_tensor(st["exp_avg"]).to(eng.device))
             eng.flat.view(eng.flat.V2, name).copy_(torch.as_tensor(st["exp_avg_sq"]).to(eng.device))
             step = max(step, int(float(torch.as_tensor(st["step"]).reshape(-1)[0])))
-        eng.step_count = step
+        eng.set_step_count(step)
         self._pending_opt_state = None
 
     def make_loader(self, dataset, shuffle: bool, batch_size: Optional[int] = None) -> CsrMinibatchLoader:

@@ -48,6 +48,7 @@ class GfEncArgs(C.Structure):
         ("mu_pre", _p), ("ls_pre", _p),
         ("bn_sums", _p),
         ("seed", _u64),
+        ("step_ctr", _p),
     ]
 
 
@@ -64,6 +65,7 @@ class GfLatentArgs(C.Structure):
         ("theta_colsum", _p), ("kl", _p), ("loss", _p),
         ("kl_weight", _f),
         ("seed", _u64),
+        ("step_ctr", _p),
     ]
 
 
@@ -93,6 +95,7 @@ class GfEncBwdArgs(C.Structure):
         ("dpre0", _p),
         ("xdense", _p), ("C", _i), ("dWdT", _p),
         ("seed", _u64),
+        ("step_ctr", _p),
     ]
 
 
@@ -128,6 +131,7 @@ class GfFedArgs(C.Structure):
         ("w", _f * GF_MAX_RANKS),
         ("lr", _f), ("b1", _f), ("b2", _f), ("eps", _f), ("wd", _f),
         ("step", _i),
+        ("step_ctr", _p),
         ("ranks", GfFabricRank * GF_MAX_RANKS),
     ]
 
@@ -158,6 +162,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_latent_bwd.argtypes = [C.POINTER(GfLatentBwdArgs), _p]
     lib.gf_enc_bwd.argtypes = [C.POINTER(GfEncBwdArgs), _p]
     lib.gf_csr_to_csc.argtypes = [_p, _p, _i, _i, _i, _p, _p, _p, _p, _p]
+    lib.gf_step_begin.argtypes = [_p, _i, _i, _p]
+    lib.gf_step_begin.restype = _i
+    lib.gf_csr_to_csc_dyn.argtypes = [_p, _p, _i, _i, _i, _p, _p, _p, _p, _p]
+    lib.gf_csr_to_csc_dyn.restype = _i
     lib.gf_csr_to_csc_static.argtypes = [_p, _p, _i, _i, _i, _p, _p, _p, _p]
     lib.gf_csr_to_csc_static.restype = _i
     lib.gf_dec_sparse_doc.argtypes = [C.POINTER(GfDecSparseArgs), _p]
@@ -167,9 +175,9 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_lda_doc.argtypes = [_p, _p, _p, _p, _p, _i, _i, _i, _f, _p, _p, _p, _i, _p, _p]
     lib.gf_lda_beta_bwd.argtypes = [_p, _p, _i, _p, _p, _p, _p, _i, _i, _i, _i, _p]
     lib.gf_row_topk.argtypes = [_p, _i, _i, _i, _i, _p, _p, _p]
-    lib.gf_adam_flat.argtypes = [_p, _p, _p, _p, ll, _f, _f, _f, _f, _f, _i, _f, _p]
+    lib.gf_adam_flat.argtypes = [_p, _p, _p, _p, ll, _f, _f, _f, _f, _f, _i, _f, _p, _p]
     lib.gf_adam_beta.argtypes = [_p, _p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i,
-                                 _f, _f, _f, _f, _f, _i, _f, _i, _p]
+                                 _f, _f, _f, _f, _f, _i, _f, _i, _p, _p]
     lib.gf_fed_aggregate.argtypes = [C.POINTER(GfFedArgs), _p]
     lib.gf_fed_aggregate.restype = _i
     lib.gf_host_gather_csr.argtypes = [_p, _p, _p, _p, _i, _p, _p, _p, ll, _i]

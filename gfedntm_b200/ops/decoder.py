@@ -67,10 +67,11 @@ class CscWorkspace:
         self.row = torch.zeros(max(max_nnz, 1), dtype=torch.int32, device=device)
         self.src = torch.zeros(max(max_nnz, 1), dtype=torch.int32, device=device)
 
-    def build(self, batch: CsrBatch) -> None:
+    def build(self, batch: CsrBatch, dynamic_nnz: bool = False) -> None:
         assert batch.nnz <= self.row.numel(), "CSC workspace too small for this minibatch"
-        K_.csr_to_csc(batch.indptr, batch.indices, B=batch.B, V=self.V, nnz=batch.nnz,
-                      colptr=self.colptr, cursor=self.cursor, csc_row=self.row, csc_src=self.src)
+        nnz = self.row.numel() if dynamic_nnz else batch.nnz
+        K_.csr_to_csc(batch.indptr, batch.indices, B=batch.B, V=self.V, nnz=nnz, colptr=self.colptr,
+                      cursor=self.cursor, csc_row=self.row, csc_src=self.src, dynamic_nnz=dynamic_nnz)
 
 
 class ProdLDADecoder:

@@ -90,7 +90,7 @@ def _fill_ptr_array(arr, tensors: Sequence[Optional[torch.Tensor]]) -> None:
 
 def enc_fwd(*, B: int, V: int, K: int, hidden: Sequence[int], act: int, training: bool,
             indptr, indices, counts, W1T, b1, xdense, WdT, Wh, bh, Wmu, bmu, Wsig, bsig, pre,
-            enc_drop_p: float, mask_enc_in, mask_enc, mu_pre, ls_pre, bn_sums, seed: int) -> None:
+            enc_drop_p: float, mask_enc_in, mask_enc, mu_pre, ls_pre, bn_sums, seed: int, step_ctr=None) -> None:
     lib = _lib.load()
     a = GfEncArgs()
     a.B, a.V, a.K, a.L = B, V, K, len(hidden)
@@ -108,13 +108,14 @@ def enc_fwd(*, B: int, V: int, K: int, hidden: Sequence[int], act: int, training
     a.mask_enc_in, a.mask_enc = _ptr(mask_enc_in), _ptr(mask_enc)
     a.mu_pre, a.ls_pre, a.bn_sums = _ptr(mu_pre), _ptr(ls_pre), _ptr(bn_sums)
     a.seed = seed & 0xFFFFFFFFFFFFFFFF
+    a.step_ctr = _ptr(step_ctr)
     check(lib.gf_enc_fwd(C.byref(a), _stream()), "gf_enc_fwd")
 
 
 def latent_fwd(*, B: int, K: int, training: bool, sample: bool, mu_pre, ls_pre, bn_sums, mu_rm,
                mu_rv, ls_rm, ls_rv, bn_eps: float, bn_momentum: float, prior_mean, prior_var, eps_in,
                mask_theta_in, theta_drop_p: float, mu, logvar, eps, theta_s, mask_theta, theta,
-               theta_colsum, kl, loss, kl_weight: float, seed: int) -> None:
+               theta_colsum, kl, loss, kl_weight: float, seed: int, step_ctr=None) -> None:
     lib = _lib.load()
     a = GfLatentArgs()
     a.B, a.K, a.training, a.sample = B, K, int(training), int(sample)
@@ -127,6 +128,7 @@ def latent_fwd(*, B: int, K: int, training: bool, sample: bool, mu_pre, ls_pre, 
     a.mask_theta, a.theta = _ptr(mask_theta), _ptr(theta)
     a.theta_colsum, a.kl, a.loss, a.kl_weight = _ptr(theta_colsum), _ptr(kl), _ptr(loss), kl_weight
     a.seed = seed & 0xFFFFFFFFFFFFFFFF
+    a.step_ctr = _ptr(step_ctr)
     check(lib.gf_latent_fwd(C.byref(a), _stream()), "gf_latent_fwd")
 
 
@@ -155,7 +157,7 @@ def latent_bwd(*, B: int, K: int, dtheta, mask_theta, theta_s, mu, logvar, eps, 
 
 def enc_bwd(*, B: int, V: int, K: int, hidden: Sequence[int], act: int, dmu, dlv, mu, logvar,
             bn_sums, bn_bsums, bn_eps: float, pre, mask_enc, Wh, Wmu, Wsig, dWh, dbh, dWmu, dbmu,
-            dWsig, dbsig, db1, dpre0, xdense, dWdT, seed: int) -> None:
+            dWsig, dbsig, db1, dpre0, xdense, dWdT, seed: int, step_ctr=None) -> None:
     lib = _lib.load()
     a = GfEncBwdArgs()
     a.B, a.V, a.K, a.L = B, V, K, len(hidden)
@@ -174,16 +176,26 @@ def enc_bwd(*, B: int, V: int, K: int, hidden: Sequence[int], act: int, dmu, dlv
     a.dpre0 = _ptr(dpre0)
     a.xdense, a.C, a.dWdT = _ptr(xdense), (xdense.shape[1] if xdense is not None else 0), _ptr(dWdT)
     a.seed = seed & 0xFFFFFFFFFFFFFFFF
+    a.step_ctr = _ptr(step_ctr)
     check(lib.gf_enc_bwd(C.byref(a), _stream()), "gf_enc_bwd")
 
 
 # ----------------------------------------------------------------------------------------------
 # sparse side
 # ----------------------------------------------------------------------------------------------
-def csr_to_csc(indptr, indices, *, B: int, V: int, nnz: int, colptr, cursor, csc_row, csc_src) -> None:
+def csr_to_csc(indptr, indices, *, B: int, V: int, nnz: int, colptr, cursor, csc_row, csc_src,
+               dynamic_nnz: bool = False) -> None:
+    """``dynamic_nnz``: ``nnz`` is only a capacity; the real count is read from ``indptr[B]`` on the device
+    (needed when the launch is replayed from a CUDA graph on other minibatches)."""
     lib = _lib.load()
-    check(lib.gf_csr_to_csc(_ptr(indptr), _ptr(indices), B, V, nnz, _ptr(colptr), _ptr(cursor),
-                            _ptr(csc_row), _ptr(csc_src), _stream()), "gf_csr_to_csc")
+    fn = lib.gf_csr_to_csc_dyn if dynamic_nnz else lib.gf_csr_to_csc
+    check(fn(_ptr(indptr), _ptr(indices), B, V, nnz, _ptr(colptr), _ptr(cursor), _ptr(csc_row), _ptr(csc_src),
+             _stream()), "gf_csr_to_csc")
+
+
+def step_begin(ctr: torch.Tensor, inc_rng: int = 1, inc_opt: int = 0) -> None:
+    lib = _lib.load()
+    check(lib.gf_step_begin(_ptr(ctr), inc_rng, inc_opt, _stream()), "gf_step_begin")
 
 
 def dec_sparse_doc(*, B: int, n_chunks: int, indptr, indices, counts, theta_bf, betaT_bf, colc,
@@ -252,19 +264,19 @@ def row_topk(mat: torch.Tensor, k: int):
 # optimiser
 # ----------------------------------------------------------------------------------------------
 def adam_flat(p, g, m, v, *, lr: float, b1: float, b2: float, eps: float, wd: float, step: int,
-              gscale: float = 1.0) -> None:
+              gscale: float = 1.0, step_ctr=None) -> None:
     lib = _lib.load()
     n = p.numel()
     assert g.numel() == n and m.numel() == n and v.numel() == n
     check(lib.gf_adam_flat(_ptr(p), _ptr(g), _ptr(m), _ptr(v), n, lr, b1, b2, eps, wd, step, gscale,
-                           _stream()), "gf_adam_flat")
+                           _ptr(step_ctr), _stream()), "gf_adam_flat")
 
 
 def adam_beta(p, g, m, v, beta_bf, betaT_bf, *, K: int, V: int, lr: float = 0.0, b1: float = 0.9,
               b2: float = 0.999, eps: float = 1e-8, wd: float = 0.0, step: int = 1, gscale: float = 1.0,
-              do_update: bool = True) -> None:
+              do_update: bool = True, step_ctr=None) -> None:
     lib = _lib.load()
     check(lib.gf_adam_beta(_ptr(p), _ptr(g), _ptr(m), _ptr(v), K, V, p.stride(0),
                            (g.stride(0) if g is not None else 0), _ptr(beta_bf), beta_bf.stride(0),
                            _ptr(betaT_bf), betaT_bf.shape[1], lr, b1, b2, eps, wd, step, gscale,
-                           int(do_update), _stream()), "gf_adam_beta")
+                           int(do_update), _ptr(step_ctr), _stream()), "gf_adam_beta")

@@ -177,13 +177,16 @@ class FusedAggregator:
     def set_lr(self, lr: float, betas) -> None:
         self.args.lr, self.args.b1, self.args.b2 = lr, betas[0], betas[1]
 
-    def launch(self, *, mode: str, step: int) -> None:
+    def launch(self, *, mode: str, step: int, step_ctr=None) -> None:
         """``mode``: 'grad' (weighted gradients + global sharded Adam) or 'param' (weighted mean of the
-        parameters).  Every rank must call this once per global step."""
+        parameters).  Every rank must call this once per global step.  With ``step_ctr`` (device counters
+        of the engine) the epoch flag and the Adam step are read on the device, so the launch can be
+        replayed from a CUDA graph."""
         self.epoch += 1
         a = self.args
         a.mode = 0 if mode == "grad" else 1
         a.epoch = self.epoch
         a.step = step
+        a.step_ctr = step_ctr.data_ptr() if step_ctr is not None else None
         lib = _lib.load()
         check(lib.gf_fed_aggregate(C.byref(a), torch.cuda.current_stream().cuda_stream), "gf_fed_aggregate")

@@ -105,7 +105,12 @@ typedef struct GfEncArgs {
   float* mu_pre; float* ls_pre; /* out: [B,K] head outputs before BatchNorm                   */
   double* bn_sums;           /* out (+=): [4K] sum mu, sum mu^2, sum ls, sum ls^2 (zeroed by caller) */
   unsigned long long seed;
+  const long long* step_ctr; /* optional device counters (gf_step_begin): seed advances by ctr[0]    */
 } GfEncArgs;
+/* Device-side step counters, so that a whole training step can be replayed from a CUDA graph:
+ * ctr[0] counts forward passes (advances the dropout / reparameterisation seeds), ctr[1] counts
+ * optimiser steps (Adam bias correction, federated epoch flag).                                  */
+int gf_step_begin(long long* ctr, int inc_rng, int inc_opt, void* stream);
 int gf_enc_fwd(const GfEncArgs* args, void* stream);
 
 typedef struct GfLatentArgs {
@@ -123,6 +128,7 @@ typedef struct GfLatentArgs {
   double* loss;                 /* (+=) scalar, may be null                                   */
   float kl_weight;
   unsigned long long seed;
+  const long long* step_ctr;
 } GfLatentArgs;
 int gf_latent_fwd(const GfLatentArgs* args, void* stream);
 
@@ -157,6 +163,7 @@ typedef struct GfEncBwdArgs {
   float* dpre0;              /* out: [B,H0] gradient w.r.t. first pre-activation              */
   const float* xdense; int C; float* dWdT; /* CTM dense input: (+=) [C,H0]                     */
   unsigned long long seed;
+  const long long* step_ctr;
 } GfEncBwdArgs;
 int gf_enc_bwd(const GfEncBwdArgs* args, void* stream);
 
@@ -167,6 +174,10 @@ int gf_enc_bwd(const GfEncBwdArgs* args, void* stream);
  * scratch owned by the caller.  Ref: client.py:461-462 builds a dense [n_docs,V] array instead. */
 int gf_csr_to_csc(const int* indptr, const int* indices, int B, int V, int nnz, int* colptr,
                   int* cursor_scratch, int* csc_row, int* csc_src, void* stream);
+/* Same, with the number of non-zeros read on the device (indptr[B]); `nnz_capacity` only sizes the
+ * launch.  Lets a captured CUDA graph be replayed on minibatches with different nnz.            */
+int gf_csr_to_csc_dyn(const int* indptr, const int* indices, int B, int V, int nnz_capacity, int* colptr,
+                      int* cursor_scratch, int* csc_row, int* csc_src, void* stream);
 
 /* Same transpose, for callers that cannot allocate device memory (a host whose own pool already owns
  * the whole device, or a latency-critical loop where cudaMalloc/cudaFree would stall every stream).
@@ -225,13 +236,15 @@ int gf_row_topk(const float* mat, int ld, int rows, int V, int topk, int* out_id
 /* ------------------------------------------------------------------------------------------
  * Optimiser.  Ref: torch.optim.Adam in avitm.py:141-143 / federated_avitm.py:78.
  * ---------------------------------------------------------------------------------------- */
+/* `step_ctr` (optional, device): when non-null the step number is read from step_ctr[1] on the
+ * device instead of the `step` argument.                                                        */
 int gf_adam_flat(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
-                 float eps, float wd, int step, float gscale, void* stream);
+                 float eps, float wd, int step, float gscale, const long long* step_ctr, void* stream);
 /* Adam on beta [K,ldp] plus the bf16 operand shadows beta_bf [Kp,ldb] and betaT_bf [V,Kp];
  * do_update = 0 only refreshes the shadows.                                                  */
 int gf_adam_beta(float* p, const float* g, float* m, float* v, int K, int V, int ldp, int ldg,
                  void* beta_bf, int ldb, void* betaT_bf, int Kp, float lr, float b1, float b2, float eps,
-                 float wd, int step, float gscale, int do_update, void* stream);
+                 float wd, int step, float gscale, int do_update, const long long* step_ctr, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused federated aggregation over NVLink peer memory (no NCCL on this path).
@@ -264,6 +277,7 @@ typedef struct GfFedArgs {
   float w[GF_MAX_RANKS];          /* client weights n_c / sum n                                 */
   float lr, b1, b2, eps, wd;
   int step;                       /* Adam step count (>= 1) for the bias correction             */
+  const long long* step_ctr;      /* optional device counters: epoch = step = step_ctr[1]       */
   GfFabricRank ranks[GF_MAX_RANKS];
 } GfFedArgs;
 

@@ -16,6 +16,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 def main():
     from gfedntm_b200.federated.trainer import FederatedTrainer
     from gfedntm_b200.models import AVITM, BOWDataset
+    from gfedntm_b200.ops import kernels as Kx
 
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -54,6 +55,7 @@ def main():
             g = {n: eng.flat.view(eng.flat.G, n).detach().clone().contiguous() for n in names}
             s_local = eng.flat.S.detach().clone() * tr.weights[rank]
             eng.step_count += 1
+            Kx.step_begin(eng.ctr, 0, 1)
             tr._launch("grad", eng.step_count)
             for n in names:
                 dist.all_reduce(g[n])
