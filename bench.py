@@ -185,7 +185,8 @@ def run_ours(args, cfg: dict) -> dict:
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    launches0 = lib.gf_launch_count()
+    eng = model.engine
+    launches0 = lib.gf_launch_count() + eng.replayed_launches
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     if flush is None:
@@ -201,7 +202,7 @@ def run_ours(args, cfg: dict) -> dict:
     if flush is None:
         ends[-1].record()
     barrier()
-    launches = lib.gf_launch_count() - launches0
+    launches = lib.gf_launch_count() + eng.replayed_launches - launches0
     if flush is None:
         ms = starts[0].elapsed_time(ends[-1])
     else:

@@ -81,15 +81,32 @@ enc_fwd_kernel(const GfEncArgs a_) {
       acc[c] = (j < H0) ? a.b1[j] : 0.f;
     }
     if (a.indptr != nullptr) {
+      // 32 non-zeros per round: every lane fetches one (word, count) pair, then the warp walks them
+      // with the row gathers of 8 words in flight at a time (independent loads, no serial chain)
       const int e0 = a.indptr[b], e1 = a.indptr[b + 1];
-      for (int e = e0; e < e1; ++e) {
-        const int v = a.indices[e];
-        const float x = a.counts[e];
-        const float* wr = a.W1T + (size_t)v * H0;
+      for (int base = e0; base < e1; base += 32) {
+        const int e = base + lane;
+        const int v_l = (e < e1) ? a.indices[e] : 0;
+        const float x_l = (e < e1) ? a.counts[e] : 0.f;
+        const int n = min(32, e1 - base);
+        for (int i0 = 0; i0 < n; i0 += 8) {
+          float w[8][kMaxH / 32];
+          float xs[8];
 #pragma unroll
-        for (int c = 0; c < kMaxH / 32; ++c) {
-          const int j = c * 32 + lane;
-          if (j < H0) acc[c] = fmaf(x, __ldg(wr + j), acc[c]);
+          for (int u = 0; u < 8; ++u) {
+            const int vi = __shfl_sync(0xffffffffu, v_l, (i0 + u) & 31);
+            xs[u] = (i0 + u < n) ? __shfl_sync(0xffffffffu, x_l, (i0 + u) & 31) : 0.f;
+            const float* wr = a.W1T + (size_t)vi * H0;
+#pragma unroll
+            for (int c = 0; c < kMaxH / 32; ++c) {
+              const int j = c * 32 + lane;
+              w[u][c] = (j < H0) ? __ldg(wr + j) : 0.f;
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+#pragma unroll
+            for (int c = 0; c < kMaxH / 32; ++c) acc[c] = fmaf(xs[u], w[u][c], acc[c]);
         }
       }
     }

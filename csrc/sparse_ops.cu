@@ -111,45 +111,69 @@ __global__ void __launch_bounds__(256) dec_sparse_doc_kernel(const GfDecSparseAr
   ssum = warp_sum(ssum);
   const float lse2 = m + log2f(ssum);
 
-  float th[kMaxKp / 32], dth[kMaxKp / 32];
+  // theta_c row of this document in shared memory (read by every lane in phase 1)
+  __shared__ float th_s[8][kMaxKp];
+  const int wslot = threadIdx.x >> 5;
+  for (int k = lane; k < Kp; k += 32) th_s[wslot][k] = __bfloat162float(theta_bf[(size_t)b * a.ld_theta + k]);
+  __syncwarp();
+  float dth[kMaxKp / 32];
 #pragma unroll
-  for (int c = 0; c < kMaxKp / 32; ++c) {
-    const int k = c * 32 + lane;
-    th[c] = (k < Kp) ? __bfloat162float(theta_bf[(size_t)b * a.ld_theta + k]) : 0.f;
-    dth[c] = 0.f;
-  }
+  for (int c = 0; c < kMaxKp / 32; ++c) dth[c] = 0.f;
   float rl = 0.f, S = 0.f;
   const int e0 = a.indptr[b], e1 = a.indptr[b + 1];
-  for (int e = e0; e < e1; ++e) {
-    const int v = a.indices[e];
-    const float x = a.counts[e];
-    const __nv_bfloat16* br = betaT_bf + (size_t)v * Kp;
-    float bv[kMaxKp / 32];
+  for (int base = e0; base < e1; base += 32) {
+    // ---- phase 1: one non-zero per lane (32 independent row gathers in flight)
+    const int e = base + lane;
+    const bool valid = e < e1;
+    const int v = valid ? a.indices[e] : 0;
+    const float x = valid ? a.counts[e] : 0.f;
+    const uint4* br = reinterpret_cast<const uint4*>(betaT_bf + (size_t)v * Kp);
     float dot = 0.f;
+    for (int k8 = 0; k8 < (Kp >> 3); ++k8) {
+      const uint4 q = __ldg(br + k8);
+      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
+      const float* t = &th_s[wslot][k8 * 8];
 #pragma unroll
-    for (int c = 0; c < kMaxKp / 32; ++c) {
-      const int k = c * 32 + lane;
-      bv[c] = (k < Kp) ? __bfloat162float(br[k]) : 0.f;
-      dot = fmaf(th[c], bv[c], dot);
+      for (int u = 0; u < 4; ++u) {
+        const float2 f = __bfloat1622float2(h2[u]);
+        dot = fmaf(t[2 * u], f.x, dot);
+        dot = fmaf(t[2 * u + 1], f.y, dot);
+      }
     }
-    dot = warp_sum(dot);
     const float4 cc = colc[v];
     const float t2 = fmaf(dot, cc.x, cc.y);
     const float p = exp2f(t2 - lse2);
     const float y = t2 * kLn2_s;
     const float rstd = cc.x * kLn2_s;
-    rl -= x * __logf(p + 1e-10f);
-    const float t = a.gscale * x * p / (p + 1e-10f);
-    S += t;
-    if (lane == 0 && a.asp != nullptr) {
-      atomicAdd(&a.asp[v], t);
-      atomicAdd(&a.csp[v], t * y);
-      a.tnnz[e] = rstd * t;
+    float w = 0.f;
+    if (valid) {
+      rl -= x * __logf(p + 1e-10f);
+      const float t = a.gscale * x * p / (p + 1e-10f);
+      S += t;
+      w = rstd * t;
+      if (a.asp != nullptr) {
+        atomicAdd(&a.asp[v], t);
+        atomicAdd(&a.csp[v], t * y);
+        a.tnnz[e] = w;
+      }
     }
-    const float w = rstd * t;
+    // ---- phase 2: d theta[b,:] -= sum_e w_e * beta[:, v_e]   (lanes over topics, rows now cached)
+    if (a.dtheta != nullptr) {
+      const int n = min(32, e1 - base);
+      for (int i = 0; i < n; ++i) {
+        const int vi = __shfl_sync(0xffffffffu, v, i);
+        const float wi = __shfl_sync(0xffffffffu, w, i);
+        const __nv_bfloat16* bri = betaT_bf + (size_t)vi * Kp;
 #pragma unroll
-    for (int c = 0; c < kMaxKp / 32; ++c) dth[c] = fmaf(-w, bv[c], dth[c]);
+        for (int c = 0; c < kMaxKp / 32; ++c) {
+          const int k = c * 32 + lane;
+          if (k < Kp) dth[c] = fmaf(-wi, __bfloat162float(bri[k]), dth[c]);
+        }
+      }
+    }
   }
+  rl = warp_sum(rl);
+  S = warp_sum(S);
   if (a.dtheta != nullptr) {
 #pragma unroll
     for (int c = 0; c < kMaxKp / 32; ++c) {

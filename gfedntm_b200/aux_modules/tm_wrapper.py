@@ -1,0 +1,112 @@
+"""In-process topic-model wrapper: preprocessing, centralized training and evaluation.
+
+Ref: src/aux_modules/tmWrapper/tm_wrapper.py:1-400.  The reference shells out to the vendored
+IntelComp ``topicmodeler`` (Dask/Spark preprocessing, Mallet, gensim coherence).  None of that is on the
+north-star surface or installed on the target boxes; this wrapper offers the same entry points
+(``preproc_corpus_tm``, ``train_root_model``, ``calculate_cohr_vs_ref``, ``calculate_rbo``,
+``calculate_td``) implemented with gfedntm_b200's own trainers and metrics."""
+from __future__ import annotations
+
+import json
+import logging
+import time
+from pathlib import Path
+from typing import List, Optional, Sequence
+
+import numpy as np
+import pandas as pd
+from sklearn.feature_extraction.text import CountVectorizer
+
+from ..models import AVITM, CTM, BOWDataset, CTMDataset
+from ..utils import metrics
+
+
+def load_wordlists(paths: Sequence[str]):
+    """Stop-word / equivalence lists in the reference's JSON format
+    (``{"name", "description", "valid_for", "visibility", "wordlist": [...]}``; equivalences as ``a:b``)."""
+    stop, equiv = set(), {}
+    for p in paths:
+        with open(p, encoding="utf-8") as f:
+            d = json.load(f)
+        for w in d.get("wordlist", []):
+            if d.get("valid_for") == "equivalences" or ":" in w:
+                a, _, b = w.partition(":")
+                equiv[a.strip()] = b.strip()
+            else:
+                stop.add(w.strip())
+    return stop, equiv
+
+
+class TMWrapper:
+    def __init__(self, logger: Optional[logging.Logger] = None) -> None:
+        self._logger = logger or logging.getLogger("TMWrapper")
+
+    # -- preprocessing ---------------------------------------------------------------------------
+    def preproc_corpus_tm(self, df: pd.DataFrame, text_col: str = "lemmas", stw_files: Sequence[str] = (),
+                          eq_files: Sequence[str] = (), min_lemas: int = 3, no_below: int = 1,
+                          no_above: float = 1.0, keep_n: int = 100000, out_path: Optional[str] = None
+                          ) -> pd.DataFrame:
+        """Stop-word removal, equivalence replacement, minimum-length filter and vocabulary pruning
+        (``no_below`` / ``no_above`` / ``keep_n`` as in gensim's ``filter_extremes``).  Returns a frame with
+        ``id``, ``bow_text`` (+ ``embeddings`` / ``fos`` when present) and optionally writes parquet."""
+        stop, equiv = load_wordlists(list(stw_files) + list(eq_files))
+        docs = []
+        for text in df[text_col].astype(str):
+            toks = [equiv.get(t, t) for t in text.split()]
+            docs.append([t for t in toks if t not in stop])
+        cv = CountVectorizer(tokenizer=lambda s: s.split(), lowercase=False, token_pattern=None,
+                             min_df=no_below, max_df=no_above, max_features=keep_n)
+        cv.fit([" ".join(d) for d in docs])
+        vocab = set(cv.vocabulary_)
+        docs = [[t for t in d if t in vocab] for d in docs]
+        keep = [len(d) >= min_lemas for d in docs]
+        out = pd.DataFrame({"id": df["id"].values if "id" in df else np.arange(len(df)),
+                            "bow_text": [" ".join(d) for d in docs]})
+        for col in ("embeddings", "fos", "fieldsOfStudy"):
+            if col in df:
+                out[col if col != "fieldsOfStudy" else "fos"] = df[col].values
+        out = out[np.asarray(keep)].reset_index(drop=True)
+        if out_path:
+            Path(out_path).parent.mkdir(parents=True, exist_ok=True)
+            out.to_parquet(out_path)
+        return out
+
+    # -- training --------------------------------------------------------------------------------
+    def train_root_model(self, corpus: Sequence[str], trainer: str = "prod", ntopics: int = 50,
+                         embeddings: Optional[np.ndarray] = None, max_features: Optional[int] = 2000,
+                         num_epochs: int = 100, **kw):
+        """Centralized training of ProdLDA / NeuralLDA ('prod' / 'lda') or CTM ('ctm' / 'zeroshot').
+        Returns ``(model, dataset, seconds)``."""
+        t0 = time.perf_counter()
+        cv = CountVectorizer(lowercase=True, stop_words="english", max_features=max_features)
+        bow = cv.fit_transform(corpus)
+        vocab = cv.get_feature_names_out()
+        if trainer in ("prod", "prodlda", "lda"):
+            ds = BOWDataset(bow, vocab)
+            m = AVITM(input_size=len(vocab), n_components=ntopics,
+                      model_type="LDA" if trainer == "lda" else "prodLDA", num_epochs=num_epochs,
+                      verbose=False, **kw)
+        else:
+            if embeddings is None:
+                raise ValueError("CTM training needs document embeddings")
+            ds = CTMDataset(embeddings, bow, vocab)
+            m = CTM(input_size=len(vocab), contextual_size=int(embeddings.shape[1]),
+                    inference_type="zeroshot" if trainer == "zeroshot" else "combined", n_components=ntopics,
+                    num_epochs=num_epochs, verbose=False, **kw)
+        m.fit(ds)
+        return m, ds, time.perf_counter() - t0
+
+    # -- evaluation ------------------------------------------------------------------------------
+    @staticmethod
+    def calculate_cohr_vs_ref(model, reference_bow, k: int = 10) -> float:
+        """NPMI coherence of the model's topics with co-occurrences counted on a reference corpus
+        (document-term matrix over the same vocabulary)."""
+        return metrics.npmi_coherence(model.get_topic_word_distribution(), reference_bow, k)
+
+    @staticmethod
+    def calculate_rbo(model, k: int = 10) -> float:
+        return metrics.inverted_rbo(model.get_topic_word_distribution(), k)
+
+    @staticmethod
+    def calculate_td(model, k: int = 25) -> float:
+        return metrics.topic_diversity(model.get_topic_word_distribution(), k)

@@ -12,6 +12,7 @@ Ref: the per-minibatch body of ``FederatedAVITM.train_mb_delta`` (federated_avit
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
@@ -197,8 +198,10 @@ class FusedEngine:
         # federated epoch flag are derived from them on the device, so a captured step can be replayed
         self.ctr = torch.zeros(2, dtype=torch.int64, device=dev)
         self._graphs = {}
+        self._graph_launches = {}
+        self.replayed_launches = 0   # kernels launched through graph replays (not seen by gf_launch_count)
         self._warm = set()
-        self.use_graphs = True
+        self.use_graphs = os.environ.get("GFEDNTM_NO_GRAPHS", "0") != "1"
         self._nbt_pending = 0
         self.model.register_state_dict_pre_hook(lambda *a, **k: self.flush_counters())
         self.sync_shadows()
@@ -417,12 +420,17 @@ class FusedEngine:
                 self._warm.add(key)
                 body()          # eager warm-up (this is a real step; host counters advance inside)
                 return self.loss
+            from ..ops import _lib
+
             graph = torch.cuda.CUDAGraph()
             torch.cuda.synchronize()
+            n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
                 body()          # capture only: nothing executes, host counters are left alone
+            self._graph_launches[key] = _lib.launch_count() - n0
             self._graphs[key] = graph
         graph.replay()
+        self.replayed_launches += self._graph_launches[key]
         self.step_count += n_opt_steps
         self._nbt_pending += 1
         return self.loss
