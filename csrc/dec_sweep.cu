@@ -22,6 +22,7 @@
 //
 // Warp roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
 // warps 4..7 = epilogue (warp w owns TMEM lanes 32*(w-4)..+31).
+#include <stdlib.h>
 #include "ptx.cuh"
 #include "tmap.h"
 #include "../include/gfedntm_kernels.h"
@@ -38,8 +39,13 @@ enum : int {
 };
 
 constexpr int kTile = 128;
+// Streamed-tile width of the gradient modes.  64 doubles the pipeline depth but measured slower
+// (per-tile hand-off overhead dominates): ROW_GRAD 949 vs 850 us, COL_GRAD 1735 vs 1478 us at V=200k.
+#ifndef GF_GRAD_BN
+#define GF_GRAD_BN 128
+#endif
 constexpr int kThreads = 256;
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 6;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -48,6 +54,7 @@ struct SweepParams {
   int B, V, K, Kp;
   int n_stat, n_stream, n_chunks, n_pass, stages;
   int p_bufs;               // 1 or 2 shared-memory P tiles (gradient modes)
+  int debug;                // profiling experiments: bit0 = epilogue skips TMEM loads/math, bit1 = skip MMA1 issue
   const float4* sb_stream;  // side band per streamed index (padded to a multiple of 128)
   // generic
   float* out;               // LOGITS modes: [B,V] fp32
@@ -106,24 +113,29 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
              const SweepParams p) {
   constexpr bool kRow = (kMode == ROW_LOGITS || kMode == ROW_LSE || kMode == ROW_GRAD);
   constexpr bool kHasMMA2 = (kMode == ROW_GRAD || kMode == COL_GRAD);
-  constexpr int kSbStages = kHasMMA2 ? 2 : kSbStagesMax;
+  // Width of a streamed tile.  The gradient modes hold every streamed tile until its MMA2 has
+  // completed, so they use 64-wide tiles: half the bytes per stage -> twice the pipeline depth.
+  constexpr int kBN = (kHasMMA2 && GF_GRAD_BN == 64) ? 64 : 128;
+  constexpr int kSbStages = kSbStagesMax;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  constexpr uint32_t kSbBytes = kTile * sizeof(float4);
+  constexpr uint32_t kSbBytes = kBN * sizeof(float4);
+  constexpr uint32_t kPBytes = kBN * 256u;          // P tile: 128 rows x kBN bf16
   const int stages = p.stages;
   const int Kp = p.Kp;
-  const uint32_t tile_bytes = (uint32_t)Kp * 256u;  // 2 boxes of Kp rows x 128 B
+  const uint32_t tile_bytes = (uint32_t)Kp * 256u;  // stationary tile: 2 boxes of Kp rows x 128 B
+  const uint32_t stile_bytes = (uint32_t)Kp * 2u * kBN;  // streamed tile: kBN/64 boxes
 
   Smem s;
   s.a = base;
   uint8_t* cur = base + tile_bytes;
   for (int i = 0; i < kMaxStages; ++i) {
     s.b[i] = cur;
-    if (i < stages) cur += tile_bytes;
+    if (i < stages) cur += stile_bytes;
   }
   s.p[0] = cur;
-  s.p[1] = cur + 32768;
-  if (kHasMMA2) cur += 32768u * p.p_bufs;  // double-buffered when it fits: epilogue(t+1) overlaps MMA2(t)
+  s.p[1] = cur + kPBytes;
+  if (kHasMMA2) cur += kPBytes * p.p_bufs;  // double-buffered when it fits: epilogue(t+1) overlaps MMA2(t)
   for (int i = 0; i < kSbStagesMax; ++i) {
     s.sb[i] = reinterpret_cast<float4*>(cur);
     if (i < kSbStages) cur += kSbBytes;
@@ -204,16 +216,16 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
             const int st = b_it % stages, sbs = b_it % kSbStages;
             mbar_wait(&s.b_empty[st], ((b_it / stages) & 1) ^ 1);
             mbar_wait(&s.sb_empty[sbs], ((b_it / kSbStages) & 1) ^ 1);
-            mbar_arrive_expect_tx(&s.b_full[st], tile_bytes);
-            tma_load_2d(s.b[st], tm_strm, &s.b_full[st], t * kTile, 0);
-            tma_load_2d(s.b[st] + blk, tm_strm, &s.b_full[st], t * kTile + 64, 0);
+            mbar_arrive_expect_tx(&s.b_full[st], stile_bytes);
+            tma_load_2d(s.b[st], tm_strm, &s.b_full[st], t * kBN, 0);
+            if (kBN == 128) tma_load_2d(s.b[st] + blk, tm_strm, &s.b_full[st], t * kBN + 64, 0);
             // side band: 128 float4 = 2 KB, plain bulk copy with its own full/empty pair (its ring
             // slot is only reused after the epilogue released it, so the parity can never alias)
             mbar_arrive_expect_tx(&s.sb_full[sbs], kSbBytes);
             asm volatile(
                 "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::
                     "r"(smem_u32(s.sb[sbs])),
-                "l"(reinterpret_cast<uint64_t>(p.sb_stream + (size_t)t * kTile)), "r"(kSbBytes),
+                "l"(reinterpret_cast<uint64_t>(p.sb_stream + (size_t)t * kBN)), "r"(kSbBytes),
                 "r"(smem_u32(&s.sb_full[sbs]))
                 : "memory");
             ++b_it;
@@ -224,7 +236,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   } else if (warp == 1) {
     // ============================ MMA issuer ============================
     if (lane == 0) {
-      const uint32_t idesc1 = umma_idesc_bf16(128, 128, 1u, 1u);
+      const uint32_t idesc1 = umma_idesc_bf16(128, kBN, 1u, 1u);
       const uint32_t idesc2 = umma_idesc_bf16(128, (uint32_t)Kp, 0u, 0u);
       const uint32_t a_base = smem_u32(s.a);
       uint32_t a_it = 0, b_it = 0, d1_it = 0, p_it = 0, d2_it = 0;
@@ -236,10 +248,10 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         const uint32_t p_base = smem_u32(s.p[pb]);
         const uint32_t b_base = smem_u32(s.b[st]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {  // 128-wide contraction = 8 k-steps of 16
+        for (int j = 0; j < kBN / 16; ++j) {  // contraction over the kBN streamed columns, 16 per step
           const uint64_t da = umma_smem_desc(p_base + (j >> 2) * 16384u + (j & 3) * 32u, 16, 1024);
           const uint64_t db = umma_smem_desc(b_base + (j >> 2) * blk + (j & 3) * 32u, 16, 1024);
-          umma_f16(tmem + 256, da, db, idesc2, (first && j == 0) ? 0u : 1u);
+          if (!(p.debug & 4)) umma_f16(tmem + 256, da, db, idesc2, (first && j == 0) ? 0u : 1u);
         }
         umma_commit(&s.p_empty[pb]);
         umma_commit(&s.b_empty[st]);
@@ -252,7 +264,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         const int t1 = (int)(((long long)(chunk + 1) * p.n_stream) / p.n_chunks);
         mbar_wait(s.a_full, a_it & 1);
         for (int pass = 0; pass < p.n_pass; ++pass) {
-          const bool m2 = kHasMMA2 && (pass == p.n_pass - 1);
+          const bool m2 = kHasMMA2 && (pass == p.n_pass - 1) && !(p.debug & 8);
           int pending = -1;
           bool first2 = true;
           if (m2) mbar_wait(s.d2_empty, (d2_it & 1) ^ 1);
@@ -262,11 +274,16 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
             const uint32_t buf = d1_it & 1;
             mbar_wait(&s.d1_empty[buf], ((d1_it >> 1) & 1) ^ 1);
             tc_fence_after();
+            // Descriptors differ between k-steps only in the start-address field (+2048 B = +128 in
+            // 16-byte units): build them once and issue from a fully unrolled, predicated loop so the
+            // issuing thread keeps the tensor pipe fed (one tcgen05.mma every ~64 cycles).
             const uint32_t b_base = smem_u32(s.b[st]);
-            for (int j = 0; j < n_ksteps; ++j) {
-              const uint64_t da = umma_smem_desc(a_base + j * 2048u, blk, 1024);
-              const uint64_t db = umma_smem_desc(b_base + j * 2048u, blk, 1024);
-              umma_f16(tmem + buf * 128, da, db, idesc1, j > 0 ? 1u : 0u);
+            const uint32_t d_addr = tmem + buf * kBN;
+#pragma unroll
+            for (int j = 0; j < 15; ++j) {
+              if (j < n_ksteps && !(p.debug & 2))
+                umma_f16(d_addr, umma_smem_desc(a_base + j * 2048u, blk, 1024),
+                         umma_smem_desc(b_base + j * 2048u, blk, 1024), idesc1, j > 0 ? 1u : 0u);
             }
             umma_commit(&s.d1_full[buf]);
             ++d1_it;
@@ -322,7 +339,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       }
 
       for (int pass = 0; pass < p.n_pass; ++pass) {
-        const bool m2 = kHasMMA2 && (pass == p.n_pass - 1);
+        const bool m2 = kHasMMA2 && (pass == p.n_pass - 1) && !(p.debug & 8);
         for (int t = t0; t < t1; ++t) {
           const int sbs = b_it % kSbStages;
           const uint32_t buf = d1_it & 1;
@@ -330,14 +347,14 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           mbar_wait(&s.d1_full[buf], (d1_it >> 1) & 1);
           tc_fence_after();
           const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;
-          uint8_t* const pbuf = s.p[pb];
+          const uint32_t pbuf = smem_u32(s.p[pb]);
           if (m2) mbar_wait(&s.p_empty[pb], (((p.p_bufs == 2) ? (p_it >> 1) : p_it) & 1) ^ 1);
-          const float4* sb = s.sb[sbs];
-          const uint32_t taddr = lane_addr + buf * 128;
+          const uint32_t sb = smem_u32(s.sb[sbs]);  // shared-space address of this tile's side band
+          const uint32_t taddr = lane_addr + buf * kBN;
 
           // consume one 32-column chunk `c` of the accumulator held in v[]
           auto process = [&](const int c, float (&v)[32]) {
-            const int col0 = t * kTile + c * 32;  // global streamed index of v[0]
+            const int col0 = t * kBN + c * 32;  // global streamed index of v[0]
             if (kMode == ROW_LOGITS) {
               if (grow < p.B) {
                 float* o = p.out + (size_t)grow * p.V + col0;
@@ -355,7 +372,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
               float cmax = -INFINITY;
 #pragma unroll
               for (int i = 0; i < 32; ++i) {
-                const float4 cc = sb[c * 32 + i];
+                const float2 cc = lds_f2(sb + (c * 32 + i) * 16);
                 v[i] = fmaf(v[i], cc.x, cc.y);
                 cmax = fmaxf(cmax, v[i]);
               }
@@ -372,8 +389,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
               uint32_t pk[16];
 #pragma unroll
               for (int i = 0; i < 32; i += 2) {
-                const float4 c0 = sb[c * 32 + i];
-                const float4 c1 = sb[c * 32 + i + 1];
+                const float4 c0 = lds_f4(sb + (c * 32 + i) * 16);
+                const float4 c1 = lds_f4(sb + (c * 32 + i + 1) * 16);
                 const float p0 = ex2_approx(fmaf(v[i], c0.x, c0.y) - d_lse2);
                 const float p1 = ex2_approx(fmaf(v[i + 1], c1.x, c1.y) - d_lse2);
                 const float g0 = fmaf(-c0.w, v[i], fmaf(c0.x * d_sp, p0, -c0.z));
@@ -381,12 +398,11 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 pk[i >> 1] = pack_bf16(g0, g1);
               }
               // P tile, K-major SW128: chunk = (c>>1), slots (c&1)*4 .. +3 of row `row`
-              uint8_t* prow = pbuf + (c >> 1) * 16384 + row * 128;
+              const uint32_t prow = pbuf + (c >> 1) * 16384 + row * 128;
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
                 const uint32_t slot = ((c & 1) * 4 + g) ^ (row & 7);
-                *reinterpret_cast<uint4*>(prow + slot * 16) =
-                    make_uint4(pk[g * 4], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
+                sts_u4(prow + slot * 16, pk[g * 4], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
               }
             } else if (kMode == COL_STATS) {
 #pragma unroll
@@ -396,7 +412,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 // pass 1: a += S*p ; c' += S*p*yc
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
-                  const float4 dc = sb[c * 32 + i];  // {lse2_b, S_b, -, -}
+                  const float2 dc = lds_f2(sb + (c * 32 + i) * 16);  // {lse2_b, S_b, -, -}
                   const float d = dc.y * ex2_approx(fmaf(v[i], c_r2, c_bias - dc.x));
                   acc0 += d;
                   acc1 = fmaf(d, v[i], acc1);
@@ -405,20 +421,19 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 uint32_t pk[16];
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {
-                  const float4 d0 = sb[c * 32 + i];
-                  const float4 d1 = sb[c * 32 + i + 1];
+                  const float2 d0 = lds_f2(sb + (c * 32 + i) * 16);
+                  const float2 d1 = lds_f2(sb + (c * 32 + i + 1) * 16);
                   const float p0 = ex2_approx(fmaf(v[i], c_r2, c_bias - d0.x));
                   const float p1 = ex2_approx(fmaf(v[i + 1], c_r2, c_bias - d1.x));
                   const float g0 = fmaf(-c_gamma, v[i], fmaf(c_rstd * d0.y, p0, -c_alpha));
                   const float g1 = fmaf(-c_gamma, v[i + 1], fmaf(c_rstd * d1.y, p1, -c_alpha));
                   pk[i >> 1] = pack_bf16(g0, g1);
                 }
-                uint8_t* prow = pbuf + (c >> 1) * 16384 + row * 128;
+                const uint32_t prow = pbuf + (c >> 1) * 16384 + row * 128;
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
                   const uint32_t slot = ((c & 1) * 4 + g) ^ (row & 7);
-                  *reinterpret_cast<uint4*>(prow + slot * 16) =
-                      make_uint4(pk[g * 4], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
+                  sts_u4(prow + slot * 16, pk[g * 4], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
                 }
               }
             }
@@ -426,18 +441,38 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
 
           // TMEM -> registers two chunks ahead of their use
           float va[32], vb[32];
+          if (p.debug & 1) {  // profiling experiment: no TMEM loads / math / P writes
+            tc_fence_before();
+            mbar_arrive(&s.d1_empty[buf]);
+            mbar_arrive(&s.sb_empty[sbs]);
+            ++d1_it;
+            ++b_it;
+            if (m2) {
+              fence_proxy_async_smem();
+              mbar_arrive(&s.p_full[pb]);
+              ++p_it;
+            }
+            continue;
+          }
           tmem_ld32(taddr + 0, va);
           tmem_ld32(taddr + 32, vb);
           tmem_ld_wait();
-          process(0, va);
-          tmem_ld32(taddr + 64, va);
-          process(1, vb);
-          tmem_ld32(taddr + 96, vb);
-          tmem_ld_wait();
-          tc_fence_before();
-          mbar_arrive(&s.d1_empty[buf]);  // accumulator buffer can be overwritten by the next MMA1
-          process(2, va);
-          process(3, vb);
+          if (kBN == 128) {
+            process(0, va);
+            tmem_ld32(taddr + 64, va);
+            process(1, vb);
+            tmem_ld32(taddr + 96, vb);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&s.d1_empty[buf]);  // accumulator buffer can be overwritten by the next MMA1
+            process(2, va);
+            process(3, vb);
+          } else {
+            tc_fence_before();
+            mbar_arrive(&s.d1_empty[buf]);
+            process(0, va);
+            process(1, vb);
+          }
           mbar_arrive(&s.sb_empty[sbs]);  // side band of this tile fully consumed
           ++d1_it;
           ++b_it;
@@ -465,7 +500,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           tc_fence_after();
           const bool has_corr = (kMode == COL_GRAD) && p.corr != nullptr && grow < p.V &&
                                 (p.colptr[grow + 1] > p.colptr[grow]);
-          for (int c = 0; c * 32 < Kp; ++c) {
+          for (int c = 0; c * 32 < Kp && !(p.debug & 16); ++c) {
             float v[32];
             tmem_ld32(lane_addr + 256 + c * 32, v);
             tmem_ld_wait();
@@ -538,19 +573,19 @@ template <int kMode>
 static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, SweepParams& p,
                         cudaStream_t stream) {
   constexpr bool kHasMMA2 = (kMode == ROW_GRAD || kMode == COL_GRAD);
-  const size_t tile = (size_t)p.Kp * 256;
+  constexpr int kBN = (kHasMMA2 && GF_GRAD_BN == 64) ? 64 : 128;
+  const size_t tile = (size_t)p.Kp * 256, stile = (size_t)p.Kp * 2 * kBN, ptile = (size_t)kBN * 256;
   int max_smem = 0, dev = 0;
   GF_CUDA_CHECK(cudaGetDevice(&dev));
   GF_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  const size_t base_fixed = 1024 + tile + (kHasMMA2 ? 2 : kSbStagesMax) * kTile * sizeof(float4) + 1024;
+  const size_t base_fixed = 1024 + tile + kSbStagesMax * kBN * sizeof(float4) + 1024;
   p.p_bufs = kHasMMA2 ? 2 : 0;
-  if (kHasMMA2 && (size_t)max_smem < base_fixed + 65536 + 2 * tile) p.p_bufs = 1;  // large Kp: single P tile
-  const size_t fixed = base_fixed + 32768 * (size_t)p.p_bufs;
-  int stages = (int)(((size_t)max_smem - fixed) / tile);
+  const size_t fixed = base_fixed + ptile * (size_t)p.p_bufs;
+  int stages = (int)(((size_t)max_smem - fixed) / stile);
   if (stages > kMaxStages) stages = kMaxStages;
   GF_ARG_CHECK(stages >= 2, "n_components too large for the fused decoder sweeps (need Kp <= 240)");
   p.stages = stages;
-  size_t smem = fixed + (size_t)stages * tile;
+  size_t smem = fixed + (size_t)stages * stile;
   if (kHasMMA2 && smem < 120 * 1024) smem = 120 * 1024;  // 512 TMEM columns => one CTA per SM
   auto kern = sweep_kernel<kMode>;
   GF_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -584,13 +619,13 @@ static int sweep_grid_capacity(int mode, int Kp) {
   const bool m2 = (mode == ROW_GRAD || mode == COL_GRAD);
   const size_t tile = (size_t)Kp * 256;
   int max_smem = 232448;
-  const size_t base_fixed = 1024 + tile + (m2 ? 2 : kSbStagesMax) * kTile * sizeof(float4) + 1024;
-  const int p_bufs = m2 ? (((size_t)max_smem < base_fixed + 65536 + 2 * tile) ? 1 : 2) : 0;
-  const size_t fixed = base_fixed + 32768 * (size_t)p_bufs;
-  int stages = (int)(((size_t)max_smem - fixed) / tile);
+  const int bn = (m2 && GF_GRAD_BN == 64) ? 64 : 128;
+  const size_t stile = (size_t)Kp * 2 * bn;
+  const size_t fixed = 1024 + tile + kSbStagesMax * bn * sizeof(float4) + 1024 + (m2 ? 2 * (size_t)bn * 256 : 0);
+  int stages = (int)(((size_t)max_smem - fixed) / stile);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) stages = 2;
-  const size_t smem = fixed + (size_t)stages * tile;
+  const size_t smem = fixed + (size_t)stages * stile;
   const int occ = m2 ? 1 : ((smem <= 110 * 1024) ? 2 : 1);
   return num_sms() * occ;
 }
@@ -602,7 +637,8 @@ using namespace gf;
 // Vocabulary split for the ROW modes: the smallest chunk count whose (document tiles x chunks) work
 // items fill the persistent grid in whole waves (>= 95 % wave efficiency), so no SM idles in the tail.
 extern "C" int gf_dec_row_chunks(int mode, int B, int V, int Kp) {
-  const int doc_tiles = (B + kTile - 1) / kTile, word_tiles = (V + kTile - 1) / kTile;
+  const int bn = (mode == ROW_GRAD && GF_GRAD_BN == 64) ? 64 : 128;
+  const int doc_tiles = (B + kTile - 1) / kTile, word_tiles = (V + bn - 1) / bn;
   const int grid = sweep_grid_capacity(mode, Kp);
   int best = 1;
   double best_eff = 0.0;
@@ -642,9 +678,10 @@ extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
   p.mode = a->mode;
   p.B = a->B; p.V = a->V; p.K = a->K; p.Kp = a->Kp;
   const bool row = (a->mode == ROW_LOGITS || a->mode == ROW_LSE || a->mode == ROW_GRAD);
+  const int bn = ((a->mode == ROW_GRAD || a->mode == COL_GRAD) && GF_GRAD_BN == 64) ? 64 : 128;  // streamed tile width
   const int doc_tiles = (a->B + kTile - 1) / kTile, word_tiles = (a->V + kTile - 1) / kTile;
   p.n_stat = row ? doc_tiles : word_tiles;
-  p.n_stream = row ? word_tiles : doc_tiles;
+  p.n_stream = row ? (a->V + bn - 1) / bn : (a->B + bn - 1) / bn;
   p.n_chunks = row ? a->n_chunks : 1;
   GF_ARG_CHECK(p.n_chunks >= 1 && p.n_chunks <= p.n_stream, "n_chunks");
   p.n_pass = (a->mode == COL_GRAD) ? 2 : 1;
@@ -666,5 +703,9 @@ extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
   p.asp = a->asp; p.csp = a->csp;
   p.dbeta = a->dbeta; p.ldg = a->ld_dbeta;
   p.corr = a->corr; p.colptr = a->colptr;
+  {
+    const char* dbg = getenv("GFEDNTM_SWEEP_DEBUG");
+    p.debug = dbg ? atoi(dbg) : 0;
+  }
   return dispatch_sweep(tm_theta, tm_beta, p, stream);
 }
