@@ -57,10 +57,10 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
                           if len(emb) and isinstance(emb[0], str) else np.stack([np.asarray(e, np.float32) for e in emb]))
     cv = CountVectorizer(input="content", lowercase=True, stop_words="english", binary=False)
     cv.fit(docs)
-    gathered = [None] * world
-    dist.all_gather_object(gathered, sorted(cv.vocabulary_.keys()))
-    vocab = sorted(set().union(*[set(v) for v in gathered]))
-    gcv = CountVectorizer(vocabulary={t: i for i, t in enumerate(vocab)})
+    from ..parallel.consensus import consensus_vocabulary
+
+    vocab_map, _ = consensus_vocabulary(list(cv.vocabulary_.keys()), len(docs))
+    gcv = CountVectorizer(vocabulary=vocab_map)
     bow = gcv.transform(docs)
     idx2token = gcv.get_feature_names_out()
 
