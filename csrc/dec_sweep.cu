@@ -39,8 +39,9 @@ enum : int {
 };
 
 constexpr int kTile = 128;
-// Streamed-tile width of the gradient modes.  64 doubles the pipeline depth but measured slower
-// (per-tile hand-off overhead dominates): ROW_GRAD 949 vs 850 us, COL_GRAD 1735 vs 1478 us at V=200k.
+// Streamed-tile width of the gradient modes.  64-wide tiles double the pipeline depth but measured
+// slower at V=200k, K=200 (per-tile hand-off overhead dominates; the epilogue is the bottleneck, not
+// the issue order): ROW_GRAD 1034 vs 826 us, COL_GRAD 1829 vs 1556 us.
 #ifndef GF_GRAD_BN
 #define GF_GRAD_BN 128
 #endif
@@ -116,7 +117,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   // Width of a streamed tile.  The gradient modes hold every streamed tile until its MMA2 has
   // completed, so they use 64-wide tiles: half the bytes per stage -> twice the pipeline depth.
   constexpr int kBN = (kHasMMA2 && GF_GRAD_BN == 64) ? 64 : 128;
-  constexpr int kSbStages = kSbStagesMax;
+  constexpr int kSbStages = (kHasMMA2 && kBN == 128) ? 2 : kSbStagesMax;  // 128-wide gradient tiles: smem is tight
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t kSbBytes = kBN * sizeof(float4);
@@ -242,8 +243,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       uint32_t a_it = 0, b_it = 0, d1_it = 0, p_it = 0, d2_it = 0;
 
       auto issue_mma2 = [&](int st, bool first) {
-        const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;
-        mbar_wait(&s.p_full[pb], ((p.p_bufs == 2) ? (p_it >> 1) : p_it) & 1);
+        const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;  // caller observed p_full[pb]
         tc_fence_after();
         const uint32_t p_base = smem_u32(s.p[pb]);
         const uint32_t b_base = smem_u32(s.b[st]);
@@ -265,41 +265,48 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         mbar_wait(s.a_full, a_it & 1);
         for (int pass = 0; pass < p.n_pass; ++pass) {
           const bool m2 = kHasMMA2 && (pass == p.n_pass - 1) && !(p.debug & 8);
-          int pending = -1;
-          bool first2 = true;
+          // ---- event-driven issue.  Two independent streams of work share this thread: MMA1 of the
+          // next tile (needs its operands landed and a free accumulator buffer) and, in a gradient
+          // pass, MMA2 of the oldest tile whose epilogue has published P (which releases that tile's
+          // stage).  Polling both instead of a fixed order lets MMA1 run ahead of the epilogue ->
+          // MMA2 chain, so no iteration waits for a full epilogue round trip.  (One MMA1 site and one
+          // MMA2 site on purpose: with several inlined copies of the predicated k-step sequence the
+          // gradient sweeps returned wrong results for Kp > 64.)
           if (m2) mbar_wait(s.d2_empty, (d2_it & 1) ^ 1);
-          for (int t = t0; t < t1; ++t) {
-            const int st = b_it % stages;
-            mbar_wait(&s.b_full[st], (b_it / stages) & 1);
-            const uint32_t buf = d1_it & 1;
-            mbar_wait(&s.d1_empty[buf], ((d1_it >> 1) & 1) ^ 1);
-            tc_fence_after();
-            // Descriptors differ between k-steps only in the start-address field (+2048 B = +128 in
-            // 16-byte units): build them once and issue from a fully unrolled, predicated loop so the
-            // issuing thread keeps the tensor pipe fed (one tcgen05.mma every ~64 cycles).
-            const uint32_t b_base = smem_u32(s.b[st]);
-            const uint32_t d_addr = tmem + buf * kBN;
-#pragma unroll
-            for (int j = 0; j < 15; ++j) {
-              if (j < n_ksteps && !(p.debug & 2))
-                umma_f16(d_addr, umma_smem_desc(a_base + j * 2048u, blk, 1024),
-                         umma_smem_desc(b_base + j * 2048u, blk, 1024), idesc1, j > 0 ? 1u : 0u);
-            }
-            umma_commit(&s.d1_full[buf]);
-            ++d1_it;
-            if (m2) {
-              if (pending >= 0) {
-                issue_mma2(pending, first2);
-                first2 = false;
+          const uint32_t b_it0 = b_it;
+          int n1 = t0, n2 = m2 ? t0 : t1;
+          while (n1 < t1 || n2 < t1) {
+            if (kHasMMA2 && n2 < n1) {
+              const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;
+              if (mbar_test_wait(&s.p_full[pb], ((p.p_bufs == 2) ? (p_it >> 1) : p_it) & 1)) {
+                issue_mma2((int)((b_it0 + (uint32_t)(n2 - t0)) % stages), n2 == t0);
+                ++n2;
               }
-              pending = st;
-            } else {
-              umma_commit(&s.b_empty[st]);  // operand tile is free as soon as MMA1 has read it
             }
-            ++b_it;
+            if (n1 < t1) {
+              const uint32_t bi = b_it0 + (uint32_t)(n1 - t0);
+              const int st = bi % stages;
+              const uint32_t buf = d1_it & 1;
+              if (mbar_test_wait(&s.b_full[st], (bi / stages) & 1) &&
+                  mbar_test_wait(&s.d1_empty[buf], ((d1_it >> 1) & 1) ^ 1)) {
+                tc_fence_after();
+                const uint32_t b_base = smem_u32(s.b[st]);
+                const uint32_t d_addr = tmem + buf * kBN;
+#pragma unroll
+                for (int j = 0; j < 15; ++j) {
+                  if (j < n_ksteps && !(p.debug & 2))
+                    umma_f16(d_addr, umma_smem_desc(a_base + j * 2048u, blk, 1024),
+                             umma_smem_desc(b_base + j * 2048u, blk, 1024), idesc1, j > 0 ? 1u : 0u);
+                }
+                umma_commit(&s.d1_full[buf]);
+                ++d1_it;
+                if (!m2) umma_commit(&s.b_empty[st]);  // no MMA2: the tile is free once MMA1 has read it
+                ++n1;
+              }
+            }
           }
+          b_it += (uint32_t)(t1 - t0);
           if (m2) {
-            if (pending >= 0) issue_mma2(pending, first2);
             umma_commit(s.d2_full);
             ++d2_it;
           }
@@ -578,8 +585,10 @@ static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta,
   int max_smem = 0, dev = 0;
   GF_CUDA_CHECK(cudaGetDevice(&dev));
   GF_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  const size_t base_fixed = 1024 + tile + kSbStagesMax * kBN * sizeof(float4) + 1024;
+  const size_t sb_stages = (kHasMMA2 && kBN == 128) ? 2 : kSbStagesMax;
+  const size_t base_fixed = 1024 + tile + sb_stages * kBN * sizeof(float4) + 1024;
   p.p_bufs = kHasMMA2 ? 2 : 0;
+  if (kHasMMA2 && (size_t)max_smem < base_fixed + 2 * ptile + 2 * stile) p.p_bufs = 1;  // large Kp: single P tile
   const size_t fixed = base_fixed + ptile * (size_t)p.p_bufs;
   int stages = (int)(((size_t)max_smem - fixed) / stile);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -621,7 +630,10 @@ static int sweep_grid_capacity(int mode, int Kp) {
   int max_smem = 232448;
   const int bn = (m2 && GF_GRAD_BN == 64) ? 64 : 128;
   const size_t stile = (size_t)Kp * 2 * bn;
-  const size_t fixed = 1024 + tile + kSbStagesMax * bn * sizeof(float4) + 1024 + (m2 ? 2 * (size_t)bn * 256 : 0);
+  const size_t sb_stages = (m2 && bn == 128) ? 2 : kSbStagesMax;
+  const size_t base_fixed = 1024 + tile + sb_stages * bn * sizeof(float4) + 1024;
+  const size_t ptile = (size_t)bn * 256;
+  const size_t fixed = base_fixed + (m2 ? (((size_t)max_smem < base_fixed + 2 * ptile + 2 * stile) ? 1 : 2) * ptile : 0);
   int stages = (int)(((size_t)max_smem - fixed) / stile);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) stages = 2;

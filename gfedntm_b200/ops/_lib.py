@@ -7,6 +7,7 @@ silently falling back to PyTorch.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 from typing import Optional
 
@@ -201,7 +202,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     if not LIB_PATH.exists():
         raise KernelLibraryError(
             f"{LIB_PATH} is missing: run `python -m gfedntm_b200.ops.build` (needs nvcc)")
-    lib = C.CDLL(str(LIB_PATH))
+    # GFEDNTM_KERNEL_LIB: load an alternative build of the same ABI (kernel A/B experiments)
+    lib = C.CDLL(os.environ.get("GFEDNTM_KERNEL_LIB") or str(LIB_PATH))
     _declare(lib)
     for idx, st in enumerate(_STRUCTS):
         want = lib.gf_sizeof(idx)
