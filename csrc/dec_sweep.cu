@@ -45,7 +45,8 @@ constexpr int kTile = 128;
 #ifndef GF_GRAD_BN
 #define GF_GRAD_BN 128
 #endif
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;     // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..11 epilogue
+constexpr int kEpiThreads = 256;  // two epilogue warps per SM sub-partition: each takes half of a tile's columns
 constexpr int kMaxStages = 6;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -81,6 +82,7 @@ struct SweepParams {
   const int* colptr;        // [V+1] CSC pointer of the batch (with corr)
 };
 
+constexpr int kBarRegion = 3072;  // mbarriers (512 B) + the two 1 KB epilogue exchange arrays
 constexpr int kSbStagesMax = 4;  // side-band ring depth (2 KB per entry); 2 in the gradient modes
 
 struct Smem {
@@ -101,6 +103,8 @@ struct Smem {
   uint64_t* d2_full;
   uint64_t* d2_empty;
   uint32_t* tmem_ptr;
+  float2* xa;          // [128] epilogue half 1 -> half 0 partial accumulators
+  float2* xb;          // [128] epilogue half 0 -> half 1 finalised per-word constants
 };
 
 // Both operands are stored "topics x contiguous axis" in global memory:
@@ -155,6 +159,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   s.d2_full = s.p_empty + 2;
   s.d2_empty = s.d2_full + 1;
   s.tmem_ptr = reinterpret_cast<uint32_t*>(s.d2_empty + 1);
+  s.xa = reinterpret_cast<float2*>(bars + 64);
+  s.xb = s.xa + kTile;
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31;
@@ -172,18 +178,18 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
     }
     for (int i = 0; i < kSbStages; ++i) {
       mbar_init(&s.sb_full[i], 1);
-      mbar_init(&s.sb_empty[i], 128);
+      mbar_init(&s.sb_empty[i], kEpiThreads);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&s.d1_full[i], 1);
-      mbar_init(&s.d1_empty[i], 128);
+      mbar_init(&s.d1_empty[i], kEpiThreads);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&s.p_full[i], 128);
+      mbar_init(&s.p_full[i], kEpiThreads);
       mbar_init(&s.p_empty[i], 1);
     }
     mbar_init(s.d2_full, 1);
-    mbar_init(s.d2_empty, 128);
+    mbar_init(s.d2_empty, kEpiThreads);
     mbar_fence_init();
   }
   constexpr uint32_t kTmemCols = kHasMMA2 ? 512 : 256;
@@ -317,8 +323,13 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
     }
   } else if (warp >= 4) {
     // ============================ epilogue ============================
-    const uint32_t q = warp - 4;
+    // Two warps per TMEM lane quarter (a warp may only touch lanes 32*(warp%4)..+31): warps 4..7 take
+    // the first half of every tile's columns, warps 8..11 the second half.  One epilogue warp per
+    // sub-partition was latency bound (MUFU / TMEM-load / LDS chains with nothing to overlap).
+    const uint32_t q = warp & 3;
+    const uint32_t h = (warp - 4) >> 2;
     const uint32_t row = q * 32 + lane;  // TMEM lane == tile row
+    auto epi_sync = [] { asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory"); };
     const uint32_t lane_addr = tmem + ((q * 32) << 16);
     uint32_t b_it = 0, d1_it = 0, p_it = 0, d2_it = 0;
 
@@ -461,24 +472,20 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
             }
             continue;
           }
-          tmem_ld32(taddr + 0, va);
-          tmem_ld32(taddr + 32, vb);
-          tmem_ld_wait();
           if (kBN == 128) {
-            process(0, va);
-            tmem_ld32(taddr + 64, va);
-            process(1, vb);
-            tmem_ld32(taddr + 96, vb);
+            tmem_ld32(taddr + h * 64, va);
+            tmem_ld32(taddr + h * 64 + 32, vb);
             tmem_ld_wait();
             tc_fence_before();
             mbar_arrive(&s.d1_empty[buf]);  // accumulator buffer can be overwritten by the next MMA1
-            process(2, va);
-            process(3, vb);
+            process(2 * h, va);
+            process(2 * h + 1, vb);
           } else {
+            tmem_ld32(taddr + h * 32, va);
+            tmem_ld_wait();
             tc_fence_before();
             mbar_arrive(&s.d1_empty[buf]);
-            process(0, va);
-            process(1, vb);
+            process(h, va);
           }
           mbar_arrive(&s.sb_empty[sbs]);  // side band of this tile fully consumed
           ++d1_it;
@@ -493,13 +500,27 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         // ---- end of a pass
         if (kMode == COL_GRAD && !m2) {
           // finalise BN-backward column means, publish the per-word constants
-          if (grow < p.V) {
-            const float invB = 1.0f / (float)p.B;
-            const float abar = (acc0 - p.asp[grow]) * invB;
-            const float cbar = (c_rstd * acc1 - p.csp[grow]) * invB;
-            c_alpha = c_rstd * abar;
-            c_gamma = c_rstd * c_rstd * cbar;
-            p.colc[grow] = make_float4(c_r2, c_bias, c_alpha, c_gamma);
+          if (h == 1) s.xa[row] = make_float2(acc0, acc1);
+          epi_sync();
+          if (h == 0) {
+            const float2 o = s.xa[row];
+            acc0 += o.x;
+            acc1 += o.y;
+            if (grow < p.V) {
+              const float invB = 1.0f / (float)p.B;
+              const float abar = (acc0 - p.asp[grow]) * invB;
+              const float cbar = (c_rstd * acc1 - p.csp[grow]) * invB;
+              c_alpha = c_rstd * abar;
+              c_gamma = c_rstd * c_rstd * cbar;
+              p.colc[grow] = make_float4(c_r2, c_bias, c_alpha, c_gamma);
+            }
+            s.xb[row] = make_float2(c_alpha, c_gamma);
+          }
+          epi_sync();
+          if (h == 1) {
+            const float2 o = s.xb[row];
+            c_alpha = o.x;
+            c_gamma = o.y;
           }
         }
         if (m2) {
@@ -507,7 +528,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           tc_fence_after();
           const bool has_corr = (kMode == COL_GRAD) && p.corr != nullptr && grow < p.V &&
                                 (p.colptr[grow + 1] > p.colptr[grow]);
-          for (int c = 0; c * 32 < Kp && !(p.debug & 16); ++c) {
+          for (int c = (int)h; c * 32 < Kp && !(p.debug & 16); c += 2) {  // halves interleave the chunks
             float v[32];
             tmem_ld32(lane_addr + 256 + c * 32, v);
             tmem_ld_wait();
@@ -538,9 +559,24 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       }
 
       // ---- end of work item
+      if (kMode == ROW_LSE || kMode == COL_STATS) {  // merge the two column halves of every row
+        if (h == 1) s.xa[row] = make_float2(acc0, acc1);
+        epi_sync();
+        if (h == 0) {
+          const float2 o = s.xa[row];
+          if (kMode == ROW_LSE) {
+            const float nm = fmaxf(acc0, o.x);
+            acc1 = (nm > -INFINITY) ? acc1 * ex2_approx(acc0 - nm) + o.y * ex2_approx(o.x - nm) : 0.f;
+            acc0 = nm;
+          } else {
+            acc0 += o.x;
+          }
+        }
+        epi_sync();  // xa may be rewritten by the next work item only after it has been read
+      }
       if (kMode == ROW_LSE) {
-        if (grow < p.B) p.lse_part[(size_t)grow * p.n_chunks + chunk] = make_float2(acc0, acc1);
-      } else if (kMode == COL_STATS) {
+        if (h == 0 && grow < p.B) p.lse_part[(size_t)grow * p.n_chunks + chunk] = make_float2(acc0, acc1);
+      } else if (kMode == COL_STATS && h == 0) {
         if (grow < p.V) {
           float mean = 0.f;
           if (p.theta_mean != nullptr) {
@@ -586,7 +622,7 @@ static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta,
   GF_CUDA_CHECK(cudaGetDevice(&dev));
   GF_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
   const size_t sb_stages = (kHasMMA2 && kBN == 128) ? 2 : kSbStagesMax;
-  const size_t base_fixed = 1024 + tile + sb_stages * kBN * sizeof(float4) + 1024;
+  const size_t base_fixed = 1024 + tile + sb_stages * kBN * sizeof(float4) + kBarRegion;
   p.p_bufs = kHasMMA2 ? 2 : 0;
   if (kHasMMA2 && (size_t)max_smem < base_fixed + 2 * ptile + 2 * stile) p.p_bufs = 1;  // large Kp: single P tile
   const size_t fixed = base_fixed + ptile * (size_t)p.p_bufs;
@@ -599,7 +635,7 @@ static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta,
   auto kern = sweep_kernel<kMode>;
   GF_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int total = p.n_stat * p.n_chunks;
-  const int occ = kHasMMA2 ? 1 : ((smem <= 110 * 1024) ? 2 : 1);
+  const int occ = 1;  // 12 warps with up to 168 registers each: one CTA per SM
   int grid = num_sms() * occ;
   if (grid > total) grid = total;
   if (grid < 1) grid = 1;
@@ -631,14 +667,14 @@ static int sweep_grid_capacity(int mode, int Kp) {
   const int bn = (m2 && GF_GRAD_BN == 64) ? 64 : 128;
   const size_t stile = (size_t)Kp * 2 * bn;
   const size_t sb_stages = (m2 && bn == 128) ? 2 : kSbStagesMax;
-  const size_t base_fixed = 1024 + tile + sb_stages * bn * sizeof(float4) + 1024;
+  const size_t base_fixed = 1024 + tile + sb_stages * bn * sizeof(float4) + kBarRegion;
   const size_t ptile = (size_t)bn * 256;
   const size_t fixed = base_fixed + (m2 ? (((size_t)max_smem < base_fixed + 2 * ptile + 2 * stile) ? 1 : 2) * ptile : 0);
   int stages = (int)(((size_t)max_smem - fixed) / stile);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) stages = 2;
   const size_t smem = fixed + (size_t)stages * stile;
-  const int occ = m2 ? 1 : ((smem <= 110 * 1024) ? 2 : 1);
+  const int occ = 1;
   return num_sms() * occ;
 }
 
