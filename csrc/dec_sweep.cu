@@ -35,16 +35,23 @@ enum : int {
   ROW_GRAD = 2,    // d theta (dense part)
   COL_STATS = 3,   // per-word second moment over the batch -> BatchNorm rstd, running stats
   COL_GRAD = 4,    // pass 1: BN-backward column sums; pass 2: d beta (dense part)
-  COL_LOGITS = 5   // out[b,v] via the COL family                          (debug)
+  COL_LOGITS = 5,  // out[b,v] via the COL family                          (debug)
+  // "Folded" modes: every per-word and per-document constant of the epilogue is carried by the GEMM
+  // itself (beta' = beta*rstd*log2e plus bias rows, theta_c^T plus constant-one rows and -e_b rows,
+  // e_b = lse2_b - log2 S_b), so the accumulator IS the exponent and the epilogue needs no side band:
+  ROW_LSE2 = 6,    // online (max2,sum) of 2^D1
+  COL_GRAD2 = 7,   // ONE pass: P = 2^D1 (= S_b p_bv), D2 = P^T-free d beta accumulation, BN-backward
+                   // constants from D2 in the drain, (C beta) correction from two pseudo-document tiles
+  ROW_GRAD2 = 8,   // P = 2^D1, d theta += ln2 * P . beta'^T
+  // Batch variance of the centred logits WITHOUT a pass over the batch:
+  //   sum_b yc_bv^2 = beta_v^T C beta_v,  C = theta_c^T theta_c  (K x K, streamed as hi + lo bf16 tiles)
+  COL_STATS2 = 9
 };
 
 constexpr int kTile = 128;
-// Streamed-tile width of the gradient modes.  64-wide tiles double the pipeline depth but measured
-// slower at V=200k, K=200 (per-tile hand-off overhead dominates; the epilogue is the bottleneck, not
-// the issue order): ROW_GRAD 1034 vs 826 us, COL_GRAD 1829 vs 1556 us.
-#ifndef GF_GRAD_BN
-#define GF_GRAD_BN 128
-#endif
+// (64-wide streamed tiles for the gradient modes were measured slower at V=200k, K=200: ROW_GRAD
+// 1034 vs 826 us, COL_GRAD 1829 vs 1556 us -- per-tile hand-off overhead dominates.)
+constexpr int kBN = 128;  // streamed-tile width
 constexpr int kThreads = 384;     // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..11 epilogue
 constexpr int kEpiThreads = 256;  // two epilogue warps per SM sub-partition: each takes half of a tile's columns
 constexpr int kMaxStages = 6;
@@ -56,6 +63,11 @@ struct SweepParams {
   int B, V, K, Kp;
   int n_stat, n_stream, n_chunks, n_pass, stages;
   int p_bufs;               // 1 or 2 shared-memory P tiles (gradient modes)
+  int n_ext, ext_tile0;     // COL_GRAD2: pseudo-document tiles (C = theta_c^T theta_c) streamed after the batch
+                            // COL_STATS2: the streamed tiles are 2*n_ext C tiles (hi then lo) from ext_tile0
+  const __nv_bfloat16* betaT_bf;  // COL_GRAD2: [V, Kp] unscaled beta^T (drain)
+  __nv_bfloat16* beta3;     // COL_GRAD2 out: [Kp, ld3] rows k<K = gamma_v*beta[k,v], row K = alpha_v
+  int ld3;
   int debug;                // profiling experiments: bit0 = epilogue skips TMEM loads/math, bit1 = skip MMA1 issue
   const float4* sb_stream;  // side band per streamed index (padded to a multiple of 128)
   // generic
@@ -78,12 +90,21 @@ struct SweepParams {
   const float* csp;         // [V] sparse part of sum_b dy*y
   float* dbeta;             // [K, ldg] fp32 gradient (COL_GRAD output)
   int ldg;
-  const float* corr;        // [V, Kp] sparse correction to d beta^T (may be null)
+  const float* corr;        // COL_GRAD: [V, Kp] sparse correction to d beta^T (may be null); COL_GRAD2: [Kp, ldc]
+  int ldc;
   const int* colptr;        // [V+1] CSC pointer of the batch (with corr)
 };
 
 constexpr int kBarRegion = 3072;  // mbarriers (512 B) + the two 1 KB epilogue exchange arrays
 constexpr int kSbStagesMax = 4;  // side-band ring depth (2 KB per entry); 2 in the gradient modes
+
+__host__ __device__ constexpr bool mode_is_row(int m) {
+  return m == ROW_LOGITS || m == ROW_LSE || m == ROW_GRAD || m == ROW_LSE2 || m == ROW_GRAD2;
+}
+__host__ __device__ constexpr bool mode_has_mma2(int m) { return m == ROW_GRAD || m == COL_GRAD || m == ROW_GRAD2 || m == COL_GRAD2; }
+__host__ __device__ constexpr bool mode_has_sb(int m) { return m == ROW_LSE || m == ROW_GRAD || m == COL_GRAD; }
+// side-band ring depth: 4 for ROW_LSE, 2 where the P tiles need the shared memory, none in the other modes
+__host__ __device__ constexpr int mode_sb_stages(int m) { return mode_has_sb(m) ? (mode_has_mma2(m) ? 2 : kSbStagesMax) : 0; }
 
 struct Smem {
   uint8_t* a;
@@ -116,12 +137,13 @@ template <int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant__ CUtensorMap tm_beta,
              const SweepParams p) {
-  constexpr bool kRow = (kMode == ROW_LOGITS || kMode == ROW_LSE || kMode == ROW_GRAD);
-  constexpr bool kHasMMA2 = (kMode == ROW_GRAD || kMode == COL_GRAD);
-  // Width of a streamed tile.  The gradient modes hold every streamed tile until its MMA2 has
-  // completed, so they use 64-wide tiles: half the bytes per stage -> twice the pipeline depth.
-  constexpr int kBN = (kHasMMA2 && GF_GRAD_BN == 64) ? 64 : 128;
-  constexpr int kSbStages = (kHasMMA2 && kBN == 128) ? 2 : kSbStagesMax;  // 128-wide gradient tiles: smem is tight
+  constexpr bool kRow = mode_is_row(kMode);
+  constexpr bool kHasMMA2 = mode_has_mma2(kMode);
+  constexpr bool kSb = mode_has_sb(kMode);
+  constexpr bool kExt = (kMode == COL_GRAD2 || kMode == ROW_GRAD2);
+  constexpr bool kEpiHoldsA = (kMode == COL_GRAD2);  // the drain reads the stationary tile from shared memory
+  constexpr bool kFolded = (kMode == ROW_LSE2 || kMode == COL_GRAD2 || kMode == ROW_GRAD2);
+  constexpr int kSbStages = mode_sb_stages(kMode);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t kSbBytes = kBN * sizeof(float4);
@@ -171,12 +193,12 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   }
   if (warp == 1 && lane == 0) {
     mbar_init(s.a_full, 1);
-    mbar_init(s.a_empty, 1);
+    mbar_init(s.a_empty, kEpiHoldsA ? 1 + kEpiThreads : 1);
     for (int i = 0; i < kMaxStages; ++i) {
       mbar_init(&s.b_full[i], 1);
       mbar_init(&s.b_empty[i], 1);  // tcgen05.commit of the last MMA that reads the tile
     }
-    for (int i = 0; i < kSbStages; ++i) {
+    for (int i = 0; i < kSbStagesMax; ++i) {
       mbar_init(&s.sb_full[i], 1);
       mbar_init(&s.sb_empty[i], kEpiThreads);
     }
@@ -208,7 +230,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   if (warp == 0) {
     // ============================ TMA producer ============================
     if (lane == 0) {
-      uint32_t a_it = 0, b_it = 0;
+      uint32_t a_it = 0, b_it = 0, sb_it = 0;
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
         const int stat = w / p.n_chunks, chunk = w - stat * p.n_chunks;
         const int t0 = (int)(((long long)chunk * p.n_stream) / p.n_chunks);
@@ -220,22 +242,40 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         ++a_it;
         for (int pass = 0; pass < p.n_pass; ++pass) {
           for (int t = t0; t < t1; ++t) {
-            const int st = b_it % stages, sbs = b_it % kSbStages;
+            const int st = b_it % stages;
             mbar_wait(&s.b_empty[st], ((b_it / stages) & 1) ^ 1);
-            mbar_wait(&s.sb_empty[sbs], ((b_it / kSbStages) & 1) ^ 1);
             mbar_arrive_expect_tx(&s.b_full[st], stile_bytes);
-            tma_load_2d(s.b[st], tm_strm, &s.b_full[st], t * kBN, 0);
-            if (kBN == 128) tma_load_2d(s.b[st] + blk, tm_strm, &s.b_full[st], t * kBN + 64, 0);
-            // side band: 128 float4 = 2 KB, plain bulk copy with its own full/empty pair (its ring
-            // slot is only reused after the epilogue released it, so the parity can never alias)
-            mbar_arrive_expect_tx(&s.sb_full[sbs], kSbBytes);
-            asm volatile(
-                "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::
-                    "r"(smem_u32(s.sb[sbs])),
-                "l"(reinterpret_cast<uint64_t>(p.sb_stream + (size_t)t * kBN)), "r"(kSbBytes),
-                "r"(smem_u32(&s.sb_full[sbs]))
-                : "memory");
+            const int tc = (kMode == COL_STATS2) ? (p.ext_tile0 + t) : t;
+            tma_load_2d(s.b[st], tm_strm, &s.b_full[st], tc * kBN, 0);
+            tma_load_2d(s.b[st] + blk, tm_strm, &s.b_full[st], tc * kBN + 64, 0);
+            if (kSb) {
+              // side band: 128 float4 = 2 KB, plain bulk copy with its own full/empty pair (its ring
+              // slot is only reused after the epilogue released it, so the parity can never alias)
+              const int sbs = sb_it % (kSb ? kSbStages : 1);
+              mbar_wait(&s.sb_empty[sbs], ((sb_it / (kSb ? kSbStages : 1)) & 1) ^ 1);
+              mbar_arrive_expect_tx(&s.sb_full[sbs], kSbBytes);
+              asm volatile(
+                  "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::
+                      "r"(smem_u32(s.sb[sbs])),
+                  "l"(reinterpret_cast<uint64_t>(p.sb_stream + (size_t)t * kBN)), "r"(kSbBytes),
+                  "r"(smem_u32(&s.sb_full[sbs]))
+                  : "memory");
+              ++sb_it;
+            }
             ++b_it;
+          }
+          if (kExt && pass == p.n_pass - 1) {
+            // COL_GRAD2: pseudo-document tiles (columns of C = theta_c^T theta_c, appended to theta_c^T);
+            // ROW_GRAD2: pseudo-word tiles (M hi/lo, appended to beta'), first vocabulary chunk only
+            const int n_x = (kMode == ROW_GRAD2 && chunk != 0) ? 0 : p.n_ext;
+            for (int i = 0; i < n_x; ++i) {
+              const int st = b_it % stages;
+              mbar_wait(&s.b_empty[st], ((b_it / stages) & 1) ^ 1);
+              mbar_arrive_expect_tx(&s.b_full[st], stile_bytes);
+              tma_load_2d(s.b[st], tm_strm, &s.b_full[st], (p.ext_tile0 + i) * kBN, 0);
+              tma_load_2d(s.b[st] + blk, tm_strm, &s.b_full[st], (p.ext_tile0 + i) * kBN + 64, 0);
+              ++b_it;
+            }
           }
         }
       }
@@ -254,7 +294,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         const uint32_t p_base = smem_u32(s.p[pb]);
         const uint32_t b_base = smem_u32(s.b[st]);
 #pragma unroll
-        for (int j = 0; j < kBN / 16; ++j) {  // contraction over the kBN streamed columns, 16 per step
+        for (int j = 0; j < kBN / 16; ++j) {  // contraction over the 128 streamed columns, 16 per step
           const uint64_t da = umma_smem_desc(p_base + (j >> 2) * 16384u + (j & 3) * 32u, 16, 1024);
           const uint64_t db = umma_smem_desc(b_base + (j >> 2) * blk + (j & 3) * 32u, 16, 1024);
           if (!(p.debug & 4)) umma_f16(tmem + 256, da, db, idesc2, (first && j == 0) ? 0u : 1u);
@@ -280,8 +320,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           // gradient sweeps returned wrong results for Kp > 64.)
           if (m2) mbar_wait(s.d2_empty, (d2_it & 1) ^ 1);
           const uint32_t b_it0 = b_it;
+          const int t1x = t1 + ((kExt && m2 && !(kMode == ROW_GRAD2 && chunk != 0)) ? p.n_ext : 0);  // pseudo tiles: MMA1 only
           int n1 = t0, n2 = m2 ? t0 : t1;
-          while (n1 < t1 || n2 < t1) {
+          while (n1 < t1x || n2 < t1) {
             if (kHasMMA2 && n2 < n1) {
               const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;
               if (mbar_test_wait(&s.p_full[pb], ((p.p_bufs == 2) ? (p_it >> 1) : p_it) & 1)) {
@@ -289,7 +330,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 ++n2;
               }
             }
-            if (n1 < t1) {
+            if (n1 < t1x) {
               const uint32_t bi = b_it0 + (uint32_t)(n1 - t0);
               const int st = bi % stages;
               const uint32_t buf = d1_it & 1;
@@ -306,12 +347,12 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 }
                 umma_commit(&s.d1_full[buf]);
                 ++d1_it;
-                if (!m2) umma_commit(&s.b_empty[st]);  // no MMA2: the tile is free once MMA1 has read it
+                if (!m2 || n1 >= t1) umma_commit(&s.b_empty[st]);  // no MMA2: free once MMA1 has read it
                 ++n1;
               }
             }
           }
-          b_it += (uint32_t)(t1 - t0);
+          b_it += (uint32_t)(t1x - t0);
           if (m2) {
             umma_commit(s.d2_full);
             ++d2_it;
@@ -343,13 +384,13 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       float acc0 = 0.f, acc1 = 0.f;   // ROW_LSE: (max2, sum); COL: (a, c') / sumsq
       float c_r2 = 0.f, c_alpha = 0.f, c_gamma = 0.f, c_rstd = 0.f, c_bias = 0.f;
       float d_lse2 = 0.f, d_sp = 0.f;
-      if (kMode == ROW_LSE) acc0 = -INFINITY;
+      if (kMode == ROW_LSE || kMode == ROW_LSE2) acc0 = -INFINITY;
       if (kMode == ROW_GRAD && grow < p.B) {
         const float2 dc = p.doc_const[grow];
         d_lse2 = dc.x;
         d_sp = dc.y;
       }
-      if (kMode == COL_GRAD && grow < p.V) {
+      if ((kMode == COL_GRAD || kMode == COL_GRAD2) && grow < p.V) {
         const float4 cc = p.colc[grow];
         c_r2 = cc.x;
         c_bias = cc.y;
@@ -359,9 +400,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       for (int pass = 0; pass < p.n_pass; ++pass) {
         const bool m2 = kHasMMA2 && (pass == p.n_pass - 1) && !(p.debug & 8);
         for (int t = t0; t < t1; ++t) {
-          const int sbs = b_it % kSbStages;
+          const int sbs = kSb ? (int)(b_it % (kSb ? kSbStages : 1)) : 0;
           const uint32_t buf = d1_it & 1;
-          mbar_wait(&s.sb_full[sbs], (b_it / kSbStages) & 1);
+          if (kSb) mbar_wait(&s.sb_full[sbs], (b_it / (kSb ? kSbStages : 1)) & 1);
           mbar_wait(&s.d1_full[buf], (d1_it >> 1) & 1);
           tc_fence_after();
           const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;
@@ -422,6 +463,52 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 const uint32_t slot = ((c & 1) * 4 + g) ^ (row & 7);
                 sts_u4(prow + slot * 16, pk[g * 4], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
               }
+            } else if (kMode == ROW_LSE2) {
+              // the accumulator already is the exponent (log2 units): online max / sum only
+              float cmax = v[0];
+#pragma unroll
+              for (int i = 1; i < 32; ++i) cmax = fmaxf(cmax, v[i]);
+              const float nm = fmaxf(acc0, cmax);
+              float sum = acc1 * ex2_approx(acc0 - nm);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) sum += ex2_approx(v[i] - nm);
+              acc1 = sum;
+              acc0 = nm;
+            } else if (kMode == COL_GRAD2 || kMode == ROW_GRAD2) {
+              // P = 2^D1 = S_b * p_bv  (D1 = BN'd logit in log2 units minus e_b = lse2_b - log2 S_b)
+              uint32_t pk[16];
+#pragma unroll
+              for (int i = 0; i < 32; i += 2) {
+                const float p0 = ex2_approx(v[i]);
+                const float p1 = ex2_approx(v[i + 1]);
+                if (kMode == COL_GRAD2) acc0 += p0 + p1;  // sum_b dy (dense part)
+                pk[i >> 1] = pack_bf16(p0, p1);
+              }
+              const uint32_t prow = pbuf + (c >> 1) * 16384 + row * 128;
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                const uint32_t slot = ((c & 1) * 4 + g) ^ (row & 7);
+                sts_u4(prow + slot * 16, pk[g * 4], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
+              }
+            } else if (kMode == COL_STATS2) {
+              // v[i] = (C beta)[k, word] for k = k0 + i; accumulate beta[k,word] * v[i]
+              const int k0 = (t % p.n_ext) * kBN + c * 32;
+              if (grow < p.V) {
+                const __nv_bfloat16* brow = p.betaT_bf + (size_t)grow * Kp;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  if (k0 + u * 8 < Kp) {
+                    const uint4 q = __ldg(reinterpret_cast<const uint4*>(brow + k0 + u * 8));
+                    const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+                    for (int w2 = 0; w2 < 4; ++w2) {
+                      const float2 f = __bfloat1622float2(h2[w2]);
+                      acc0 = fmaf(f.x, v[u * 8 + 2 * w2], acc0);
+                      acc0 = fmaf(f.y, v[u * 8 + 2 * w2 + 1], acc0);
+                    }
+                  }
+                }
+              }
             } else if (kMode == COL_STATS) {
 #pragma unroll
               for (int i = 0; i < 32; ++i) acc0 = fmaf(v[i], v[i], acc0);
@@ -462,7 +549,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           if (p.debug & 1) {  // profiling experiment: no TMEM loads / math / P writes
             tc_fence_before();
             mbar_arrive(&s.d1_empty[buf]);
-            mbar_arrive(&s.sb_empty[sbs]);
+            if (kSb) mbar_arrive(&s.sb_empty[sbs]);
             ++d1_it;
             ++b_it;
             if (m2) {
@@ -472,22 +559,14 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
             }
             continue;
           }
-          if (kBN == 128) {
-            tmem_ld32(taddr + h * 64, va);
-            tmem_ld32(taddr + h * 64 + 32, vb);
-            tmem_ld_wait();
-            tc_fence_before();
-            mbar_arrive(&s.d1_empty[buf]);  // accumulator buffer can be overwritten by the next MMA1
-            process(2 * h, va);
-            process(2 * h + 1, vb);
-          } else {
-            tmem_ld32(taddr + h * 32, va);
-            tmem_ld_wait();
-            tc_fence_before();
-            mbar_arrive(&s.d1_empty[buf]);
-            process(h, va);
-          }
-          mbar_arrive(&s.sb_empty[sbs]);  // side band of this tile fully consumed
+          tmem_ld32(taddr + h * 64, va);
+          tmem_ld32(taddr + h * 64 + 32, vb);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(&s.d1_empty[buf]);  // accumulator buffer can be overwritten by the next MMA1
+          process(2 * h, va);
+          process(2 * h + 1, vb);
+          if (kSb) mbar_arrive(&s.sb_empty[sbs]);  // side band of this tile fully consumed
           ++d1_it;
           ++b_it;
           if (m2) {
@@ -497,6 +576,29 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           }
         }
 
+        if (kMode == ROW_GRAD2 && m2 && chunk == 0) {
+          // pseudo-word tiles: D1[doc, k] = a_k + (theta_c M)[doc,k] (hi tiles then lo tiles); subtract
+          for (int x = 0; x < p.n_ext; ++x) {
+            const uint32_t buf = d1_it & 1;
+            mbar_wait(&s.d1_full[buf], (d1_it >> 1) & 1);
+            tc_fence_after();
+            float va[32], vb[32];
+            tmem_ld32(lane_addr + buf * kBN + h * 64, va);
+            tmem_ld32(lane_addr + buf * kBN + h * 64 + 32, vb);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&s.d1_empty[buf]);
+            ++d1_it;
+            const int k0 = (x % ((Kp + kBN - 1) / kBN)) * kBN + (int)h * 64;
+            if (grow < p.B) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                if (k0 + i < p.K) atomicAdd(&p.dtheta[(size_t)grow * Kp + k0 + i], -va[i]);
+                if (k0 + 32 + i < p.K) atomicAdd(&p.dtheta[(size_t)grow * Kp + k0 + 32 + i], -vb[i]);
+              }
+            }
+          }
+        }
         // ---- end of a pass
         if (kMode == COL_GRAD && !m2) {
           // finalise BN-backward column means, publish the per-word constants
@@ -526,17 +628,103 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         if (m2) {
           mbar_wait(s.d2_full, d2_it & 1);
           tc_fence_after();
-          const bool has_corr = (kMode == COL_GRAD) && p.corr != nullptr && grow < p.V &&
+          const bool has_corr = (kMode == COL_GRAD || kMode == COL_GRAD2) && p.corr != nullptr && grow < p.V &&
                                 (p.colptr[grow + 1] > p.colptr[grow]);
-          for (int c = (int)h; c * 32 < Kp && !(p.debug & 16); c += 2) {  // halves interleave the chunks
+          if (kMode == COL_GRAD2) {
+            // The two pseudo-document tiles (C = theta_c^T theta_c, bf16) are parked in the D1 buffers:
+            // D1x[word, k] = sum_j beta'[j,word] C[j,k] = r2_word * (C beta)[k,word].
+            const uint32_t d1_base = d1_it;
+            for (int i = 0; i < p.n_ext; ++i) mbar_wait(&s.d1_full[(d1_base + i) & 1], ((d1_base + i) >> 1) & 1);
+            tc_fence_after();
+            const bool vw = grow < p.V;
+            const int nchunk = (Kp + 31) >> 5;
+            // beta'[k, word] of this thread's word from the stationary tile (MN-major, 128B swizzle):
+            // box = word>>6, row k, 16-byte chunk ((word&63)>>3) ^ (k&7), element word&7
+            const uint32_t a_word = smem_u32(s.a) + (row >> 6) * blk + (row & 7) * 2;
+            const uint32_t a_chunk = (row & 63) >> 3;
+            auto beta_s = [&](int k) -> float {
+              uint16_t raw;
+              asm("ld.shared.u16 %0, [%1];" : "=h"(raw) : "r"(a_word + (uint32_t)k * 128u + ((a_chunk ^ ((uint32_t)k & 7u)) << 4)));
+              return __uint_as_float((uint32_t)raw << 16);
+            };
+            // ---- drain pass 1: r2 * c' = sum_k beta'[k,word] * D2[word,k]   (c' = sum_b dy*yc, dense part)
+            float cp = 0.f;
+            for (int c = (int)h; c < nchunk; c += 2) {
+              float v[32];
+              tmem_ld32(lane_addr + 256 + c * 32, v);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (c * 32 + i < p.K) cp = fmaf(beta_s(c * 32 + i), v[i], cp);
+            }
+            const float inv_r2 = (c_r2 > 0.f) ? 1.0f / c_r2 : 0.f;
+            cp *= inv_r2;
+            if (h == 1) s.xa[row] = make_float2(acc0, cp);
+            epi_sync();
+            if (h == 0) {
+              const float2 o = s.xa[row];
+              acc0 += o.x;
+              cp += o.y;
+              if (vw) {
+                const float invB = 1.0f / (float)p.B;
+                const float abar = (acc0 - p.asp[grow]) * invB;
+                const float cbar = (c_rstd * cp - p.csp[grow]) * invB;
+                c_alpha = c_rstd * abar;
+                c_gamma = c_rstd * c_rstd * cbar;
+                p.colc[grow] = make_float4(c_r2, c_bias, c_alpha, c_gamma);
+                if (p.beta3 != nullptr) p.beta3[(size_t)p.K * p.ld3 + grow] = __float2bfloat16(c_alpha);
+              }
+              s.xb[row] = make_float2(c_alpha, c_gamma);
+            }
+            epi_sync();
+            if (h == 1) {
+              const float2 o = s.xb[row];
+              c_alpha = o.x;
+              c_gamma = o.y;
+            }
+            // ---- drain pass 2: d beta[k,word] = rstd * D2 - gamma * (C beta)[k,word] - sparse correction
+            const float g_cb = c_gamma * inv_r2;
+            for (int c = (int)h; c < nchunk && !(p.debug & 16); c += 2) {
+              float v[32], e[32];
+              tmem_ld32(lane_addr + 256 + c * 32, v);
+              tmem_ld32(lane_addr + ((d1_base + (uint32_t)(c >> 2)) & 1) * kBN + (c & 3) * 32, e);
+              tmem_ld_wait();
+              if (vw) {
+                // all loads first (non-coherent path): a load behind a store to a possibly aliasing
+                // pointer would otherwise serialise the chunk on memory latency
+                float cr[32], bs[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                  const int k = c * 32 + i;
+                  cr[i] = (has_corr && k < p.K) ? __ldg(&p.corr[(size_t)k * p.ldc + grow]) : 0.f;
+                  bs[i] = (k < p.K) ? beta_s(k) : 0.f;
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                  const int k = c * 32 + i;
+                  if (k < p.K) {
+                    p.dbeta[(size_t)k * p.ldg + grow] = fmaf(c_rstd, v[i], -g_cb * e[i]) - cr[i];
+                    if (p.beta3 != nullptr) p.beta3[(size_t)k * p.ld3 + grow] = __float2bfloat16(g_cb * bs[i]);
+                  }
+                }
+              }
+            }
+            mbar_arrive(s.a_empty);  // the stationary tile may be overwritten now
+            tc_fence_before();
+            for (int i = 0; i < p.n_ext; ++i) mbar_arrive(&s.d1_empty[(d1_base + i) & 1]);
+            d1_it += (uint32_t)p.n_ext;
+          }
+          for (int c = (int)h; c * 32 < Kp && !(p.debug & 16) && kMode != COL_GRAD2; c += 2) {  // halves interleave the chunks
             float v[32];
             tmem_ld32(lane_addr + 256 + c * 32, v);
             tmem_ld_wait();
-            if (kMode == ROW_GRAD) {
+            if (kMode == ROW_GRAD || kMode == ROW_GRAD2) {
               if (grow < p.B) {
+                const float sc = (kMode == ROW_GRAD2) ? kLn2 : 1.0f;  // rstd = r2 * ln2 is folded into beta'
+                const int klim = (kMode == ROW_GRAD2) ? p.K : Kp;
 #pragma unroll
                 for (int i = 0; i < 32; ++i)
-                  if (c * 32 + i < Kp) atomicAdd(&p.dtheta[(size_t)grow * Kp + c * 32 + i], v[i]);
+                  if (c * 32 + i < klim) atomicAdd(&p.dtheta[(size_t)grow * Kp + c * 32 + i], sc * v[i]);
               }
             } else {  // COL_GRAD: d beta[k, word]
               if (grow < p.V) {
@@ -545,7 +733,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                   const int k = c * 32 + i;
                   if (k < p.K) {
                     float g = v[i];
-                    if (has_corr) g -= p.corr[(size_t)grow * Kp + k];
+                    if (has_corr) g -= __ldg(&p.corr[(size_t)grow * Kp + k]);
                     p.dbeta[(size_t)k * p.ldg + grow] = g;
                   }
                 }
@@ -559,12 +747,12 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       }
 
       // ---- end of work item
-      if (kMode == ROW_LSE || kMode == COL_STATS) {  // merge the two column halves of every row
+      if (kMode == ROW_LSE || kMode == ROW_LSE2 || kMode == COL_STATS || kMode == COL_STATS2) {  // merge the two column halves of every row
         if (h == 1) s.xa[row] = make_float2(acc0, acc1);
         epi_sync();
         if (h == 0) {
           const float2 o = s.xa[row];
-          if (kMode == ROW_LSE) {
+          if (kMode == ROW_LSE || kMode == ROW_LSE2) {
             const float nm = fmaxf(acc0, o.x);
             acc1 = (nm > -INFINITY) ? acc1 * ex2_approx(acc0 - nm) + o.y * ex2_approx(o.x - nm) : 0.f;
             acc0 = nm;
@@ -574,16 +762,16 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         }
         epi_sync();  // xa may be rewritten by the next work item only after it has been read
       }
-      if (kMode == ROW_LSE) {
+      if (kMode == ROW_LSE || kMode == ROW_LSE2) {
         if (h == 0 && grow < p.B) p.lse_part[(size_t)grow * p.n_chunks + chunk] = make_float2(acc0, acc1);
-      } else if (kMode == COL_STATS && h == 0) {
+      } else if ((kMode == COL_STATS || kMode == COL_STATS2) && h == 0) {
         if (grow < p.V) {
           float mean = 0.f;
           if (p.theta_mean != nullptr) {
             for (int k = 0; k < p.K; ++k)
               mean = fmaf(p.theta_mean[k], __bfloat162float(p.beta_bf[(size_t)k * p.ldb + grow]), mean);
           }
-          const float var = acc0 / (float)p.B;  // biased batch variance of the centred logits
+          const float var = fmaxf(acc0, 0.f) / (float)p.B;  // biased batch variance of the centred logits
           float rstd, bias;
           if (p.use_running) {
             rstd = rsqrtf(p.running_var[grow] + p.bn_eps);
@@ -612,34 +800,45 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   if (warp == 2) tmem_dealloc<kTmemCols>(tmem);
 }
 
+// Shared-memory plan of one mode (host side; mirrors the carve-up at the top of the kernel).
+struct SmemPlan {
+  int stages, p_bufs;
+  size_t bytes;
+};
+static bool plan_smem(int mode, int Kp, int max_smem, SmemPlan* out) {
+  const bool m2 = mode_has_mma2(mode);
+  const size_t tile = (size_t)Kp * 256, stile = (size_t)Kp * 2 * kBN, ptile = (size_t)kBN * 256;
+  const size_t base_fixed = 1024 + tile + (size_t)mode_sb_stages(mode) * kBN * sizeof(float4) + kBarRegion;
+  int p_bufs = m2 ? 2 : 0;
+  if (m2 && (size_t)max_smem < base_fixed + 2 * ptile + 2 * stile) p_bufs = 1;  // large Kp: single P tile
+  const size_t fixed = base_fixed + ptile * (size_t)p_bufs;
+  if ((size_t)max_smem < fixed + 2 * stile) return false;
+  int stages = (int)(((size_t)max_smem - fixed) / stile);
+  if (stages > kMaxStages) stages = kMaxStages;
+  out->stages = stages;
+  out->p_bufs = p_bufs;
+  out->bytes = fixed + (size_t)stages * stile;
+  return true;
+}
+
 template <int kMode>
 static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, SweepParams& p,
                         cudaStream_t stream) {
-  constexpr bool kHasMMA2 = (kMode == ROW_GRAD || kMode == COL_GRAD);
-  constexpr int kBN = (kHasMMA2 && GF_GRAD_BN == 64) ? 64 : 128;
-  const size_t tile = (size_t)p.Kp * 256, stile = (size_t)p.Kp * 2 * kBN, ptile = (size_t)kBN * 256;
   int max_smem = 0, dev = 0;
   GF_CUDA_CHECK(cudaGetDevice(&dev));
   GF_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  const size_t sb_stages = (kHasMMA2 && kBN == 128) ? 2 : kSbStagesMax;
-  const size_t base_fixed = 1024 + tile + sb_stages * kBN * sizeof(float4) + kBarRegion;
-  p.p_bufs = kHasMMA2 ? 2 : 0;
-  if (kHasMMA2 && (size_t)max_smem < base_fixed + 2 * ptile + 2 * stile) p.p_bufs = 1;  // large Kp: single P tile
-  const size_t fixed = base_fixed + ptile * (size_t)p.p_bufs;
-  int stages = (int)(((size_t)max_smem - fixed) / stile);
-  if (stages > kMaxStages) stages = kMaxStages;
-  GF_ARG_CHECK(stages >= 2, "n_components too large for the fused decoder sweeps (need Kp <= 240)");
-  p.stages = stages;
-  size_t smem = fixed + (size_t)stages * stile;
-  if (kHasMMA2 && smem < 120 * 1024) smem = 120 * 1024;  // 512 TMEM columns => one CTA per SM
+  SmemPlan plan;
+  GF_ARG_CHECK(plan_smem(kMode, p.Kp, max_smem, &plan),
+               "n_components too large for the fused decoder sweeps (need Kp <= 240)");
+  p.stages = plan.stages;
+  p.p_bufs = plan.p_bufs;
   auto kern = sweep_kernel<kMode>;
-  GF_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  GF_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.bytes));
   const int total = p.n_stat * p.n_chunks;
-  const int occ = 1;  // 12 warps with up to 168 registers each: one CTA per SM
-  int grid = num_sms() * occ;
+  int grid = num_sms();  // 12 warps with up to 168 registers each: one CTA per SM
   if (grid > total) grid = total;
   if (grid < 1) grid = 1;
-  kern<<<grid, kThreads, smem, stream>>>(tm_theta, tm_beta, p);
+  kern<<<grid, kThreads, plan.bytes, stream>>>(tm_theta, tm_beta, p);
   GF_LAUNCHED();
   return GF_OK;
 }
@@ -651,31 +850,16 @@ static int dispatch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_bet
     case ROW_LSE: return launch_sweep<ROW_LSE>(tm_theta, tm_beta, p, stream);
     case ROW_GRAD: return launch_sweep<ROW_GRAD>(tm_theta, tm_beta, p, stream);
     case COL_STATS: return launch_sweep<COL_STATS>(tm_theta, tm_beta, p, stream);
+    case COL_STATS2: return launch_sweep<COL_STATS2>(tm_theta, tm_beta, p, stream);
     case COL_GRAD: return launch_sweep<COL_GRAD>(tm_theta, tm_beta, p, stream);
     case COL_LOGITS: return launch_sweep<COL_LOGITS>(tm_theta, tm_beta, p, stream);
+    case ROW_LSE2: return launch_sweep<ROW_LSE2>(tm_theta, tm_beta, p, stream);
+    case COL_GRAD2: return launch_sweep<COL_GRAD2>(tm_theta, tm_beta, p, stream);
+    case ROW_GRAD2: return launch_sweep<ROW_GRAD2>(tm_theta, tm_beta, p, stream);
     default: break;
   }
   fprintf(stderr, "[gfedntm] dec sweep: unsupported mode %d\n", p.mode);
   return GF_ERR_ARG;
-}
-
-// Number of persistent CTAs the ROW modes of this configuration will run (for chunk planning).
-static int sweep_grid_capacity(int mode, int Kp) {
-  const bool m2 = (mode == ROW_GRAD || mode == COL_GRAD);
-  const size_t tile = (size_t)Kp * 256;
-  int max_smem = 232448;
-  const int bn = (m2 && GF_GRAD_BN == 64) ? 64 : 128;
-  const size_t stile = (size_t)Kp * 2 * bn;
-  const size_t sb_stages = (m2 && bn == 128) ? 2 : kSbStagesMax;
-  const size_t base_fixed = 1024 + tile + sb_stages * bn * sizeof(float4) + kBarRegion;
-  const size_t ptile = (size_t)bn * 256;
-  const size_t fixed = base_fixed + (m2 ? (((size_t)max_smem < base_fixed + 2 * ptile + 2 * stile) ? 1 : 2) * ptile : 0);
-  int stages = (int)(((size_t)max_smem - fixed) / stile);
-  if (stages > kMaxStages) stages = kMaxStages;
-  if (stages < 2) stages = 2;
-  const size_t smem = fixed + (size_t)stages * stile;
-  const int occ = 1;
-  return num_sms() * occ;
 }
 
 }  // namespace gf
@@ -685,9 +869,10 @@ using namespace gf;
 // Vocabulary split for the ROW modes: the smallest chunk count whose (document tiles x chunks) work
 // items fill the persistent grid in whole waves (>= 95 % wave efficiency), so no SM idles in the tail.
 extern "C" int gf_dec_row_chunks(int mode, int B, int V, int Kp) {
-  const int bn = (mode == ROW_GRAD && GF_GRAD_BN == 64) ? 64 : 128;
-  const int doc_tiles = (B + kTile - 1) / kTile, word_tiles = (V + bn - 1) / bn;
-  const int grid = sweep_grid_capacity(mode, Kp);
+  (void)mode;
+  (void)Kp;
+  const int doc_tiles = (B + kTile - 1) / kTile, word_tiles = (V + kBN - 1) / kBN;
+  const int grid = num_sms();
   int best = 1;
   double best_eff = 0.0;
   const int cmax = word_tiles < 4 * grid ? word_tiles : 4 * grid;
@@ -710,23 +895,28 @@ extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
   GF_ARG_CHECK(a->Kp % 16 == 0 && a->Kp >= 16 && a->Kp <= 240, "Kp must be a multiple of 16 in [16,240]");
   GF_ARG_CHECK(a->K <= a->Kp && a->K > 0, "K");
   GF_ARG_CHECK(a->ld_theta % 8 == 0 && a->ld_beta % 8 == 0, "bf16 leading dims must be multiples of 8");
-  GF_ARG_CHECK(a->ld_theta >= a->B && a->ld_beta >= a->V, "leading dims too small");
-  GF_ARG_CHECK(a->mode >= 0 && a->mode <= 5, "mode");
+  GF_ARG_CHECK(a->mode >= 0 && a->mode <= 9, "mode");
+  // Tensor extents along the contiguous axis: B / V by default (columns beyond read as zero); the
+  // folded modes pass the padded widths so padded documents / words read their masking rows.
+  const int theta_cols = a->theta_cols > 0 ? a->theta_cols : a->B;
+  const int beta_cols = a->beta_cols > 0 ? a->beta_cols : a->V;
+  GF_ARG_CHECK(a->ld_theta >= theta_cols && a->ld_beta >= beta_cols && theta_cols >= a->B && beta_cols >= a->V,
+               "leading dims too small");
   CUtensorMap tm_theta, tm_beta;
-  // theta_c^T [Kp, ld_theta] bf16: box = 64 documents x Kp topics; documents beyond B read as zero
-  int rc = make_tmap_bf16_2d(&tm_theta, a->theta_bf, (uint64_t)a->B, (uint64_t)a->Kp,
+  // theta_c^T [Kp, ld_theta] bf16: box = 64 documents x Kp topics
+  int rc = make_tmap_bf16_2d(&tm_theta, a->theta_bf, (uint64_t)theta_cols, (uint64_t)a->Kp,
                              (uint64_t)a->ld_theta * 2, 64, (uint32_t)a->Kp);
   if (rc) return rc;
-  // beta [Kp, ld_beta] bf16: box = 64 words x Kp topics; words beyond V read as zero
-  rc = make_tmap_bf16_2d(&tm_beta, a->beta_bf, (uint64_t)a->V, (uint64_t)a->Kp,
+  // beta [Kp, ld_beta] bf16: box = 64 words x Kp topics
+  rc = make_tmap_bf16_2d(&tm_beta, a->beta_bf, (uint64_t)beta_cols, (uint64_t)a->Kp,
                          (uint64_t)a->ld_beta * 2, 64, (uint32_t)a->Kp);
   if (rc) return rc;
 
   SweepParams p{};
   p.mode = a->mode;
   p.B = a->B; p.V = a->V; p.K = a->K; p.Kp = a->Kp;
-  const bool row = (a->mode == ROW_LOGITS || a->mode == ROW_LSE || a->mode == ROW_GRAD);
-  const int bn = ((a->mode == ROW_GRAD || a->mode == COL_GRAD) && GF_GRAD_BN == 64) ? 64 : 128;  // streamed tile width
+  const bool row = mode_is_row(a->mode);
+  const int bn = kBN;
   const int doc_tiles = (a->B + kTile - 1) / kTile, word_tiles = (a->V + kTile - 1) / kTile;
   p.n_stat = row ? doc_tiles : word_tiles;
   p.n_stream = row ? (a->V + bn - 1) / bn : (a->B + bn - 1) / bn;
@@ -734,7 +924,35 @@ extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
   GF_ARG_CHECK(p.n_chunks >= 1 && p.n_chunks <= p.n_stream, "n_chunks");
   p.n_pass = (a->mode == COL_GRAD) ? 2 : 1;
   p.sb_stream = reinterpret_cast<const float4*>(a->sb_stream);
-  GF_ARG_CHECK(p.sb_stream != nullptr, "sb_stream (padded side band) is required");
+  GF_ARG_CHECK(p.sb_stream != nullptr || !mode_has_sb(a->mode), "sb_stream (padded side band) is required");
+  if (a->mode == COL_STATS2) {
+    p.n_ext = (a->Kp + kBN - 1) / kBN;
+    GF_ARG_CHECK(a->ext_col0 % kBN == 0 && a->ext_col0 >= a->B && a->ext_col0 + 2 * p.n_ext * kBN <= theta_cols,
+                 "ext_col0: the hi and lo C blocks must be tile aligned and inside theta_cols");
+    p.ext_tile0 = a->ext_col0 / kBN;
+    p.n_stream = 2 * p.n_ext;
+    GF_ARG_CHECK(a->betaT_bf != nullptr, "betaT_bf");
+    p.betaT_bf = reinterpret_cast<const __nv_bfloat16*>(a->betaT_bf);
+  }
+  if (a->mode == COL_GRAD2) {
+    p.n_ext = (a->Kp + kBN - 1) / kBN;
+    GF_ARG_CHECK(a->ext_col0 % kBN == 0 && a->ext_col0 >= a->B && a->ext_col0 + p.n_ext * kBN <= theta_cols,
+                 "ext_col0: pseudo-document block must be tile aligned and inside theta_cols");
+    p.ext_tile0 = a->ext_col0 / kBN;
+    GF_ARG_CHECK(a->betaT_bf != nullptr, "betaT_bf");
+    p.betaT_bf = reinterpret_cast<const __nv_bfloat16*>(a->betaT_bf);
+    p.beta3 = reinterpret_cast<__nv_bfloat16*>(a->beta3);
+    p.ld3 = a->ld_beta3;
+    p.ldc = a->ld_corr;
+    GF_ARG_CHECK(a->corr == nullptr || a->ld_corr >= a->V, "ld_corr");
+  }
+  if (a->mode == ROW_GRAD2) {
+    // pseudo-word tiles: M hi then M lo (tile aligned) behind the padded vocabulary of beta'
+    p.n_ext = 2 * ((a->Kp + kBN - 1) / kBN);
+    GF_ARG_CHECK(a->ext_col0 % kBN == 0 && a->ext_col0 >= a->V && a->ext_col0 + p.n_ext * kBN <= beta_cols,
+                 "ext_col0: the M hi/lo blocks must be tile aligned and inside beta_cols");
+    p.ext_tile0 = a->ext_col0 / kBN;
+  }
   p.out = a->out;
   p.lse_part = reinterpret_cast<float2*>(a->lse_part);
   p.doc_const = reinterpret_cast<const float2*>(a->doc_const);

@@ -186,6 +186,14 @@ __global__ void __launch_bounds__(256) dec_sparse_doc_kernel(const GfDecSparseAr
     if (a.loss != nullptr) atomicAdd(a.loss, (double)rl);
     if (doc_const != nullptr) doc_const[b] = make_float2(lse2, S * kLn2_s);
     if (sb_doc != nullptr) sb_doc[b] = make_float4(lse2, S, 0.f, 0.f);
+    if (a.thetaT_bf != nullptr) {
+      // folded sweeps: 2^(z - e) = S_b * p_bv with e = lse2 - log2 S; -e as a hi/lo bf16 pair
+      __nv_bfloat16* tT = reinterpret_cast<__nv_bfloat16*>(a.thetaT_bf);
+      const float ne = (S > 0.f) ? (log2f(S) - lse2) : -30000.f;
+      const __nv_bfloat16 hi = __float2bfloat16(ne);
+      tT[(size_t)(a.K + 2) * a.ldT + b] = hi;
+      tT[(size_t)(a.K + 3) * a.ldT + b] = __float2bfloat16(ne - __bfloat162float(hi));
+    }
   }
 }
 
@@ -215,6 +223,52 @@ __global__ void __launch_bounds__(256) csc_corr_kernel(const int* __restrict__ c
   for (int c = 0; c < kMaxKp / 32; ++c) {
     const int k = c * 32 + lane;
     if (k < Kp) corr[(size_t)v * Kp + k] = acc[c];
+  }
+}
+
+// Same sums, written transposed (corrT[k, v]) so that a reader whose threads own consecutive words
+// gets coalesced rows: a block covers 32 consecutive words (4 per warp), stages the [32 x Kp] block in
+// shared memory and writes 128-byte rows.  Words without entries are not written.
+__global__ void __launch_bounds__(256) csc_corr_t_kernel(const int* __restrict__ colptr, const int* __restrict__ csc_row,
+                                                         const int* __restrict__ csc_src, const float* __restrict__ tnnz,
+                                                         const __nv_bfloat16* __restrict__ theta_bf, int ld_theta,
+                                                         float* __restrict__ corrT, int ldc, int V, int Kp) {
+  __shared__ float tile[32][kMaxKp + 1];
+  __shared__ int nonempty[32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int v0 = blockIdx.x * 32;
+  for (int i = 0; i < 4; ++i) {
+    const int wl = warp * 4 + i, v = v0 + wl;
+    int e0 = 0, e1 = 0;
+    if (v < V) {
+      e0 = colptr[v];
+      e1 = colptr[v + 1];
+    }
+    if (lane == 0) nonempty[wl] = e1 > e0;
+    if (e1 == e0) continue;
+    float acc[kMaxKp / 32];
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) acc[c] = 0.f;
+    for (int e = e0; e < e1; ++e) {
+      const int b = csc_row[e];
+      const float w = tnnz[csc_src[e]];
+      const __nv_bfloat16* tr = theta_bf + (size_t)b * ld_theta;
+#pragma unroll
+      for (int c = 0; c < kMaxKp / 32; ++c) {
+        const int k = c * 32 + lane;
+        if (k < Kp) acc[c] = fmaf(w, __bfloat162float(tr[k]), acc[c]);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < kMaxKp / 32; ++c) {
+      const int k = c * 32 + lane;
+      if (k < Kp) tile[wl][k] = acc[c];
+    }
+  }
+  __syncthreads();
+  const int v = v0 + lane;
+  if (v < V && nonempty[lane]) {
+    for (int k = warp; k < Kp; k += 8) corrT[(size_t)k * ldc + v] = tile[lane][k];
   }
 }
 
@@ -513,6 +567,17 @@ extern "C" int gf_csc_corr(const int* colptr, const int* csc_row, const int* csc
   csc_corr_kernel<<<((size_t)V * 32 + 255) / 256, 256, 0, st>>>(colptr, csc_row, csc_src, tnnz,
                                                                 reinterpret_cast<const __nv_bfloat16*>(theta_bf), ld_theta,
                                                                 corr, V, Kp);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_csc_corr_t(const int* colptr, const int* csc_row, const int* csc_src, const float* tnnz,
+                             const void* theta_bf, int ld_theta, float* corrT, int ldc, int V, int Kp, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(Kp <= kMaxKp && ldc >= V, "Kp / ldc");
+  csc_corr_t_kernel<<<(V + 31) / 32, 256, 0, st>>>(colptr, csc_row, csc_src, tnnz,
+                                                   reinterpret_cast<const __nv_bfloat16*>(theta_bf), ld_theta, corrT,
+                                                   ldc, V, Kp);
   GF_LAUNCHED();
   return GF_OK;
 }

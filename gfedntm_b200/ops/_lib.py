@@ -30,6 +30,8 @@ class GfSweepArgs(C.Structure):
         ("bn_eps", _f), ("bn_momentum", _f), ("use_running", _i),
         ("asp", _p), ("csp", _p), ("dbeta", _p), ("ld_dbeta", _i),
         ("corr", _p), ("colptr", _p),
+        ("theta_cols", _i), ("beta_cols", _i), ("ext_col0", _i),
+        ("betaT_bf", _p), ("beta3", _p), ("ld_beta3", _i), ("ld_corr", _i),
     ]
 
 
@@ -109,6 +111,7 @@ class GfDecSparseArgs(C.Structure):
         ("gscale", _f),
         ("rl", _p), ("loss", _p), ("asp", _p), ("csp", _p), ("tnnz", _p), ("dtheta", _p),
         ("doc_const", _p), ("sb_doc", _p),
+        ("thetaT_bf", _p), ("ldT", _i), ("K", _i),
     ]
 
 
@@ -158,6 +161,16 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_enc_fwd.argtypes = [C.POINTER(GfEncArgs), _p]
     lib.gf_latent_fwd.argtypes = [C.POINTER(GfLatentArgs), _p]
     lib.gf_theta_center.argtypes = [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]
+    lib.gf_theta_center_fold.argtypes = [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]
+    lib.gf_scale_beta.argtypes = [_p, _i, _p, _p, _i, _i, _i, _i, _i, _p]
+    lib.gf_theta_gram.argtypes = [_p, _i, _i, _i, _p, _i, _i, _i, _p, _p]
+    lib.gf_gram_parts.argtypes = []
+    lib.gf_gram_parts.restype = _i
+    lib.gf_gram.argtypes = [_p, _i, _p, _i, _i, _i, _p, _p]
+    lib.gf_gram_finish.argtypes = [_p, _i, _i, _i, _p, _i, _i, _i, _p]
+    lib.gf_csc_corr_t.argtypes = [_p, _p, _p, _p, _p, _i, _p, _i, _i, _i, _p]
+    for fn in ("gf_theta_center_fold", "gf_scale_beta", "gf_theta_gram", "gf_gram", "gf_gram_finish", "gf_csc_corr_t"):
+        getattr(lib, fn).restype = _i
     lib.gf_dec_row_chunks.argtypes = [_i, _i, _i, _i]
     lib.gf_dec_row_chunks.restype = _i
     lib.gf_latent_bwd.argtypes = [C.POINTER(GfLatentBwdArgs), _p]

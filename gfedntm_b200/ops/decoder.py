@@ -4,18 +4,25 @@ composed from the sm_100a kernels.  Nothing of size [B,V] is ever materialised.
 Ref: avitm_network/decoder_network.py:121-126, avitm.py:225 and their autograd
 (`loss.backward()` in federated_avitm.py:75).
 
-Kernel sequence of one training step (see csrc/dec_sweep.cu for the operand families):
+Kernel sequence of one training step (see csrc/dec_sweep.cu for the operand families and
+csrc/fold_ops.cu for the algebra that folds every epilogue constant into the GEMM operands):
 
-  theta_center     theta_c = bf16(theta - mean_b theta)
-  COL_STATS        per-word batch variance of the centred logits -> rstd, running stats
-  ROW_LSE          per-document log-sum-exp partials over vocabulary chunks
-  dec_sparse_doc   non-zeros: RL, S_b, sparse d theta, sparse BN-backward sums
-  csc_corr         sparse correction of d beta (through the CSC of the minibatch)
-  COL_GRAD         pass 1: BN-backward column means; pass 2: d beta
-  ROW_GRAD         d theta (dense part, atomically added to the sparse part)
+  theta_center_fold  theta_c = bf16(theta - mean_b theta), plus the constant rows of theta_c^T
+  theta_gram         C = theta_c^T theta_c appended to theta_c^T as pseudo documents (bf16 hi + lo)
+  COL_STATS2         per-word batch variance beta_v^T C beta_v / B -> rstd, running stats
+  scale_beta         beta' = bf16(beta * rstd*log2e) with bias / ones rows
+  ROW_LSE2           per-document log-sum-exp partials over vocabulary chunks
+  dec_sparse_doc     non-zeros: RL, S_b, sparse d theta, sparse BN-backward sums, -e_b rows
+  csc_corr           sparse correction of d beta (through the CSC of the minibatch)
+  COL_GRAD2          one pass: BN-backward constants and d beta; beta3 = gamma-scaled beta
+  gram, gram_finish  M = beta diag(gamma) beta^T, a = beta.alpha (split-V tcgen05 GEMM) -> pseudo-word tiles
+  ROW_GRAD2          d theta += ln2 * P . beta'^T - (a + theta_c M)   (dense part)
+
+``GFEDNTM_DECODER_V1=1`` selects the earlier side-band sweeps (ROW_LSE / COL_GRAD / ROW_GRAD).
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Optional
 
@@ -88,8 +95,20 @@ class ProdLDADecoder:
         f32 = dict(dtype=torch.float32, device=dev)
         self.Bpad = round_up(max_B, TILE)
         self.Vpad = round_up(V, TILE)
-        self.theta_bf = torch.zeros(max_B, self.Kp, dtype=torch.bfloat16, device=dev)        # sparse kernels
-        self.thetaT_bf = torch.zeros(self.Kp, round_up(max_B, 8), dtype=torch.bfloat16, device=dev)  # sweeps
+        self.folded = os.environ.get("GFEDNTM_DECODER_V1", "0") != "1"
+        self.n_ext = (self.Kp + TILE - 1) // TILE          # pseudo-document tiles holding C = theta_c^T theta_c
+        self.ext_col0 = self.Bpad
+        bf = dict(dtype=torch.bfloat16, device=dev)
+        self.theta_bf = torch.zeros(max_B, self.Kp, **bf)                                # sparse kernels
+        self.thetaT_bf = torch.zeros(self.Kp, self.Bpad + 2 * self.n_ext * TILE, **bf)  # sweeps (+ C hi, C lo)
+        if self.folded:
+            # scaled operand shadow (per step) + pseudo-word blocks holding M hi / lo for ROW_GRAD2
+            self.beta_s = torch.zeros(self.Kp, self.Vpad + 2 * self.n_ext * TILE, **bf)
+            self.corrT = torch.zeros(self.Kp, round_up(V, 8), **f32)
+            self.beta3 = torch.zeros(self.Kp, round_up(V, 8), **bf)       # gamma-scaled beta (per step)
+            self.gram_parts = K_.gram_parts()
+            self.gram_partial = torch.zeros(self.gram_parts * self.Kp * self.Kp, **f32)
+            self.c_scratch = torch.zeros(K * K, **f32)
         self.theta_mean = torch.zeros(K, **f32)
         self.colc = torch.zeros(self.Vpad, 4, **f32)
         self.sb_doc = torch.zeros(self.Bpad, 4, **f32)
@@ -111,6 +130,55 @@ class ProdLDADecoder:
         """Runs the sweeps.  Returns (rl[B], dtheta[B,Kp] or None).  ``dbeta`` [K,ld] is overwritten."""
         B, V, Kt = batch.B, self.V, self.K
         assert B <= self.max_B
+        if not self.folded:
+            return self._forward_backward_v1(theta, theta_colsum, beta_bf, betaT_bf, batch, csc, training=training,
+                                             running_mean=running_mean, running_var=running_var, dbeta=dbeta,
+                                             loss=loss, gscale=gscale, need_grad=need_grad)
+        tcols = self.thetaT_bf.shape[1]
+        K_.theta_center_fold(theta, theta_colsum, self.theta_bf, self.thetaT_bf, self.theta_mean, B=B, K=Kt,
+                             Bpad=round_up(B, TILE), center=training)
+        K_.theta_gram(self.theta_bf, self.thetaT_bf, self.c_scratch, B=B, K=Kt, ext_col0=self.ext_col0,
+                      lo_col0=self.ext_col0 + self.n_ext * TILE)
+        K_.dec_sweep(K_.COL_STATS2, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=beta_bf, colc=self.colc,
+                     theta_mean=self.theta_mean if training else None,
+                     running_mean=running_mean, running_var=running_var, bn_eps=self.bn_eps,
+                     bn_momentum=self.bn_momentum, use_running=not training, theta_cols=tcols,
+                     ext_col0=self.ext_col0, betaT_bf=betaT_bf)
+        K_.scale_beta(beta_bf, self.colc, self.beta_s[:, :self.Vpad], K=Kt, V=V)
+        n_chunks = K_.default_row_chunks(B, V, Kp=self.Kp)
+        K_.dec_sweep(K_.ROW_LSE2, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=self.beta_s,
+                     n_chunks=n_chunks, lse_part=self.lse_part, theta_cols=tcols, beta_cols=self.Vpad)
+        bcols = self.beta_s.shape[1]
+        grad = need_grad and training
+        if grad:
+            self.asp_csp.zero_()
+        K_.dec_sparse_doc(B=B, n_chunks=n_chunks, indptr=batch.indptr, indices=batch.indices,
+                          counts=batch.counts, theta_bf=self.theta_bf, betaT_bf=betaT_bf, colc=self.colc,
+                          lse_part=self.lse_part, gscale=gscale, rl=self.rl, loss=loss,
+                          asp=self.asp_csp[0] if grad else None, csp=self.asp_csp[1] if grad else None,
+                          tnnz=self.tnnz if grad else None, dtheta=self.dtheta if grad else None,
+                          doc_const=None, sb_doc=None, thetaT_bf=self.thetaT_bf if grad else None, K=Kt)
+        if not grad:
+            return self.rl[:B], None
+        assert csc is not None and dbeta is not None
+        K_.csc_corr_t(csc.colptr, csc.row, csc.src, self.tnnz, self.theta_bf, self.corrT, V=V)
+        K_.dec_sweep(K_.COL_GRAD2, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=self.beta_s,
+                     colc=self.colc, asp=self.asp_csp[0], csp=self.asp_csp[1], dbeta=dbeta, corr=self.corrT,
+                     colptr=csc.colptr, theta_cols=tcols, beta_cols=self.Vpad, ext_col0=self.ext_col0,
+                     betaT_bf=betaT_bf, beta3=self.beta3)
+        K_.gram(self.beta3, beta_bf, self.gram_partial, V=V)
+        K_.gram_finish(self.gram_partial, self.gram_parts, self.beta_s, K=Kt, col_hi=self.Vpad,
+                       col_lo=self.Vpad + self.n_ext * TILE)
+        n_chunks_g = K_.default_row_chunks(B, V, second_mma=True, Kp=self.Kp)
+        K_.dec_sweep(K_.ROW_GRAD2, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=self.beta_s,
+                     n_chunks=n_chunks_g, dtheta=self.dtheta, theta_cols=tcols, beta_cols=bcols,
+                     ext_col0=self.Vpad)
+        return self.rl[:B], self.dtheta[:B]
+
+    def _forward_backward_v1(self, theta, theta_colsum, beta_bf, betaT_bf, batch, csc, *, training,
+                             running_mean, running_var, dbeta, loss, gscale, need_grad):
+        """Earlier formulation: epilogue constants through the float4 side bands."""
+        B, V, Kt = batch.B, self.V, self.K
         K_.theta_center(theta, theta_colsum, self.theta_bf, self.thetaT_bf, self.theta_mean, B=B, K=Kt,
                         center=training)
         K_.dec_sweep(K_.COL_STATS, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=beta_bf,

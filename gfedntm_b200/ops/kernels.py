@@ -15,7 +15,9 @@ from . import _lib
 from ._lib import (GF_MAX_HIDDEN, GfDecSparseArgs, GfEncArgs, GfEncBwdArgs, GfLatentArgs,
                    GfLatentBwdArgs, GfSweepArgs, check)
 
-ROW_LOGITS, ROW_LSE, ROW_GRAD, COL_STATS, COL_GRAD, COL_LOGITS = range(6)
+(ROW_LOGITS, ROW_LSE, ROW_GRAD, COL_STATS, COL_GRAD, COL_LOGITS, ROW_LSE2, COL_GRAD2, ROW_GRAD2,
+ COL_STATS2) = range(10)
+FOLD_ROWS = 4  # spare operand rows above K: bias hi/lo and the -e_b hi/lo pair of the folded sweeps
 TILE = 128
 LOG2E = 1.4426950408889634
 LN2 = 0.6931471805599453
@@ -40,8 +42,8 @@ def round_up(x: int, m: int) -> int:
 
 
 def padded_topics(k: int) -> int:
-    """Topics padded to the UMMA K granularity (16)."""
-    return round_up(k, 16)
+    """Topics plus the four constant rows of the folded sweeps, padded to the UMMA K granularity (16)."""
+    return round_up(k + FOLD_ROWS, 16)
 
 
 def default_row_chunks(B: int, V: int, second_mma: bool = False, Kp: int = 64) -> int:
@@ -55,10 +57,11 @@ def default_row_chunks(B: int, V: int, second_mma: bool = False, Kp: int = 64) -
 # decoder sweeps
 # ----------------------------------------------------------------------------------------------
 def dec_sweep(mode: int, *, B: int, V: int, K: int, theta_bf: torch.Tensor, beta_bf: torch.Tensor,
-              sb_stream: torch.Tensor, n_chunks: int = 1, out=None, lse_part=None, doc_const=None,
-              dtheta=None, colc=None, theta_mean=None, running_mean=None, running_var=None,
+              sb_stream: Optional[torch.Tensor] = None, n_chunks: int = 1, out=None, lse_part=None,
+              doc_const=None, dtheta=None, colc=None, theta_mean=None, running_mean=None, running_var=None,
               bn_eps: float = 1e-5, bn_momentum: float = 0.1, use_running: bool = False, asp=None,
-              csp=None, dbeta=None, corr=None, colptr=None) -> None:
+              csp=None, dbeta=None, corr=None, colptr=None, theta_cols: int = 0, beta_cols: int = 0,
+              ext_col0: int = 0, betaT_bf=None, beta3=None) -> None:
     lib = _lib.load()
     Kp = beta_bf.shape[0]
     assert theta_bf.dtype == torch.bfloat16 and beta_bf.dtype == torch.bfloat16
@@ -77,6 +80,10 @@ def dec_sweep(mode: int, *, B: int, V: int, K: int, theta_bf: torch.Tensor, beta
     a.asp, a.csp = _ptr(asp), _ptr(csp)
     a.dbeta, a.ld_dbeta = _ptr(dbeta), (dbeta.stride(0) if dbeta is not None else 0)
     a.corr, a.colptr = _ptr(corr), _ptr(colptr)
+    a.theta_cols, a.beta_cols, a.ext_col0 = theta_cols, beta_cols, ext_col0
+    a.betaT_bf, a.beta3 = _ptr(betaT_bf), _ptr(beta3)
+    a.ld_beta3 = beta3.stride(0) if beta3 is not None else 0
+    a.ld_corr = corr.stride(0) if corr is not None else 0
     check(lib.gf_dec_sweep(C.byref(a), _stream()), "gf_dec_sweep")
 
 
@@ -139,6 +146,46 @@ def theta_center(theta, colsum, out_bf16, outT_bf16, mean_out, *, B: int, K: int
                               out_bf16.stride(0), outT_bf16.stride(0), int(center), _stream()), "gf_theta_center")
 
 
+def theta_center_fold(theta, colsum, out_bf16, outT_bf16, mean_out, *, B: int, K: int, Bpad: int,
+                      center: bool) -> None:
+    """theta_center plus the constant rows of the folded sweeps (ones, zeroed e rows, padded-doc mask)."""
+    lib = _lib.load()
+    check(lib.gf_theta_center_fold(_ptr(theta), _ptr(colsum), _ptr(out_bf16), _ptr(outT_bf16), _ptr(mean_out),
+                                   B, K, out_bf16.stride(0), outT_bf16.stride(0), Bpad, int(center), _stream()),
+          "gf_theta_center_fold")
+
+
+def scale_beta(beta_bf, colc, out, *, K: int, V: int) -> None:
+    """out = bf16(beta * rstd*log2e) + bias / ones rows (operand of the folded sweeps)."""
+    lib = _lib.load()
+    check(lib.gf_scale_beta(_ptr(beta_bf), beta_bf.stride(0), _ptr(colc), _ptr(out), out.stride(0), K,
+                            out.shape[0], V, out.shape[1], _stream()), "gf_scale_beta")
+
+
+def theta_gram(theta_bf, thetaT_bf, c_scratch, *, B: int, K: int, ext_col0: int, lo_col0: int) -> None:
+    """C = theta_c^T theta_c as bf16 hi/lo pseudo-document blocks of theta_c^T (c_scratch stays zeroed)."""
+    lib = _lib.load()
+    check(lib.gf_theta_gram(_ptr(theta_bf), theta_bf.stride(0), B, K, _ptr(thetaT_bf), thetaT_bf.stride(0),
+                            ext_col0, lo_col0, _ptr(c_scratch), _stream()), "gf_theta_gram")
+
+
+def gram_parts() -> int:
+    return int(_lib.load().gf_gram_parts())
+
+
+def gram(x_bf, y_bf, partial, *, V: int) -> None:
+    lib = _lib.load()
+    check(lib.gf_gram(_ptr(x_bf), x_bf.stride(0), _ptr(y_bf), y_bf.stride(0), V, x_bf.shape[0], _ptr(partial),
+                      _stream()), "gf_gram")
+
+
+def gram_finish(partial, n_parts: int, out_bf, *, K: int, col_hi: int, col_lo: int) -> None:
+    """Sums the Gram partials into M (row K = a) and stores it as bf16 hi/lo pseudo-word blocks of ``out_bf``."""
+    lib = _lib.load()
+    check(lib.gf_gram_finish(_ptr(partial), n_parts, K, out_bf.shape[0], _ptr(out_bf), out_bf.stride(0), col_hi,
+                             col_lo, _stream()), "gf_gram_finish")
+
+
 def latent_bwd(*, B: int, K: int, dtheta, mask_theta, theta_s, mu, logvar, eps, prior_mean,
                prior_var, kl_weight: float, gscale: float, dmu, dlv, bn_bsums, d_prior_mean,
                d_prior_var) -> None:
@@ -199,7 +246,8 @@ def step_begin(ctr: torch.Tensor, inc_rng: int = 1, inc_opt: int = 0) -> None:
 
 
 def dec_sparse_doc(*, B: int, n_chunks: int, indptr, indices, counts, theta_bf, betaT_bf, colc,
-                   lse_part, gscale: float, rl, loss, asp, csp, tnnz, dtheta, doc_const, sb_doc) -> None:
+                   lse_part, gscale: float, rl, loss, asp, csp, tnnz, dtheta, doc_const, sb_doc,
+                   thetaT_bf=None, K: int = 0) -> None:
     lib = _lib.load()
     a = GfDecSparseArgs()
     a.B, a.Kp, a.n_chunks = B, betaT_bf.shape[1], n_chunks
@@ -209,6 +257,8 @@ def dec_sparse_doc(*, B: int, n_chunks: int, indptr, indices, counts, theta_bf, 
     a.gscale = gscale
     a.rl, a.loss, a.asp, a.csp, a.tnnz = _ptr(rl), _ptr(loss), _ptr(asp), _ptr(csp), _ptr(tnnz)
     a.dtheta, a.doc_const, a.sb_doc = _ptr(dtheta), _ptr(doc_const), _ptr(sb_doc)
+    a.thetaT_bf = _ptr(thetaT_bf)
+    a.ldT, a.K = (thetaT_bf.stride(0) if thetaT_bf is not None else 0), K
     check(lib.gf_dec_sparse_doc(C.byref(a), _stream()), "gf_dec_sparse_doc")
 
 
@@ -216,6 +266,14 @@ def csc_corr(colptr, csc_row, csc_src, tnnz, theta_bf, corr, *, V: int) -> None:
     lib = _lib.load()
     check(lib.gf_csc_corr(_ptr(colptr), _ptr(csc_row), _ptr(csc_src), _ptr(tnnz), _ptr(theta_bf),
                           theta_bf.stride(0), _ptr(corr), V, corr.shape[1], _stream()), "gf_csc_corr")
+
+
+def csc_corr_t(colptr, csc_row, csc_src, tnnz, theta_bf, corrT, *, V: int) -> None:
+    """csc_corr with the result transposed: corrT [Kp, ldc >= V]."""
+    lib = _lib.load()
+    check(lib.gf_csc_corr_t(_ptr(colptr), _ptr(csc_row), _ptr(csc_src), _ptr(tnnz), _ptr(theta_bf),
+                            theta_bf.stride(0), _ptr(corrT), corrT.stride(0), V, corrT.shape[0], _stream()),
+          "gf_csc_corr_t")
 
 
 def csc_spmm(colptr, csc_row, csc_src, val, dense, out, *, V: int, N: int, accumulate: bool = False) -> None:

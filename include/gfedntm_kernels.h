@@ -37,7 +37,13 @@ enum GfSweepMode {
   GF_ROW_GRAD = 2,   /* dtheta[b,:] += sum_v dlogit[b,v] * beta[:,v]      (dense part)         */
   GF_COL_STATS = 3,  /* colc[v] = {rstd*log2e, bias, 0, 0}; running stats update               */
   GF_COL_GRAD = 4,   /* colc[v].zw = BN-backward constants; dbeta[:,v] = sum_b dlogit*theta_c  */
-  GF_COL_LOGITS = 5  /* same result as GF_ROW_LOGITS through the word-major operand family     */
+  GF_COL_LOGITS = 5, /* same result as GF_ROW_LOGITS through the word-major operand family     */
+  /* Folded modes (no side band): beta_bf is the SCALED shadow written by gf_scale_beta, theta_bf
+     carries the constant-one rows K, K+1 and the -e_b rows K+2, K+3 (see gf_theta_center).      */
+  GF_ROW_LSE2 = 6,   /* lse_part[b,chunk] = online (max2,sum) of 2^D1                           */
+  GF_COL_GRAD2 = 7,  /* one pass: colc[v].zw, dbeta[:,v], beta3 (gamma-scaled beta for gf_gram)  */
+  GF_ROW_GRAD2 = 8,  /* dtheta[b,:K] += ln2 * sum_v 2^D1[b,v] * beta'[:,v]                      */
+  GF_COL_STATS2 = 9  /* GF_COL_STATS from beta_v^T C beta_v (C hi/lo tiles at ext_col0 of theta_bf) */
 };
 
 typedef struct GfSweepArgs {
@@ -68,6 +74,15 @@ typedef struct GfSweepArgs {
   int ld_dbeta;
   const float* corr;     /* COL_GRAD: [V, Kp] sparse correction (subtracted), may be null       */
   const int* colptr;     /* COL_GRAD: [V+1] CSC pointer of the batch (required with corr)       */
+  /* --- folded modes --- */
+  int theta_cols;        /* readable columns of theta_bf (0 => B): padded documents + pseudo docs */
+  int beta_cols;         /* readable columns of beta_bf (0 => V): vocabulary padded to 128        */
+  int ext_col0;          /* COL_STATS2 / COL_GRAD2: first column of the C = theta_c^T theta_c block (hi, then lo)
+                            in theta_bf; ROW_GRAD2: first column of the M hi / lo blocks in beta_bf   */
+  const void* betaT_bf;  /* COL_GRAD2: [V, Kp] bf16 UNSCALED beta^T                               */
+  void* beta3;           /* COL_GRAD2 out: [Kp, ld_beta3] bf16, rows k<K gamma_v*beta[k,v], row K alpha_v */
+  int ld_beta3;
+  int ld_corr;           /* COL_GRAD2: corr is TRANSPOSED, [Kp, ld_corr] (gf_csc_corr_t)                */
 } GfSweepArgs;
 
 int gf_dec_sweep(const GfSweepArgs* args, void* stream);
@@ -137,6 +152,30 @@ int gf_latent_fwd(const GfLatentArgs* args, void* stream);
  * outT_bf16 [Kp, ldT] (row per topic, documents contiguous; tensor-core sweeps).               */
 int gf_theta_center(const float* theta, const float* colsum, void* out_bf16, void* outT_bf16,
                     float* mean_out, int B, int K, int ld, int ldT, int center, void* stream);
+/* Same, plus the folded-mode rows of outT for all documents up to Bpad (multiple of 128, <= ldT):
+   rows K, K+1 = 1; rows K+2, K+3 = 0 for b < B (filled in by gf_dec_sparse_doc) and row K+2 =
+   -30000 for padded documents (their probabilities vanish).  Needs ld >= K + 4.                 */
+int gf_theta_center_fold(const float* theta, const float* colsum, void* out_bf16, void* outT_bf16,
+                         float* mean_out, int B, int K, int ld, int ldT, int Bpad, int center, void* stream);
+/* Scaled operand shadow for the folded sweeps: out[k,v] = bf16(beta_bf[k,v] * colc[v].x) for k < K,
+   rows K, K+1 = hi/lo bf16 split of colc[v].y, rows K+2, K+3 = 1; words v in [V, cols) get row K =
+   -30000 and zeros elsewhere.  colc is the float4 array written by GF_COL_STATS.                */
+int gf_scale_beta(const void* beta_bf, int ld_beta, const void* colc, void* out, int ld_out, int K, int Kp,
+                  int V, int cols, void* stream);
+/* C = theta_c^T theta_c (fp32 accumulate) written as a bf16 hi / lo pair into outT[j, ext_col0 + k]
+   and outT[j, lo_col0 + k], j,k < K.  c_scratch: [K*K] fp32, zero on entry, left zero on return.  */
+int gf_theta_gram(const void* theta_bf, int ld, int B, int K, void* outT_bf16, int ldT, int ext_col0,
+                  int lo_col0, float* c_scratch, void* stream);
+/* Split-V tcgen05 GEMM: partial[g] [Kp,Kp] = sum over the CTA's words of x[:,v] y[:,v]^T
+   (x = beta3 of GF_COL_GRAD2, y = unscaled beta shadow), each partial stored TRANSPOSED.
+   partial must hold gf_gram_parts()*Kp*Kp floats. */
+int gf_gram_parts(void);
+int gf_gram(const void* x_bf, int ldx, const void* y_bf, int ldy, int V, int Kp, float* partial, void* stream);
+/* M = sum of the partials (rows j <= K; row K is a = beta.alpha) written as a bf16 hi / lo pair into
+   out[j, col_hi + k] and out[j, col_lo + k]: the pseudo-word blocks of beta' read by GF_ROW_GRAD2,
+   whose MMA1 then yields a_k + (theta_c M)[b,k] (theta_c^T row K is the constant one).           */
+int gf_gram_finish(const float* partial, int n_parts, int K, int Kp, void* out_bf16, int ld_out, int col_hi,
+                   int col_lo, void* stream);
 
 typedef struct GfLatentBwdArgs {
   int B, K;
@@ -209,11 +248,16 @@ typedef struct GfDecSparseArgs {
   float* dtheta;                        /* out [B,Kp] sparse part (plain store); may be null   */
   void* doc_const;                      /* out float2 [B]                                      */
   void* sb_doc;                         /* out float4 [Bpad]                                   */
+  void* thetaT_bf; int ldT; int K;      /* folded modes: rows K+2, K+3 of theta_c^T receive the
+                                           hi/lo bf16 split of -(lse2_b - log2 S_b); may be null */
 } GfDecSparseArgs;
 int gf_dec_sparse_doc(const GfDecSparseArgs* args, void* stream);
 
 int gf_csc_corr(const int* colptr, const int* csc_row, const int* csc_src, const float* tnnz,
                 const void* theta_bf, int ld_theta, float* corr, int V, int Kp, void* stream);
+/* Same values, stored transposed: corrT[k, v] ([Kp, ldc], only words with entries are written).     */
+int gf_csc_corr_t(const int* colptr, const int* csc_row, const int* csc_src, const float* tnnz,
+                  const void* theta_bf, int ld_theta, float* corrT, int ldc, int V, int Kp, void* stream);
 /* out[v,:N] (+)= sum_{entries of column v} val[src] * dense[row,:N]                          */
 int gf_csc_spmm(const int* colptr, const int* csc_row, const int* csc_src, const float* val,
                 const float* dense, int ldd, float* out, int ldo, int V, int N, int accumulate,
