@@ -57,12 +57,14 @@ def _reference(theta, beta_bf, x, K, V, eps=1e-5):
     return rl.detach(), thc.grad, bb.grad, var
 
 
-@pytest.mark.parametrize("B,V,K", [(64, 1000, 10), (200, 5000, 50), (257, 2100, 100), (130, 3000, 200)])
-def test_prodlda_decoder_fwd_bwd(B, V, K):
+@pytest.mark.parametrize("folded", [True, False])
+@pytest.mark.parametrize("B,V,K", [(64, 1000, 10), (200, 5000, 50), (257, 2100, 100), (130, 3000, 200), (300, 1500, 13)])
+def test_prodlda_decoder_fwd_bwd(B, V, K, folded):
     from gfedntm_b200.ops.decoder import CscWorkspace, ProdLDADecoder
 
     theta, beta, x, beta_bf, betaT_bf, batch, Kx = _mk(B, V, K, seed=1)
-    dec = ProdLDADecoder(B, V, K, batch.nnz, "cuda")
+    dec = ProdLDADecoder(B, V, K, batch.nnz, "cuda", folded=folded)
+    assert dec.folded == folded
     csc = CscWorkspace(V, batch.nnz, "cuda")
     csc.build(batch)
     dbeta = torch.zeros(K, V, device="cuda")
@@ -109,3 +111,29 @@ def test_csr_to_csc_roundtrip():
     rows_of_src = torch.repeat_interleave(torch.arange(77, device="cuda"),
                                           (batch.indptr[1:] - batch.indptr[:-1]).long())
     assert torch.equal(rows_of_src[src], csc.row[: batch.nnz].long())
+
+
+@pytest.mark.parametrize("folded", [True, False])
+@pytest.mark.parametrize("B,V,K", [(96, 1300, 20), (257, 2100, 100)])
+def test_prodlda_decoder_eval_mode(B, V, K, folded):
+    """Inference path: BatchNorm with running statistics (non-zero bias rows in the folded operands)."""
+    from gfedntm_b200.ops.decoder import ProdLDADecoder
+
+    theta, beta, x, beta_bf, betaT_bf, batch, Kx = _mk(B, V, K, seed=5)
+    g = torch.Generator(device="cuda").manual_seed(11)
+    rm = torch.randn(V, device="cuda", generator=g) * 0.05
+    rv = torch.rand(V, device="cuda", generator=g) * 0.02 + 0.005
+    dec = ProdLDADecoder(B, V, K, batch.nnz, "cuda", folded=folded)
+    loss = torch.zeros(1, dtype=torch.float64, device="cuda")
+    rm0, rv0 = rm.clone(), rv.clone()
+    rl, dth = dec.forward_backward(theta, theta.sum(0), beta_bf, betaT_bf, batch, None, training=False,
+                                   running_mean=rm, running_var=rv, dbeta=None, loss=loss)
+    torch.cuda.synchronize()
+    assert dth is None
+    torch.testing.assert_close(rm, rm0)  # eval mode must not touch the running statistics
+    torch.testing.assert_close(rv, rv0)
+    logits = theta.to(torch.bfloat16).float() @ beta_bf[:K, :V].float()
+    y = F.batch_norm(logits, rm0, rv0, training=False, eps=1e-5)
+    rl_ref = -(x * torch.log(torch.softmax(y, 1) + 1e-10)).sum(1)
+    torch.testing.assert_close(rl, rl_ref, rtol=3e-3, atol=2e-2)
+    assert abs(loss.item() - rl_ref.sum().item()) <= 3e-3 * abs(rl_ref.sum().item())
