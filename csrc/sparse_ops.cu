@@ -21,50 +21,88 @@ __global__ void csc_hist_kernel(const int* __restrict__ indices, int nnz, int* _
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < nnz) atomicAdd(&count[indices[i] + 1], 1);
 }
-// exclusive scan of count[0..n] in place (count[0] == 0 on entry => colptr), single block.
-__global__ void __launch_bounds__(1024) scan_kernel(int* __restrict__ data, int n) {
+// In-place inclusive scan of data[0..n) (data[0] == 0 on entry => CSC column pointer), two kernels:
+// per-block sums of 4096-element segments, then every block adds the sums of its predecessors to a
+// local scan.  (A single-block version took 95 us at V = 200k.)
+constexpr int kScanSeg = 4096;
+__global__ void __launch_bounds__(1024) scan_sums_kernel(const int* __restrict__ data, int n, int* __restrict__ sums) {
+  __shared__ int warp_tot[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int i0 = blockIdx.x * kScanSeg + tid * 4;
+  int s = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) s += (i0 + j < n) ? data[i0 + j] : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) warp_tot[warp] = s;
+  __syncthreads();
+  if (warp == 0) {
+    int w = warp_tot[lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+    if (lane == 0) sums[blockIdx.x] = w;
+  }
+}
+__global__ void __launch_bounds__(1024) scan_apply_kernel(int* __restrict__ data, int n, const int* __restrict__ sums) {
   __shared__ int warp_tot[32];
   __shared__ int carry_s;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) carry_s = 0;
-  __syncthreads();
-  for (int base = 0; base < n; base += 1024 * 4) {
-    int v[4], s = 0;
-    const int i0 = base + tid * 4;
+  // carry = sum of the preceding segments
+  int c = 0;
+  for (int b = tid; b < (int)blockIdx.x; b += 1024) c += sums[b];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      v[j] = (i0 + j < n) ? data[i0 + j] : 0;
-      s += v[j];
-    }
-    int inc = s;
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if (lane == 0) warp_tot[warp] = c;
+  __syncthreads();
+  if (warp == 0) {
+    int w = warp_tot[lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+    if (lane == 0) carry_s = w;
+  }
+  __syncthreads();
+  const int carry = carry_s;
+  __syncthreads();
+  int v[4], s = 0;
+  const int i0 = blockIdx.x * kScanSeg + tid * 4;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    v[j] = (i0 + j < n) ? data[i0 + j] : 0;
+    s += v[j];
+  }
+  int inc = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) warp_tot[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    int w = warp_tot[lane];
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
+      const int t = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += t;
     }
-    if (lane == 31) warp_tot[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-      int w = warp_tot[lane];
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, w, o);
-        if (lane >= o) w += t;
-      }
-      warp_tot[lane] = w;
-    }
-    __syncthreads();
-    const int carry = carry_s;
-    int run = carry + (warp > 0 ? warp_tot[warp - 1] : 0) + inc - s;  // exclusive prefix of this thread
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      run += v[j];
-      if (i0 + j < n) data[i0 + j] = run;  // inclusive => data[i] = sum_{<=i}; with data[0]=0 this is colptr
-    }
-    __syncthreads();
-    if (tid == 1023) carry_s = run;
-    __syncthreads();
+    warp_tot[lane] = w;
   }
+  __syncthreads();
+  int run = carry + (warp > 0 ? warp_tot[warp - 1] : 0) + inc - s;  // exclusive prefix of this thread
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    run += v[j];
+    if (i0 + j < n) data[i0 + j] = run;
+  }
+}
+// scratch: >= ceil(n / 4096) ints, fully overwritten
+static int launch_scan(int* data, int n, int* scratch, cudaStream_t st) {
+  const int nb = (n + kScanSeg - 1) / kScanSeg;
+  scan_sums_kernel<<<nb, 1024, 0, st>>>(data, n, scratch);
+  GF_LAUNCHED();
+  scan_apply_kernel<<<nb, 1024, 0, st>>>(data, n, scratch);
+  GF_LAUNCHED();
+  return GF_OK;
 }
 __global__ void csc_scatter_kernel(const int* __restrict__ indptr, const int* __restrict__ indices, int B,
                                    const int* __restrict__ colptr, int* __restrict__ cursor,
@@ -511,13 +549,12 @@ extern "C" int gf_csr_to_csc(const int* indptr, const int* indices, int B, int V
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(B >= 0 && V > 0 && nnz >= 0, "sizes");
   GF_CUDA_CHECK(cudaMemsetAsync(colptr, 0, sizeof(int) * (size_t)(V + 1), st));
-  GF_CUDA_CHECK(cudaMemsetAsync(cursor_scratch, 0, sizeof(int) * (size_t)V, st));
   if (nnz > 0) {
     csc_hist_kernel<<<(nnz + 255) / 256, 256, 0, st>>>(indices, nnz, colptr);
     GF_LAUNCHED();
   }
-  scan_kernel<<<1, 1024, 0, st>>>(colptr, V + 1);
-  GF_LAUNCHED();
+  { const int rc = launch_scan(colptr, V + 1, cursor_scratch, st); if (rc) return rc; }
+  GF_CUDA_CHECK(cudaMemsetAsync(cursor_scratch, 0, sizeof(int) * (size_t)V, st));
   if (nnz > 0) {
     csc_scatter_kernel<<<(B * 32 + 255) / 256, 256, 0, st>>>(indptr, indices, B, colptr, cursor_scratch, csc_row, csc_src);
     GF_LAUNCHED();
@@ -538,13 +575,12 @@ extern "C" int gf_csr_to_csc_dyn(const int* indptr, const int* indices, int B, i
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(B >= 0 && V > 0 && nnz_capacity >= 0, "sizes");
   GF_CUDA_CHECK(cudaMemsetAsync(colptr, 0, sizeof(int) * (size_t)(V + 1), st));
-  GF_CUDA_CHECK(cudaMemsetAsync(cursor_scratch, 0, sizeof(int) * (size_t)V, st));
   if (nnz_capacity > 0) {
     gf::csc_hist_dyn_kernel<<<(nnz_capacity + 255) / 256, 256, 0, st>>>(indptr, B, indices, colptr);
     GF_LAUNCHED();
   }
-  scan_kernel<<<1, 1024, 0, st>>>(colptr, V + 1);
-  GF_LAUNCHED();
+  { const int rc = launch_scan(colptr, V + 1, cursor_scratch, st); if (rc) return rc; }
+  GF_CUDA_CHECK(cudaMemsetAsync(cursor_scratch, 0, sizeof(int) * (size_t)V, st));
   if (nnz_capacity > 0) {
     csc_scatter_kernel<<<(B * 32 + 255) / 256, 256, 0, st>>>(indptr, indices, B, colptr, cursor_scratch, csc_row, csc_src);
     GF_LAUNCHED();
