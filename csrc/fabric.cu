@@ -77,7 +77,8 @@ __device__ __forceinline__ void wait_peers(const GfFabricRank& me, int world, in
 }
 
 __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, AdamF h) {
-  __shared__ float tile[32][33];
+  __shared__ __align__(16) float tile_v[32 * 132];  // 32 x 128 (+4 pad) tile of the vectorised beta phase
+  float(*tile)[33] = reinterpret_cast<float(*)[33]>(tile_v);  // 32 x 32 view used by the scalar fallback
   __shared__ int is_last;
   const GfFabricRank& me = a.ranks[blockIdx.y];
   const int world = a.world, rank = me.rank;
@@ -159,7 +160,78 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
 
   // ---------------- phase B.3: beta [K,V] in 32x32 tiles, owner = contiguous range of word tiles;
   //                  writes fp32 beta, bf16 beta_bf [Kp,ldb] and bf16 betaT_bf [V,Kp] to every rank
-  if (a.K > 0) {
+  if (a.K > 0 && a.V % 4 == 0 && a.ldb % 4 == 0 && a.Kp % 16 == 0) {
+    // vectorised: 32 topics x 128 words per tile, float4 peer loads (all peers of a row in flight
+    // together), float4 / 8-byte / 32-byte stores to every rank
+    float(*tv)[132] = reinterpret_cast<float(*)[132]>(tile_v);
+    const int vt = (a.V + 127) / 128, kt = (a.K + 31) / 32;
+    const int per = (vt + world - 1) / world;
+    const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const long long n_tiles = (long long)(t_hi > t_lo ? t_hi - t_lo : 0) * kt;
+    for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      const int v0 = (t_lo + (int)(t / kt)) * 128, k0 = (int)(t % kt) * 32;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int k = k0 + ty + r * 8, vv = v0 + tx * 4;
+        float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k < a.K && vv < a.V) {
+          const long long ip = a.beta_off + (long long)k * a.V + vv;
+          float4 in[GF_MAX_RANKS];
+#pragma unroll
+          for (int c = 0; c < GF_MAX_RANKS; ++c)
+            if (c < world) in[c] = ld_peer_f4((a.mode == 0 ? me.G[c] : me.P[c]) + ip);
+          if (a.mode == 0) {
+            float4 gsum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int c = 0; c < GF_MAX_RANKS; ++c)
+              if (c < world) { gsum.x += in[c].x; gsum.y += in[c].y; gsum.z += in[c].z; gsum.w += in[c].w; }
+            val = *reinterpret_cast<const float4*>(me.P[rank] + ip);
+            float4 m = *reinterpret_cast<const float4*>(me.M + ip);
+            float4 v2 = *reinterpret_cast<const float4*>(me.V2 + ip);
+            val.x = adam_upd(val.x, gsum.x, m.x, v2.x, h);
+            val.y = adam_upd(val.y, gsum.y, m.y, v2.y, h);
+            val.z = adam_upd(val.z, gsum.z, m.z, v2.z, h);
+            val.w = adam_upd(val.w, gsum.w, m.w, v2.w, h);
+            *reinterpret_cast<float4*>(me.M + ip) = m;
+            *reinterpret_cast<float4*>(me.V2 + ip) = v2;
+          } else {
+#pragma unroll
+            for (int c = 0; c < GF_MAX_RANKS; ++c)
+              if (c < world) {
+                const float w = a.w[c];
+                val.x = fmaf(w, in[c].x, val.x); val.y = fmaf(w, in[c].y, val.y);
+                val.z = fmaf(w, in[c].z, val.z); val.w = fmaf(w, in[c].w, val.w);
+              }
+          }
+          __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
+                                            __float2bfloat16(val.z), __float2bfloat16(val.w)};
+          for (int c = 0; c < world; ++c) {
+            st_peer_f4(me.P[c] + ip, val);
+            if (me.beta_bf[c] != nullptr)
+              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c]) + (size_t)k * a.ldb + vv) =
+                  *reinterpret_cast<const uint2*>(o);
+          }
+        }
+        *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
+      }
+      __syncthreads();
+      const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
+      const int vv = v0 + wv, kb = k0 + half * 16;
+      if (vv < a.V && kb < a.Kp) {
+        __align__(16) __nv_bfloat16 o[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
+        for (int c = 0; c < world; ++c)
+          if (me.betaT_bf[c] != nullptr) {
+            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c]) + (size_t)vv * a.Kp + kb);
+            dst[0] = reinterpret_cast<const uint4*>(o)[0];
+            dst[1] = reinterpret_cast<const uint4*>(o)[1];
+          }
+      }
+      __syncthreads();
+    }
+  } else if (a.K > 0) {
     const int vt = (a.V + 31) / 32, kt = (a.K + 31) / 32;
     const int per = (vt + world - 1) / world;
     const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;

@@ -93,6 +93,56 @@ __global__ void __launch_bounds__(256) adam_beta_kernel(float* __restrict__ p, c
   }
 }
 
+// Vectorised variant (V, ldp, ldg multiples of 4): 32 topics x 128 words per block, float4 global
+// accesses, 8-byte bf16 stores for beta_bf and 32-byte rows for the transposed shadow.
+__global__ void __launch_bounds__(256) adam_beta_vec_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                            float* __restrict__ m, float* __restrict__ v, int K, int V,
+                                                            int ldp, int ldg, __nv_bfloat16* __restrict__ beta_bf,
+                                                            int ldb, __nv_bfloat16* __restrict__ betaT_bf, int Kp,
+                                                            AdamH h_, float gscale, int do_update) {
+  const AdamH h = resolve_step(h_);
+  __shared__ __align__(16) float tile[32][132];
+  const int v0 = blockIdx.x * 128, k0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int k = k0 + ty + r * 8, vv = v0 + tx * 4;
+    float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k < K && vv < V) {
+      const size_t ip = (size_t)k * ldp + vv;
+      val = *reinterpret_cast<const float4*>(p + ip);
+      if (do_update) {
+        float4 gg = *reinterpret_cast<const float4*>(g + (size_t)k * ldg + vv);
+        float4 mm = *reinterpret_cast<const float4*>(m + ip);
+        float4 v2 = *reinterpret_cast<const float4*>(v + ip);
+        val.x = adam_one(val.x, gg.x * gscale, mm.x, v2.x, h);
+        val.y = adam_one(val.y, gg.y * gscale, mm.y, v2.y, h);
+        val.z = adam_one(val.z, gg.z * gscale, mm.z, v2.z, h);
+        val.w = adam_one(val.w, gg.w * gscale, mm.w, v2.w, h);
+        *reinterpret_cast<float4*>(p + ip) = val;
+        *reinterpret_cast<float4*>(m + ip) = mm;
+        *reinterpret_cast<float4*>(v + ip) = v2;
+      }
+      __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y), __float2bfloat16(val.z),
+                                        __float2bfloat16(val.w)};
+      *reinterpret_cast<uint2*>(beta_bf + (size_t)k * ldb + vv) = *reinterpret_cast<const uint2*>(o);
+    }
+    *reinterpret_cast<float4*>(&tile[ty + r * 8][tx * 4]) = val;
+  }
+  __syncthreads();
+  // transposed shadow: thread -> (word, 16-topic half); rows of 16 bf16 = 32 bytes
+  const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
+  const int vv = v0 + wv, kb = k0 + half * 16;
+  if (vv < V && kb < Kp) {
+    __align__(16) __nv_bfloat16 o[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tile[half * 16 + j][wv]);
+    uint4* dst = reinterpret_cast<uint4*>(betaT_bf + (size_t)vv * Kp + kb);
+    dst[0] = reinterpret_cast<const uint4*>(o)[0];
+    dst[1] = reinterpret_cast<const uint4*>(o)[1];
+  }
+}
+
 }  // namespace gf
 
 using namespace gf;
@@ -124,6 +174,15 @@ extern "C" int gf_adam_beta(float* p, const float* g, float* m, float* v, int K,
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(!do_update || step >= 1 || step_ctr != nullptr, "Adam step must be >= 1");
   if (step < 1) step = 1;
+  if (V % 4 == 0 && ldp % 4 == 0 && ldg % 4 == 0 && ldb % 4 == 0 && Kp % 16 == 0) {
+    dim3 gridv((V + 127) / 128, (K + 31) / 32);
+    adam_beta_vec_kernel<<<gridv, 256, 0, st>>>(p, g, m, v, K, V, ldp, ldg, reinterpret_cast<__nv_bfloat16*>(beta_bf), ldb,
+                                                reinterpret_cast<__nv_bfloat16*>(betaT_bf), Kp,
+                                                make_h(lr, b1, b2, eps, wd, do_update ? step : 1, do_update ? step_ctr : nullptr),
+                                                gscale, do_update);
+    GF_LAUNCHED();
+    return GF_OK;
+  }
   dim3 grid((V + 31) / 32, (K + 31) / 32);
   adam_beta_kernel<<<grid, 256, 0, st>>>(p, g, m, v, K, V, ldp, ldg, reinterpret_cast<__nv_bfloat16*>(beta_bf), ldb,
                                          reinterpret_cast<__nv_bfloat16*>(betaT_bf), Kp,
