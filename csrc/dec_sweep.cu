@@ -26,6 +26,7 @@
 #include "ptx.cuh"
 #include "tmap.h"
 #include "../include/gfedntm_kernels.h"
+#include "fabric_dev.cuh"
 
 namespace gf {
 
@@ -68,6 +69,9 @@ struct SweepParams {
   const __nv_bfloat16* betaT_bf;  // COL_GRAD2: [V, Kp] unscaled beta^T (drain)
   __nv_bfloat16* beta3;     // COL_GRAD2 out: [Kp, ld3] rows k<K = gamma_v*beta[k,v], row K = alpha_v
   int ld3;
+  const GfFedArgs* fed;     // ROW_GRAD2: device copy of the aggregation arguments (or null)
+  int fed_ctas;             // number of trailing CTAs that run the beta aggregation instead of the sweep
+  uint32_t smem_bytes;      // dynamic shared memory of the launch (the aggregation CTAs use all of it)
   int debug;                // profiling experiments: bit0 = epilogue skips TMEM loads/math, bit1 = skip MMA1 issue
   const float4* sb_stream;  // side band per streamed index (padded to a multiple of 128)
   // generic
@@ -227,11 +231,37 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   const CUtensorMap* tm_strm = kRow ? &tm_beta : &tm_theta;
   const uint32_t blk = (uint32_t)Kp * 128u;  // bytes of one 64-column block
 
-  if (warp == 0) {
+  // ROW_GRAD2 with a federation context: the last fed_ctas CTAs of the grid overlap the beta part of the
+  // federated aggregation (NVLink peer loads / stores) with the sweep the other CTAs are running.
+  int n_sweep = (int)gridDim.x;
+  bool agg_role = false;
+  if (kMode == ROW_GRAD2 && p.fed != nullptr) {
+    n_sweep = (int)gridDim.x - p.fed_ctas;
+    agg_role = (int)blockIdx.x >= n_sweep;
+  }
+
+  if (kMode == ROW_GRAD2 && agg_role) {
+    const GfFedArgs& fa = *p.fed;
+    const GfFabricRank& me = fa.ranks[0];
+    const long long tstep = fa.step_ctr[1];
+    if (threadIdx.x < (unsigned)fa.world) {  // every peer's beta gradient final, its shadows no longer read
+      const uint32_t* f = me.flags[me.rank] + GF_FED_PHASE_BETA_READY * GF_MAX_RANKS + threadIdx.x;
+      while (ld_acquire_sys(f) < (uint32_t)tstep) __nanosleep(64);
+    }
+    __syncthreads();
+    asm volatile("fence.proxy.async;" ::: "memory");  // peer data is read through the async proxy below
+    const AdamF hh = fed_adam_consts(fa, tstep);
+    if (fa.V % 4 == 0 && fa.ldb % 4 == 0 && fa.Kp % 16 == 0 && fa.world > 1) {
+      fed_beta_phase_bulk(fa, me, hh, (int)blockIdx.x - n_sweep, p.fed_ctas, base, p.smem_bytes - 1024);
+    } else if (threadIdx.x < 256) {
+      fed_beta_phase(fa, me, hh, (int)blockIdx.x - n_sweep, p.fed_ctas, reinterpret_cast<float*>(base));
+    }
+    __threadfence_system();  // the completion handshake is phase C of the closing gf_fed_aggregate(parts=1)
+  } else if (warp == 0) {
     // ============================ TMA producer ============================
     if (lane == 0) {
       uint32_t a_it = 0, b_it = 0, sb_it = 0;
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      for (int w = blockIdx.x; w < total_work; w += n_sweep) {
         const int stat = w / p.n_chunks, chunk = w - stat * p.n_chunks;
         const int t0 = (int)(((long long)chunk * p.n_stream) / p.n_chunks);
         const int t1 = (int)(((long long)(chunk + 1) * p.n_stream) / p.n_chunks);
@@ -304,7 +334,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         ++p_it;
       };
 
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      for (int w = blockIdx.x; w < total_work; w += n_sweep) {
         const int stat = w / p.n_chunks, chunk = w - stat * p.n_chunks;
         const int t0 = (int)(((long long)chunk * p.n_stream) / p.n_chunks);
         const int t1 = (int)(((long long)(chunk + 1) * p.n_stream) / p.n_chunks);
@@ -374,7 +404,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
     const uint32_t lane_addr = tmem + ((q * 32) << 16);
     uint32_t b_it = 0, d1_it = 0, p_it = 0, d2_it = 0;
 
-    for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+    for (int w = blockIdx.x; w < total_work; w += n_sweep) {
       const int stat = w / p.n_chunks, chunk = w - stat * p.n_chunks;
       const int t0 = (int)(((long long)chunk * p.n_stream) / p.n_chunks);
       const int t1 = (int)(((long long)(chunk + 1) * p.n_stream) / p.n_chunks);
@@ -832,12 +862,16 @@ static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta,
                "n_components too large for the fused decoder sweeps (need Kp <= 240)");
   p.stages = plan.stages;
   p.p_bufs = plan.p_bufs;
+  p.smem_bytes = (uint32_t)plan.bytes;
   auto kern = sweep_kernel<kMode>;
   GF_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.bytes));
   const int total = p.n_stat * p.n_chunks;
-  int grid = num_sms();  // 12 warps with up to 168 registers each: one CTA per SM
+  const int fed_ctas = (kMode == ROW_GRAD2 && p.fed != nullptr) ? p.fed_ctas : 0;
+  int grid = num_sms() - fed_ctas;  // 12 warps with up to 168 registers each: one CTA per SM
+  GF_ARG_CHECK(grid >= 1, "fed_ctas leaves no CTA for the sweep");
   if (grid > total) grid = total;
   if (grid < 1) grid = 1;
+  grid += fed_ctas;
   kern<<<grid, kThreads, plan.bytes, stream>>>(tm_theta, tm_beta, p);
   GF_LAUNCHED();
   return GF_OK;
@@ -871,8 +905,14 @@ using namespace gf;
 extern "C" int gf_dec_row_chunks(int mode, int B, int V, int Kp) {
   (void)mode;
   (void)Kp;
+  return gf_dec_row_chunks_grid(B, V, num_sms());
+}
+
+extern "C" int gf_num_sms(void) { return num_sms(); }
+
+extern "C" int gf_dec_row_chunks_grid(int B, int V, int grid) {
   const int doc_tiles = (B + kTile - 1) / kTile, word_tiles = (V + kBN - 1) / kBN;
-  const int grid = num_sms();
+  if (grid < 1) grid = 1;
   int best = 1;
   double best_eff = 0.0;
   const int cmax = word_tiles < 4 * grid ? word_tiles : 4 * grid;
@@ -952,6 +992,9 @@ extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
     GF_ARG_CHECK(a->ext_col0 % kBN == 0 && a->ext_col0 >= a->V && a->ext_col0 + p.n_ext * kBN <= beta_cols,
                  "ext_col0: the M hi/lo blocks must be tile aligned and inside beta_cols");
     p.ext_tile0 = a->ext_col0 / kBN;
+    p.fed = reinterpret_cast<const GfFedArgs*>(a->fed);
+    p.fed_ctas = a->fed != nullptr ? a->fed_ctas : 0;
+    GF_ARG_CHECK(a->fed == nullptr || (a->fed_ctas >= 1 && a->fed_ctas < num_sms()), "fed_ctas");
   }
   p.out = a->out;
   p.lse_part = reinterpret_cast<float2*>(a->lse_part);

@@ -24,61 +24,12 @@
 #include "ptx.cuh"
 #include "tmap.h"
 #include "../include/gfedntm_kernels.h"
+#include "fabric_dev.cuh"
 
 namespace gf {
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
-  float4 v;
-  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-               : "l"(p)
-               : "memory");
-  return v;
-}
-__device__ __forceinline__ float ld_peer_f1(const float* p) {
-  float v;
-  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
-  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
-               "f"(v.w)
-               : "memory");
-}
-
-struct AdamF {
-  float lr, b1, b2, eps, bc1, bc2_sqrt, wd;
-};
-__device__ __forceinline__ float adam_upd(float p, float g, float& m, float& v, const AdamF& h) {
-  if (h.wd != 0.f) g = fmaf(h.wd, p, g);
-  m = fmaf(h.b1, m, (1.f - h.b1) * g);
-  v = fmaf(h.b2, v, (1.f - h.b2) * g * g);
-  const float denom = sqrtf(v) / h.bc2_sqrt + h.eps;
-  return p - (h.lr / h.bc1) * (m / denom);
-}
-
-// all threads of the block return once every peer's flag of `phase` has reached `epoch`
-__device__ __forceinline__ void wait_peers(const GfFabricRank& me, int world, int phase, uint32_t epoch) {
-  if (threadIdx.x < (unsigned)world) {
-    const uint32_t* f = me.flags[me.rank] + phase * GF_MAX_RANKS + threadIdx.x;
-    while (ld_acquire_sys(f) < epoch) {
-      __nanosleep(64);
-    }
-  }
-  __syncthreads();
-}
-
 __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, AdamF h) {
   __shared__ __align__(16) float tile_v[32 * 132];  // 32 x 128 (+4 pad) tile of the vectorised beta phase
-  float(*tile)[33] = reinterpret_cast<float(*)[33]>(tile_v);  // 32 x 32 view used by the scalar fallback
   __shared__ int is_last;
   const GfFabricRank& me = a.ranks[blockIdx.y];
   const int world = a.world, rank = me.rank;
@@ -100,8 +51,10 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long nthr = (long long)gridDim.x * blockDim.x;
 
+  const int parts = a.parts ? a.parts : 3;  // bit 0: flat region + BatchNorm statistics, bit 1: beta
+
   // ---------------- phase B.1: flat region [0, flat_n), float4 granularity, owner = contiguous slice
-  {
+  if (parts & 1) {
     const long long n4 = (a.flat_n + 3) / 4;
     const long long per = (n4 + world - 1) / world;
     const long long lo = rank * per, hi = (lo + per < n4) ? lo + per : n4;
@@ -141,7 +94,7 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
   }
 
   // ---------------- phase B.2: BatchNorm running statistics (weighted mean in both modes)
-  {
+  if (parts & 1) {
     const long long n4 = (a.s_n + 3) / 4;
     const long long per = (n4 + world - 1) / world;
     const long long lo = rank * per, hi = (lo + per < n4) ? lo + per : n4;
@@ -158,126 +111,9 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
     }
   }
 
-  // ---------------- phase B.3: beta [K,V] in 32x32 tiles, owner = contiguous range of word tiles;
-  //                  writes fp32 beta, bf16 beta_bf [Kp,ldb] and bf16 betaT_bf [V,Kp] to every rank
-  if (a.K > 0 && a.V % 4 == 0 && a.ldb % 4 == 0 && a.Kp % 16 == 0) {
-    // vectorised: 32 topics x 128 words per tile, float4 peer loads (all peers of a row in flight
-    // together), float4 / 8-byte / 32-byte stores to every rank
-    float(*tv)[132] = reinterpret_cast<float(*)[132]>(tile_v);
-    const int vt = (a.V + 127) / 128, kt = (a.K + 31) / 32;
-    const int per = (vt + world - 1) / world;
-    const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const long long n_tiles = (long long)(t_hi > t_lo ? t_hi - t_lo : 0) * kt;
-    for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-      const int v0 = (t_lo + (int)(t / kt)) * 128, k0 = (int)(t % kt) * 32;
-#pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int k = k0 + ty + r * 8, vv = v0 + tx * 4;
-        float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (k < a.K && vv < a.V) {
-          const long long ip = a.beta_off + (long long)k * a.V + vv;
-          float4 in[GF_MAX_RANKS];
-#pragma unroll
-          for (int c = 0; c < GF_MAX_RANKS; ++c)
-            if (c < world) in[c] = ld_peer_f4((a.mode == 0 ? me.G[c] : me.P[c]) + ip);
-          if (a.mode == 0) {
-            float4 gsum = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int c = 0; c < GF_MAX_RANKS; ++c)
-              if (c < world) { gsum.x += in[c].x; gsum.y += in[c].y; gsum.z += in[c].z; gsum.w += in[c].w; }
-            val = *reinterpret_cast<const float4*>(me.P[rank] + ip);
-            float4 m = *reinterpret_cast<const float4*>(me.M + ip);
-            float4 v2 = *reinterpret_cast<const float4*>(me.V2 + ip);
-            val.x = adam_upd(val.x, gsum.x, m.x, v2.x, h);
-            val.y = adam_upd(val.y, gsum.y, m.y, v2.y, h);
-            val.z = adam_upd(val.z, gsum.z, m.z, v2.z, h);
-            val.w = adam_upd(val.w, gsum.w, m.w, v2.w, h);
-            *reinterpret_cast<float4*>(me.M + ip) = m;
-            *reinterpret_cast<float4*>(me.V2 + ip) = v2;
-          } else {
-#pragma unroll
-            for (int c = 0; c < GF_MAX_RANKS; ++c)
-              if (c < world) {
-                const float w = a.w[c];
-                val.x = fmaf(w, in[c].x, val.x); val.y = fmaf(w, in[c].y, val.y);
-                val.z = fmaf(w, in[c].z, val.z); val.w = fmaf(w, in[c].w, val.w);
-              }
-          }
-          __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
-                                            __float2bfloat16(val.z), __float2bfloat16(val.w)};
-          for (int c = 0; c < world; ++c) {
-            st_peer_f4(me.P[c] + ip, val);
-            if (me.beta_bf[c] != nullptr)
-              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c]) + (size_t)k * a.ldb + vv) =
-                  *reinterpret_cast<const uint2*>(o);
-          }
-        }
-        *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
-      }
-      __syncthreads();
-      const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
-      const int vv = v0 + wv, kb = k0 + half * 16;
-      if (vv < a.V && kb < a.Kp) {
-        __align__(16) __nv_bfloat16 o[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
-        for (int c = 0; c < world; ++c)
-          if (me.betaT_bf[c] != nullptr) {
-            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c]) + (size_t)vv * a.Kp + kb);
-            dst[0] = reinterpret_cast<const uint4*>(o)[0];
-            dst[1] = reinterpret_cast<const uint4*>(o)[1];
-          }
-      }
-      __syncthreads();
-    }
-  } else if (a.K > 0) {
-    const int vt = (a.V + 31) / 32, kt = (a.K + 31) / 32;
-    const int per = (vt + world - 1) / world;
-    const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const long long n_tiles = (long long)(t_hi > t_lo ? t_hi - t_lo : 0) * kt;
-    for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-      const int v0 = (t_lo + (int)(t / kt)) * 32, k0 = (int)(t % kt) * 32;
-#pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int k = k0 + ty + r * 8, vv = v0 + tx;
-        float val = 0.f;
-        if (k < a.K && vv < a.V) {
-          const long long ip = a.beta_off + (long long)k * a.V + vv;
-          if (a.mode == 0) {
-            float g = 0.f;
-            for (int c = 0; c < world; ++c) g += ld_peer_f1(me.G[c] + ip);
-            float m = me.M[ip], v2 = me.V2[ip];
-            val = adam_upd(me.P[rank][ip], g, m, v2, h);
-            me.M[ip] = m;
-            me.V2[ip] = v2;
-          } else {
-            for (int c = 0; c < world; ++c) val = fmaf(a.w[c], ld_peer_f1(me.P[c] + ip), val);
-          }
-          const __nv_bfloat16 bv = __float2bfloat16(val);
-          for (int c = 0; c < world; ++c) {
-            me.P[c][ip] = val;
-            if (me.beta_bf[c] != nullptr)
-              reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c])[(size_t)k * a.ldb + vv] = bv;
-          }
-        }
-        tile[ty + r * 8][tx] = val;
-      }
-      __syncthreads();
-#pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int vv = v0 + ty + r * 8, k = k0 + tx;
-        if (vv < a.V && k < a.K) {
-          const __nv_bfloat16 bv = __float2bfloat16(tile[tx][ty + r * 8]);
-          for (int c = 0; c < world; ++c)
-            if (me.betaT_bf[c] != nullptr)
-              reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c])[(size_t)vv * a.Kp + k] = bv;
-        }
-      }
-      __syncthreads();
-    }
-  }
+  // ---------------- phase B.3: beta [K,V], owner = contiguous range of word tiles; writes fp32 beta,
+  //                  bf16 beta_bf [Kp,ldb] and bf16 betaT_bf [V,Kp] to every rank (fabric_dev.cuh)
+  if (parts & 2) fed_beta_phase(a, me, h, (int)blockIdx.x, (int)gridDim.x, tile_v);
 
   // ---------------- phase C: all my pushes are done -> tell the peers, wait for theirs
   __threadfence_system();
@@ -297,9 +133,30 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
   }
 }
 
+// Raises flag `phase` of this rank on every peer ("my beta gradient is final and I no longer read my
+// beta shadows"): lets the peers' overlapped beta aggregation (d-theta sweep, csrc/dec_sweep.cu) start.
+__global__ void fed_signal_kernel(const GfFedArgs a, int phase) {
+  const GfFabricRank& me = a.ranks[0];
+  uint32_t epoch = (uint32_t)a.epoch;
+  if (a.step_ctr != nullptr) epoch = (uint32_t)a.step_ctr[1];
+  if (threadIdx.x < (unsigned)a.world) {
+    __threadfence_system();
+    st_release_sys(me.flags[threadIdx.x] + phase * GF_MAX_RANKS + me.rank, epoch);
+  }
+}
+
 }  // namespace gf
 
 using namespace gf;
+
+extern "C" int gf_fed_signal(const GfFedArgs* a, int phase, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(a->world >= 1 && a->world <= GF_MAX_RANKS && a->n_rank_ctx == 1, "world / n_rank_ctx");
+  GF_ARG_CHECK(phase >= 2 && phase < 8, "phase slots 0 and 1 belong to gf_fed_aggregate");
+  fed_signal_kernel<<<1, 32, 0, st>>>(*a, phase);
+  GF_LAUNCHED();
+  return GF_OK;
+}
 
 extern "C" int gf_fed_aggregate(const GfFedArgs* a, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);

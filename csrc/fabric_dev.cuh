@@ -1,0 +1,358 @@
+// Device-side pieces of the fused federated aggregation shared by csrc/fabric.cu (the stand-alone
+// aggregation kernel) and csrc/dec_sweep.cu (the d-theta sweep whose spare CTAs run the beta part of the
+// aggregation over NVLink while the others keep the tensor cores busy).
+#pragma once
+#include <cuda_bf16.h>
+#include "ptx.cuh"
+#include "../include/gfedntm_kernels.h"
+
+namespace gf {
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_peer_f1(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+
+struct AdamF {
+  float lr, b1, b2, eps, bc1, bc2_sqrt, wd;
+};
+__device__ __forceinline__ float adam_upd(float p, float g, float& m, float& v, const AdamF& h) {
+  if (h.wd != 0.f) g = fmaf(h.wd, p, g);
+  m = fmaf(h.b1, m, (1.f - h.b1) * g);
+  v = fmaf(h.b2, v, (1.f - h.b2) * g * g);
+  const float denom = sqrtf(v) / h.bc2_sqrt + h.eps;
+  return p - (h.lr / h.bc1) * (m / denom);
+}
+
+// all threads of the block return once every peer's flag of `phase` has reached `epoch`
+__device__ __forceinline__ void wait_peers(const GfFabricRank& me, int world, int phase, uint32_t epoch) {
+  if (threadIdx.x < (unsigned)world) {
+    const uint32_t* f = me.flags[me.rank] + phase * GF_MAX_RANKS + threadIdx.x;
+    while (ld_acquire_sys(f) < epoch) {
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+}
+
+
+// 256 threads of the calling block (threadIdx.x < 256) synchronise on named barrier 2
+__device__ __forceinline__ void fed_sync256() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
+
+// Adam constants for step `t` (bias corrections on the device: graph replays read t from a counter)
+__device__ __forceinline__ AdamF fed_adam_consts(const GfFedArgs& a, long long t) {
+  AdamF h;
+  h.lr = a.lr; h.b1 = a.b1; h.b2 = a.b2; h.eps = a.eps; h.wd = a.wd;
+  h.bc1 = 1.f - powf(h.b1, (float)t);
+  h.bc2_sqrt = sqrtf(1.f - powf(h.b2, (float)t));
+  return h;
+}
+
+// beta [K,V] part of the aggregation for the word-tile range owned by `me.rank`: reduce the peers'
+// gradients (P2P loads), Adam on the owner's shard, push fp32 beta and both bf16 operand shadows to every
+// rank (P2P stores).  Called by threads 0..255 of `n_cta` cooperating blocks (`cta` = index among them);
+// `tile_v` is 32*132 floats of shared memory.
+__device__ __forceinline__ void fed_beta_phase(const GfFedArgs& a, const GfFabricRank& me, const AdamF& h, int cta,
+                                               int n_cta, float* tile_v) {
+  const int world = a.world, rank = me.rank;
+  float(*tile)[33] = reinterpret_cast<float(*)[33]>(tile_v);  // 32 x 32 view used by the scalar fallback
+  if (a.K > 0 && a.V % 4 == 0 && a.ldb % 4 == 0 && a.Kp % 16 == 0) {
+    // vectorised: 32 topics x 128 words per tile, float4 peer loads (all peers of a row in flight
+    // together), float4 / 8-byte / 32-byte stores to every rank
+    float(*tv)[132] = reinterpret_cast<float(*)[132]>(tile_v);
+    const int vt = (a.V + 127) / 128, kt = (a.K + 31) / 32;
+    const int per = (vt + world - 1) / world;
+    const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const long long n_tiles = (long long)(t_hi > t_lo ? t_hi - t_lo : 0) * kt;
+    for (long long t = cta; t < n_tiles; t += n_cta) {
+      const int v0 = (t_lo + (int)(t / kt)) * 128, k0 = (int)(t % kt) * 32;
+      // All peer loads of the thread's four rows are issued before the first use (one NVLink round trip
+      // per tile instead of four); more than four peers are reduced in two groups to bound registers.
+      const int vv = v0 + tx * 4;
+      float4 gsum[4];
+      bool live[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        gsum[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+        live[r] = (k0 + ty + r * 8 < a.K) && (vv < a.V);
+      }
+#pragma unroll
+      for (int c0 = 0; c0 < GF_MAX_RANKS; c0 += 4) {
+        if (c0 < world) {
+          float4 in[4][4];
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const long long ip = a.beta_off + (long long)(k0 + ty + r * 8) * a.V + vv;
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc)
+              if (live[r] && c0 + cc < world) in[r][cc] = ld_peer_f4((a.mode == 0 ? me.G[c0 + cc] : me.P[c0 + cc]) + ip);
+          }
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc)
+              if (live[r] && c0 + cc < world) {
+                const float w = (a.mode == 0) ? 1.f : a.w[c0 + cc];
+                gsum[r].x = fmaf(w, in[r][cc].x, gsum[r].x); gsum[r].y = fmaf(w, in[r][cc].y, gsum[r].y);
+                gsum[r].z = fmaf(w, in[r][cc].z, gsum[r].z); gsum[r].w = fmaf(w, in[r][cc].w, gsum[r].w);
+              }
+          }
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int k = k0 + ty + r * 8;
+        float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (live[r]) {
+          const long long ip = a.beta_off + (long long)k * a.V + vv;
+          if (a.mode == 0) {
+            val = *reinterpret_cast<const float4*>(me.P[rank] + ip);
+            float4 m = *reinterpret_cast<const float4*>(me.M + ip);
+            float4 v2 = *reinterpret_cast<const float4*>(me.V2 + ip);
+            val.x = adam_upd(val.x, gsum[r].x, m.x, v2.x, h);
+            val.y = adam_upd(val.y, gsum[r].y, m.y, v2.y, h);
+            val.z = adam_upd(val.z, gsum[r].z, m.z, v2.z, h);
+            val.w = adam_upd(val.w, gsum[r].w, m.w, v2.w, h);
+            *reinterpret_cast<float4*>(me.M + ip) = m;
+            *reinterpret_cast<float4*>(me.V2 + ip) = v2;
+          } else {
+            val = gsum[r];
+          }
+          __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
+                                            __float2bfloat16(val.z), __float2bfloat16(val.w)};
+          for (int c = 0; c < world; ++c) {
+            st_peer_f4(me.P[c] + ip, val);
+            if (me.beta_bf[c] != nullptr)
+              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c]) + (size_t)k * a.ldb + vv) =
+                  *reinterpret_cast<const uint2*>(o);
+          }
+        }
+        *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
+      }
+      fed_sync256();
+      const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
+      const int vw = v0 + wv, kb = k0 + half * 16;
+      if (vw < a.V && kb < a.Kp) {
+        __align__(16) __nv_bfloat16 o[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
+        for (int c = 0; c < world; ++c)
+          if (me.betaT_bf[c] != nullptr) {
+            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c]) + (size_t)vw * a.Kp + kb);
+            dst[0] = reinterpret_cast<const uint4*>(o)[0];
+            dst[1] = reinterpret_cast<const uint4*>(o)[1];
+          }
+      }
+      fed_sync256();
+    }
+  } else if (a.K > 0) {
+    const int vt = (a.V + 31) / 32, kt = (a.K + 31) / 32;
+    const int per = (vt + world - 1) / world;
+    const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const long long n_tiles = (long long)(t_hi > t_lo ? t_hi - t_lo : 0) * kt;
+    for (long long t = cta; t < n_tiles; t += n_cta) {
+      const int v0 = (t_lo + (int)(t / kt)) * 32, k0 = (int)(t % kt) * 32;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int k = k0 + ty + r * 8, vv = v0 + tx;
+        float val = 0.f;
+        if (k < a.K && vv < a.V) {
+          const long long ip = a.beta_off + (long long)k * a.V + vv;
+          if (a.mode == 0) {
+            float g = 0.f;
+            for (int c = 0; c < world; ++c) g += ld_peer_f1(me.G[c] + ip);
+            float m = me.M[ip], v2 = me.V2[ip];
+            val = adam_upd(me.P[rank][ip], g, m, v2, h);
+            me.M[ip] = m;
+            me.V2[ip] = v2;
+          } else {
+            for (int c = 0; c < world; ++c) val = fmaf(a.w[c], ld_peer_f1(me.P[c] + ip), val);
+          }
+          const __nv_bfloat16 bv = __float2bfloat16(val);
+          for (int c = 0; c < world; ++c) {
+            me.P[c][ip] = val;
+            if (me.beta_bf[c] != nullptr)
+              reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c])[(size_t)k * a.ldb + vv] = bv;
+          }
+        }
+        tile[ty + r * 8][tx] = val;
+      }
+      fed_sync256();
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int vv = v0 + ty + r * 8, k = k0 + tx;
+        if (vv < a.V && k < a.K) {
+          const __nv_bfloat16 bv = __float2bfloat16(tile[tx][ty + r * 8]);
+          for (int c = 0; c < world; ++c)
+            if (me.betaT_bf[c] != nullptr)
+              reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c])[(size_t)vv * a.Kp + k] = bv;
+        }
+      }
+      fed_sync256();
+    }
+  }
+
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Bulk-copy variant of the beta phase (gradient mode), used by the aggregation CTAs inside the d-theta
+// sweep.  A handful of CTAs must keep the NVLink busy, so the peers' gradient tiles are fetched with
+// cp.async.bulk (one 512-byte row per instruction, issued by a producer warp) into a multi-stage
+// shared-memory ring: ~100-200 KB in flight per CTA instead of the 16 KB a register-based tile allows.
+//   threads 0..255   consumers: reduce the staged peer tiles + the local gradient, Adam, push P and shadows
+//   threads 256..287 producer warp (lane r issues row r of every remote peer's tile)
+// `smem` must be 1024-byte aligned; layout: [tile 32x132 f32][stages x n_remote x 16 KB][mbarriers].
+// Requires V % 4 == 0, ldb % 4 == 0, Kp % 16 == 0 (callers fall back to fed_beta_phase otherwise).
+// ---------------------------------------------------------------------------------------------------
+constexpr int kFedTileBytes = 32 * 128 * 4;  // one peer's 32-topic x 128-word fp32 tile
+constexpr int kFedMaxStages = 8;
+
+__device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const GfFabricRank& me, const AdamF& h,
+                                                    int cta, int n_cta, uint8_t* smem, uint32_t smem_bytes) {
+  const int world = a.world, rank = me.rank, n_remote = world - 1;
+  float* tile_v = reinterpret_cast<float*>(smem);
+  float(*tv)[132] = reinterpret_cast<float(*)[132]>(tile_v);
+  uint8_t* ring = smem + 17408;  // 32*132*4 = 16896, rounded up to 1 KB
+  const uint32_t stage_bytes = (uint32_t)n_remote * kFedTileBytes;
+  int stages = (int)((smem_bytes - 17408 - 256) / stage_bytes);
+  if (stages > kFedMaxStages) stages = kFedMaxStages;
+  uint64_t* full = reinterpret_cast<uint64_t*>(ring + (size_t)stages * stage_bytes);
+  uint64_t* empty = full + kFedMaxStages;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();  // all threads of the CTA call this function
+
+  const int vt = (a.V + 127) / 128, kt = (a.K + 31) / 32;
+  const int per = (vt + world - 1) / world;
+  const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;
+  const long long n_tiles = (long long)(t_hi > t_lo ? t_hi - t_lo : 0) * kt;
+
+  if (threadIdx.x >= 256 && threadIdx.x < 288) {
+    // ---------------- producer warp
+    const int lane = threadIdx.x - 256;
+    uint32_t it = 0;
+    for (long long t = cta; t < n_tiles; t += n_cta, ++it) {
+      const int st = it % stages;
+      const int v0 = (t_lo + (int)(t / kt)) * 128, k0 = (int)(t % kt) * 32;
+      const int rows = min(32, a.K - k0);
+      const uint32_t row_bytes = (uint32_t)min(128, a.V - v0) * 4u;
+      mbar_wait(&empty[st], ((it / stages) & 1) ^ 1);
+      if (lane == 0) mbar_arrive_expect_tx(&full[st], (uint32_t)n_remote * (uint32_t)rows * row_bytes);
+      __syncwarp();
+      if (lane < rows) {
+        int slot = 0;
+        for (int c = 0; c < world; ++c) {
+          if (c == rank) continue;
+          const float* src = me.G[c] + a.beta_off + (long long)(k0 + lane) * a.V + v0;
+          const uint32_t dst = smem_u32(ring + (size_t)st * stage_bytes + (size_t)slot * kFedTileBytes + lane * 512);
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                       "l"(src), "r"(row_bytes), "r"(smem_u32(&full[st]))
+                       : "memory");
+          ++slot;
+        }
+      }
+    }
+  } else if (threadIdx.x < 256) {
+    // ---------------- consumers
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    uint32_t it = 0;
+    for (long long t = cta; t < n_tiles; t += n_cta, ++it) {
+      const int st = it % stages;
+      const int v0 = (t_lo + (int)(t / kt)) * 128, k0 = (int)(t % kt) * 32;
+      const int vv = v0 + tx * 4;
+      // local operands first (their latency overlaps the wait for the peers' tile)
+      float4 gl[4], pp[4], mm[4], v2[4];
+      bool live[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int k = k0 + ty + r * 8;
+        live[r] = (k < a.K) && (vv < a.V);
+        if (live[r]) {
+          const long long ip = a.beta_off + (long long)k * a.V + vv;
+          gl[r] = *reinterpret_cast<const float4*>(me.G[rank] + ip);
+          pp[r] = *reinterpret_cast<const float4*>(me.P[rank] + ip);
+          mm[r] = *reinterpret_cast<const float4*>(me.M + ip);
+          v2[r] = *reinterpret_cast<const float4*>(me.V2 + ip);
+        }
+      }
+      mbar_wait(&full[st], (it / stages) & 1);
+      const uint8_t* sb = ring + (size_t)st * stage_bytes;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int k = k0 + ty + r * 8;
+        float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (live[r]) {
+          float4 g = gl[r];
+          for (int c = 0; c < n_remote; ++c) {
+            const float4 x = *reinterpret_cast<const float4*>(sb + (size_t)c * kFedTileBytes + (ty + r * 8) * 512 + tx * 16);
+            g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+          }
+          const long long ip = a.beta_off + (long long)k * a.V + vv;
+          val = pp[r];
+          val.x = adam_upd(val.x, g.x, mm[r].x, v2[r].x, h);
+          val.y = adam_upd(val.y, g.y, mm[r].y, v2[r].y, h);
+          val.z = adam_upd(val.z, g.z, mm[r].z, v2[r].z, h);
+          val.w = adam_upd(val.w, g.w, mm[r].w, v2[r].w, h);
+          *reinterpret_cast<float4*>(me.M + ip) = mm[r];
+          *reinterpret_cast<float4*>(me.V2 + ip) = v2[r];
+          __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
+                                            __float2bfloat16(val.z), __float2bfloat16(val.w)};
+          for (int c = 0; c < world; ++c) {
+            st_peer_f4(me.P[c] + ip, val);
+            if (me.beta_bf[c] != nullptr)
+              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c]) + (size_t)k * a.ldb + vv) =
+                  *reinterpret_cast<const uint2*>(o);
+          }
+        }
+        *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
+      }
+      fed_sync256();
+      if (threadIdx.x == 0) mbar_arrive(&empty[st]);  // every consumer has read the stage
+      const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
+      const int vw = v0 + wv, kb = k0 + half * 16;
+      if (vw < a.V && kb < a.Kp) {
+        __align__(16) __nv_bfloat16 o[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
+        for (int c = 0; c < world; ++c)
+          if (me.betaT_bf[c] != nullptr) {
+            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c]) + (size_t)vw * a.Kp + kb);
+            dst[0] = reinterpret_cast<const uint4*>(o)[0];
+            dst[1] = reinterpret_cast<const uint4*>(o)[1];
+          }
+      }
+      fed_sync256();
+    }
+  }
+}
+
+}  // namespace gf

@@ -268,7 +268,7 @@ class FusedEngine:
 
     def forward_backward(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *,
                          training: bool = True, sample: bool = True, gscale: float = 1.0,
-                         need_grad: bool = True, eps_in=None, mask_enc_in=None, mask_theta_in=None):
+                         need_grad: bool = True, eps_in=None, mask_enc_in=None, mask_theta_in=None, fed=None):
         """Runs forward (and backward when ``need_grad``); returns the device scalar
         ``loss = sum_b (kl_weight*KL_b + RL_b)`` (float64, shape [1])."""
         B, K, V = batch.B, self.K, self.V
@@ -313,7 +313,8 @@ class FusedEngine:
             _, dtheta = self.decoder.forward_backward(
                 self.theta, self.theta_colsum, self.beta_bf, self.betaT_bf, batch, self.csc,
                 training=training, running_mean=bbn.running_mean, running_var=bbn.running_var,
-                dbeta=self._g("beta") if grad else None, loss=self.loss, gscale=gscale, need_grad=grad)
+                dbeta=self._g("beta") if grad else None, loss=self.loss, gscale=gscale, need_grad=grad,
+                fed=fed if (grad and self.decoder.folded) else None)
         else:
             beta = self._p("beta")
             K_.lda_beta_fwd(beta, K=K, V=V, eps=BN_EPS, momentum=BN_MOMENTUM, training=training,

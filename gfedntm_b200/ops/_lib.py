@@ -32,6 +32,7 @@ class GfSweepArgs(C.Structure):
         ("corr", _p), ("colptr", _p),
         ("theta_cols", _i), ("beta_cols", _i), ("ext_col0", _i),
         ("betaT_bf", _p), ("beta3", _p), ("ld_beta3", _i), ("ld_corr", _i),
+        ("fed", _p), ("fed_ctas", _i),
     ]
 
 
@@ -136,6 +137,7 @@ class GfFedArgs(C.Structure):
         ("lr", _f), ("b1", _f), ("b2", _f), ("eps", _f), ("wd", _f),
         ("step", _i),
         ("step_ctr", _p),
+        ("parts", _i),
         ("ranks", GfFabricRank * GF_MAX_RANKS),
     ]
 
@@ -171,6 +173,12 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_csc_corr_t.argtypes = [_p, _p, _p, _p, _p, _i, _p, _i, _i, _i, _p]
     for fn in ("gf_theta_center_fold", "gf_scale_beta", "gf_theta_gram", "gf_gram", "gf_gram_finish", "gf_csc_corr_t"):
         getattr(lib, fn).restype = _i
+    lib.gf_fed_signal.argtypes = [C.POINTER(GfFedArgs), _i, _p]
+    lib.gf_fed_signal.restype = _i
+    lib.gf_dec_row_chunks_grid.argtypes = [_i, _i, _i]
+    lib.gf_dec_row_chunks_grid.restype = _i
+    lib.gf_num_sms.argtypes = []
+    lib.gf_num_sms.restype = _i
     lib.gf_dec_row_chunks.argtypes = [_i, _i, _i, _i]
     lib.gf_dec_row_chunks.restype = _i
     lib.gf_latent_bwd.argtypes = [C.POINTER(GfLatentBwdArgs), _p]

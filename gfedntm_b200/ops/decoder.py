@@ -134,8 +134,12 @@ class ProdLDADecoder:
                          betaT_bf: torch.Tensor, batch: CsrBatch, csc: Optional[CscWorkspace], *,
                          training: bool, running_mean: Optional[torch.Tensor],
                          running_var: Optional[torch.Tensor], dbeta: Optional[torch.Tensor],
-                         loss: Optional[torch.Tensor], gscale: float = 1.0, need_grad: bool = True):
-        """Runs the sweeps.  Returns (rl[B], dtheta[B,Kp] or None).  ``dbeta`` [K,ld] is overwritten."""
+                         loss: Optional[torch.Tensor], gscale: float = 1.0, need_grad: bool = True, fed=None):
+        """Runs the sweeps.  Returns (rl[B], dtheta[B,Kp] or None).  ``dbeta`` [K,ld] is overwritten.
+
+        ``fed`` (folded formulation only): an object with ``signal_beta_ready()``, ``dev_args`` (device
+        pointer of the aggregation arguments) and ``ctas``; the beta part of the federated aggregation then
+        runs on ``ctas`` CTAs of the d-theta sweep, overlapped with it (see parallel/fabric.py)."""
         B, V, Kt = batch.B, self.V, self.K
         assert B <= self.max_B
         if not self.folded:
@@ -177,6 +181,14 @@ class ProdLDADecoder:
         K_.gram(self.beta3, beta_bf, self.gram_partial, V=V)
         K_.gram_finish(self.gram_partial, self.gram_parts, self.beta_s, K=Kt, col_hi=self.Vpad,
                        col_lo=self.Vpad + self.n_ext * TILE)
+        if fed is not None:
+            # d beta is final and this rank no longer reads its unscaled beta shadows: peers may push
+            fed.signal_beta_ready()
+            n_chunks_g = K_.default_row_chunks(B, V, second_mma=True, Kp=self.Kp, grid=K_.num_sms() - fed.ctas)
+            K_.dec_sweep(K_.ROW_GRAD2, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=self.beta_s,
+                         n_chunks=n_chunks_g, dtheta=self.dtheta, theta_cols=tcols, beta_cols=bcols,
+                         ext_col0=self.Vpad, fed=fed.dev_args, fed_ctas=fed.ctas)
+            return self.rl[:B], self.dtheta[:B]
         n_chunks_g = K_.default_row_chunks(B, V, second_mma=True, Kp=self.Kp)
         K_.dec_sweep(K_.ROW_GRAD2, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=self.beta_s,
                      n_chunks=n_chunks_g, dtheta=self.dtheta, theta_cols=tcols, beta_cols=bcols,

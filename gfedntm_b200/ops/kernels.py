@@ -46,10 +46,17 @@ def padded_topics(k: int) -> int:
     return round_up(k + FOLD_ROWS, 16)
 
 
-def default_row_chunks(B: int, V: int, second_mma: bool = False, Kp: int = 64) -> int:
+def num_sms() -> int:
+    return int(_lib.load().gf_num_sms())
+
+
+def default_row_chunks(B: int, V: int, second_mma: bool = False, Kp: int = 64, grid: Optional[int] = None) -> int:
     """Vocabulary split of the ROW sweeps: smallest chunk count that fills the persistent grid in
-    whole waves (computed by the library, which knows the grid each mode launches)."""
+    whole waves (computed by the library, which knows the grid each mode launches).  ``grid``: number of
+    sweep CTAs when some are set aside (overlapped aggregation)."""
     lib = _lib.load()
+    if grid is not None:
+        return int(lib.gf_dec_row_chunks_grid(B, V, grid))
     return int(lib.gf_dec_row_chunks(ROW_GRAD if second_mma else ROW_LSE, B, V, Kp))
 
 
@@ -61,7 +68,7 @@ def dec_sweep(mode: int, *, B: int, V: int, K: int, theta_bf: torch.Tensor, beta
               doc_const=None, dtheta=None, colc=None, theta_mean=None, running_mean=None, running_var=None,
               bn_eps: float = 1e-5, bn_momentum: float = 0.1, use_running: bool = False, asp=None,
               csp=None, dbeta=None, corr=None, colptr=None, theta_cols: int = 0, beta_cols: int = 0,
-              ext_col0: int = 0, betaT_bf=None, beta3=None) -> None:
+              ext_col0: int = 0, betaT_bf=None, beta3=None, fed: int = 0, fed_ctas: int = 0) -> None:
     lib = _lib.load()
     Kp = beta_bf.shape[0]
     assert theta_bf.dtype == torch.bfloat16 and beta_bf.dtype == torch.bfloat16
@@ -84,6 +91,7 @@ def dec_sweep(mode: int, *, B: int, V: int, K: int, theta_bf: torch.Tensor, beta
     a.betaT_bf, a.beta3 = _ptr(betaT_bf), _ptr(beta3)
     a.ld_beta3 = beta3.stride(0) if beta3 is not None else 0
     a.ld_corr = corr.stride(0) if corr is not None else 0
+    a.fed, a.fed_ctas = (fed or None), fed_ctas
     check(lib.gf_dec_sweep(C.byref(a), _stream()), "gf_dec_sweep")
 
 

@@ -177,7 +177,20 @@ class FusedAggregator:
     def set_lr(self, lr: float, betas) -> None:
         self.args.lr, self.args.b1, self.args.b2 = lr, betas[0], betas[1]
 
-    def launch(self, *, mode: str, step: int, step_ctr=None) -> None:
+    # ---- overlapped beta aggregation (grad mode): see csrc/dec_sweep.cu, GF_ROW_GRAD2 with `fed`
+    def overlap_handle(self, step_ctr: torch.Tensor, ctas: int) -> "BetaOverlap":
+        """Uploads the aggregation arguments once (they are constant across steps: the epoch and the Adam
+        step are read from ``step_ctr`` on the device) and returns the handle the decoder uses."""
+        assert self.args.n_rank_ctx == 1, "the overlapped path runs one rank per process"
+        a = self.args
+        a.mode, a.epoch, a.step, a.parts = 0, 0, 0, 2
+        a.step_ctr = step_ctr.data_ptr()
+        raw = bytes(memoryview(a).cast("B"))
+        dev = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(step_ctr.device)
+        self._keep.append(dev)
+        return BetaOverlap(self, dev, step_ctr, ctas)
+
+    def launch(self, *, mode: str, step: int, step_ctr=None, parts: int = 3) -> None:
         """``mode``: 'grad' (weighted gradients + global sharded Adam) or 'param' (weighted mean of the
         parameters).  Every rank must call this once per global step.  With ``step_ctr`` (device counters
         of the engine) the epoch flag and the Adam step are read on the device, so the launch can be
@@ -188,5 +201,23 @@ class FusedAggregator:
         a.epoch = self.epoch
         a.step = step
         a.step_ctr = step_ctr.data_ptr() if step_ctr is not None else None
+        a.parts = parts
         lib = _lib.load()
         check(lib.gf_fed_aggregate(C.byref(a), torch.cuda.current_stream().cuda_stream), "gf_fed_aggregate")
+
+
+class BetaOverlap:
+    """Handle passed down to the decoder: raises this rank's "beta gradient ready" flag on the peers and
+    carries the device copy of the aggregation arguments for the sweep kernel's aggregation CTAs."""
+
+    PHASE_BETA_READY = 2
+
+    def __init__(self, agg: FusedAggregator, dev_args: torch.Tensor, step_ctr: torch.Tensor, ctas: int) -> None:
+        self.agg, self._dev, self.step_ctr, self.ctas = agg, dev_args, step_ctr, int(ctas)
+        self.dev_args = dev_args.data_ptr()
+
+    def signal_beta_ready(self) -> None:
+        a = self.agg.args
+        a.step_ctr = self.step_ctr.data_ptr()
+        check(_lib.load().gf_fed_signal(C.byref(a), self.PHASE_BETA_READY, torch.cuda.current_stream().cuda_stream),
+              "gf_fed_signal")

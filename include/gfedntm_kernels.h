@@ -83,11 +83,21 @@ typedef struct GfSweepArgs {
   void* beta3;           /* COL_GRAD2 out: [Kp, ld_beta3] bf16, rows k<K gamma_v*beta[k,v], row K alpha_v */
   int ld_beta3;
   int ld_corr;           /* COL_GRAD2: corr is TRANSPOSED, [Kp, ld_corr] (gf_csc_corr_t)                */
+  const void* fed;       /* ROW_GRAD2: DEVICE copy of a GfFedArgs (n_rank_ctx 1, step_ctr set) or null.  The
+                            last fed_ctas CTAs of the grid then wait for every peer's
+                            GF_FED_PHASE_BETA_READY flag and run the beta part of the aggregation (P2P
+                            reduce + Adam + P2P pushes) while the other CTAs do the sweep; finish the step
+                            with gf_fed_aggregate(parts = 1).                                            */
+  int fed_ctas;
 } GfSweepArgs;
 
 int gf_dec_sweep(const GfSweepArgs* args, void* stream);
 /* Vocabulary chunk count for the ROW modes that fills the persistent grid in whole waves.       */
 int gf_dec_row_chunks(int mode, int B, int V, int Kp);
+/* Same for an explicit number of sweep CTAs (GF_ROW_GRAD2 with fed_ctas CTAs set aside).            */
+int gf_dec_row_chunks_grid(int B, int V, int grid);
+/* Number of SMs (= persistent CTAs of a sweep) on the current device.                            */
+int gf_num_sms(void);
 
 /* ------------------------------------------------------------------------------------------
  * Encoder / latent layer (CUDA-core kernels on [B,H] / [B,K] data; the BoW input is CSR).
@@ -304,7 +314,8 @@ typedef struct GfFabricRank {
   float* S[GF_MAX_RANKS];         /* flat BatchNorm running statistics of every rank            */
   void* beta_bf[GF_MAX_RANKS];    /* bf16 [Kp, ldb] shadow of every rank (may be null)          */
   void* betaT_bf[GF_MAX_RANKS];   /* bf16 [V, Kp] shadow of every rank (may be null)            */
-  uint32_t* flags[GF_MAX_RANKS];  /* flag array of every rank: uint32 [2][GF_MAX_RANKS], zeroed once */
+  uint32_t* flags[GF_MAX_RANKS];  /* flag array of every rank: uint32 [4][GF_MAX_RANKS], zeroed once:
+                                     slot 0 gradients ready, 1 pushes done, 2 beta gradient ready      */
   float* M; float* V2;            /* this rank's Adam moments (same indexing as P)              */
   unsigned int* done_counter;     /* this rank, zeroed once                                     */
 } GfFabricRank;
@@ -322,11 +333,16 @@ typedef struct GfFedArgs {
   float lr, b1, b2, eps, wd;
   int step;                       /* Adam step count (>= 1) for the bias correction             */
   const long long* step_ctr;      /* optional device counters: epoch = step = step_ctr[1]       */
+  int parts;                      /* 0 or 3 = everything; bit 0 = flat region + BatchNorm statistics, bit 1 =
+                                     beta (which GF_ROW_GRAD2 can run on spare CTAs, see GfSweepArgs.fed) */
   GfFabricRank ranks[GF_MAX_RANKS];
 } GfFedArgs;
 
 /* One call per rank and step, on every rank of the federation, with the same `epoch`.          */
 int gf_fed_aggregate(const GfFedArgs* args, void* stream);
+/* Raise flag slot `phase` (>= 2) of this rank on every peer with the current epoch.             */
+int gf_fed_signal(const GfFedArgs* args, int phase, void* stream);
+#define GF_FED_PHASE_BETA_READY 2
 
 /* ------------------------------------------------------------------------------------------
  * Host-side data loader helpers (no device code).

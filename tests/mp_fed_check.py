@@ -51,12 +51,22 @@ def main():
             mb = next(it)
         if agg == "grad":
             # replicate what trainer.step does, but keep the gradients for the oracle
-            loss = eng.forward_backward(mb.bow, None, training=True, gscale=tr.weights[rank])
-            g = {n: eng.flat.view(eng.flat.G, n).detach().clone().contiguous() for n in names}
-            s_local = eng.flat.S.detach().clone() * tr.weights[rank]
-            eng.step_count += 1
-            Kx.step_begin(eng.ctr, 0, 1)
-            tr._launch("grad", eng.step_count)
+            if tr._overlap is not None:
+                # overlapped path: the beta part of the aggregation runs inside the d-theta sweep (the
+                # gradient buffers are only read by it, so they can still be cloned for the oracle)
+                Kx.step_begin(eng.ctr, 0, 1)
+                loss = eng.forward_backward(mb.bow, None, training=True, gscale=tr.weights[rank], fed=tr._overlap)
+                g = {n: eng.flat.view(eng.flat.G, n).detach().clone().contiguous() for n in names}
+                s_local = eng.flat.S.detach().clone() * tr.weights[rank]
+                eng.step_count += 1
+                tr._launch("grad", eng.step_count, parts=1)
+            else:
+                loss = eng.forward_backward(mb.bow, None, training=True, gscale=tr.weights[rank])
+                g = {n: eng.flat.view(eng.flat.G, n).detach().clone().contiguous() for n in names}
+                s_local = eng.flat.S.detach().clone() * tr.weights[rank]
+                eng.step_count += 1
+                Kx.step_begin(eng.ctr, 0, 1)
+                tr._launch("grad", eng.step_count)
             for n in names:
                 dist.all_reduce(g[n])
                 ref[n].grad = g[n]
@@ -94,6 +104,7 @@ def main():
     flag = torch.tensor([1.0 if ok else 0.0], device=device)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
+        print(f"overlap={'on' if tr._overlap is not None else 'off'} ", end="")
         print(f"agg={agg} world={world} losses/doc={['%.1f' % l for l in losses]} agg_us={tr.last_aggregation_us():.1f} "
               f"{'OK' if flag.item() == 1.0 else 'MISMATCH'}")
     dist.barrier()
