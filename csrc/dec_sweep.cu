@@ -862,6 +862,8 @@ static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta,
                "n_components too large for the fused decoder sweeps (need Kp <= 240)");
   p.stages = plan.stages;
   p.p_bufs = plan.p_bufs;
+  // aggregation CTAs stage (world-1) peer tiles of 16 KB per pipeline stage: give them the whole SM
+  if (kMode == ROW_GRAD2 && p.fed != nullptr) plan.bytes = (size_t)max_smem;
   p.smem_bytes = (uint32_t)plan.bytes;
   auto kern = sweep_kernel<kMode>;
   GF_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.bytes));

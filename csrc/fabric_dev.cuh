@@ -240,6 +240,7 @@ __device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const Gf
   const uint32_t stage_bytes = (uint32_t)n_remote * kFedTileBytes;
   int stages = (int)((smem_bytes - 17408 - 256) / stage_bytes);
   if (stages > kFedMaxStages) stages = kFedMaxStages;
+  if (stages < 1) stages = 1;  // (the launcher sizes the shared memory so that this never triggers)
   uint64_t* full = reinterpret_cast<uint64_t*>(ring + (size_t)stages * stage_bytes);
   uint64_t* empty = full + kFedMaxStages;
   if (threadIdx.x == 0) {
