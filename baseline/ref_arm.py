@@ -91,7 +91,7 @@ def run_reference_arm(args, cfg, ClockSampler, dist_env, make_corpus, allreduce_
     if world == 1:
         if is_ctm:
             model = RefCTM(logger=logger, contextual_size=cfg["C"], inference_type=cfg["inference_type"], **common)
-            data = RefCTMData(ctx, dense, idx2token)
+            data = RefCTMData(ctx, dense, idx2token, None)  # (X_contextual, X_bow, idx2token, qt)
         else:
             model = RefAVITM(logger=logger, **common)
             data = RefBOW(dense, idx2token)
@@ -105,7 +105,7 @@ def run_reference_arm(args, cfg, ClockSampler, dist_env, make_corpus, allreduce_
                 return {"impl": "reference",
                         "unavailable": "the reference's federated CTM is always CombinedTM (federated_ctm.py:24-45)"}
             model = RefFedCTM(tm, [], logger)
-            data = RefCTMData(ctx, dense, idx2token)
+            data = RefCTMData(ctx, dense, idx2token, None)  # (X_contextual, X_bow, idx2token, qt)
         else:
             model = RefFedAVITM(tm, [], logger)
             data = RefBOW(dense, idx2token)
