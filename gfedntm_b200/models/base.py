@@ -158,12 +158,12 @@ class NeuralTopicModel:
         self.early_stopping = EarlyStopping(patience=5, verbose=False)
 
         fused_ok = (self.device.type == "cuda" and solver == "adam" and label_size == 0
-                    and activation != "swish" and n_components <= 240 and max(hidden_sizes) <= 256
+                    and activation != "swish" and n_components <= 236 and max(hidden_sizes) <= 256
                     and len(hidden_sizes) <= 8 and not reduce_on_plateau)
         if backend == "auto":
             backend = "fused" if fused_ok else "eager"
         if backend == "fused" and not fused_ok:
-            raise ValueError("the fused backend needs CUDA, solver='adam', label_size=0, n_components<=240, "
+            raise ValueError("the fused backend needs CUDA, solver='adam', label_size=0, n_components<=236, "
                              "hidden sizes<=256 and reduce_on_plateau=False")
         self.backend = backend
         self.engine = None

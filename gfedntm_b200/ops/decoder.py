@@ -94,7 +94,7 @@ class ProdLDADecoder:
         self.max_B, self.V, self.K = max_B, V, K
         self.Kp = padded_topics(K)
         if self.Kp > 240:
-            raise ValueError("the fused decoder supports n_components <= 240")
+            raise ValueError("the fused decoder supports n_components <= 236 (four operand rows are reserved)")
         self.bn_eps, self.bn_momentum = bn_eps, bn_momentum
         dev = device
         f32 = dict(dtype=torch.float32, device=dev)

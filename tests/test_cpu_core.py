@@ -279,3 +279,40 @@ def test_weighted_aggregation_matches_reference_formula():
     want = np.sum(np.stack([t["beta"] * n for t, n in zip(tensors, nr)]), axis=0) / N.sum()
     np.testing.assert_allclose(got["beta"], want, rtol=1e-6)
     assert got["beta"].dtype == np.float32 and got["n"].dtype == np.int64
+
+
+def test_resource_sampler_writes_rows(tmp_path):
+    import csv
+    import time
+
+    from gfedntm_b200.utils.mem_usage import ResourceSampler
+
+    path = tmp_path / "usage.csv"
+    with ResourceSampler(str(path), period_s=0.05) as rs:
+        time.sleep(0.2)
+    rows = list(csv.reader(open(path)))
+    assert rows[0][:6] == ResourceSampler.HEADER and len(rows) >= 3 and rs.rows_written == len(rows) - 1
+    assert int(rows[1][3]) > 0  # rss
+
+
+def test_hierarchical_corpus_selection():
+    import numpy as np
+    import scipy.sparse as sp
+
+    from gfedntm_b200.aux_modules.hierarchical import htm_ds, htm_ws
+
+    rng = np.random.default_rng(0)
+    K, V, D = 3, 12, 40
+    betas = np.zeros((K, V))
+    for k in range(K):
+        betas[k, 4 * k:4 * k + 4] = 0.25  # disjoint vocabularies per topic
+    thetas = rng.dirichlet(np.full(K, 0.3), D)
+    counts = sp.csr_matrix(rng.poisson(1.0, (D, V)))
+    sub, keep = htm_ds(counts, thetas, topic=1, thr=0.5)
+    assert (thetas[keep, 1] >= 0.5).all() and sub.shape[0] == keep.size
+    ws, keep_ws = htm_ws(counts, thetas, betas, topic=2)
+    dense = ws.toarray()
+    assert dense[:, :8].sum() == 0  # only words of topic 2's vocabulary survive the arg-max selection
+    np.testing.assert_array_equal(dense[:, 8:], counts[keep_ws].toarray()[:, 8:] * (thetas[keep_ws, 2:3] > 0))
+    ws2, _ = htm_ws(counts, thetas, betas, topic=2, sample=True, seed=1)
+    assert ws2.toarray()[:, :8].sum() == 0
