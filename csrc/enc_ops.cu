@@ -67,6 +67,7 @@ enc_fwd_kernel(const GfEncArgs a_) {
   GfEncArgs a = a_;
   a.seed = step_seed(a_.seed, a_.step_ctr);
   __shared__ float hbuf[2][kDocsPerBlock][kMaxH];
+  extern __shared__ float wsm[];  // optional staging of the head weights, rows padded to HL+1 (a.w_smem)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b0 = blockIdx.x * kDocsPerBlock;
   const int b = b0 + warp;
@@ -175,21 +176,46 @@ enc_fwd_kernel(const GfEncArgs a_) {
   }
   __syncthreads();
 
-  // ---- heads: mu_pre / ls_pre, plus BatchNorm partial sums
+  // ---- heads: mu_pre / ls_pre, plus BatchNorm partial sums.
+  // Thread = one output n2 for ALL documents of the block: the weight row is read once (from the padded
+  // shared-memory copy when it fits: consecutive threads -> consecutive rows, stride HL+1 words, no bank
+  // conflicts; a thread-per-row walk over global memory touched 32 sectors per load), the BatchNorm sums of
+  // the block's documents are combined in registers -> kDocsPerBlock times fewer fp64 atomics.
   const int K = a.K;
-  for (int idx = threadIdx.x; idx < kDocsPerBlock * 2 * K; idx += blockDim.x) {
-    const int r = idx / (2 * K), n2 = idx - r * 2 * K;
-    const int bb = b0 + r;
-    if (bb >= a.B) continue;
+  const int ldw = HL + 1;
+  if (a.w_smem) {
+    for (int idx = threadIdx.x; idx < 2 * K * HL; idx += blockDim.x) {
+      const int n2 = idx / HL, m = idx - n2 * HL;
+      wsm[n2 * ldw + m] = __ldg((n2 >= K ? a.Wsig + (size_t)(n2 - K) * HL : a.Wmu + (size_t)n2 * HL) + m);
+    }
+    __syncthreads();
+  }
+  for (int n2 = threadIdx.x; n2 < 2 * K; n2 += blockDim.x) {
     const bool is_sig = n2 >= K;
     const int n = is_sig ? n2 - K : n2;
-    const float* wr = (is_sig ? a.Wsig : a.Wmu) + (size_t)n * HL;
-    float s = (is_sig ? a.bsig : a.bmu)[n];
-    for (int m = 0; m < HL; ++m) s = fmaf(__ldg(wr + m), hbuf[cur][r][m], s);
-    (is_sig ? a.ls_pre : a.mu_pre)[(size_t)bb * K + n] = s;
+    const float* wg = (is_sig ? a.Wsig : a.Wmu) + (size_t)n * HL;
+    const float* ws = wsm + n2 * ldw;
+    const float bias = (is_sig ? a.bsig : a.bmu)[n];
+    float s[kDocsPerBlock];
+#pragma unroll
+    for (int r = 0; r < kDocsPerBlock; ++r) s[r] = bias;
+    for (int m = 0; m < HL; ++m) {
+      const float w = a.w_smem ? ws[m] : __ldg(wg + m);
+#pragma unroll
+      for (int r = 0; r < kDocsPerBlock; ++r) s[r] = fmaf(w, hbuf[cur][r][m], s[r]);
+    }
+    double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+    for (int r = 0; r < kDocsPerBlock; ++r) {
+      if (b0 + r < a.B) {
+        (is_sig ? a.ls_pre : a.mu_pre)[(size_t)(b0 + r) * K + n] = s[r];
+        s1 += (double)s[r];
+        s2 += (double)s[r] * (double)s[r];
+      }
+    }
     if (a.bn_sums != nullptr) {
-      atomicAdd(&a.bn_sums[(is_sig ? 2 * K : 0) + n], (double)s);
-      atomicAdd(&a.bn_sums[(is_sig ? 3 * K : K) + n], (double)s * (double)s);
+      atomicAdd(&a.bn_sums[(is_sig ? 2 * K : 0) + n], s1);
+      atomicAdd(&a.bn_sums[(is_sig ? 3 * K : K) + n], s2);
     }
   }
 }
@@ -586,7 +612,12 @@ extern "C" int gf_enc_fwd(const GfEncArgs* a, void* stream_) {
   for (int l = 0; l < a->L; ++l) GF_ARG_CHECK(a->H[l] >= 1 && a->H[l] <= kMaxH, "hidden size must be <= 256");
   GF_ARG_CHECK(a->K >= 1 && a->K <= kMaxH, "n_components must be <= 256");
   const int grid = (a->B + kDocsPerBlock - 1) / kDocsPerBlock;
-  enc_fwd_kernel<<<grid, kDocsPerBlock * 32, 0, st>>>(*a);
+  GfEncArgs aa = *a;
+  const size_t wbytes = (size_t)2 * a->K * (a->H[a->L - 1] + 1) * sizeof(float);
+  aa.w_smem = wbytes <= 160 * 1024;  // head weights staged in shared memory when they fit
+  const size_t dyn = aa.w_smem ? wbytes : 0;
+  if (dyn > 0) GF_CUDA_CHECK(cudaFuncSetAttribute(enc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+  enc_fwd_kernel<<<grid, kDocsPerBlock * 32, dyn, st>>>(aa);
   GF_LAUNCHED();
   return GF_OK;
 }

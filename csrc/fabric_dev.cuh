@@ -236,9 +236,13 @@ __device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const Gf
   const int world = a.world, rank = me.rank, n_remote = world - 1;
   float* tile_v = reinterpret_cast<float*>(smem);
   float(*tv)[132] = reinterpret_cast<float(*)[132]>(tile_v);
-  uint8_t* ring = smem + 17408;  // 32*132*4 = 16896, rounded up to 1 KB
+  // transposed-shadow staging: 128 words x Kp topics bf16 (rows padded by 8), flushed as whole rows
+  const int ldt = a.Kp + 8;
+  __nv_bfloat16* tT = reinterpret_cast<__nv_bfloat16*>(smem + 17408);  // 32*132*4 = 16896, rounded up to 1 KB
+  const uint32_t tT_bytes = ((uint32_t)(128 * ldt * 2) + 1023u) & ~1023u;
+  uint8_t* ring = smem + 17408 + tT_bytes;
   const uint32_t stage_bytes = (uint32_t)n_remote * kFedTileBytes;
-  int stages = (int)((smem_bytes - 17408 - 256) / stage_bytes);
+  int stages = (int)((smem_bytes - 17408 - tT_bytes - 256) / stage_bytes);
   if (stages > kFedMaxStages) stages = kFedMaxStages;
   if (stages < 1) stages = 1;  // (the launcher sizes the shared memory so that this never triggers)
   uint64_t* full = reinterpret_cast<uint64_t*>(ring + (size_t)stages * stage_bytes);
@@ -250,35 +254,39 @@ __device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const Gf
     }
     mbar_fence_init();
   }
+  for (int i = threadIdx.x; i < 128 * ldt / 2; i += blockDim.x) reinterpret_cast<uint32_t*>(tT)[i] = 0u;
   __syncthreads();  // all threads of the CTA call this function
 
   const int vt = (a.V + 127) / 128, kt = (a.K + 31) / 32;
   const int per = (vt + world - 1) / world;
   const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;
-  const long long n_tiles = (long long)(t_hi > t_lo ? t_hi - t_lo : 0) * kt;
+  const int n_wt = t_hi > t_lo ? t_hi - t_lo : 0;  // word tiles owned by this rank; a CTA takes whole word tiles
 
   if (threadIdx.x >= 256 && threadIdx.x < 288) {
     // ---------------- producer warp
     const int lane = threadIdx.x - 256;
     uint32_t it = 0;
-    for (long long t = cta; t < n_tiles; t += n_cta, ++it) {
-      const int st = it % stages;
-      const int v0 = (t_lo + (int)(t / kt)) * 128, k0 = (int)(t % kt) * 32;
-      const int rows = min(32, a.K - k0);
+    for (int wt = cta; wt < n_wt; wt += n_cta) {
+      const int v0 = (t_lo + wt) * 128;
       const uint32_t row_bytes = (uint32_t)min(128, a.V - v0) * 4u;
-      mbar_wait(&empty[st], ((it / stages) & 1) ^ 1);
-      if (lane == 0) mbar_arrive_expect_tx(&full[st], (uint32_t)n_remote * (uint32_t)rows * row_bytes);
-      __syncwarp();
-      if (lane < rows) {
-        int slot = 0;
-        for (int c = 0; c < world; ++c) {
-          if (c == rank) continue;
-          const float* src = me.G[c] + a.beta_off + (long long)(k0 + lane) * a.V + v0;
-          const uint32_t dst = smem_u32(ring + (size_t)st * stage_bytes + (size_t)slot * kFedTileBytes + lane * 512);
-          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                       "l"(src), "r"(row_bytes), "r"(smem_u32(&full[st]))
-                       : "memory");
-          ++slot;
+      for (int kti = 0; kti < kt; ++kti, ++it) {
+        const int st = it % stages;
+        const int k0 = kti * 32;
+        const int rows = min(32, a.K - k0);
+        mbar_wait(&empty[st], ((it / stages) & 1) ^ 1);
+        if (lane == 0) mbar_arrive_expect_tx(&full[st], (uint32_t)n_remote * (uint32_t)rows * row_bytes);
+        __syncwarp();
+        if (lane < rows) {
+          int slot = 0;
+          for (int c = 0; c < world; ++c) {
+            if (c == rank) continue;
+            const float* src = me.G[c] + a.beta_off + (long long)(k0 + lane) * a.V + v0;
+            const uint32_t dst = smem_u32(ring + (size_t)st * stage_bytes + (size_t)slot * kFedTileBytes + lane * 512);
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                         "l"(src), "r"(row_bytes), "r"(smem_u32(&full[st]))
+                         : "memory");
+            ++slot;
+          }
         }
       }
     }
@@ -286,70 +294,84 @@ __device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const Gf
     // ---------------- consumers
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     uint32_t it = 0;
-    for (long long t = cta; t < n_tiles; t += n_cta, ++it) {
-      const int st = it % stages;
-      const int v0 = (t_lo + (int)(t / kt)) * 128, k0 = (int)(t % kt) * 32;
+    for (int wt = cta; wt < n_wt; wt += n_cta) {
+      const int v0 = (t_lo + wt) * 128;
       const int vv = v0 + tx * 4;
-      // local operands first (their latency overlaps the wait for the peers' tile)
-      float4 gl[4], pp[4], mm[4], v2[4];
-      bool live[4];
+      for (int kti = 0; kti < kt; ++kti, ++it) {
+        const int st = it % stages;
+        const int k0 = kti * 32;
+        // local operands first (their latency overlaps the wait for the peers' tile)
+        float4 gl[4], pp[4], mm[4], v2[4];
+        bool live[4];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int k = k0 + ty + r * 8;
-        live[r] = (k < a.K) && (vv < a.V);
-        if (live[r]) {
-          const long long ip = a.beta_off + (long long)k * a.V + vv;
-          gl[r] = *reinterpret_cast<const float4*>(me.G[rank] + ip);
-          pp[r] = *reinterpret_cast<const float4*>(me.P[rank] + ip);
-          mm[r] = *reinterpret_cast<const float4*>(me.M + ip);
-          v2[r] = *reinterpret_cast<const float4*>(me.V2 + ip);
-        }
-      }
-      mbar_wait(&full[st], (it / stages) & 1);
-      const uint8_t* sb = ring + (size_t)st * stage_bytes;
-#pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int k = k0 + ty + r * 8;
-        float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (live[r]) {
-          float4 g = gl[r];
-          for (int c = 0; c < n_remote; ++c) {
-            const float4 x = *reinterpret_cast<const float4*>(sb + (size_t)c * kFedTileBytes + (ty + r * 8) * 512 + tx * 16);
-            g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
-          }
-          const long long ip = a.beta_off + (long long)k * a.V + vv;
-          val = pp[r];
-          val.x = adam_upd(val.x, g.x, mm[r].x, v2[r].x, h);
-          val.y = adam_upd(val.y, g.y, mm[r].y, v2[r].y, h);
-          val.z = adam_upd(val.z, g.z, mm[r].z, v2[r].z, h);
-          val.w = adam_upd(val.w, g.w, mm[r].w, v2[r].w, h);
-          *reinterpret_cast<float4*>(me.M + ip) = mm[r];
-          *reinterpret_cast<float4*>(me.V2 + ip) = v2[r];
-          __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
-                                            __float2bfloat16(val.z), __float2bfloat16(val.w)};
-          for (int c = 0; c < world; ++c) {
-            st_peer_f4(me.P[c] + ip, val);
-            if (me.beta_bf[c] != nullptr)
-              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c]) + (size_t)k * a.ldb + vv) =
-                  *reinterpret_cast<const uint2*>(o);
+        for (int r = 0; r < 4; ++r) {
+          const int k = k0 + ty + r * 8;
+          live[r] = (k < a.K) && (vv < a.V);
+          if (live[r]) {
+            const long long ip = a.beta_off + (long long)k * a.V + vv;
+            gl[r] = *reinterpret_cast<const float4*>(me.G[rank] + ip);
+            pp[r] = *reinterpret_cast<const float4*>(me.P[rank] + ip);
+            mm[r] = *reinterpret_cast<const float4*>(me.M + ip);
+            v2[r] = *reinterpret_cast<const float4*>(me.V2 + ip);
           }
         }
-        *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
-      }
-      fed_sync256();
-      if (threadIdx.x == 0) mbar_arrive(&empty[st]);  // every consumer has read the stage
-      const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
-      const int vw = v0 + wv, kb = k0 + half * 16;
-      if (vw < a.V && kb < a.Kp) {
-        __align__(16) __nv_bfloat16 o[16];
+        mbar_wait(&full[st], (it / stages) & 1);
+        const uint8_t* sb = ring + (size_t)st * stage_bytes;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
-        for (int c = 0; c < world; ++c)
-          if (me.betaT_bf[c] != nullptr) {
-            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c]) + (size_t)vw * a.Kp + kb);
-            dst[0] = reinterpret_cast<const uint4*>(o)[0];
-            dst[1] = reinterpret_cast<const uint4*>(o)[1];
+        for (int r = 0; r < 4; ++r) {
+          const int k = k0 + ty + r * 8;
+          float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (live[r]) {
+            float4 g = gl[r];
+            for (int c = 0; c < n_remote; ++c) {
+              const float4 x = *reinterpret_cast<const float4*>(sb + (size_t)c * kFedTileBytes + (ty + r * 8) * 512 + tx * 16);
+              g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+            }
+            const long long ip = a.beta_off + (long long)k * a.V + vv;
+            val = pp[r];
+            val.x = adam_upd(val.x, g.x, mm[r].x, v2[r].x, h);
+            val.y = adam_upd(val.y, g.y, mm[r].y, v2[r].y, h);
+            val.z = adam_upd(val.z, g.z, mm[r].z, v2[r].z, h);
+            val.w = adam_upd(val.w, g.w, mm[r].w, v2[r].w, h);
+            *reinterpret_cast<float4*>(me.M + ip) = mm[r];
+            *reinterpret_cast<float4*>(me.V2 + ip) = v2[r];
+            __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
+                                              __float2bfloat16(val.z), __float2bfloat16(val.w)};
+            for (int c = 0; c < world; ++c) {
+              st_peer_f4(me.P[c] + ip, val);
+              if (me.beta_bf[c] != nullptr)
+                *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c]) + (size_t)k * a.ldb + vv) =
+                    *reinterpret_cast<const uint2*>(o);
+            }
           }
+          *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
+        }
+        fed_sync256();
+        if (threadIdx.x == 0) mbar_arrive(&empty[st]);  // every consumer has read the stage
+        // transpose this 32-topic slab into the row-major [word][topic] staging tile
+        const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
+        const int kb = k0 + half * 16;
+        if (kb < a.Kp) {
+          __align__(16) __nv_bfloat16 o[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
+          uint4* dst = reinterpret_cast<uint4*>(tT + (size_t)wv * ldt + kb);
+          dst[0] = reinterpret_cast<const uint4*>(o)[0];
+          dst[1] = reinterpret_cast<const uint4*>(o)[1];
+        }
+        fed_sync256();
+      }
+      // flush the transposed shadow of this word tile: whole rows of Kp bf16, 16-byte pieces, consecutive
+      // threads -> consecutive addresses (large NVLink packets instead of one 32-byte store per topic slab)
+      const int cpr = a.Kp >> 3;  // 16-byte chunks per row
+      for (int idx = threadIdx.x; idx < 128 * cpr; idx += 256) {
+        const int rw = idx / cpr, ch = idx - rw * cpr;
+        if (v0 + rw < a.V) {
+          const uint4 q = *reinterpret_cast<const uint4*>(tT + (size_t)rw * ldt + ch * 8);
+          for (int c = 0; c < world; ++c)
+            if (me.betaT_bf[c] != nullptr)
+              *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c]) + (size_t)(v0 + rw) * a.Kp + ch * 8) = q;
+        }
       }
       fed_sync256();
     }

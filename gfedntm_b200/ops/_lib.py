@@ -53,6 +53,7 @@ class GfEncArgs(C.Structure):
         ("bn_sums", _p),
         ("seed", _u64),
         ("step_ctr", _p),
+        ("w_smem", _i),
     ]
 
 

@@ -131,6 +131,7 @@ typedef struct GfEncArgs {
   double* bn_sums;           /* out (+=): [4K] sum mu, sum mu^2, sum ls, sum ls^2 (zeroed by caller) */
   unsigned long long seed;
   const long long* step_ctr; /* optional device counters (gf_step_begin): seed advances by ctr[0]    */
+  int w_smem;                /* set by gf_enc_fwd (callers leave 0): head weights staged in shared memory */
 } GfEncArgs;
 /* Device-side step counters, so that a whole training step can be replayed from a CUDA graph:
  * ctr[0] counts forward passes (advances the dropout / reparameterisation seeds), ctr[1] counts
