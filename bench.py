@@ -214,7 +214,7 @@ def run_ours(args, cfg: dict) -> dict:
     loss_host = torch.zeros(1, dtype=torch.float64).pin_memory()
     it = iter(loader)
     h2d = 0
-    for _ in range(max(args.warmup, 5)):
+    for _ in range(max(args.warmup, 9)):  # three staging slots x (eager warm-up + graph capture) + slack
         try:
             mb = next(it)
         except StopIteration:

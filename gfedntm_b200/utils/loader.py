@@ -2,7 +2,9 @@
 
 The corpus stays on the host as one CSR matrix.  Each minibatch is assembled by the native helper
 ``gf_host_gather_csr`` straight into pinned staging buffers and copied with one async H2D copy
-per array; two staging slots alternate so the next batch is assembled while the current step runs.
+per array.  On CUDA a background thread assembles and uploads the following batches (three staging slots
+rotate) while the current step runs, so neither the host gather nor the H2D copy sits on the step's
+critical path even when the caller synchronises on every step's loss.
 
 Ref: ``DataLoader(train_data, batch_size, shuffle=True)`` in federated_model.py:82-86 and
 avitm.py:371-375 (dense rows, default collate, ``.cuda()`` per batch).
@@ -10,6 +12,8 @@ avitm.py:371-375 (dense rows, default collate, ``.cuda()`` per batch).
 from __future__ import annotations
 
 import ctypes as C
+import queue
+import threading
 from dataclasses import dataclass
 from typing import Iterator, Optional
 
@@ -56,6 +60,9 @@ class _Slot:
             self.ctx_d = torch.empty(max_B, C_ctx, dtype=torch.float32, device=device) if C_ctx else None
             self.lab_d = torch.empty(max_B, L, dtype=torch.float32, device=device) if L else None
         self.ready = torch.cuda.Event() if pin else None
+        self.consumed = None                      # CUDA event: every kernel reading this slot has been queued
+        self.free = threading.Event()             # host side: `consumed` is valid (or the slot is unused)
+        self.free.set()
         self.in_flight = False
 
 
@@ -63,7 +70,7 @@ class CsrMinibatchLoader:
     """Iterates over a ``BOWDataset`` / ``CTMDataset`` in (optionally shuffled) CSR minibatches."""
 
     def __init__(self, dataset, batch_size: int, shuffle: bool = True, drop_last: bool = False,
-                 device=None, seed: int = 0, n_threads: int = 4) -> None:
+                 device=None, seed: int = 0, n_threads: int = 4, prefetch: Optional[bool] = None) -> None:
         self.dataset = dataset
         self.batch_size = int(batch_size)
         self.shuffle, self.drop_last = shuffle, drop_last
@@ -82,7 +89,13 @@ class CsrMinibatchLoader:
         self.labels = getattr(dataset, "labels", None)
         C_ctx = self.ctx.shape[1] if self.ctx is not None else 0
         L = self.labels.shape[1] if self.labels is not None else 0
-        self.slots = [_Slot(self.batch_size, self.max_nnz, C_ctx, L, self.device) for _ in range(2)]
+        if prefetch is None:
+            # the hand-off to the staging thread costs ~30 us per batch: only worth it when assembling a
+            # batch takes longer than that (measured: B=64 217k -> 199k docs/s, B=4096 1.02M -> 1.09M)
+            prefetch = self.max_nnz >= 65536
+        self.prefetch = bool(prefetch) and self.device.type == "cuda"
+        self.slots = [_Slot(self.batch_size, self.max_nnz, C_ctx, L, self.device)
+                      for _ in range(3 if self.prefetch else 2)]
         self.lib = _native()
         self.copy_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
 
@@ -150,6 +163,9 @@ class CsrMinibatchLoader:
         starts = list(range(0, self.N, self.batch_size))
         if self.drop_last and starts and self.N - starts[-1] < self.batch_size:
             starts.pop()
+        if self.prefetch:
+            yield from self._iter_prefetch(order, starts)
+            return
         pending = None
         for i, s in enumerate(starts):
             slot = self.slots[i & 1]
@@ -164,3 +180,62 @@ class CsrMinibatchLoader:
             pending = mb
         if pending is not None:
             yield pending
+
+    # -- background staging: the worker is at most two batches ahead (one queued, one being assembled)
+    def _iter_prefetch(self, order: np.ndarray, starts) -> Iterator[Minibatch]:
+        q: "queue.Queue" = queue.Queue(maxsize=1)
+        stop = threading.Event()
+        dev = self.device
+
+        def worker() -> None:
+            try:
+                torch.cuda.set_device(dev)
+                for i, s in enumerate(starts):
+                    slot = self.slots[i % 3]
+                    while not slot.free.wait(0.05):
+                        if stop.is_set():
+                            return
+                    if slot.consumed is not None:
+                        self.copy_stream.wait_event(slot.consumed)  # the step that read this slot is queued
+                    mb = self._stage(slot, order[s:s + self.batch_size])
+                    while True:
+                        if stop.is_set():
+                            return
+                        try:
+                            q.put((mb, slot), timeout=0.05)
+                            break
+                        except queue.Full:
+                            continue
+                q.put(None)
+            except BaseException as ex:  # surface staging errors in the consumer
+                q.put(ex)
+
+        t = threading.Thread(target=worker, name="gfedntm-loader", daemon=True)
+        t.start()
+        prev = None
+        try:
+            while True:
+                item = q.get()
+                if item is None:
+                    break
+                if isinstance(item, BaseException):
+                    raise item
+                mb, slot = item
+                cur = torch.cuda.current_stream(dev)
+                if prev is not None:  # everything that reads the previous batch has been queued by now
+                    prev.consumed = torch.cuda.Event()
+                    prev.consumed.record(cur)
+                    prev.free.set()
+                slot.free.clear()
+                cur.wait_event(slot.ready)
+                prev = slot
+                yield mb
+        finally:
+            stop.set()
+            if prev is not None:
+                prev.consumed = torch.cuda.Event()
+                prev.consumed.record(torch.cuda.current_stream(dev))
+                prev.free.set()
+            for sl in self.slots:
+                sl.free.set()
+            t.join(timeout=5)
