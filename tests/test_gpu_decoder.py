@@ -137,3 +137,71 @@ def test_prodlda_decoder_eval_mode(B, V, K, folded):
     rl_ref = -(x * torch.log(torch.softmax(y, 1) + 1e-10)).sum(1)
     torch.testing.assert_close(rl, rl_ref, rtol=3e-3, atol=2e-2)
     assert abs(loss.item() - rl_ref.sum().item()) <= 3e-3 * abs(rl_ref.sum().item())
+
+
+def test_csr_to_csc_large_vocabulary():
+    """Many scan segments (V = 300k -> 74 blocks of 4096) and the dynamic-nnz variant."""
+    from gfedntm_b200.ops.decoder import CscWorkspace, CsrBatch
+
+    B, V, nnz_doc = 512, 300_001, 64
+    g = torch.Generator(device="cuda").manual_seed(9)
+    idx = torch.randint(0, V, (B, nnz_doc), device="cuda", generator=g).sort(1).values.to(torch.int32)
+    indptr = (torch.arange(B + 1, device="cuda") * nnz_doc).to(torch.int32)
+    batch = CsrBatch(indptr, idx.reshape(-1).contiguous(), torch.ones(B * nnz_doc, device="cuda"), B, V)
+    for dyn in (False, True):
+        csc = CscWorkspace(V, batch.nnz + (1000 if dyn else 0), "cuda")
+        csc.build(batch, dynamic_nnz=dyn)
+        torch.cuda.synchronize()
+        ref = torch.zeros(V + 1, dtype=torch.int64, device="cuda")
+        ref[1:] = torch.cumsum(torch.bincount(batch.indices.long(), minlength=V), 0)
+        assert torch.equal(csc.colptr.long(), ref)
+        src = csc.src[: batch.nnz].long()
+        assert torch.equal(torch.sort(src).values, torch.arange(batch.nnz, device="cuda"))
+        cols = torch.repeat_interleave(torch.arange(V, device="cuda"), (ref[1:] - ref[:-1]))
+        assert torch.equal(batch.indices.long()[src], cols)
+
+
+@pytest.mark.parametrize("V,K", [(1000, 10), (70_000, 200), (5000, 124)])
+def test_gram_gemm_matches_torch(V, K):
+    """Split-V tcgen05 Gram GEMM (+ finish): M = X Y^T summed over the CTAs' partials, stored as bf16 hi/lo."""
+    from gfedntm_b200.ops import kernels as Kx
+
+    Kp = Kx.padded_topics(K)
+    g = torch.Generator(device="cuda").manual_seed(4)
+    ld = Kx.round_up(V, 8)
+    x = torch.zeros(Kp, ld, dtype=torch.bfloat16, device="cuda")
+    y = torch.zeros(Kp, ld, dtype=torch.bfloat16, device="cuda")
+    x[: K + 1, :V] = (torch.randn(K + 1, V, device="cuda", generator=g) * 0.3).to(torch.bfloat16)
+    y[:K, :V] = (torch.randn(K, V, device="cuda", generator=g) * 0.3).to(torch.bfloat16)
+    parts = Kx.gram_parts()
+    partial = torch.full((parts * Kp * Kp,), float("nan"), device="cuda")
+    n_ext = (Kp + 127) // 128
+    out = torch.zeros(Kp, 2 * n_ext * 128, dtype=torch.bfloat16, device="cuda")
+    Kx.gram(x, y, partial, V=V)
+    Kx.gram_finish(partial, parts, out, K=K, col_hi=0, col_lo=n_ext * 128)
+    torch.cuda.synchronize()
+    ref = x[: K + 1, :V].float() @ y[:K, :V].float().t()
+    got = out[: K + 1, :K].float() + out[: K + 1, n_ext * 128: n_ext * 128 + K].float()
+    torch.testing.assert_close(got, ref, rtol=1e-4, atol=1e-4 * ref.abs().max().item())
+    assert torch.count_nonzero(out[K + 1:]) == 0
+
+
+def test_csc_corr_transposed_matches_row_major():
+    from gfedntm_b200.ops import kernels as Kx
+    from gfedntm_b200.ops.decoder import CscWorkspace
+
+    theta, beta, x, beta_bf, betaT_bf, batch, _ = _mk(150, 1234, 50, seed=8)
+    Kp = beta_bf.shape[0]
+    csc = CscWorkspace(1234, batch.nnz, "cuda")
+    csc.build(batch)
+    th_bf = torch.zeros(150, Kp, dtype=torch.bfloat16, device="cuda")
+    th_bf[:, :50] = theta.to(torch.bfloat16)
+    tn = torch.rand(batch.nnz, device="cuda")
+    corr = torch.zeros(1234, Kp, device="cuda")
+    corrT = torch.full((Kp, Kx.round_up(1234, 8)), 7.0, device="cuda")
+    Kx.csc_corr(csc.colptr, csc.row, csc.src, tn, th_bf, corr, V=1234)
+    Kx.csc_corr_t(csc.colptr, csc.row, csc.src, tn, th_bf, corrT, V=1234)
+    torch.cuda.synchronize()
+    nonempty = (csc.colptr[1:] > csc.colptr[:-1])
+    torch.testing.assert_close(corrT[:, :1234].t()[nonempty], corr[nonempty])
+    assert (corrT[:, :1234].t()[~nonempty] == 7.0).all()  # words without entries are left untouched
