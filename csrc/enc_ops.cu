@@ -112,14 +112,30 @@ enc_fwd_kernel(const GfEncArgs a_) {
       }
     }
     if (a.xdense != nullptr) {
+      // dense part (contextual embedding): 32 inputs per round (one per lane), weight rows of 8 inputs in
+      // flight at a time -- a one-input-at-a-time loop was a serial chain of C dependent L2 round trips
       const float* xr = a.xdense + (size_t)b * a.C;
-      for (int c0 = 0; c0 < a.C; ++c0) {
-        const float x = __ldg(xr + c0);
-        const float* wr = a.WdT + (size_t)c0 * H0;
+      for (int base = 0; base < a.C; base += 32) {
+        const float x_l = (base + lane < a.C) ? __ldg(xr + base + lane) : 0.f;
+        const int n = min(32, a.C - base);
+        for (int i0 = 0; i0 < n; i0 += 8) {
+          float w[8][kMaxH / 32];
+          float xs[8];
 #pragma unroll
-        for (int c = 0; c < kMaxH / 32; ++c) {
-          const int j = c * 32 + lane;
-          if (j < H0) acc[c] = fmaf(x, __ldg(wr + j), acc[c]);
+          for (int u = 0; u < 8; ++u) {
+            xs[u] = (i0 + u < n) ? __shfl_sync(0xffffffffu, x_l, (i0 + u) & 31) : 0.f;
+            const int ci = min(base + i0 + u, a.C - 1);
+            const float* wr = a.WdT + (size_t)ci * H0;
+#pragma unroll
+            for (int c = 0; c < kMaxH / 32; ++c) {
+              const int j = c * 32 + lane;
+              w[u][c] = (j < H0) ? __ldg(wr + j) : 0.f;
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+#pragma unroll
+            for (int c = 0; c < kMaxH / 32; ++c) acc[c] = fmaf(xs[u], w[u][c], acc[c]);
         }
       }
     }
