@@ -383,48 +383,65 @@ __global__ void theta_center_kernel(const float* __restrict__ theta, const float
 // prior gradients and the BatchNorm-backward batch sums.  One warp per document.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) latent_bwd_kernel(const GfLatentBwdArgs a) {
+  // per-block partial sums of the six per-topic reductions (8 documents per block): one global atomic per
+  // block and topic instead of one per document and topic
+  __shared__ float red[6][kMaxH];
+  for (int i = threadIdx.x; i < 6 * kMaxH; i += blockDim.x) (&red[0][0])[i] = 0.f;
+  __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * 8 + warp;
-  if (b >= a.B) return;
   const int K = a.K;
-  float g[kMaxH / 32], ths[kMaxH / 32];
-  float dot = 0.f;
+  if (b < a.B) {
+    float g[kMaxH / 32], ths[kMaxH / 32];
+    float dot = 0.f;
 #pragma unroll
-  for (int c = 0; c < kMaxH / 32; ++c) {
-    const int k = c * 32 + lane;
-    g[c] = 0.f; ths[c] = 0.f;
-    if (k < K) {
-      const size_t o = (size_t)b * K + k;
-      g[c] = a.dtheta[(size_t)b * a.ld_dtheta + k] * a.mask_theta[o];
-      ths[c] = a.theta_s[o];
-      dot = fmaf(g[c], ths[c], dot);
+    for (int c = 0; c < kMaxH / 32; ++c) {
+      const int k = c * 32 + lane;
+      g[c] = 0.f; ths[c] = 0.f;
+      if (k < K) {
+        const size_t o = (size_t)b * K + k;
+        g[c] = a.dtheta[(size_t)b * a.ld_dtheta + k] * a.mask_theta[o];
+        ths[c] = a.theta_s[o];
+        dot = fmaf(g[c], ths[c], dot);
+      }
+    }
+    dot = warp_sum(dot);
+#pragma unroll
+    for (int c = 0; c < kMaxH / 32; ++c) {
+      const int k = c * 32 + lane;
+      if (k < K) {
+        const size_t o = (size_t)b * K + k;
+        const float dz = ths[c] * (g[c] - dot);
+        const float mu = a.mu[o], lv = a.logvar[o], ep = a.eps[o];
+        const float pv = a.prior_var[k], pm = a.prior_mean[k];
+        const float var = __expf(lv), sd = __expf(0.5f * lv);
+        const float w = a.kl_weight * a.gscale;
+        const float dmu = dz + w * (mu - pm) / pv;
+        const float dlv = dz * 0.5f * ep * sd + w * 0.5f * (var / pv - 1.f);
+        a.dmu[o] = dmu;
+        a.dlv[o] = dlv;
+        // BatchNorm backward needs sum_b d and sum_b d*xhat per topic
+        atomicAdd(&red[0][k], dmu);
+        atomicAdd(&red[1][k], dmu * mu);
+        atomicAdd(&red[2][k], dlv);
+        atomicAdd(&red[3][k], dlv * lv);
+        if (a.d_prior_mean != nullptr) {
+          const float d = pm - mu;
+          atomicAdd(&red[4][k], w * d / pv);
+          atomicAdd(&red[5][k], w * 0.5f * (-var / (pv * pv) - d * d / (pv * pv) + 1.f / pv));
+        }
+      }
     }
   }
-  dot = warp_sum(dot);
-#pragma unroll
-  for (int c = 0; c < kMaxH / 32; ++c) {
-    const int k = c * 32 + lane;
-    if (k < K) {
-      const size_t o = (size_t)b * K + k;
-      const float dz = ths[c] * (g[c] - dot);
-      const float mu = a.mu[o], lv = a.logvar[o], ep = a.eps[o];
-      const float pv = a.prior_var[k], pm = a.prior_mean[k];
-      const float var = __expf(lv), sd = __expf(0.5f * lv);
-      const float w = a.kl_weight * a.gscale;
-      const float dmu = dz + w * (mu - pm) / pv;
-      const float dlv = dz * 0.5f * ep * sd + w * 0.5f * (var / pv - 1.f);
-      a.dmu[o] = dmu;
-      a.dlv[o] = dlv;
-      // BatchNorm backward needs sum_b d and sum_b d*xhat per topic
-      atomicAdd(&a.bn_bsums[k], dmu);
-      atomicAdd(&a.bn_bsums[K + k], dmu * mu);
-      atomicAdd(&a.bn_bsums[2 * K + k], dlv);
-      atomicAdd(&a.bn_bsums[3 * K + k], dlv * lv);
-      if (a.d_prior_mean != nullptr) {
-        const float d = pm - mu;
-        atomicAdd(&a.d_prior_mean[k], w * d / pv);
-        atomicAdd(&a.d_prior_var[k], w * 0.5f * (-var / (pv * pv) - d * d / (pv * pv) + 1.f / pv));
-      }
+  __syncthreads();
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    atomicAdd(&a.bn_bsums[k], red[0][k]);
+    atomicAdd(&a.bn_bsums[K + k], red[1][k]);
+    atomicAdd(&a.bn_bsums[2 * K + k], red[2][k]);
+    atomicAdd(&a.bn_bsums[3 * K + k], red[3][k]);
+    if (a.d_prior_mean != nullptr) {
+      atomicAdd(&a.d_prior_mean[k], red[4][k]);
+      atomicAdd(&a.d_prior_var[k], red[5][k]);
     }
   }
 }
