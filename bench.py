@@ -247,6 +247,9 @@ def run_ours(args, cfg: dict) -> dict:
         "config": {"model": cfg["desc"], "name": args.config, "global_batch": world * B, "seq_len": None,
                    "vocab": V, "topics": K, "hidden": list(cfg["hidden"]),
                    "parallelism": f"fed{world}" + (f"-{args.agg}" if world > 1 else ""),
+                   "aggregation": None if world == 1 else {
+                       "overlap_ctas": getattr(getattr(trainer, "_overlap", None), "ctas", 0),
+                       "nvls_multicast": bool(trainer.aggregator.args.ranks[0].P_mc)},
                    "l2": "flush 252 MB between timed steps" if flush is not None else
                          "working set (params+shadows+grads) larger than L2"},
         "e2e": {"value": docs / e2e_s, "unit": "docs/s", "h2d_bytes_per_step": int(h2d),

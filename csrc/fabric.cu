@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
             acc.z = fmaf(w, in[c].z, acc.z); acc.w = fmaf(w, in[c].w, acc.w);
           }
       }
-      for (int c = 0; c < world; ++c) st_peer_f4(me.P[c] + i, acc);
+      fed_push_f4(me.P, me.P_mc, i, acc, world);
     }
   }
 
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
         acc.x = fmaf(w, s.x, acc.x); acc.y = fmaf(w, s.y, acc.y);
         acc.z = fmaf(w, s.z, acc.z); acc.w = fmaf(w, s.w, acc.w);
       }
-      for (int c = 0; c < world; ++c) st_peer_f4(me.S[c] + i, acc);
+      fed_push_f4(me.S, me.S_mc, i, acc, world);
     }
   }
 

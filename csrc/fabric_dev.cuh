@@ -35,6 +35,37 @@ __device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
                : "memory");
 }
 
+// NVLS multicast stores: the address is the multicast alias of a symmetric buffer; the switch delivers
+// the store to every rank of the group (including the issuing one).
+__device__ __forceinline__ void mc_st_f4(float* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void mc_st_b64(void* p, uint2 v) {
+  const unsigned long long q = ((unsigned long long)v.y << 32) | v.x;
+  asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(p), "l"(q) : "memory");
+}
+__device__ __forceinline__ void mc_st_b128(void* p, uint4 v) {
+  mc_st_b64(p, make_uint2(v.x, v.y));
+  mc_st_b64(reinterpret_cast<uint8_t*>(p) + 8, make_uint2(v.z, v.w));
+}
+// store helpers used by every aggregation path: multicast when the alias is present, else one store per rank
+__device__ __forceinline__ void fed_push_f4(float* const* per_rank, float* mc, long long off, float4 v, int world) {
+  if (mc != nullptr) { mc_st_f4(mc + off, v); return; }
+  for (int c = 0; c < world; ++c) st_peer_f4(per_rank[c] + off, v);
+}
+__device__ __forceinline__ void fed_push_b64(void* const* per_rank, void* mc, size_t elem_off_bf16, uint2 v, int world) {
+  if (mc != nullptr) { mc_st_b64(reinterpret_cast<__nv_bfloat16*>(mc) + elem_off_bf16, v); return; }
+  for (int c = 0; c < world; ++c)
+    if (per_rank[c] != nullptr) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(per_rank[c]) + elem_off_bf16) = v;
+}
+__device__ __forceinline__ void fed_push_b128(void* const* per_rank, void* mc, size_t elem_off_bf16, uint4 v, int world) {
+  if (mc != nullptr) { mc_st_b128(reinterpret_cast<__nv_bfloat16*>(mc) + elem_off_bf16, v); return; }
+  for (int c = 0; c < world; ++c)
+    if (per_rank[c] != nullptr) *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(per_rank[c]) + elem_off_bf16) = v;
+}
+
 struct AdamF {
   float lr, b1, b2, eps, bc1, bc2_sqrt, wd;
 };
@@ -143,12 +174,8 @@ __device__ __forceinline__ void fed_beta_phase(const GfFedArgs& a, const GfFabri
           }
           __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
                                             __float2bfloat16(val.z), __float2bfloat16(val.w)};
-          for (int c = 0; c < world; ++c) {
-            st_peer_f4(me.P[c] + ip, val);
-            if (me.beta_bf[c] != nullptr)
-              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c]) + (size_t)k * a.ldb + vv) =
-                  *reinterpret_cast<const uint2*>(o);
-          }
+          fed_push_f4(me.P, me.P_mc, ip, val, world);
+          fed_push_b64(me.beta_bf, me.beta_bf_mc, (size_t)k * a.ldb + vv, *reinterpret_cast<const uint2*>(o), world);
         }
         *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
       }
@@ -159,12 +186,8 @@ __device__ __forceinline__ void fed_beta_phase(const GfFedArgs& a, const GfFabri
         __align__(16) __nv_bfloat16 o[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
-        for (int c = 0; c < world; ++c)
-          if (me.betaT_bf[c] != nullptr) {
-            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c]) + (size_t)vw * a.Kp + kb);
-            dst[0] = reinterpret_cast<const uint4*>(o)[0];
-            dst[1] = reinterpret_cast<const uint4*>(o)[1];
-          }
+        fed_push_b128(me.betaT_bf, me.betaT_bf_mc, (size_t)vw * a.Kp + kb, reinterpret_cast<const uint4*>(o)[0], world);
+        fed_push_b128(me.betaT_bf, me.betaT_bf_mc, (size_t)vw * a.Kp + kb + 8, reinterpret_cast<const uint4*>(o)[1], world);
       }
       fed_sync256();
     }
@@ -337,12 +360,8 @@ __device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const Gf
             *reinterpret_cast<float4*>(me.V2 + ip) = v2[r];
             __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
                                               __float2bfloat16(val.z), __float2bfloat16(val.w)};
-            for (int c = 0; c < world; ++c) {
-              st_peer_f4(me.P[c] + ip, val);
-              if (me.beta_bf[c] != nullptr)
-                *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(me.beta_bf[c]) + (size_t)k * a.ldb + vv) =
-                    *reinterpret_cast<const uint2*>(o);
-            }
+            fed_push_f4(me.P, me.P_mc, ip, val, world);
+            fed_push_b64(me.beta_bf, me.beta_bf_mc, (size_t)k * a.ldb + vv, *reinterpret_cast<const uint2*>(o), world);
           }
           *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
         }
@@ -368,9 +387,7 @@ __device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const Gf
         const int rw = idx / cpr, ch = idx - rw * cpr;
         if (v0 + rw < a.V) {
           const uint4 q = *reinterpret_cast<const uint4*>(tT + (size_t)rw * ldt + ch * 8);
-          for (int c = 0; c < world; ++c)
-            if (me.betaT_bf[c] != nullptr)
-              *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(me.betaT_bf[c]) + (size_t)(v0 + rw) * a.Kp + ch * 8) = q;
+          fed_push_b128(me.betaT_bf, me.betaT_bf_mc, (size_t)(v0 + rw) * a.Kp + ch * 8, q, world);
         }
       }
       fed_sync256();

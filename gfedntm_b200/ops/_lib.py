@@ -126,6 +126,7 @@ class GfFabricRank(C.Structure):
         ("G", _p * GF_MAX_RANKS), ("P", _p * GF_MAX_RANKS), ("S", _p * GF_MAX_RANKS),
         ("beta_bf", _p * GF_MAX_RANKS), ("betaT_bf", _p * GF_MAX_RANKS), ("flags", _p * GF_MAX_RANKS),
         ("M", _p), ("V2", _p), ("done_counter", _p),
+        ("P_mc", _p), ("S_mc", _p), ("beta_bf_mc", _p), ("betaT_bf_mc", _p),
     ]
 
 

@@ -16,6 +16,7 @@ Three arena flavours:
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -148,6 +149,13 @@ def fill_rank_ctx(ctx, arena, rank: int, *, M: torch.Tensor, V2: torch.Tensor, d
         ctx.betaT_bf[c] = arena.peer_ptr(c, "betaT_bf") if has_shadows else None
     ctx.M, ctx.V2 = M.data_ptr(), V2.data_ptr()
     ctx.done_counter = done_counter.data_ptr()
+    # NVLS: one multimem.st per element instead of one P2P store per rank (opt-in until validated at scale)
+    mc = int(getattr(arena, "multicast_ptr", 0) or 0)
+    use_mc = mc != 0 and os.environ.get("GFEDNTM_NVLS", "0") == "1"
+    ctx.P_mc = (mc + arena.offsets["P"]) if use_mc else None
+    ctx.S_mc = (mc + arena.offsets["S"]) if use_mc else None
+    ctx.beta_bf_mc = (mc + arena.offsets["beta_bf"]) if (use_mc and has_shadows) else None
+    ctx.betaT_bf_mc = (mc + arena.offsets["betaT_bf"]) if (use_mc and has_shadows) else None
 
 
 class FusedAggregator:

@@ -319,6 +319,9 @@ typedef struct GfFabricRank {
                                      slot 0 gradients ready, 1 pushes done, 2 beta gradient ready      */
   float* M; float* V2;            /* this rank's Adam moments (same indexing as P)              */
   unsigned int* done_counter;     /* this rank, zeroed once                                     */
+  /* Optional NVLS multicast aliases of the same buffers (one multimem.st reaches every rank, the
+     NVSwitch replicates it); null => one P2P store per rank.                                    */
+  float* P_mc; float* S_mc; void* beta_bf_mc; void* betaT_bf_mc;
 } GfFabricRank;
 
 typedef struct GfFedArgs {
