@@ -3,7 +3,8 @@
 // Used by the folded ProdLDA decoder backward (csrc/fold_ops.cu header): with x = beta3 (rows
 // gamma_v*beta[j,v], row K = alpha_v, written by the COL_GRAD2 drain) and y = the unscaled bf16 beta
 // shadow, the sum of the partials is M = beta diag(gamma) beta^T with a = beta.alpha in row K; the
-// BatchNorm-backward part of d theta is then  -(a + theta_c M)  (gf_dtheta_base).
+// BatchNorm-backward part of d theta is then  -(a + theta_c M): gf_gram_finish stores M (hi/lo bf16) as
+// pseudo-word tiles of beta', so the MMA1 of GF_ROW_GRAD2 produces that term.
 // Ref math: autograd of decoder_network.py:123-124 (BatchNorm1d over the batch of theta.beta).
 //
 // Both operands are [Kp, V] bf16 with the vocabulary contiguous, i.e. K-major for a contraction
