@@ -20,8 +20,15 @@
 //   ROW_GRAD : D2[doc, topic]  = dLogit . beta^T      (d theta)
 //   COL_GRAD : D2[word, topic] = dLogit^T . theta_c   (d beta, transposed)
 //
-// Warp roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
-// warps 4..7 = epilogue (warp w owns TMEM lanes 32*(w-4)..+31).
+// Warp roles (384 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one thread, event driven),
+// warp 2 = TMEM allocator, warps 4..11 = epilogue (warp w owns TMEM lanes 32*(w%4)..+31; warps 4..7 take
+// the first 64 columns of every tile, warps 8..11 the second 64).
+//
+// The "folded" modes (ROW_LSE2, COL_GRAD2, ROW_GRAD2, COL_STATS2) carry every epilogue constant in the
+// GEMM operands (csrc/fold_ops.cu) and need no side band; the earlier side-band modes are kept for small
+// problems, where their shorter launch sequence wins.  With a federation context, the last CTAs of a
+// ROW_GRAD2 grid run the beta part of the federated aggregation over NVLink instead of the sweep
+// (csrc/fabric_dev.cuh).
 #include <stdlib.h>
 #include "ptx.cuh"
 #include "tmap.h"
