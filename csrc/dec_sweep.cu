@@ -252,8 +252,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
     const GfFabricRank& me = fa.ranks[0];
     const long long tstep = fa.step_ctr[1];
     if (threadIdx.x < (unsigned)fa.world) {  // every peer's beta gradient final, its shadows no longer read
-      const uint32_t* f = me.flags[me.rank] + GF_FED_PHASE_BETA_READY * GF_MAX_RANKS + threadIdx.x;
-      while (ld_acquire_sys(f) < (uint32_t)tstep) __nanosleep(64);
+      fed_wait_flag(me.flags[me.rank] + GF_FED_PHASE_BETA_READY * GF_MAX_RANKS + threadIdx.x, (uint32_t)tstep,
+                    (int)threadIdx.x, GF_FED_PHASE_BETA_READY);
     }
     __syncthreads();
     asm volatile("fence.proxy.async;" ::: "memory");  // peer data is read through the async proxy below

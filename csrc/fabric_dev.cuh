@@ -3,6 +3,7 @@
 // aggregation over NVLink while the others keep the tensor cores busy).
 #pragma once
 #include <cuda_bf16.h>
+#include <stdio.h>
 #include "ptx.cuh"
 #include "../include/gfedntm_kernels.h"
 
@@ -77,14 +78,32 @@ __device__ __forceinline__ float adam_upd(float p, float g, float& m, float& v, 
   return p - (h.lr / h.bc1) * (m / denom);
 }
 
-// all threads of the block return once every peer's flag of `phase` has reached `epoch`
-__device__ __forceinline__ void wait_peers(const GfFabricRank& me, int world, int phase, uint32_t epoch) {
-  if (threadIdx.x < (unsigned)world) {
-    const uint32_t* f = me.flags[me.rank] + phase * GF_MAX_RANKS + threadIdx.x;
-    while (ld_acquire_sys(f) < epoch) {
-      __nanosleep(64);
+// A peer that died (out of memory, crashed process) would otherwise leave every other rank spinning on its
+// flag for ever, i.e. a hung GPU.  After kFedTimeoutNs without the flag the kernel traps: the process gets
+// a CUDA error and the job fails instead of hanging.
+constexpr unsigned long long kFedTimeoutNs = 120ull * 1000ull * 1000ull * 1000ull;
+__device__ __forceinline__ unsigned long long fed_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void fed_wait_flag(const uint32_t* f, uint32_t epoch, int peer, int phase) {
+  const unsigned long long t0 = fed_now_ns();
+  unsigned int polls = 0;
+  while (ld_acquire_sys(f) < epoch) {
+    __nanosleep(64);
+    if ((++polls & 0x3fffu) == 0u && fed_now_ns() - t0 > kFedTimeoutNs) {
+      printf("[gfedntm] aggregation: no flag from rank %d (phase %d, epoch %u) after 120 s - aborting\n", peer, phase,
+             epoch);
+      __trap();
     }
   }
+}
+
+// all threads of the block return once every peer's flag of `phase` has reached `epoch`
+__device__ __forceinline__ void wait_peers(const GfFabricRank& me, int world, int phase, uint32_t epoch) {
+  if (threadIdx.x < (unsigned)world)
+    fed_wait_flag(me.flags[me.rank] + phase * GF_MAX_RANKS + threadIdx.x, epoch, (int)threadIdx.x, phase);
   __syncthreads();
 }
 
