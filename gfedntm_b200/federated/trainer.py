@@ -79,7 +79,10 @@ class FederatedTrainer:
         # Overlap: the beta part of the aggregation (the bulk of the bytes) runs on a few CTAs of the d-theta
         # sweep, i.e. concurrently with ~1 ms of backward compute that no longer touches beta.
         self._overlap = None
-        ctas = int(os.environ.get("GFEDNTM_AGG_CTAS", "40"))  # measured best at 2 GPUs (16: 5.40, 24: 4.46, 40: 3.64, 56: 3.76 ms; off: 3.81)
+        # 40 CTAs measured best with P2P pushes (N=2: 16: 5.40, 24: 4.46, 32: 3.88, 40: 3.55-3.64, 56: 3.76 ms/step);
+        # with NVLS multicast pushes the aggregation needs fewer (N=8: 32 CTAs 3.41 ms/step, 40 CTAs 3.50)
+        nvls = bool(self.aggregator.args.ranks[0].P_mc)
+        ctas = int(os.environ.get("GFEDNTM_AGG_CTAS", "32" if (nvls and self.world >= 8) else "40"))
         if (self.world > 1 and self.agg == "grad" and ctas > 0 and eng.is_prod and eng.decoder.folded
                 and isinstance(self.arena, SymmetricArena)):
             self._overlap = self.aggregator.overlap_handle(eng.ctr, ctas)
