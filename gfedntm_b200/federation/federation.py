@@ -8,6 +8,7 @@ also addressable by their numeric id, which is what a reconnecting client keeps 
 """
 from __future__ import annotations
 
+import logging
 import threading
 from typing import Dict, List
 
@@ -15,7 +16,8 @@ from .federation_client import FederationClient
 
 
 class Federation:
-    def __init__(self) -> None:
+    def __init__(self, logger=None) -> None:
+        self.logger = logger if logger is not None else logging.getLogger("Federation")
         self.federation_lock = threading.RLock()
         self.federation: Dict[str, int] = {}            # peer string -> open-connection count
         self.federation_clients: List[FederationClient] = []
@@ -48,6 +50,7 @@ class Federation:
             pos = FederationClient.get_pos_by_key(client, self.federation_clients)
             c = self.federation_clients[pos]
             c.update_client_state(gradient, current_mb, current_epoch, current_id_msg)
+            c.set_num_max_iter(max_epochs)
             c.num_max_epochs = max_epochs
 
     def disconnect(self, client: str) -> None:

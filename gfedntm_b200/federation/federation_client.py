@@ -19,9 +19,14 @@ class FederationClient:
         self.ready_for_training = ready_for_training
         self.client_id = client_id
         self.nr_samples = nr_samples
+        self.num_max_iter = -3                    # reference default (federation_client.py:24)
         self.finished = False                     # reached num_epochs (server stops polling it)
         self.last_seen = 0.0                      # heartbeat: time of the last successful RPC
         self.failures = 0
+
+    def set_num_max_iter(self, num_max_iter: int) -> None:
+        """Maximum number of training iterations announced by the client (federation_client.py:32-46)."""
+        self.num_max_iter = num_max_iter
 
     def update_client_state(self, tensors: Dict, current_mb: int, current_epoch: int, current_id_msg) -> None:
         self.tensors = tensors

@@ -15,7 +15,10 @@ from .bow_dataset import to_csr32
 class CTMDataset(Dataset):
     """Bag of words + a fixed-size contextual embedding per document (+ optional one-hot labels)."""
 
-    def __init__(self, X_contextual, X_bow, idx2token, labels=None) -> None:
+    def __init__(self, X_contextual, X_bow, idx2token, qt=None, labels=None) -> None:
+        # `qt`: opaque preparation object the reference stores on the dataset (datasets/dataset.py:9,24);
+        # fourth positional argument there, optional here
+        self.qt = qt
         self.X_bow = to_csr32(X_bow)
         self.X_contextual = np.ascontiguousarray(np.asarray(X_contextual, dtype=np.float32))
         if self.X_bow.shape[0] != len(self.X_contextual):

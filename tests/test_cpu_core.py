@@ -316,3 +316,65 @@ def test_hierarchical_corpus_selection():
     np.testing.assert_array_equal(dense[:, 8:], counts[keep_ws].toarray()[:, 8:] * (thetas[keep_ws, 2:3] > 0))
     ws2, _ = htm_ws(counts, thetas, betas, topic=2, sample=True, seed=1)
     assert ws2.toarray()[:, :8].sum() == 0
+
+
+def test_public_signatures_cover_the_reference():
+    """Every constructor argument and public method of the reference's user-facing classes exists here."""
+    import importlib
+    import inspect
+    import types
+
+    ref_root = "/root/reference"
+    if not os.path.isdir(ref_root):
+        pytest.skip("reference tree not mounted")
+    np.Inf = np.inf
+    for name in ("matplotlib", "matplotlib.pyplot", "waiting", "wordcloud"):
+        if name not in sys.modules:
+            try:
+                __import__(name)
+            except Exception:
+                m = types.ModuleType(name)
+                m.wait = lambda *a, **k: True
+                sys.modules[name] = m
+    sys.path.insert(0, ref_root)
+    pairs = [
+        ("src.models.base.pytorchavitm.avitm_network.avitm", "AVITM", "gfedntm_b200.models", "AVITM"),
+        ("src.models.base.contextualized_topic_models.ctm_network.ctm", "CTM", "gfedntm_b200.models", "CTM"),
+        ("src.models.base.contextualized_topic_models.ctm_network.ctm", "ZeroShotTM", "gfedntm_b200.models", "ZeroShotTM"),
+        ("src.models.base.contextualized_topic_models.ctm_network.ctm", "CombinedTM", "gfedntm_b200.models", "CombinedTM"),
+        ("src.models.base.pytorchavitm.datasets.bow_dataset", "BOWDataset", "gfedntm_b200.models", "BOWDataset"),
+        ("src.models.base.contextualized_topic_models.datasets.dataset", "CTMDataset", "gfedntm_b200.models", "CTMDataset"),
+        ("src.models.federated.federated_model", "FederatedModel", "gfedntm_b200.federated.federated_model", "FederatedModel"),
+        ("src.models.federated.federated_avitm", "FederatedAVITM", "gfedntm_b200.federated.federated_avitm", "FederatedAVITM"),
+        ("src.models.federated.federated_ctm", "FederatedCTM", "gfedntm_b200.federated.federated_ctm", "FederatedCTM"),
+        ("src.federation.server", "FederatedServer", "gfedntm_b200.federation.server", "FederatedServer"),
+        ("src.federation.client", "Client", "gfedntm_b200.federation.client", "Client"),
+        ("src.federation.client", "FederatedClientServer", "gfedntm_b200.federation.client", "FederatedClientServer"),
+        ("src.federation.federation", "Federation", "gfedntm_b200.federation.federation", "Federation"),
+        ("src.federation.federation_client", "FederationClient", "gfedntm_b200.federation.federation_client", "FederationClient"),
+        ("src.models.base.utils.early_stopping.pytorchtools", "EarlyStopping", "gfedntm_b200.models.early_stopping", "EarlyStopping"),
+    ]
+    try:
+        problems = []
+        for rm, rn, om, on in pairs:
+            ref = getattr(importlib.import_module(rm), rn)
+            ours = getattr(importlib.import_module(om), on)
+            pr = [p for p in inspect.signature(ref.__init__).parameters if p != "self"]
+            po = [p for p in inspect.signature(ours.__init__).parameters if p != "self"]
+            missing = [p for p in pr if p not in po]
+            is_fn = lambda x: inspect.isfunction(x) or inspect.ismethod(x)  # noqa: E731
+            rmeth = {n for n, _ in inspect.getmembers(ref, is_fn) if not n.startswith("__")}
+            ometh = {n for n, _ in inspect.getmembers(ours, is_fn)}
+            if missing or (rmeth - ometh):
+                problems.append((rn, missing, sorted(rmeth - ometh)))
+        import src.utils.auxiliary_functions as raf
+
+        import gfedntm_b200.utils.auxiliary_functions as oaf
+
+        rf = {n for n, v in inspect.getmembers(raf, inspect.isfunction) if v.__module__ == raf.__name__}
+        of = {n for n, _ in inspect.getmembers(oaf, inspect.isfunction)}
+        assert not problems and not (rf - of), (problems, sorted(rf - of))
+    finally:
+        sys.path.remove(ref_root)
+        for k in [k for k in sys.modules if k == "src" or k.startswith("src.")]:
+            del sys.modules[k]
