@@ -87,3 +87,67 @@ def corpus_df_to_mallet(corpus_df: pd.DataFrame, out_file: str) -> None:
     with open(out_file, "w", encoding="utf-8") as f:
         for _id, text in zip(corpus_df["id"], corpus_df["text"]):
             f.write(f"{_id} 0 {text}\n")
+
+
+# ---------------------------------------------------------------------------------------------
+# Remaining helpers of src/aux_modules/utils/misc.py (keyboard string reader, title clean-up, pickles)
+# ---------------------------------------------------------------------------------------------
+def var_string_keyboard(option: str, default, question: str, reader=input):
+    """Ask for a structured value on the keyboard (ref: misc.py:86-136).  ``option`` selects the expected
+    format: ``comma_separated`` (a parenthesised tuple of ints such as ``(50, 50)``), ``bool``
+    (``True`` / ``False``), ``dict`` (a JSON object) or ``str``.  Empty or malformed input returns
+    ``default`` (with a notice when something was typed)."""
+    import json
+
+    raw = reader(f"{question} [{default}]: ")
+    invalid = "The value you provided is not valid. Using default value."
+    value = None
+    if option == "comma_separated":
+        parts = [p.strip() for p in raw.split(",") if p]
+        if len(parts) <= 1:
+            print(invalid)
+            return default
+        try:
+            value = tuple(int(p) for p in raw.strip()[1:-1].split(","))
+        except ValueError:
+            print(invalid)
+            return default
+    elif option == "bool":
+        if raw not in ("True", "False"):
+            print(invalid)
+            return default
+        value = raw == "True"
+    elif option == "dict":
+        if raw in ("", "None"):
+            return default
+        try:
+            value = json.loads(raw)
+        except ValueError:
+            print(invalid)
+            return default
+    elif option == "str":
+        value = raw if raw != "" else None
+    if value is None:
+        if raw != "":
+            print(invalid)
+        return default
+    return value
+
+
+def format_title(tgt_str: str) -> str:
+    """Title as stored in the corpus tables: double quotes and line breaks removed (misc.py:185-190)."""
+    return tgt_str.replace('"', "").replace("\n", "")
+
+
+def unpickler(file: str):
+    import pickle
+
+    with open(file, "rb") as f:
+        return pickle.load(f)
+
+
+def pickler(file: str, ob) -> None:
+    import pickle
+
+    with open(file, "wb") as f:
+        pickle.dump(ob, f)

@@ -58,6 +58,29 @@ def bert_embeddings_from_list(texts: Sequence[str], sbert_model_to_load: str, ba
     return np.array(model.encode(list(texts), show_progress_bar=True, batch_size=batch_size))
 
 
+def check_max_local_length(max_seq_length: Optional[int], texts: Sequence[str]) -> None:
+    """Warns when the longest document (in whitespace tokens) exceeds what the embedding model keeps
+    (utils/data_preparation.py:57-62)."""
+    import warnings
+
+    if max_seq_length is None or not len(texts):
+        return
+    longest = max(len(t.split()) for t in texts)
+    if longest > max_seq_length:
+        warnings.warn(f"the longest document in your collection has {longest} words, the model instead "
+                      f"truncates to {max_seq_length} tokens.")
+
+
+def bert_embeddings_from_file(text_file: str, sbert_model_to_load: str, batch_size: int = 32,
+                              max_seq_length: Optional[int] = None) -> np.ndarray:
+    """Sentence-BERT embeddings of a text file with one document per line (utils/data_preparation.py:25-40)."""
+    with open(text_file, encoding="utf-8") as f:
+        texts = f.readlines()
+    check_max_local_length(max_seq_length, texts)
+    return bert_embeddings_from_list(texts, sbert_model_to_load, batch_size=batch_size,
+                                     max_seq_length=max_seq_length)
+
+
 class TopicModelDataPreparation:
     """Builds ``CTMDataset`` objects from text (fit / transform) or from ready-made matrices (load)."""
 

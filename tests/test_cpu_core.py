@@ -378,3 +378,29 @@ def test_public_signatures_cover_the_reference():
         sys.path.remove(ref_root)
         for k in [k for k in sys.modules if k == "src" or k.startswith("src.")]:
             del sys.modules[k]
+
+
+def test_misc_keyboard_and_pickle_helpers(tmp_path):
+    import warnings
+
+    from gfedntm_b200.aux_modules import misc
+    from gfedntm_b200.models.data_preparation import check_max_local_length
+
+    ask = lambda ans: (lambda prompt: ans)  # noqa: E731
+    assert misc.var_string_keyboard("comma_separated", (50, 50), "hidden", reader=ask("(100, 50)")) == (100, 50)
+    assert misc.var_string_keyboard("comma_separated", (50, 50), "hidden", reader=ask("100")) == (50, 50)
+    assert misc.var_string_keyboard("bool", True, "flag", reader=ask("False")) is False
+    assert misc.var_string_keyboard("bool", True, "flag", reader=ask("nope")) is True
+    assert misc.var_string_keyboard("dict", {"a": 1}, "d", reader=ask('{"b": 2}')) == {"b": 2}
+    assert misc.var_string_keyboard("dict", {"a": 1}, "d", reader=ask("None")) == {"a": 1}
+    assert misc.var_string_keyboard("str", "x", "s", reader=ask("")) == "x"
+    assert misc.var_string_keyboard("str", "x", "s", reader=ask("abc")) == "abc"
+    assert misc.format_title('A "quoted"\ntitle') == "A quotedtitle"
+    path = str(tmp_path / "ob.pkl")
+    misc.pickler(path, {"k": [1, 2, 3]})
+    assert misc.unpickler(path) == {"k": [1, 2, 3]}
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        check_max_local_length(3, ["a b c d e", "a"])
+        check_max_local_length(10, ["a b c"])
+    assert len(w) == 1 and "5 words" in str(w[0].message)
