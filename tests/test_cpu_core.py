@@ -374,6 +374,19 @@ def test_public_signatures_cover_the_reference():
         rf = {n for n, v in inspect.getmembers(raf, inspect.isfunction) if v.__module__ == raf.__name__}
         of = {n for n, _ in inspect.getmembers(oaf, inspect.isfunction)}
         assert not problems and not (rf - of), (problems, sorted(rf - of))
+        # module-level helpers of the side modules (skipped when a third-party import of the reference fails)
+        for rm, om in (("src.aux_modules.utils.misc", "gfedntm_b200.aux_modules.misc"),
+                       ("src.models.base.contextualized_topic_models.utils.data_preparation",
+                        "gfedntm_b200.models.data_preparation"),
+                       ("src.models.base.pytorchavitm.utils.data_preparation", "gfedntm_b200.models.data_preparation")):
+            try:
+                r = importlib.import_module(rm)
+            except Exception:
+                continue
+            o = importlib.import_module(om)
+            rfn = {n for n, v in inspect.getmembers(r, inspect.isfunction) if v.__module__ == r.__name__}
+            ofn = {n for n, _ in inspect.getmembers(o, inspect.isfunction)}
+            assert not (rfn - ofn), (rm, sorted(rfn - ofn))
     finally:
         sys.path.remove(ref_root)
         for k in [k for k in sys.modules if k == "src" or k.startswith("src.")]:
