@@ -96,6 +96,46 @@ class TMWrapper:
         m.fit(ds)
         return m, ds, time.perf_counter() - t0
 
+    def train_htm_submodel(self, version: str, father_model, father_dataset, trainer: str = "prod",
+                           expansion_topic: int = 0, thr: Optional[float] = None, ntopics: int = 10,
+                           num_epochs: int = 100, n_samples: int = 20, sample: bool = False,
+                           seed: Optional[int] = None, **kw):
+        """Second-level (hierarchical) model for ``expansion_topic`` of ``father_model`` (ref:
+        tm_wrapper.py:279-355 -> topicmodeling.py:1562-1830).  ``version`` is ``"HTM-WS"`` (keep the word
+        occurrences assigned to the topic) or ``"HTM-DS"`` (keep the documents whose topic weight is at least
+        ``thr``).  The child is trained on the sub-corpus over the father's vocabulary.
+        Returns ``(model, dataset, kept_document_indices, seconds)``."""
+        from .hierarchical import htm_ds, htm_ws
+
+        t0 = time.perf_counter()
+        thetas = np.asarray(father_model.get_doc_topic_distribution(father_dataset, n_samples=n_samples))
+        bow = father_dataset.X if hasattr(father_dataset, "X") else father_dataset.X_bow
+        if version.upper() == "HTM-DS":
+            sub, keep = htm_ds(bow, thetas, expansion_topic, 0.1 if thr is None else thr)
+        elif version.upper() == "HTM-WS":
+            betas = np.asarray(father_model.get_topic_word_distribution())
+            sub, keep = htm_ws(bow, thetas, betas, expansion_topic, sample=sample, seed=seed)
+        else:
+            raise ValueError("version must be 'HTM-WS' or 'HTM-DS'")
+        if sub.shape[0] < 2:
+            raise ValueError(f"the expansion of topic {expansion_topic} keeps {sub.shape[0]} documents")
+        vocab = father_dataset.idx2token
+        self._logger.info("%s expansion of topic %d: %d of %d documents, %d word occurrences", version,
+                          expansion_topic, sub.shape[0], bow.shape[0], int(sub.sum()))
+        if trainer in ("prod", "prodlda", "lda"):
+            ds = BOWDataset(sub.astype(np.float32), vocab)
+            m = AVITM(input_size=sub.shape[1], n_components=ntopics,
+                      model_type="LDA" if trainer == "lda" else "prodLDA", num_epochs=num_epochs, verbose=False,
+                      **kw)
+        else:
+            emb = np.asarray(father_dataset.X_contextual)[keep]
+            ds = CTMDataset(emb, sub.astype(np.float32), vocab)
+            m = CTM(input_size=sub.shape[1], contextual_size=int(emb.shape[1]),
+                    inference_type="zeroshot" if trainer == "zeroshot" else "combined", n_components=ntopics,
+                    num_epochs=num_epochs, verbose=False, **kw)
+        m.fit(ds)
+        return m, ds, keep, time.perf_counter() - t0
+
     # -- evaluation ------------------------------------------------------------------------------
     @staticmethod
     def calculate_cohr_vs_ref(model, reference_bow, k: int = 10) -> float:

@@ -417,3 +417,23 @@ def test_misc_keyboard_and_pickle_helpers(tmp_path):
         check_max_local_length(3, ["a b c d e", "a"])
         check_max_local_length(10, ["a b c"])
     assert len(w) == 1 and "5 words" in str(w[0].message)
+
+
+def test_tmwrapper_hierarchical_submodels():
+    from gfedntm_b200.aux_modules.tm_wrapper import TMWrapper
+
+    rng = np.random.default_rng(0)
+    vocab = [f"wd{i}" for i in range(60)]
+    corpus = []
+    for i in range(120):
+        lo = (i % 3) * 20
+        corpus.append(" ".join(rng.choice(vocab[lo:lo + 20], size=30)))
+    tw = TMWrapper()
+    father, ds, _ = tw.train_root_model(corpus, trainer="prod", ntopics=3, num_epochs=3, max_features=None,
+                                        batch_size=32, device="cpu")
+    child, cds, keep, secs = tw.train_htm_submodel("HTM-DS", father, ds, expansion_topic=0, thr=0.0, ntopics=2,
+                                                   num_epochs=1, n_samples=2, batch_size=32, device="cpu")
+    assert len(keep) == 120 and len(cds) == 120 and child.get_topic_word_distribution().shape == (2, 60)
+    child2, cds2, keep2, _ = tw.train_htm_submodel("HTM-WS", father, ds, expansion_topic=1, ntopics=2, num_epochs=1,
+                                                   n_samples=2, batch_size=16, device="cpu")
+    assert 2 <= len(keep2) <= 120 and cds2.X.sum() <= ds.X.sum()
