@@ -437,3 +437,37 @@ def test_tmwrapper_hierarchical_submodels():
     child2, cds2, keep2, _ = tw.train_htm_submodel("HTM-WS", father, ds, expansion_topic=1, ntopics=2, num_epochs=1,
                                                    n_samples=2, batch_size=16, device="cpu")
     assert 2 <= len(keep2) <= 120 and cds2.X.sum() <= ds.X.sum()
+
+
+def test_tmmodel_folder_and_curation(tmp_path):
+    from gfedntm_b200.aux_modules.tm_model import TMmodel
+
+    rng = np.random.default_rng(0)
+    K, V, D = 5, 40, 60
+    betas = rng.dirichlet(np.full(V, 0.1), K)
+    thetas = rng.dirichlet(np.full(K, 0.3), D)
+    bow = sp.csr_matrix(rng.poisson(0.3, (D, V)))
+    vocab = [f"wd{i}" for i in range(V)]
+    tm = TMmodel(tmp_path / "model")
+    tm.create(betas=betas, thetas=thetas, vocab=vocab, reference_bow=bow)
+    a = tm.get_alphas()
+    assert np.all(np.diff(a) <= 1e-12) and abs(a.sum() - 1.0) < 1e-6  # sorted by size, thetas row-normalised
+    df = tm.to_dataframe()
+    assert len(df) == K and (df["topic_entropy"] > 0).all() and (df["topic_entropy"] <= 1).all()
+    assert np.isfinite(df["topic_coherence"]).all()
+    for name in ("alphas.npy", "betas.npy", "thetas.npz", "vocab.txt", "betas_ds.npy", "tpc_descriptions.txt",
+                 "alphas_orig.npy", "edits.txt"):
+        assert (tmp_path / "model" / name).exists()
+    # fuse: the merged topic carries the summed document weight
+    before = tm.get_thetas().toarray()
+    assert tm.fuseTopics([1, 3]) == 1
+    after = tm.get_thetas().toarray()
+    assert after.shape[1] == K - 1 and np.allclose(after[:, 1], before[:, 1] + before[:, 3])
+    assert tm.deleteTopics([0]) == 1 and tm.get_betas().shape[0] == K - 2
+    assert np.allclose(np.asarray(tm.get_thetas().sum(1)).ravel()[np.asarray(tm.get_thetas().sum(1)).ravel() > 0], 1.0)
+    # a second object on the same folder sees the edited state; reset restores the original
+    tm2 = TMmodel(tmp_path / "model")
+    assert tm2.get_betas().shape[0] == K - 2 and tm2._edits == ["f 1 3", "d 0"]
+    assert tm2.resetTM() == 1 and tm2.get_betas().shape[0] == K and tm2._edits == []
+    sims = tm2.getSimilarTopics(3)
+    assert len(sims["Coocurring"]) == 3 and 0.0 <= tm2.calculate_topic_diversity(10) <= 1.0
