@@ -467,8 +467,13 @@ class NeuralTopicModel:
         fileloc = os.path.join(d, "epoch_{}.pth".format(self.nn_epoch))
         sd = {k: v.detach().cpu().contiguous() for k, v in self.model.state_dict().items()}
         with open(fileloc, "wb") as f:
-            torch.save({"state_dict": sd, "dcue_dict": self._checkpoint_attrs(),
-                        "optimizer": self.optimizer.state_dict()}, f)
+            ck = {"state_dict": sd, "dcue_dict": self._checkpoint_attrs(), "optimizer": self.optimizer.state_dict()}
+            td = getattr(self, "train_data", None)
+            if td is not None and getattr(td, "idx2token", None) is not None:
+                # extra key (ignored by the reference's loader): lets hold-out inference rebuild the vocabulary
+                i2t = td.idx2token
+                ck["vocab"] = [i2t[i] for i in range(len(i2t))]
+            torch.save(ck, f)
 
     def load(self, model_dir, epoch):
         """Restores a checkpoint written by :meth:`save`.  Ref: avitm.py:619-640."""

@@ -471,3 +471,23 @@ def test_tmmodel_folder_and_curation(tmp_path):
     assert tm2.resetTM() == 1 and tm2.get_betas().shape[0] == K and tm2._edits == []
     sims = tm2.getSimilarTopics(3)
     assert len(sims["Coocurring"]) == 3 and 0.0 <= tm2.calculate_topic_diversity(10) <= 1.0
+
+
+def test_inferencer_from_saved_checkpoint(tmp_path):
+    from gfedntm_b200.aux_modules.inferencer import Inferencer
+    from gfedntm_b200.models import AVITM, BOWDataset
+
+    X, vocab = _toy(n=96, v=80, seed=3)
+    m = AVITM(input_size=80, n_components=4, hidden_sizes=(16,), batch_size=32, num_epochs=2, verbose=False,
+              device="cpu")
+    m.fit(BOWDataset(X, vocab), save_dir=str(tmp_path))
+    model_dir = [os.path.join(tmp_path, d) for d in os.listdir(tmp_path) if os.path.isdir(os.path.join(tmp_path, d))][0]
+    inf = Inferencer(model_dir, device="cpu")
+    assert inf.vocab == vocab
+    texts = [" ".join(vocab[i] for i in np.flatnonzero(X[r])) for r in range(10)]
+    th = inf.predict(texts, n_samples=3, out_dir=str(tmp_path / "inf"))
+    assert th.shape == (10, 4) and np.allclose(th.sum(1), 1.0)
+    assert np.load(tmp_path / "inf" / "doc-topics.npy").shape == (10, 4)
+    # identical input through the document-term matrix gives the same distribution up to sampling noise
+    th2 = inf.predict(bow=sp.csr_matrix((X[:10] > 0).astype(np.float32)), n_samples=3)
+    assert th2.shape == (10, 4)
