@@ -71,3 +71,16 @@ def test_collab_vs_non_collab_tiny(tmp_path):
     cvn.main(["--source", str(src), "--trainer", "prod", "--ntopics", "3", "--epochs", "1", "--out", str(out)])
     df = pd.read_csv(out)
     assert len(df) >= 2  # the centralized model plus at least one per-field model
+
+
+def test_scalability_grid_tiny(tmp_path):
+    import csv
+
+    sys.path.insert(0, os.path.join(ROOT, "aux_scripts", "scalability"))
+    import scalability
+
+    out = scalability.main(["--docs", "60", "--topics", "2", "3", "--vocab", "80", "--epochs", "1", "--device", "cpu",
+                            "--out", str(tmp_path / "s.csv")])
+    rows = list(csv.DictReader(open(out)))
+    assert len(rows) == 2 and {r["n_topics"] for r in rows} == {"2", "3"}
+    assert all(float(r["train_s"]) > 0 and int(r["peak_rss"]) > 0 for r in rows)
