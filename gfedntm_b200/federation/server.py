@@ -19,6 +19,7 @@ reference):
 from __future__ import annotations
 
 import logging
+import os
 import sys
 import threading
 import time
@@ -35,6 +36,7 @@ from ..federated.federated_ctm import FederatedCTM
 from ..protos import federated_pb2, federated_pb2_grpc
 from ..utils.auxiliary_functions import (deserializeNumpy, dict_to_proto, modelStateDict_to_proto,
                                          optStateDict_to_proto, proto_to_vocab, vocab_to_proto)
+from ..utils.observability import PrometheusExporter
 from . import federation, federation_client
 
 FMT = "%(asctime)s [%(threadName)-12.12s] [%(levelname)-5.5s]  %(message)s"
@@ -100,6 +102,10 @@ class FederatedServer(federated_pb2_grpc.FederationServicer):
         self._rpc_retries = rpc_retries
         self._device = device
         self._logger = logger if logger else make_logger("Server", logs_server)
+
+        # optional Prometheus endpoint: GFEDNTM_METRICS_PORT=<port> (0 = registry only, no HTTP server)
+        mp = os.environ.get("GFEDNTM_METRICS_PORT")
+        self.metrics = PrometheusExporter(int(mp) if mp not in (None, "") else None)
 
         self._id_server = "IDS" + "_" + str(round(time.time()))
         self._dicts: Dict[int, Dict[str, int]] = {}
@@ -362,6 +368,9 @@ class FederatedServer(federated_pb2_grpc.FederationServicer):
                     if c.num_max_epochs > 0 and c.current_epoch >= c.num_max_epochs:
                         c.finished = True
                 self.iter_times.append(time.perf_counter() - t0)
+                self.metrics.observe_iteration(self.iter_times[-1], len(alive),
+                                               payload_bytes=sum(int(v.nbytes) for p in payloads for v in p.values()),
+                                               failures=len(active) - len(alive) + sum(a is None for a in acks))
                 if self._logger.isEnabledFor(logging.DEBUG):
                     self._logger.debug(f"-- -- global iteration {i} done in {self.iter_times[-1] * 1e3:.1f} ms")
             # ---- save + stop

@@ -76,3 +76,49 @@ class JsonlMetrics:
         if self._f is not None:
             self._f.close()
             self._f = None
+
+
+class PrometheusExporter:
+    """Optional metrics endpoint of the federation server (``prometheus_client`` is pinned but unused by the
+    reference).  ``PrometheusExporter(port)`` starts the HTTP endpoint; with ``port=None`` (or
+    without the package) every method is a no-op, so callers never need to branch."""
+
+    def __init__(self, port: Optional[int] = None, registry=None) -> None:
+        self.enabled = False
+        if port is None:
+            return
+        try:
+            import prometheus_client as pc
+        except Exception:  # package absent: stay disabled
+            return
+        self._pc = pc
+        self.registry = registry if registry is not None else pc.CollectorRegistry()
+        self.iterations = pc.Counter("gfedntm_global_iterations_total", "completed global iterations",
+                                     registry=self.registry)
+        self.clients = pc.Gauge("gfedntm_active_clients", "clients that answered the last pull",
+                                registry=self.registry)
+        self.iter_seconds = pc.Histogram("gfedntm_iteration_seconds", "wall time of one global iteration",
+                                         buckets=(.005, .01, .025, .05, .1, .25, .5, 1, 2.5, 5, 10),
+                                         registry=self.registry)
+        self.payload_bytes = pc.Counter("gfedntm_payload_bytes_total", "tensor bytes pulled from the clients",
+                                        registry=self.registry)
+        self.failures = pc.Counter("gfedntm_rpc_failures_total", "client RPCs that failed after all retries",
+                                   registry=self.registry)
+        if port > 0:
+            pc.start_http_server(port, registry=self.registry)
+        self.enabled = True
+
+    def observe_iteration(self, seconds: float, n_clients: int, payload_bytes: int = 0, failures: int = 0) -> None:
+        if not self.enabled:
+            return
+        self.iterations.inc()
+        self.clients.set(n_clients)
+        self.iter_seconds.observe(seconds)
+        if payload_bytes:
+            self.payload_bytes.inc(payload_bytes)
+        if failures:
+            self.failures.inc(failures)
+
+    def scrape(self) -> str:
+        """Current exposition text (tests / debugging)."""
+        return self._pc.generate_latest(self.registry).decode() if self.enabled else ""

@@ -491,3 +491,19 @@ def test_inferencer_from_saved_checkpoint(tmp_path):
     # identical input through the document-term matrix gives the same distribution up to sampling noise
     th2 = inf.predict(bow=sp.csr_matrix((X[:10] > 0).astype(np.float32)), n_samples=3)
     assert th2.shape == (10, 4)
+
+
+def test_prometheus_exporter_counts_iterations():
+    from gfedntm_b200.utils.observability import PrometheusExporter
+
+    off = PrometheusExporter(None)
+    off.observe_iteration(0.1, 2)  # disabled: no-op
+    assert off.scrape() == ""
+    ex = PrometheusExporter(0)  # registry only, no HTTP server
+    if not ex.enabled:
+        pytest.skip("prometheus_client not installed")
+    ex.observe_iteration(0.02, 3, payload_bytes=1000, failures=1)
+    ex.observe_iteration(0.03, 2)
+    text = ex.scrape()
+    assert "gfedntm_global_iterations_total 2.0" in text and "gfedntm_active_clients 2.0" in text
+    assert "gfedntm_payload_bytes_total 1000.0" in text and "gfedntm_rpc_failures_total 1.0" in text
