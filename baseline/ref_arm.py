@@ -44,9 +44,29 @@ def _shim_env() -> None:
         sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
 
 
+def ensure_installed(source: str | None = None) -> str:
+    """Make sure ``baseline/_ref`` holds the unmodified reference sources and return its path.
+
+    ``__graft_entry__.build()`` calls this on the build box (where ``/root/reference`` is mounted) so that
+    the copy travels with the tree to the GPU boxes, where the mount does not exist.  The source may be
+    overridden with ``GFEDNTM_REFERENCE_SRC``.  Nothing is patched: it is ``install_ref.sh`` on demand."""
+    if os.path.isdir(os.path.join(REF_ROOT, "src", "models")):
+        return REF_ROOT
+    source = source or os.environ.get("GFEDNTM_REFERENCE_SRC", "/root/reference")
+    if not os.path.isdir(os.path.join(source, "src")):
+        raise ImportError(f"baseline/_ref is empty and no reference checkout at {source} "
+                          "(run baseline/install_ref.sh <path>)")
+    import subprocess
+
+    subprocess.run(["bash", os.path.join(HERE, "install_ref.sh"), source], check=True,
+                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    if not os.path.isdir(os.path.join(REF_ROOT, "src", "models")):
+        raise ImportError("baseline/install_ref.sh did not produce baseline/_ref/src")
+    return REF_ROOT
+
+
 def _import_reference():
-    if not os.path.isdir(os.path.join(REF_ROOT, "src")):
-        raise ImportError("baseline/_ref is empty: run baseline/install_ref.sh")
+    ensure_installed()
     _shim_env()
     if REF_ROOT not in sys.path:
         sys.path.insert(0, REF_ROOT)
