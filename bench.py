@@ -128,37 +128,63 @@ def allreduce_max(x: float, world: int, device) -> float:
 
 
 # ------------------------------------------------------------------------------------------------
-def run_ours(args, cfg: dict) -> dict:
-    import torch
-    import torch.distributed as dist
+class _Ctx:
+    """Per-process state shared by the measurements of one bench run."""
 
+    def __init__(self) -> None:
+        import torch
+        import torch.distributed as dist
+
+        self.rank, self.world, self.local = dist_env()
+        torch.cuda.set_device(self.local)
+        self.device = torch.device("cuda", self.local)
+        if self.world > 1 and not dist.is_initialized():
+            dist.init_process_group("nccl", device_id=self.device)
+
+    def barrier(self) -> None:
+        import torch
+        import torch.distributed as dist
+
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+
+def build_trainer(ctx: _Ctx, cfg: dict, agg: str):
     from gfedntm_b200.federated.trainer import FederatedTrainer
     from gfedntm_b200.models import AVITM, CTM, BOWDataset, CTMDataset
-    from gfedntm_b200.ops import _lib
 
-    rank, world, local = dist_env()
-    torch.cuda.set_device(local)
-    device = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=device)
     B, V, K = cfg["B"], cfg["V"], cfg["K"]
     n_batches = 4
-    counts, ctx = make_corpus(cfg, B * n_batches, seed=1234 + rank, device=f"cuda:{local}")
-    vocab = None
+    counts, xctx = make_corpus(cfg, B * n_batches, seed=1234 + ctx.rank, device=f"cuda:{ctx.local}")
     if cfg["family"] == "ctm":
-        ds = CTMDataset(ctx, counts, vocab)
+        ds = CTMDataset(xctx, counts, None)
         model = CTM(input_size=V, contextual_size=cfg["C"], inference_type=cfg["inference_type"],
                     n_components=K, model_type=cfg["model_type"], hidden_sizes=cfg["hidden"], batch_size=B,
-                    num_epochs=1, verbose=False, device=device, seed=7)
+                    num_epochs=1, verbose=False, device=ctx.device, seed=7)
     else:
-        ds = BOWDataset(counts, vocab)
+        ds = BOWDataset(counts, None)
         model = AVITM(input_size=V, n_components=K, model_type=cfg["model_type"], hidden_sizes=cfg["hidden"],
-                      batch_size=B, num_epochs=1, verbose=False, device=device, seed=7)
+                      batch_size=B, num_epochs=1, verbose=False, device=ctx.device, seed=7)
     assert model.backend == "fused", "bench must run the sm_100a kernel path"
-    trainer = FederatedTrainer(model, n_samples=len(ds), world_size=world, rank=rank, agg=args.agg)
+    trainer = FederatedTrainer(model, n_samples=len(ds), world_size=ctx.world, rank=ctx.rank, agg=agg)
     loader = model.make_loader(ds, shuffle=True)
     trainer.prepare(loader)
+    return model, trainer, loader
+
+
+def measure_ours(ctx: _Ctx, cfg: dict, steps: int, warmup: int, agg: str, sampler=None, verify: bool = False) -> dict:
+    """Device-timed and end-to-end throughput of one configuration on the ranks of ``ctx``."""
+    import torch
+
+    from gfedntm_b200.ops import _lib
+
+    world, device = ctx.world, ctx.device
+    B = cfg["B"]
+    model, trainer, loader = build_trainer(ctx, cfg, agg)
     lib = _lib.load()
+    eng = model.engine
 
     # ---- device-resident minibatches for the kernel-only number
     staged = []
@@ -170,28 +196,20 @@ def run_ours(args, cfg: dict) -> dict:
     small_ws = trainer.working_set_bytes() < 2 * L2_BYTES
     flush = torch.empty(2 * L2_BYTES // 4, dtype=torch.float32, device=device) if small_ws else None
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
     # untimed: the engine captures one CUDA graph per input buffer set (eager warm-up + capture call),
     # so every staged minibatch is visited twice before the W warm-up steps proper
-    for i in range(2 * len(staged) + args.warmup):
+    for i in range(2 * len(staged) + warmup):
         bow, xc = staged[i % len(staged)]
         trainer.step(bow, xc)
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
+    ctx.barrier()
+    if sampler is not None and ctx.rank == 0:
         sampler.start()
-    eng = model.engine
     launches0 = lib.gf_launch_count() + eng.replayed_launches
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     if flush is None:
         starts[0].record()
-    for i in range(args.steps):
+    for i in range(steps):
         bow, xc = staged[i % len(staged)]
         if flush is not None:
             flush.add_(1.0)  # evict L2 between timed steps (write > L2 bytes)
@@ -201,61 +219,135 @@ def run_ours(args, cfg: dict) -> dict:
             ends[i].record()
     if flush is None:
         ends[-1].record()
-    barrier()
+    ctx.barrier()
     launches = lib.gf_launch_count() + eng.replayed_launches - launches0
     if flush is None:
         ms = starts[0].elapsed_time(ends[-1])
     else:
         ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
     ms = allreduce_max(ms, world, device)
-    agg_us = trainer.last_aggregation_us()
 
-    # ---- end to end through the public API: host assembly + pinned H2D + step + loss D2H
-    loss_host = torch.zeros(1, dtype=torch.float64).pin_memory()
+    # ---- end to end through the public API: host assembly + pinned H2D + step + loss D2H.  The loss of
+    # step i is copied to pinned host memory right behind the step and read by the host while step i+1
+    # runs (two slots): every step's loss reaches the host inside the timed region, without draining the
+    # GPU once per step.
+    loss_host = [torch.zeros(1, dtype=torch.float64).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
     it = iter(loader)
     h2d = 0
-    for _ in range(max(args.warmup, 9)):  # three staging slots x (eager warm-up + graph capture) + slack
-        try:
-            mb = next(it)
-        except StopIteration:
-            it = iter(loader)
-            mb = next(it)
-        trainer.step(mb.bow, mb.x_ctx)
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        try:
-            mb = next(it)
-        except StopIteration:
-            it = iter(loader)
-            mb = next(it)
-        loss = trainer.step(mb.bow, mb.x_ctx)
-        loss_host.copy_(loss.reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        h2d = mb.h2d_bytes
-    barrier()
-    e2e_s = allreduce_max(time.perf_counter() - t0, world, device)
-    clocks = sampler.stop() if rank == 0 else None
 
-    docs = world * B * args.steps
-    value = docs / (ms / 1e3)
+    def next_mb():
+        nonlocal it
+        try:
+            return next(it)
+        except StopIteration:
+            it = iter(loader)
+            return next(it)
+
+    for _ in range(max(warmup, 9)):  # three staging slots x (eager warm-up + graph capture) + slack
+        mb = next_mb()
+        trainer.step(mb.bow, mb.x_ctx)
+    ctx.barrier()
+    loss_sum = 0.0
+    t0 = time.perf_counter()
+    for i in range(steps):
+        mb = next_mb()
+        loss = trainer.step(mb.bow, mb.x_ctx)
+        loss_host[i & 1].copy_(loss.reshape(1), non_blocking=True)
+        loss_ev[i & 1].record()
+        if i > 0:
+            loss_ev[(i - 1) & 1].synchronize()
+            loss_sum += float(loss_host[(i - 1) & 1][0])
+        h2d = mb.h2d_bytes
+    loss_ev[(steps - 1) & 1].synchronize()
+    loss_sum += float(loss_host[(steps - 1) & 1][0])
+    ctx.barrier()
+    e2e_s = allreduce_max(time.perf_counter() - t0, world, device)
+    assert loss_sum == loss_sum, "NaN loss in the end-to-end loop"
+
+    docs = world * B * steps
+    out = {"value": docs / (ms / 1e3), "ms_per_step": ms / steps, "steps": steps,
+           "e2e": {"value": docs / e2e_s, "unit": "docs/s", "h2d_bytes_per_step": int(h2d),
+                   "d2h_bytes_per_step": 8, "ms_per_step": 1e3 * e2e_s / steps,
+                   "loss_per_doc": loss_sum / (steps * B)},
+           "gpu_launches": int(launches),
+           "l2": "flush 252 MB between timed steps" if flush is not None else
+                 "working set (params+shadows+grads) larger than L2",
+           "global_batch": world * B}
+    if world > 1:
+        out["aggregation"] = trainer.describe_aggregation()
+        if verify:
+            from gfedntm_b200.federated.verify import verify_against_oracle
+
+            out["verify"] = verify_against_oracle(trainer, loader, steps=2)
+        # exposed cost of the aggregation = federated step - the same step trained locally (N=1 path:
+        # local fused Adam instead of the NVLink aggregation).  Runs last: it lets the ranks diverge.
+        ctx.barrier()
+        for i in range(2 * len(staged) + 3):
+            eng.train_step(*staged[i % len(staged)])
+        ctx.barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n_loc = max(3, min(steps, 10))
+        loc_ms = 0.0
+        for i in range(n_loc):
+            if flush is not None:
+                flush.add_(1.0)
+            s.record()
+            eng.train_step(*staged[i % len(staged)])
+            e.record()
+            e.synchronize()
+            loc_ms += s.elapsed_time(e)
+        loc_ms = allreduce_max(loc_ms / n_loc, world, device)
+        out["local_ms_per_step"] = loc_ms
+        out["aggregation_us_per_step"] = 1e3 * (ms / steps - loc_ms)
+    del trainer, model, loader, staged, eng
+    import gc
+
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_ours(args, cfg: dict) -> dict:
+    import torch.distributed as dist
+
+    ctx = _Ctx()
+    world = ctx.world
+    sampler = ClockSampler(ctx.local)
+    main = measure_ours(ctx, cfg, args.steps, args.warmup, args.agg, sampler=sampler, verify=True)
+    clocks = sampler.stop() if ctx.rank == 0 else None
+    B, V, K = cfg["B"], cfg["V"], cfg["K"]
     out = {
-        "metric": "ProdLDA/CTM docs/sec (federated, one client per GPU)", "value": value, "unit": "docs/s",
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "metric": "ProdLDA/CTM docs/sec (federated, one client per GPU)", "value": main["value"], "unit": "docs/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": main["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16 operands, fp32 accumulate/master",
         "data": "synthetic LDA corpus (torch-sampled), random-init weights",
         "config": {"model": cfg["desc"], "name": args.config, "global_batch": world * B, "seq_len": None,
                    "vocab": V, "topics": K, "hidden": list(cfg["hidden"]),
                    "parallelism": f"fed{world}" + (f"-{args.agg}" if world > 1 else ""),
-                   "aggregation": None if world == 1 else {
-                       "overlap_ctas": getattr(getattr(trainer, "_overlap", None), "ctas", 0),
-                       "nvls_multicast": bool(trainer.aggregator.args.ranks[0].P_mc)},
-                   "l2": "flush 252 MB between timed steps" if flush is not None else
-                         "working set (params+shadows+grads) larger than L2"},
-        "e2e": {"value": docs / e2e_s, "unit": "docs/s", "h2d_bytes_per_step": int(h2d),
-                "d2h_bytes_per_step": 8, "ms_per_step": 1e3 * e2e_s / args.steps},
-        "gpu_launches": int(launches), "aggregation_us_per_step": agg_us, "clocks": clocks, "impl": "ours",
+                   "aggregation": main.get("aggregation"), "l2": main["l2"]},
+        "e2e": main["e2e"], "gpu_launches": main["gpu_launches"],
+        "aggregation_us_per_step": main.get("aggregation_us_per_step"),
+        "local_ms_per_step": main.get("local_ms_per_step"), "clocks": clocks, "impl": "ours",
     }
+    if "verify" in main:
+        out.update(main["verify"])
+    # the other BASELINE.json configurations, a few hundred short steps each (same protocol, same ranks)
+    if args.all_configs:
+        extra = {}
+        for name, c in CONFIGS.items():
+            if name == args.config:
+                continue
+            try:
+                r = measure_ours(ctx, c, steps=max(args.steps, 50), warmup=args.warmup, agg=args.agg)
+                extra[name] = {k: r[k] for k in ("value", "ms_per_step", "steps", "e2e", "gpu_launches", "l2",
+                                                 "global_batch", "aggregation_us_per_step", "local_ms_per_step")
+                               if k in r}
+                extra[name]["model"] = c["desc"]
+            except Exception as ex:  # noqa: BLE001 -- the headline number must survive a side config
+                extra[name] = {"error": f"{type(ex).__name__}: {ex}".splitlines()[0][:200]}
+        out["configs"] = extra
     if world > 1:
         dist.destroy_process_group()
     return out
@@ -277,10 +369,15 @@ def main() -> None:
     ap.add_argument("--impl", type=str, default="ours", choices=["ours", "reference"])
     ap.add_argument("--agg", type=str, default="grad", choices=["grad", "param"],
                     help="federated aggregation: weighted gradients + global Adam, or weighted parameters")
+    ap.add_argument("--all-configs", dest="all_configs", type=int, default=None,
+                    help="1/0: also measure the other BASELINE.json configurations into `configs` "
+                         "(default: on for the default configuration)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
     cfg = CONFIGS[args.config]
+    if args.all_configs is None:
+        args.all_configs = int(args.config == DEFAULT_CONFIG and args.impl == "ours")
     rank, world, _ = dist_env()
     if world != args.gpus and args.gpus > 1 and world == 1:
         # convenience: spawn the ranks ourselves when not started through torch.distributed.run

@@ -101,6 +101,8 @@ struct SweepParams {
   const float* csp;         // [V] sparse part of sum_b dy*y
   float* dbeta;             // [K, ldg] fp32 gradient (COL_GRAD output)
   int ldg;
+  __nv_bfloat16* dbeta_bf;  // COL_GRAD2: bf16 [K, ldgb] gradient instead of `dbeta` (federated exchange format)
+  int ldgb;
   const float* corr;        // COL_GRAD: [V, Kp] sparse correction to d beta^T (may be null); COL_GRAD2: [Kp, ldc]
   int ldc;
   const int* colptr;        // [V+1] CSC pointer of the batch (with corr)
@@ -147,7 +149,7 @@ struct Smem {
 template <int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant__ CUtensorMap tm_beta,
-             const SweepParams p) {
+             const __grid_constant__ FedTmaps fed_tm, const SweepParams p) {
   constexpr bool kRow = mode_is_row(kMode);
   constexpr bool kHasMMA2 = mode_has_mma2(kMode);
   constexpr bool kSb = mode_has_sb(kMode);
@@ -248,22 +250,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   }
 
   if (kMode == ROW_GRAD2 && agg_role) {
-    const GfFedArgs& fa = *p.fed;
-    const GfFabricRank& me = fa.ranks[0];
-    const long long tstep = fa.step_ctr[1];
-    if (threadIdx.x < (unsigned)fa.world) {  // every peer's beta gradient final, its shadows no longer read
-      fed_wait_flag(me.flags[me.rank] + GF_FED_PHASE_BETA_READY * GF_MAX_RANKS + threadIdx.x, (uint32_t)tstep,
-                    (int)threadIdx.x, GF_FED_PHASE_BETA_READY);
-    }
-    __syncthreads();
-    asm volatile("fence.proxy.async;" ::: "memory");  // peer data is read through the async proxy below
-    const AdamF hh = fed_adam_consts(fa, tstep);
-    if (fa.V % 4 == 0 && fa.ldb % 4 == 0 && fa.Kp % 16 == 0 && fa.world > 1) {
-      fed_beta_phase_bulk(fa, me, hh, (int)blockIdx.x - n_sweep, p.fed_ctas, base, p.smem_bytes - 1024);
-    } else if (threadIdx.x < 256) {
-      fed_beta_phase(fa, me, hh, (int)blockIdx.x - n_sweep, p.fed_ctas, reinterpret_cast<float*>(base));
-    }
-    __threadfence_system();  // the completion handshake is phase C of the closing gf_fed_aggregate(parts=1)
+    // (runs the aggregation after the role dispatch below, together with the sweep CTAs that are done)
   } else if (warp == 0) {
     // ============================ TMA producer ============================
     if (lane == 0) {
@@ -397,6 +384,16 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         }
         umma_commit(s.a_empty);
         ++a_it;
+      }
+      if (kMode == ROW_GRAD2 && p.fed != nullptr) {
+        // This CTA goes on to the aggregation and reuses its shared memory: wait for the asynchronous
+        // arrivals of the commits nobody else waits for (the last operand stages, P tiles and stationary tile).
+        const uint32_t nb = b_it < (uint32_t)stages ? b_it : (uint32_t)stages;
+        for (uint32_t i = b_it - nb; i < b_it; ++i) mbar_wait(&s.b_empty[i % stages], (i / stages) & 1);
+        const uint32_t np = p_it < (uint32_t)p.p_bufs ? p_it : (uint32_t)p.p_bufs;
+        for (uint32_t j = p_it - np; j < p_it; ++j)
+          mbar_wait(&s.p_empty[(p.p_bufs == 2) ? (j & 1) : 0], ((p.p_bufs == 2) ? (j >> 1) : j) & 1);
+        if (a_it > 0) mbar_wait(s.a_empty, (a_it - 1) & 1);
       }
     }
   } else if (warp >= 4) {
@@ -740,7 +737,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
                 for (int i = 0; i < 32; ++i) {
                   const int k = c * 32 + i;
                   if (k < p.K) {
-                    p.dbeta[(size_t)k * p.ldg + grow] = fmaf(c_rstd, v[i], -g_cb * e[i]) - cr[i];
+                    const float gval = fmaf(c_rstd, v[i], -g_cb * e[i]) - cr[i];
+                    if (p.dbeta_bf != nullptr) p.dbeta_bf[(size_t)k * p.ldgb + grow] = __float2bfloat16(gval);
+                    else p.dbeta[(size_t)k * p.ldg + grow] = gval;
                     if (p.beta3 != nullptr) p.beta3[(size_t)k * p.ld3 + grow] = __float2bfloat16(g_cb * bs[i]);
                   }
                 }
@@ -831,6 +830,31 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
     }
   }
 
+  // ---- ROW_GRAD2 with a federation context: beta part of the aggregation.  The CTAs set aside for it come
+  // straight here; a sweep CTA arrives once its share of the sweep is done (every MMA it issued has completed
+  // and every tile it loaded has been consumed, so its shared memory is free) and takes the word tiles the
+  // atomic counter still has.
+  if (kMode == ROW_GRAD2 && p.fed != nullptr) {
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x == 0) {  // the sweep's mbarriers die here: the aggregation lays its own over the same bytes
+      for (int i = 0; i < 32; ++i)  // a_full .. d2_empty are 32 consecutive 64-bit words
+        asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(s.a_full + i)) : "memory");
+    }
+    const GfFedArgs& fa = *p.fed;
+    const GfFabricRank& me = fa.ranks[0];
+    const long long tstep = fa.step_ctr[1];
+    if (threadIdx.x < (unsigned)fa.world) {  // every peer's beta gradient final, its shadows no longer read
+      fed_wait_flag(me.flags[me.rank] + GF_FED_PHASE_BETA_READY * GF_MAX_RANKS + threadIdx.x, (uint32_t)tstep,
+                    (int)threadIdx.x, GF_FED_PHASE_BETA_READY);
+    }
+    __syncthreads();
+    asm volatile("fence.proxy.async;" ::: "memory");  // peer data is read, shared memory rewritten, by the async proxy
+    const AdamF hh = fed_adam_consts(fa, tstep);
+    fed_beta_phase_tma(fa, me, hh, fed_tm, base, p.smem_bytes - 1024);
+    __threadfence_system();  // the completion handshake is phase C of the closing gf_fed_aggregate(parts=1)
+  }
+
   // ---- teardown
   tc_fence_before();
   __syncthreads();
@@ -859,7 +883,7 @@ static bool plan_smem(int mode, int Kp, int max_smem, SmemPlan* out) {
 }
 
 template <int kMode>
-static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, SweepParams& p,
+static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, const FedTmaps& fed_tm, SweepParams& p,
                         cudaStream_t stream) {
   int max_smem = 0, dev = 0;
   GF_CUDA_CHECK(cudaGetDevice(&dev));
@@ -881,24 +905,24 @@ static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta,
   if (grid > total) grid = total;
   if (grid < 1) grid = 1;
   grid += fed_ctas;
-  kern<<<grid, kThreads, plan.bytes, stream>>>(tm_theta, tm_beta, p);
+  kern<<<grid, kThreads, plan.bytes, stream>>>(tm_theta, tm_beta, fed_tm, p);
   GF_LAUNCHED();
   return GF_OK;
 }
 
-static int dispatch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, SweepParams& p,
-                          cudaStream_t stream) {
+static int dispatch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta, const FedTmaps& fed_tm,
+                          SweepParams& p, cudaStream_t stream) {
   switch (p.mode) {
-    case ROW_LOGITS: return launch_sweep<ROW_LOGITS>(tm_theta, tm_beta, p, stream);
-    case ROW_LSE: return launch_sweep<ROW_LSE>(tm_theta, tm_beta, p, stream);
-    case ROW_GRAD: return launch_sweep<ROW_GRAD>(tm_theta, tm_beta, p, stream);
-    case COL_STATS: return launch_sweep<COL_STATS>(tm_theta, tm_beta, p, stream);
-    case COL_STATS2: return launch_sweep<COL_STATS2>(tm_theta, tm_beta, p, stream);
-    case COL_GRAD: return launch_sweep<COL_GRAD>(tm_theta, tm_beta, p, stream);
-    case COL_LOGITS: return launch_sweep<COL_LOGITS>(tm_theta, tm_beta, p, stream);
-    case ROW_LSE2: return launch_sweep<ROW_LSE2>(tm_theta, tm_beta, p, stream);
-    case COL_GRAD2: return launch_sweep<COL_GRAD2>(tm_theta, tm_beta, p, stream);
-    case ROW_GRAD2: return launch_sweep<ROW_GRAD2>(tm_theta, tm_beta, p, stream);
+    case ROW_LOGITS: return launch_sweep<ROW_LOGITS>(tm_theta, tm_beta, fed_tm, p, stream);
+    case ROW_LSE: return launch_sweep<ROW_LSE>(tm_theta, tm_beta, fed_tm, p, stream);
+    case ROW_GRAD: return launch_sweep<ROW_GRAD>(tm_theta, tm_beta, fed_tm, p, stream);
+    case COL_STATS: return launch_sweep<COL_STATS>(tm_theta, tm_beta, fed_tm, p, stream);
+    case COL_STATS2: return launch_sweep<COL_STATS2>(tm_theta, tm_beta, fed_tm, p, stream);
+    case COL_GRAD: return launch_sweep<COL_GRAD>(tm_theta, tm_beta, fed_tm, p, stream);
+    case COL_LOGITS: return launch_sweep<COL_LOGITS>(tm_theta, tm_beta, fed_tm, p, stream);
+    case ROW_LSE2: return launch_sweep<ROW_LSE2>(tm_theta, tm_beta, fed_tm, p, stream);
+    case COL_GRAD2: return launch_sweep<COL_GRAD2>(tm_theta, tm_beta, fed_tm, p, stream);
+    case ROW_GRAD2: return launch_sweep<ROW_GRAD2>(tm_theta, tm_beta, fed_tm, p, stream);
     default: break;
   }
   fprintf(stderr, "[gfedntm] dec sweep: unsupported mode %d\n", p.mode);
@@ -1003,7 +1027,10 @@ extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
     p.ext_tile0 = a->ext_col0 / kBN;
     p.fed = reinterpret_cast<const GfFedArgs*>(a->fed);
     p.fed_ctas = a->fed != nullptr ? a->fed_ctas : 0;
-    GF_ARG_CHECK(a->fed == nullptr || (a->fed_ctas >= 1 && a->fed_ctas < num_sms()), "fed_ctas");
+    GF_ARG_CHECK(a->fed == nullptr || (a->fed_ctas >= 0 && a->fed_ctas < num_sms()), "fed_ctas");
+    GF_ARG_CHECK(a->fed == nullptr || a->fed_tmaps != nullptr, "fed_tmaps (gf_fed_make_tmaps) is required with fed");
+    GF_ARG_CHECK(a->fed == nullptr || (a->V % 8 == 0 && a->Kp % 16 == 0),
+                 "the overlapped aggregation needs V % 8 == 0 (use gf_fed_aggregate(parts=3) otherwise)");
   }
   p.out = a->out;
   p.lse_part = reinterpret_cast<float2*>(a->lse_part);
@@ -1020,10 +1047,15 @@ extern "C" int gf_dec_sweep(const GfSweepArgs* a, void* stream_) {
   p.use_running = a->use_running;
   p.asp = a->asp; p.csp = a->csp;
   p.dbeta = a->dbeta; p.ldg = a->ld_dbeta;
+  p.dbeta_bf = reinterpret_cast<__nv_bfloat16*>(a->dbeta_bf); p.ldgb = a->ld_dbeta_bf;
+  GF_ARG_CHECK(a->dbeta_bf == nullptr || a->mode == COL_GRAD2, "dbeta_bf is a COL_GRAD2 output");
   p.corr = a->corr; p.colptr = a->colptr;
   {
     const char* dbg = getenv("GFEDNTM_SWEEP_DEBUG");
     p.debug = dbg ? atoi(dbg) : 0;
   }
-  return dispatch_sweep(tm_theta, tm_beta, p, stream);
+  static const FedTmaps kNoTmaps{};
+  const FedTmaps* fed_tm = (a->mode == ROW_GRAD2 && a->fed != nullptr) ? reinterpret_cast<const FedTmaps*>(a->fed_tmaps)
+                                                                      : &kNoTmaps;
+  return dispatch_sweep(tm_theta, tm_beta, *fed_tm, p, stream);
 }

@@ -25,6 +25,7 @@
 #include "tmap.h"
 #include "../include/gfedntm_kernels.h"
 #include "fabric_dev.cuh"
+#include <string.h>
 
 namespace gf {
 
@@ -53,51 +54,82 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
 
   const int parts = a.parts ? a.parts : 3;  // bit 0: flat region + BatchNorm statistics, bit 1: beta
 
-  // ---------------- phase B.1: flat region [0, flat_n), float4 granularity, owner = contiguous slice
+  // ---------------- phase B.1: flat region [0, flat_n) as a list of ranges (one range = everything when the
+  // caller gave none), float4 granularity.  A shared range is split into contiguous owner slices; an unshared
+  // range stays client-local: in gradient mode every rank applies its own Adam step to all of it (with the
+  // client weight taken out of the gradient again), in parameter mode it is left alone.
   if (parts & 1) {
-    const long long n4 = (a.flat_n + 3) / 4;
-    const long long per = (n4 + world - 1) / world;
-    const long long lo = rank * per, hi = (lo + per < n4) ? lo + per : n4;
-    for (long long q = lo + tid; q < hi; q += nthr) {
-      const long long i = q * 4;
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      float4 in[GF_MAX_RANKS];
-      // issue every peer load before the first use so all of them are in flight together
-#pragma unroll
-      for (int c = 0; c < GF_MAX_RANKS; ++c)
-        if (c < world) in[c] = ld_peer_f4((a.mode == 0 ? me.G[c] : me.P[c]) + i);
-      if (a.mode == 0) {
-#pragma unroll
-        for (int c = 0; c < GF_MAX_RANKS; ++c)
-          if (c < world) { acc.x += in[c].x; acc.y += in[c].y; acc.z += in[c].z; acc.w += in[c].w; }
-        float4 p = *reinterpret_cast<const float4*>(me.P[rank] + i);
-        float4 m = *reinterpret_cast<const float4*>(me.M + i);
-        float4 v = *reinterpret_cast<const float4*>(me.V2 + i);
-        p.x = adam_upd(p.x, acc.x, m.x, v.x, h);
-        p.y = adam_upd(p.y, acc.y, m.y, v.y, h);
-        p.z = adam_upd(p.z, acc.z, m.z, v.z, h);
-        p.w = adam_upd(p.w, acc.w, m.w, v.w, h);
-        *reinterpret_cast<float4*>(me.M + i) = m;
-        *reinterpret_cast<float4*>(me.V2 + i) = v;
-        acc = p;
-      } else {
-#pragma unroll
-        for (int c = 0; c < GF_MAX_RANKS; ++c)
-          if (c < world) {
-            const float w = a.w[c];
-            acc.x = fmaf(w, in[c].x, acc.x); acc.y = fmaf(w, in[c].y, acc.y);
-            acc.z = fmaf(w, in[c].z, acc.z); acc.w = fmaf(w, in[c].w, acc.w);
-          }
+    const int n_ranges = a.n_ranges > 0 ? a.n_ranges : 1;
+    for (int ri = 0; ri < n_ranges; ++ri) {
+      const long long r_off = a.n_ranges > 0 ? a.ranges[ri].off : 0;
+      const long long r_len = a.n_ranges > 0 ? a.ranges[ri].len : a.flat_n;
+      const bool shared = a.n_ranges > 0 ? (a.ranges[ri].shared != 0) : true;
+      const long long n4 = (r_len + 3) / 4;
+      if (!shared) {
+        if (a.mode != 0) continue;
+        const float gs = a.local_gscale;
+        for (long long q = tid; q < n4; q += nthr) {
+          const long long i = r_off + q * 4;
+          float4 g = *reinterpret_cast<const float4*>(me.G[rank] + i);
+          float4 p = *reinterpret_cast<const float4*>(me.P[rank] + i);
+          float4 m = *reinterpret_cast<const float4*>(me.M + i);
+          float4 v = *reinterpret_cast<const float4*>(me.V2 + i);
+          p.x = adam_upd(p.x, g.x * gs, m.x, v.x, h);
+          p.y = adam_upd(p.y, g.y * gs, m.y, v.y, h);
+          p.z = adam_upd(p.z, g.z * gs, m.z, v.z, h);
+          p.w = adam_upd(p.w, g.w * gs, m.w, v.w, h);
+          *reinterpret_cast<float4*>(me.M + i) = m;
+          *reinterpret_cast<float4*>(me.V2 + i) = v;
+          *reinterpret_cast<float4*>(me.P[rank] + i) = p;
+        }
+        continue;
       }
-      fed_push_f4(me.P, me.P_mc, i, acc, world);
+      const long long per = (n4 + world - 1) / world;
+      const long long lo = rank * per, hi = (lo + per < n4) ? lo + per : n4;
+      for (long long q = lo + tid; q < hi; q += nthr) {
+        const long long i = r_off + q * 4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 in[GF_MAX_RANKS];
+        // issue every peer load before the first use so all of them are in flight together
+#pragma unroll
+        for (int c = 0; c < GF_MAX_RANKS; ++c)
+          if (c < world) in[c] = ld_peer_f4((a.mode == 0 ? me.G[c] : me.P[c]) + i);
+        if (a.mode == 0) {
+#pragma unroll
+          for (int c = 0; c < GF_MAX_RANKS; ++c)
+            if (c < world) { acc.x += in[c].x; acc.y += in[c].y; acc.z += in[c].z; acc.w += in[c].w; }
+          float4 p = *reinterpret_cast<const float4*>(me.P[rank] + i);
+          float4 m = *reinterpret_cast<const float4*>(me.M + i);
+          float4 v = *reinterpret_cast<const float4*>(me.V2 + i);
+          p.x = adam_upd(p.x, acc.x, m.x, v.x, h);
+          p.y = adam_upd(p.y, acc.y, m.y, v.y, h);
+          p.z = adam_upd(p.z, acc.z, m.z, v.z, h);
+          p.w = adam_upd(p.w, acc.w, m.w, v.w, h);
+          *reinterpret_cast<float4*>(me.M + i) = m;
+          *reinterpret_cast<float4*>(me.V2 + i) = v;
+          acc = p;
+        } else {
+#pragma unroll
+          for (int c = 0; c < GF_MAX_RANKS; ++c)
+            if (c < world) {
+              const float w = a.w[c];
+              acc.x = fmaf(w, in[c].x, acc.x); acc.y = fmaf(w, in[c].y, acc.y);
+              acc.z = fmaf(w, in[c].z, acc.z); acc.w = fmaf(w, in[c].w, acc.w);
+            }
+        }
+        fed_push_f4(me.P, me.P_mc, i, acc, world);
+      }
     }
   }
 
-  // ---------------- phase B.2: BatchNorm running statistics (weighted mean in both modes)
+  // ---------------- phase B.2: BatchNorm running statistics (weighted mean in both modes).  The buffer is
+  // {mu mean, mu var, sigma mean, sigma var}[K] then {beta mean, beta var}[V]; bit b of s_mask = block b shared
+  // (an unshared statistic keeps the client's own value).
   if (parts & 1) {
     const long long n4 = (a.s_n + 3) / 4;
     const long long per = (n4 + world - 1) / world;
     const long long lo = rank * per, hi = (lo + per < n4) ? lo + per : n4;
+    const bool all_shared = (a.n_ranges == 0) || ((a.s_mask & 63) == 63);
     for (long long q = lo + tid; q < hi; q += nthr) {
       const long long i = q * 4;
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -107,13 +139,23 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
         acc.x = fmaf(w, s.x, acc.x); acc.y = fmaf(w, s.y, acc.y);
         acc.z = fmaf(w, s.z, acc.z); acc.w = fmaf(w, s.w, acc.w);
       }
-      fed_push_f4(me.S, me.S_mc, i, acc, world);
+      if (all_shared) {
+        fed_push_f4(me.S, me.S_mc, i, acc, world);
+      } else {
+        const float vals[4] = {acc.x, acc.y, acc.z, acc.w};
+        for (int e = 0; e < 4; ++e) {
+          const long long j = i + e;
+          const int blk = j < 4LL * a.K ? (int)(j / (a.K > 0 ? a.K : 1)) : (j < 4LL * a.K + a.V ? 4 : 5);
+          if (j < 4LL * a.K + 2LL * a.V && ((a.s_mask >> blk) & 1))
+            for (int c = 0; c < world; ++c) me.S[c][j] = vals[e];
+        }
+      }
     }
   }
 
   // ---------------- phase B.3: beta [K,V], owner = contiguous range of word tiles; writes fp32 beta,
   //                  bf16 beta_bf [Kp,ldb] and bf16 betaT_bf [V,Kp] to every rank (fabric_dev.cuh)
-  if (parts & 2) fed_beta_phase(a, me, h, (int)blockIdx.x, (int)gridDim.x, tile_v);
+  if ((parts & 2) && (a.n_ranges == 0 || a.beta_shared)) fed_beta_phase(a, me, h, (int)blockIdx.x, (int)gridDim.x, tile_v);
 
   // ---------------- phase C: all my pushes are done -> tell the peers, wait for theirs
   __threadfence_system();
@@ -139,9 +181,29 @@ __global__ void fed_signal_kernel(const GfFedArgs a, int phase) {
   const GfFabricRank& me = a.ranks[0];
   uint32_t epoch = (uint32_t)a.epoch;
   if (a.step_ctr != nullptr) epoch = (uint32_t)a.step_ctr[1];
+  if (phase == GF_FED_PHASE_BETA_READY && threadIdx.x == 0 && me.agg_counter != nullptr) *me.agg_counter = 0u;
   if (threadIdx.x < (unsigned)a.world) {
     __threadfence_system();
     st_release_sys(me.flags[threadIdx.x] + phase * GF_MAX_RANKS + me.rank, epoch);
+  }
+}
+
+// Collects the fp32 master copy of beta: every word-tile range this rank does not own is read from its
+// owner (the overlapped aggregation updates the master copy on the owner only).
+__global__ void __launch_bounds__(256) fed_gather_beta_kernel(const GfFedArgs a) {
+  const GfFabricRank& me = a.ranks[0];
+  const int world = a.world, rank = me.rank;
+  const int vt = (a.V + 127) / 128;
+  const int per = (vt + world - 1) / world;
+  const long long v4 = a.V / 4;  // V % 4 == 0 (checked by the launcher)
+  const long long n = (long long)a.K * v4;
+  for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) {
+    const long long k = q / v4, c4 = q - k * v4;
+    int owner = (int)((c4 * 4) / 128) / per;
+    if (owner >= world) owner = world - 1;
+    if (owner == rank) continue;
+    const long long ip = a.beta_off + k * a.V + c4 * 4;
+    *reinterpret_cast<float4*>(me.P[rank] + ip) = ld_peer_f4(me.P[owner] + ip);
   }
 }
 
@@ -152,8 +214,44 @@ using namespace gf;
 extern "C" int gf_fed_signal(const GfFedArgs* a, int phase, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(a->world >= 1 && a->world <= GF_MAX_RANKS && a->n_rank_ctx == 1, "world / n_rank_ctx");
-  GF_ARG_CHECK(phase >= 2 && phase < 8, "phase slots 0 and 1 belong to gf_fed_aggregate");
+  GF_ARG_CHECK(phase >= 2 && phase < GF_FED_FLAG_SLOTS, "phase slots 0 and 1 belong to gf_fed_aggregate");
   fed_signal_kernel<<<1, 32, 0, st>>>(*a, phase);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_fed_make_tmaps(const GfFedArgs* a, void* out_) {
+  GF_ARG_CHECK(a != nullptr && out_ != nullptr && a->n_rank_ctx == 1, "args");
+  GF_ARG_CHECK((reinterpret_cast<uintptr_t>(out_) & 63) == 0, "the tensor-map buffer must be 64-byte aligned");
+  const GfFabricRank& me = a->ranks[0];
+  GF_ARG_CHECK(me.ld_gb % 8 == 0 && me.ld_gb >= a->V, "ld_gb must be a multiple of 8 (16-byte rows) and >= V");
+  FedTmaps* out = reinterpret_cast<FedTmaps*>(out_);
+  memset(out, 0, sizeof(FedTmaps));
+  PFN_encodeTiled fn = get_encode_fn();
+  GF_ARG_CHECK(fn != nullptr, "cuTensorMapEncodeTiled not available");
+  for (int c = 0; c < a->world; ++c) {
+    if (me.Gb[c] == nullptr) continue;
+    cuuint64_t dims[2] = {(cuuint64_t)a->V, (cuuint64_t)a->K};
+    cuuint64_t strides[1] = {(cuuint64_t)me.ld_gb * 2};
+    cuuint32_t box[2] = {128, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(&out->m[c], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, me.Gb[c], dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+      fprintf(stderr, "[gfedntm] cuTensorMapEncodeTiled failed (%d) for the beta gradient of rank %d\n", (int)r, c);
+      return GF_ERR_DRIVER;
+    }
+  }
+  return GF_OK;
+}
+
+extern "C" int gf_fed_gather_beta(const GfFedArgs* a, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(a->world >= 1 && a->world <= GF_MAX_RANKS && a->n_rank_ctx == 1, "world / n_rank_ctx");
+  GF_ARG_CHECK(a->V % 4 == 0 && a->beta_off % 4 == 0, "V and beta_off must be multiples of 4");
+  if (a->world == 1 || a->K == 0) return GF_OK;
+  fed_gather_beta_kernel<<<4 * num_sms(), 256, 0, st>>>(*a);
   GF_LAUNCHED();
   return GF_OK;
 }
@@ -166,6 +264,11 @@ extern "C" int gf_fed_aggregate(const GfFedArgs* a, void* stream_) {
   GF_ARG_CHECK(a->flat_n % 4 == 0 && a->beta_off % 4 == 0 && a->s_n % 4 == 0,
                "flat_n, beta_off and s_n must be multiples of 4 (16-byte vectors)");
   GF_ARG_CHECK(a->mode == 1 || a->step >= 1 || a->step_ctr != nullptr, "Adam step must be >= 1");
+  GF_ARG_CHECK(a->n_ranges >= 0 && a->n_ranges <= GF_FED_MAX_RANGES, "n_ranges");
+  for (int i = 0; i < a->n_ranges; ++i)
+    GF_ARG_CHECK(a->ranges[i].off % 4 == 0 && a->ranges[i].len % 4 == 0 && a->ranges[i].off >= 0 &&
+                     a->ranges[i].off + a->ranges[i].len <= a->flat_n,
+                 "ranges must be 16-byte aligned pieces of [0, flat_n)");
   AdamF h;
   h.lr = a->lr; h.b1 = a->b1; h.b2 = a->b2; h.eps = a->eps; h.wd = a->wd;
   const int step = a->step >= 1 ? a->step : 1;

@@ -4,6 +4,7 @@
 #pragma once
 #include <cuda_bf16.h>
 #include <stdio.h>
+#include <cuda.h>
 #include "ptx.cuh"
 #include "../include/gfedntm_kernels.h"
 
@@ -261,20 +262,32 @@ __device__ __forceinline__ void fed_beta_phase(const GfFedArgs& a, const GfFabri
 }
 
 // ---------------------------------------------------------------------------------------------------
-// Bulk-copy variant of the beta phase (gradient mode), used by the aggregation CTAs inside the d-theta
-// sweep.  A handful of CTAs must keep the NVLink busy, so the peers' gradient tiles are fetched with
-// cp.async.bulk (one 512-byte row per instruction, issued by a producer warp) into a multi-stage
-// shared-memory ring: ~100-200 KB in flight per CTA instead of the 16 KB a register-based tile allows.
-//   threads 0..255   consumers: reduce the staged peer tiles + the local gradient, Adam, push P and shadows
-//   threads 256..287 producer warp (lane r issues row r of every remote peer's tile)
-// `smem` must be 1024-byte aligned; layout: [tile 32x132 f32][stages x n_remote x 16 KB][mbarriers].
-// Requires V % 4 == 0, ldb % 4 == 0, Kp % 16 == 0 (callers fall back to fed_beta_phase otherwise).
+// Overlapped beta phase (gradient mode), run by CTAs of the d-theta sweep (csrc/dec_sweep.cu): the CTAs
+// set aside for it from the start, and every sweep CTA once it has run out of sweep work.
+//
+// Exchange format: every rank's beta gradient is bf16 [K, ld_gb] (GF_COL_GRAD2 writes it directly, the client
+// weight is folded into the backward pass).  The owner of a word-tile range
+//   - pulls the peers' 32-topic x 128-word tiles with ONE 2-D TMA load per peer and tile (plain
+//     cp.async.bulk.tensor on a tensor map of that peer's buffer, no multicast) into a shared-memory ring,
+//   - sums them with its own gradient in fp32 and applies Adam to ITS fp32 master copy and moments (which
+//     never leave the owner: gf_fed_gather_beta collects the master copy when somebody needs all of it),
+//   - pushes only the bf16 operand shadows beta_bf / betaT_bf to every rank (multimem.st on the NVLS
+//     alias, or one P2P store per rank).
+// Word tiles are handed out by an atomic counter (me.agg_counter), so any number of CTAs can work on them
+// and latecomers simply take what is left.
+//   threads 0..255   consumers
+//   thread  256      producer (claims word tiles, issues the TMA loads)
+// `smem` must be 1024-byte aligned; layout: [tile 32x132 f32][transposed staging 128 x (Kp+8) bf16]
+// [stages x n_remote x 8 KB][item table][mbarriers].  Requires V % 8 == 0, ldb % 4 == 0, Kp % 16 == 0.
 // ---------------------------------------------------------------------------------------------------
-constexpr int kFedTileBytes = 32 * 128 * 4;  // one peer's 32-topic x 128-word fp32 tile
+struct FedTmaps {
+  CUtensorMap m[GF_MAX_RANKS];
+};
+constexpr int kFedTileBytes = 32 * 128 * 2;  // one peer's 32-topic x 128-word bf16 tile
 constexpr int kFedMaxStages = 8;
 
-__device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const GfFabricRank& me, const AdamF& h,
-                                                    int cta, int n_cta, uint8_t* smem, uint32_t smem_bytes) {
+__device__ __forceinline__ void fed_beta_phase_tma(const GfFedArgs& a, const GfFabricRank& me, const AdamF& h,
+                                                   const FedTmaps& tm, uint8_t* smem, uint32_t smem_bytes) {
   const int world = a.world, rank = me.rank, n_remote = world - 1;
   float* tile_v = reinterpret_cast<float*>(smem);
   float(*tv)[132] = reinterpret_cast<float(*)[132]>(tile_v);
@@ -284,10 +297,12 @@ __device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const Gf
   const uint32_t tT_bytes = ((uint32_t)(128 * ldt * 2) + 1023u) & ~1023u;
   uint8_t* ring = smem + 17408 + tT_bytes;
   const uint32_t stage_bytes = (uint32_t)n_remote * kFedTileBytes;
-  int stages = (int)((smem_bytes - 17408 - tT_bytes - 256) / stage_bytes);
+  int stages = (int)((smem_bytes - 17408 - tT_bytes - 512) / stage_bytes);
   if (stages > kFedMaxStages) stages = kFedMaxStages;
   if (stages < 1) stages = 1;  // (the launcher sizes the shared memory so that this never triggers)
-  uint64_t* full = reinterpret_cast<uint64_t*>(ring + (size_t)stages * stage_bytes);
+  int* item_wt = reinterpret_cast<int*>(ring + (size_t)stages * stage_bytes);
+  int* item_k = item_wt + kFedMaxStages;
+  uint64_t* full = reinterpret_cast<uint64_t*>(item_k + kFedMaxStages);
   uint64_t* empty = full + kFedMaxStages;
   if (threadIdx.x == 0) {
     for (int i = 0; i < stages; ++i) {
@@ -304,112 +319,127 @@ __device__ __forceinline__ void fed_beta_phase_bulk(const GfFedArgs& a, const Gf
   const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;
   const int n_wt = t_hi > t_lo ? t_hi - t_lo : 0;  // word tiles owned by this rank; a CTA takes whole word tiles
 
-  if (threadIdx.x >= 256 && threadIdx.x < 288) {
-    // ---------------- producer warp
-    const int lane = threadIdx.x - 256;
+  if (threadIdx.x == 256) {
+    // ---------------- producer
     uint32_t it = 0;
-    for (int wt = cta; wt < n_wt; wt += n_cta) {
+    for (;;) {
+      const int wt = (int)atomicAdd(me.agg_counter, 1u);
+      const bool done = wt >= n_wt;
       const int v0 = (t_lo + wt) * 128;
-      const uint32_t row_bytes = (uint32_t)min(128, a.V - v0) * 4u;
-      for (int kti = 0; kti < kt; ++kti, ++it) {
+      for (int kti = 0; kti < (done ? 1 : kt); ++kti, ++it) {
         const int st = it % stages;
-        const int k0 = kti * 32;
-        const int rows = min(32, a.K - k0);
         mbar_wait(&empty[st], ((it / stages) & 1) ^ 1);
-        if (lane == 0) mbar_arrive_expect_tx(&full[st], (uint32_t)n_remote * (uint32_t)rows * row_bytes);
-        __syncwarp();
-        if (lane < rows) {
+        item_wt[st] = done ? -1 : wt;
+        item_k[st] = kti;
+        if (done || n_remote == 0) {
+          mbar_arrive(&full[st]);
+        } else {
+          mbar_arrive_expect_tx(&full[st], stage_bytes);  // out-of-range rows / words are zero-filled and counted
           int slot = 0;
           for (int c = 0; c < world; ++c) {
             if (c == rank) continue;
-            const float* src = me.G[c] + a.beta_off + (long long)(k0 + lane) * a.V + v0;
-            const uint32_t dst = smem_u32(ring + (size_t)st * stage_bytes + (size_t)slot * kFedTileBytes + lane * 512);
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                         "l"(src), "r"(row_bytes), "r"(smem_u32(&full[st]))
-                         : "memory");
+            tma_load_2d(ring + (size_t)st * stage_bytes + (size_t)slot * kFedTileBytes, &tm.m[c], &full[st], v0, kti * 32);
             ++slot;
           }
         }
       }
+      if (done) break;
     }
   } else if (threadIdx.x < 256) {
     // ---------------- consumers
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    uint32_t it = 0;
-    for (int wt = cta; wt < n_wt; wt += n_cta) {
+    const __nv_bfloat16* gb_own = reinterpret_cast<const __nv_bfloat16*>(me.Gb[rank]);
+    int wt = -1, kti = 0;
+    bool known = false;  // (wt, kti) of this item already known (second and later topic slabs of a word tile)
+    for (uint32_t it = 0;; ++it) {
+      const int st = it % stages;
+      if (!known) {
+        mbar_wait(&full[st], (it / stages) & 1);
+        wt = item_wt[st];
+        kti = item_k[st];
+        if (wt < 0) break;
+      }
       const int v0 = (t_lo + wt) * 128;
       const int vv = v0 + tx * 4;
-      for (int kti = 0; kti < kt; ++kti, ++it) {
-        const int st = it % stages;
-        const int k0 = kti * 32;
-        // local operands first (their latency overlaps the wait for the peers' tile)
-        float4 gl[4], pp[4], mm[4], v2[4];
-        bool live[4];
+      const int k0 = kti * 32;
+      // local operands (their latency overlaps the wait for the peers' tile when the item was known)
+      float4 pp[4], mm[4], v2[4];
+      uint2 gl[4];
+      bool live[4];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          const int k = k0 + ty + r * 8;
-          live[r] = (k < a.K) && (vv < a.V);
-          if (live[r]) {
-            const long long ip = a.beta_off + (long long)k * a.V + vv;
-            gl[r] = *reinterpret_cast<const float4*>(me.G[rank] + ip);
-            pp[r] = *reinterpret_cast<const float4*>(me.P[rank] + ip);
-            mm[r] = *reinterpret_cast<const float4*>(me.M + ip);
-            v2[r] = *reinterpret_cast<const float4*>(me.V2 + ip);
-          }
+      for (int r = 0; r < 4; ++r) {
+        const int k = k0 + ty + r * 8;
+        live[r] = (k < a.K) && (vv < a.V);
+        if (live[r]) {
+          const long long ip = a.beta_off + (long long)k * a.V + vv;
+          gl[r] = *reinterpret_cast<const uint2*>(gb_own + (size_t)k * me.ld_gb + vv);
+          pp[r] = *reinterpret_cast<const float4*>(me.P[rank] + ip);
+          mm[r] = *reinterpret_cast<const float4*>(me.M + ip);
+          v2[r] = *reinterpret_cast<const float4*>(me.V2 + ip);
         }
-        mbar_wait(&full[st], (it / stages) & 1);
-        const uint8_t* sb = ring + (size_t)st * stage_bytes;
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          const int k = k0 + ty + r * 8;
-          float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (live[r]) {
-            float4 g = gl[r];
-            for (int c = 0; c < n_remote; ++c) {
-              const float4 x = *reinterpret_cast<const float4*>(sb + (size_t)c * kFedTileBytes + (ty + r * 8) * 512 + tx * 16);
-              g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
-            }
-            const long long ip = a.beta_off + (long long)k * a.V + vv;
-            val = pp[r];
-            val.x = adam_upd(val.x, g.x, mm[r].x, v2[r].x, h);
-            val.y = adam_upd(val.y, g.y, mm[r].y, v2[r].y, h);
-            val.z = adam_upd(val.z, g.z, mm[r].z, v2[r].z, h);
-            val.w = adam_upd(val.w, g.w, mm[r].w, v2[r].w, h);
-            *reinterpret_cast<float4*>(me.M + ip) = mm[r];
-            *reinterpret_cast<float4*>(me.V2 + ip) = v2[r];
-            __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
-                                              __float2bfloat16(val.z), __float2bfloat16(val.w)};
-            fed_push_f4(me.P, me.P_mc, ip, val, world);
-            fed_push_b64(me.beta_bf, me.beta_bf_mc, (size_t)k * a.ldb + vv, *reinterpret_cast<const uint2*>(o), world);
-          }
-          *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
-        }
-        fed_sync256();
-        if (threadIdx.x == 0) mbar_arrive(&empty[st]);  // every consumer has read the stage
-        // transpose this 32-topic slab into the row-major [word][topic] staging tile
-        const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
-        const int kb = k0 + half * 16;
-        if (kb < a.Kp) {
-          __align__(16) __nv_bfloat16 o[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
-          uint4* dst = reinterpret_cast<uint4*>(tT + (size_t)wv * ldt + kb);
-          dst[0] = reinterpret_cast<const uint4*>(o)[0];
-          dst[1] = reinterpret_cast<const uint4*>(o)[1];
-        }
-        fed_sync256();
       }
-      // flush the transposed shadow of this word tile: whole rows of Kp bf16, 16-byte pieces, consecutive
-      // threads -> consecutive addresses (large NVLink packets instead of one 32-byte store per topic slab)
-      const int cpr = a.Kp >> 3;  // 16-byte chunks per row
-      for (int idx = threadIdx.x; idx < 128 * cpr; idx += 256) {
-        const int rw = idx / cpr, ch = idx - rw * cpr;
-        if (v0 + rw < a.V) {
-          const uint4 q = *reinterpret_cast<const uint4*>(tT + (size_t)rw * ldt + ch * 8);
-          fed_push_b128(me.betaT_bf, me.betaT_bf_mc, (size_t)(v0 + rw) * a.Kp + ch * 8, q, world);
+      if (known) mbar_wait(&full[st], (it / stages) & 1);
+      const uint8_t* sb = ring + (size_t)st * stage_bytes;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int k = k0 + ty + r * 8;
+        float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (live[r]) {
+          const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&gl[r]);
+          float2 lo = __bfloat1622float2(o2[0]), hi = __bfloat1622float2(o2[1]);
+          float4 g = make_float4(lo.x, lo.y, hi.x, hi.y);
+          for (int c = 0; c < n_remote; ++c) {
+            const uint2 x = *reinterpret_cast<const uint2*>(sb + (size_t)c * kFedTileBytes + (ty + r * 8) * 256 + tx * 8);
+            const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&x);
+            lo = __bfloat1622float2(x2[0]);
+            hi = __bfloat1622float2(x2[1]);
+            g.x += lo.x; g.y += lo.y; g.z += hi.x; g.w += hi.y;
+          }
+          const long long ip = a.beta_off + (long long)k * a.V + vv;
+          val = pp[r];
+          val.x = adam_upd(val.x, g.x, mm[r].x, v2[r].x, h);
+          val.y = adam_upd(val.y, g.y, mm[r].y, v2[r].y, h);
+          val.z = adam_upd(val.z, g.z, mm[r].z, v2[r].z, h);
+          val.w = adam_upd(val.w, g.w, mm[r].w, v2[r].w, h);
+          *reinterpret_cast<float4*>(me.P[rank] + ip) = val;  // master copy: owner only
+          *reinterpret_cast<float4*>(me.M + ip) = mm[r];
+          *reinterpret_cast<float4*>(me.V2 + ip) = v2[r];
+          __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
+                                            __float2bfloat16(val.z), __float2bfloat16(val.w)};
+          fed_push_b64(me.beta_bf, me.beta_bf_mc, (size_t)k * a.ldb + vv, *reinterpret_cast<const uint2*>(o), world);
         }
+        *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
       }
       fed_sync256();
+      if (threadIdx.x == 0) mbar_arrive(&empty[st]);  // every consumer has read the stage and its item entry
+      // transpose this 32-topic slab into the row-major [word][topic] staging tile
+      const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
+      const int kb = k0 + half * 16;
+      if (kb < a.Kp) {
+        __align__(16) __nv_bfloat16 o[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
+        uint4* dst = reinterpret_cast<uint4*>(tT + (size_t)wv * ldt + kb);
+        dst[0] = reinterpret_cast<const uint4*>(o)[0];
+        dst[1] = reinterpret_cast<const uint4*>(o)[1];
+      }
+      fed_sync256();
+      known = (kti + 1 < kt);
+      if (known) {
+        ++kti;
+      } else {
+        // flush the transposed shadow of this word tile: whole rows of Kp bf16, 16-byte pieces, consecutive
+        // threads -> consecutive addresses (large NVLink packets instead of one 32-byte store per topic slab)
+        const int cpr = a.Kp >> 3;  // 16-byte chunks per row
+        for (int idx = threadIdx.x; idx < 128 * cpr; idx += 256) {
+          const int rw = idx / cpr, ch = idx - rw * cpr;
+          if (v0 + rw < a.V) {
+            const uint4 q = *reinterpret_cast<const uint4*>(tT + (size_t)rw * ldt + ch * 8);
+            fed_push_b128(me.betaT_bf, me.betaT_bf_mc, (size_t)(v0 + rw) * a.Kp + ch * 8, q, world);
+          }
+        }
+        fed_sync256();
+      }
     }
   }
 }

@@ -21,6 +21,7 @@ extern "C" int gf_sizeof(int which) {
     case 5: return (int)sizeof(GfDecSparseArgs);
     case 6: return (int)sizeof(GfFabricRank);
     case 7: return (int)sizeof(GfFedArgs);
+    case 8: return (int)sizeof(GfFedRange);
     default: return -1;
   }
 }

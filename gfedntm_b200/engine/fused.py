@@ -64,17 +64,20 @@ class FlatParams:
         # BatchNorm running statistics: one flat buffer as well (federated clients average them)
         K, V = model.n_components, model.input_size
         self.s_n = (4 * K + 2 * V + 3) // 4 * 4
-        Kp = (K + 15) // 16 * 16
+        Kp = K_.padded_topics(K)
         ldb = (V + 7) // 8 * 8
         self.has_shadows = model.model_type.lower() == "prodlda"
         if "P" not in arena.offsets:
             arena.reserve("P", 4 * self.total)
             arena.reserve("G", 4 * self.total)
             arena.reserve("S", 4 * self.s_n)
-            arena.reserve("flags", 256)
+            arena.reserve("flags", 256)  # GF_FED_FLAG_BYTES
             if self.has_shadows:
                 arena.reserve("beta_bf", 2 * Kp * ldb)
                 arena.reserve("betaT_bf", 2 * V * Kp)
+                if getattr(arena, "world", 1) > 1:
+                    # beta gradient in the federated exchange format (bf16 [K, ldb]), pulled by the owners
+                    arena.reserve("Gb", 2 * K * ldb)
             arena.commit(device)
         self.arena = arena
         self.P = arena.tensor("P", torch.float32)
@@ -398,6 +401,21 @@ class FusedEngine:
             K_.adam_flat(fl.P[sl], fl.G[sl], fl.M[sl], fl.V2[sl], lr=self.lr, b1=b1, b2=b2,
                          eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
                          step_ctr=self.ctr)
+
+    def optimizer_step_beta(self, gscale: float = 1.0) -> None:
+        """Adam on beta alone (federated runs that do not share beta); the caller advanced the step counter."""
+        fl = self.flat
+        b1, b2 = self.betas
+        if self.is_prod:
+            K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"),
+                         fl.view(fl.V2, "beta"), self.beta_bf, self.betaT_bf, K=self.K, V=self.V, lr=self.lr, b1=b1,
+                         b2=b2, eps=self.adam_eps, wd=self.weight_decay, step=self.step_count + 1, gscale=gscale,
+                         step_ctr=self.ctr)
+        else:
+            sg = fl.segments["beta"]
+            sl = slice(sg.offset, sg.offset + sg.numel)
+            K_.adam_flat(fl.P[sl], fl.G[sl], fl.M[sl], fl.V2[sl], lr=self.lr, b1=b1, b2=b2, eps=self.adam_eps,
+                         wd=self.weight_decay, step=self.step_count + 1, gscale=gscale, step_ctr=self.ctr)
 
     def train_step(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, **kw) -> torch.Tensor:
         """Forward + backward + Adam on one minibatch.  The kernel sequence is captured into a CUDA

@@ -68,7 +68,9 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
     params["input_size"] = len(idx2token)
     params["id2token"] = dict(enumerate(idx2token))
     params["seed"] = 1234  # identical initial weights on every rank (rank 0's are broadcast anyway)
-    grads = []  # everything is shared on the fabric path
+    # subset sharing (the reference's [federation] grads_to_share): names that do not exist in this model
+    # (e.g. inf_net.adapt_bert.* for avitm) are dropped with a warning by the trainer
+    grads = [g.strip() for g in (kw.get("grads_to_share") or []) if g.strip()]
     if kw["model_type"] == "avitm":
         data = BOWDataset(bow, idx2token)
         model = FederatedAVITM(params, grads, log, backend="fused", device=device)
@@ -81,7 +83,8 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
     model.train_data = data
 
     # ---- stage 2: synchronous per-minibatch training
-    trainer = FederatedTrainer(model, n_samples=len(data), world_size=world, rank=rank, agg=kw["agg"])
+    trainer = FederatedTrainer(model, n_samples=len(data), world_size=world, rank=rank, agg=kw["agg"],
+                               grads_to_share=grads or None)
     loader = model.make_loader(data, shuffle=True)
     trainer.prepare(loader)
     # every rank must take the same number of global steps: the longest client's epoch length
@@ -103,6 +106,7 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
                      float(loss.item()) / mb.size)
     torch.cuda.synchronize()
     dist.barrier()
+    trainer.materialize()  # complete fp32 parameters on every rank (the master copy of beta is sharded by owner)
 
     # ---- results (reference layout)
     model.best_components = model.model.beta
@@ -121,7 +125,8 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
 
 def run_fabric_federation(*, n_clients: int, source: str, data_type: str, fos: str, model_type: str,
                           training_params: dict, max_iters: int, save_client: str, save_server: str,
-                          logs_client: str, agg: str = "grad", port: Optional[int] = None) -> None:
+                          logs_client: str, agg: str = "grad", port: Optional[int] = None,
+                          grads_to_share: Optional[list] = None) -> None:
     import torch
     import torch.multiprocessing as mp
 
@@ -130,5 +135,5 @@ def run_fabric_federation(*, n_clients: int, source: str, data_type: str, fos: s
     port = port or (29400 + os.getpid() % 500)
     kw = dict(source=source, data_type=data_type, fos=fos, model_type=model_type,
               training_params=training_params, max_iters=max_iters, save_client=save_client,
-              save_server=save_server, logs_client=logs_client, agg=agg)
+              save_server=save_server, logs_client=logs_client, agg=agg, grads_to_share=grads_to_share)
     mp.spawn(_worker, args=(n_clients, port, kw), nprocs=n_clients, join=True)

@@ -27,9 +27,16 @@ from ..parallel.fabric import FusedAggregator, LocalArena, SymmetricArena
 
 class FederatedTrainer:
     def __init__(self, model, n_samples: int, world_size: int = 1, rank: int = 0, agg: str = "grad",
-                 arena=None, weights: Optional[Sequence[float]] = None, group=None) -> None:
+                 arena=None, weights: Optional[Sequence[float]] = None, group=None,
+                 grads_to_share: Optional[Sequence[str]] = None) -> None:
+        """``grads_to_share``: state-dict keys that take part in the aggregation (the reference's
+        ``[federation] grads_to_share``, federated_model.py:98-131; its server default is ``prior_mean,
+        prior_variance, beta``, server.py:71).  Everything else stays client-local: its own Adam step on the
+        client's unweighted gradient in ``agg="grad"``, untouched by the averaging in ``agg="param"``.
+        ``None`` / empty = share every parameter and BatchNorm statistic."""
         if agg not in ("grad", "param"):
             raise ValueError("agg must be 'grad' or 'param'")
+        self.grads_to_share = list(grads_to_share) if grads_to_share else None
         self.model = model
         self.n_samples = int(n_samples)
         self.world, self.rank, self.agg = int(world_size), int(rank), agg
@@ -71,11 +78,16 @@ class FederatedTrainer:
         if self.weights is None:
             self.weights = [1.0 / self.world] * self.world
         fl = eng.flat
+        ranges, s_mask, self.beta_shared = self._share_plan(fl)
         self.aggregator = FusedAggregator(world=self.world, weights=self.weights, flat_n=fl.beta_off,
                                           beta_off=fl.beta_off, s_n=fl.s_n, K=eng.K, V=eng.V, Kp=eng.Kp,
                                           ldb=(eng.beta_bf.stride(0) if eng.is_prod else 0), lr=m.lr,
-                                          betas=(m.momentum, 0.99))
-        self.aggregator.add_rank(self.arena, self.rank, M=fl.M, V2=fl.V2, has_shadows=eng.is_prod)
+                                          betas=(m.momentum, 0.99), ranges=ranges, s_mask=s_mask,
+                                          beta_shared=self.beta_shared,
+                                          local_gscale=1.0 / max(self.weights[self.rank], 1e-30))
+        self.aggregator.add_rank(self.arena, self.rank, M=fl.M, V2=fl.V2, has_shadows=eng.is_prod,
+                                 ld_gb=(eng.beta_bf.stride(0) if eng.is_prod else 0))
+        self._beta_master_partial = False
         # Overlap: the beta part of the aggregation (the bulk of the bytes) runs on a few CTAs of the d-theta
         # sweep, i.e. concurrently with ~1 ms of backward compute that no longer touches beta.
         self._overlap = None
@@ -83,35 +95,93 @@ class FederatedTrainer:
         # with NVLS multicast pushes the aggregation needs fewer (N=8: 32 CTAs 3.41 ms/step, 40 CTAs 3.50)
         nvls = bool(self.aggregator.args.ranks[0].P_mc)
         ctas = int(os.environ.get("GFEDNTM_AGG_CTAS", "32" if (nvls and self.world >= 8) else "40"))
-        if (self.world > 1 and self.agg == "grad" and ctas > 0 and eng.is_prod and eng.decoder.folded
-                and isinstance(self.arena, SymmetricArena)):
+        if (self.world > 1 and self.agg == "grad" and ctas >= 0 and eng.is_prod and eng.decoder.folded
+                and isinstance(self.arena, SymmetricArena) and self.beta_shared and eng.V % 8 == 0
+                and os.environ.get("GFEDNTM_NO_OVERLAP", "0") != "1"):
             self._overlap = self.aggregator.overlap_handle(eng.ctr, ctas)
 
+    def _share_plan(self, fl):
+        """(ranges over the flat region, BatchNorm statistics mask, beta shared?) from ``grads_to_share``."""
+        if not self.grads_to_share:
+            return None, 63, True
+        keys = set(self.grads_to_share)
+        known = set(fl.segments) | {f"{bn}.{st}" for bn in ("inf_net.f_mu_batchnorm", "inf_net.f_sigma_batchnorm",
+                                                            "beta_batchnorm")
+                                    for st in ("running_mean", "running_var", "num_batches_tracked")}
+        unknown = sorted(keys - known)
+        if unknown:
+            # (the reference raises KeyError in get_gradients for such keys, SURVEY 6.3 item 10)
+            import logging
+
+            logging.getLogger(__name__).warning("grads_to_share names unknown tensors (ignored): %s", unknown)
+        ranges = []
+        segs = sorted((s for n, s in fl.segments.items() if n != "beta"), key=lambda s: s.offset)
+        cur = 0
+        for sg in segs:
+            end = (sg.offset + sg.numel + 3) // 4 * 4
+            if sg.offset > cur:  # alignment padding: harmless either way
+                ranges.append((cur, sg.offset - cur, True))
+            ranges.append((sg.offset, end - sg.offset, sg.name in keys))
+            cur = end
+        if cur < fl.beta_off:
+            ranges.append((cur, fl.beta_off - cur, True))
+        s_mask = 0
+        blocks = [("inf_net.f_mu_batchnorm", "running_mean"), ("inf_net.f_mu_batchnorm", "running_var"),
+                  ("inf_net.f_sigma_batchnorm", "running_mean"), ("inf_net.f_sigma_batchnorm", "running_var"),
+                  ("beta_batchnorm", "running_mean"), ("beta_batchnorm", "running_var")]
+        for i, (bn, st) in enumerate(blocks):
+            if f"{bn}.{st}" in keys:
+                s_mask |= 1 << i
+        return ranges, s_mask, ("beta" in keys)
+
+    def materialize(self) -> None:
+        """Makes this rank's fp32 parameters complete.  The overlapped aggregation keeps the fp32 master copy
+        of beta on the owner of each vocabulary range and ships only bf16 operand shadows; before anything
+        reads all of beta (state_dict, topics, checkpoints) the other ranges are fetched from their owners.
+        Collective: every rank calls it between steps."""
+        if self.world > 1 and self._overlap is not None and self._beta_master_partial:
+            self.arena.barrier()
+            self.aggregator.gather_beta()
+            self.arena.barrier()
+            self._beta_master_partial = False
+
     # ------------------------------------------------------------------------------------------
-    def step(self, bow: CsrBatch, x_ctx: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def step(self, bow: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *, after_backward=None) -> torch.Tensor:
         """One synchronous global step (local minibatch + aggregation).  Returns this client's summed
-        minibatch loss (device tensor)."""
+        minibatch loss (device tensor).  ``after_backward`` (verification hook): called between the local
+        backward pass and the closing aggregation launch; forces the eager (non-graph) path."""
         eng = self.model.engine
         self.global_step += 1
         if self.world == 1:
             return eng.train_step(bow, x_ctx)
         from ..ops import kernels as K_
 
+        if self._overlap is not None and self.agg == "grad":
+            self._beta_master_partial = True
+
         def body():
             if self.agg == "grad" and self._overlap is not None:
                 K_.step_begin(eng.ctr, 0, 1)  # epoch / Adam step t first: the overlapped part reads it too
                 eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], fed=self._overlap)
+                if after_backward is not None:
+                    after_backward()
                 self._launch("grad", eng.step_count + 1, parts=1)
             elif self.agg == "grad":
                 eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank])
+                if after_backward is not None:
+                    after_backward()
                 K_.step_begin(eng.ctr, 0, 1)
+                if not self.beta_shared:  # beta stays client-local: its own Adam on the unweighted gradient
+                    eng.optimizer_step_beta(gscale=1.0 / max(self.weights[self.rank], 1e-30))
                 self._launch("grad", eng.step_count + 1)
             else:
                 eng.forward_backward(bow, x_ctx, training=True)
                 eng.optimizer_step()
+                if after_backward is not None:
+                    after_backward()
                 self._launch("param", eng.step_count)
 
-        if not eng.use_graphs:
+        if not eng.use_graphs or after_backward is not None:
             body()
             if self.agg == "grad":
                 eng.step_count += 1
@@ -145,6 +215,13 @@ class FederatedTrainer:
         torch.cuda.synchronize()
         ev = self._agg_events[-64:]
         return 1e3 * sum(s.elapsed_time(e) for s, e in ev) / len(ev)
+
+    def describe_aggregation(self) -> Optional[dict]:
+        """What the per-step aggregation of this trainer consists of (for bench / log lines)."""
+        if self.world == 1 or self.aggregator is None:
+            return None
+        return {"mode": self.agg, "overlap_ctas": getattr(self._overlap, "ctas", 0),
+                "nvls_multicast": bool(self.aggregator.args.ranks[0].P_mc)}
 
     def working_set_bytes(self) -> int:
         eng = self.model.engine

@@ -33,6 +33,7 @@ class GfSweepArgs(C.Structure):
         ("theta_cols", _i), ("beta_cols", _i), ("ext_col0", _i),
         ("betaT_bf", _p), ("beta3", _p), ("ld_beta3", _i), ("ld_corr", _i),
         ("fed", _p), ("fed_ctas", _i),
+        ("fed_tmaps", _p), ("dbeta_bf", _p), ("ld_dbeta_bf", _i),
     ]
 
 
@@ -127,7 +128,17 @@ class GfFabricRank(C.Structure):
         ("beta_bf", _p * GF_MAX_RANKS), ("betaT_bf", _p * GF_MAX_RANKS), ("flags", _p * GF_MAX_RANKS),
         ("M", _p), ("V2", _p), ("done_counter", _p),
         ("P_mc", _p), ("S_mc", _p), ("beta_bf_mc", _p), ("betaT_bf_mc", _p),
+        ("Gb", _p * GF_MAX_RANKS), ("ld_gb", _i), ("agg_counter", _p),
     ]
+
+
+GF_FED_MAX_RANGES = 48
+GF_FED_FLAG_SLOTS = 8
+GF_FED_FLAG_BYTES = GF_FED_FLAG_SLOTS * GF_MAX_RANKS * 4
+
+
+class GfFedRange(C.Structure):
+    _fields_ = [("off", C.c_longlong), ("len", C.c_longlong), ("shared", _i), ("pad_", _i)]
 
 
 class GfFedArgs(C.Structure):
@@ -140,12 +151,15 @@ class GfFedArgs(C.Structure):
         ("step", _i),
         ("step_ctr", _p),
         ("parts", _i),
+        ("n_ranges", _i),
+        ("ranges", GfFedRange * GF_FED_MAX_RANGES),
+        ("s_mask", _i), ("beta_shared", _i), ("local_gscale", _f),
         ("ranks", GfFabricRank * GF_MAX_RANKS),
     ]
 
 
 _STRUCTS = [GfSweepArgs, GfEncArgs, GfLatentArgs, GfLatentBwdArgs, GfEncBwdArgs, GfDecSparseArgs,
-            GfFabricRank, GfFedArgs]
+            GfFabricRank, GfFedArgs, GfFedRange]
 
 LIB_PATH = Path(__file__).resolve().parent / "libgfedntm_kernels.so"
 _lib: Optional[C.CDLL] = None
@@ -177,6 +191,10 @@ def _declare(lib: C.CDLL) -> None:
         getattr(lib, fn).restype = _i
     lib.gf_fed_signal.argtypes = [C.POINTER(GfFedArgs), _i, _p]
     lib.gf_fed_signal.restype = _i
+    lib.gf_fed_make_tmaps.argtypes = [C.POINTER(GfFedArgs), _p]
+    lib.gf_fed_make_tmaps.restype = _i
+    lib.gf_fed_gather_beta.argtypes = [C.POINTER(GfFedArgs), _p]
+    lib.gf_fed_gather_beta.restype = _i
     lib.gf_dec_row_chunks_grid.argtypes = [_i, _i, _i]
     lib.gf_dec_row_chunks_grid.restype = _i
     lib.gf_num_sms.argtypes = []

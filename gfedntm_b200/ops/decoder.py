@@ -138,8 +138,9 @@ class ProdLDADecoder:
         """Runs the sweeps.  Returns (rl[B], dtheta[B,Kp] or None).  ``dbeta`` [K,ld] is overwritten.
 
         ``fed`` (folded formulation only): an object with ``signal_beta_ready()``, ``dev_args`` (device
-        pointer of the aggregation arguments) and ``ctas``; the beta part of the federated aggregation then
-        runs on ``ctas`` CTAs of the d-theta sweep, overlapped with it (see parallel/fabric.py)."""
+        pointer of the aggregation arguments), ``tmaps_ptr``, ``gb`` (bf16 buffer the beta gradient is
+        written to INSTEAD of ``dbeta``) and ``ctas``; the beta part of the federated aggregation then runs
+        on ``ctas`` CTAs of the d-theta sweep plus every sweep CTA that has finished (parallel/fabric.py)."""
         B, V, Kt = batch.B, self.V, self.K
         assert B <= self.max_B
         if not self.folded:
@@ -177,7 +178,8 @@ class ProdLDADecoder:
         K_.dec_sweep(K_.COL_GRAD2, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=self.beta_s,
                      colc=self.colc, asp=self.asp_csp[0], csp=self.asp_csp[1], dbeta=dbeta, corr=self.corrT,
                      colptr=csc.colptr, theta_cols=tcols, beta_cols=self.Vpad, ext_col0=self.ext_col0,
-                     betaT_bf=betaT_bf, beta3=self.beta3)
+                     betaT_bf=betaT_bf, beta3=self.beta3,
+                     dbeta_bf=fed.gb if fed is not None else None)  # federated exchange format: bf16
         K_.gram(self.beta3, beta_bf, self.gram_partial, V=V)
         K_.gram_finish(self.gram_partial, self.gram_parts, self.beta_s, K=Kt, col_hi=self.Vpad,
                        col_lo=self.Vpad + self.n_ext * TILE)
@@ -187,7 +189,7 @@ class ProdLDADecoder:
             n_chunks_g = K_.default_row_chunks(B, V, second_mma=True, Kp=self.Kp, grid=K_.num_sms() - fed.ctas)
             K_.dec_sweep(K_.ROW_GRAD2, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=self.beta_s,
                          n_chunks=n_chunks_g, dtheta=self.dtheta, theta_cols=tcols, beta_cols=bcols,
-                         ext_col0=self.Vpad, fed=fed.dev_args, fed_ctas=fed.ctas)
+                         ext_col0=self.Vpad, fed=fed.dev_args, fed_ctas=fed.ctas, fed_tmaps=fed.tmaps_ptr)
             return self.rl[:B], self.dtheta[:B]
         n_chunks_g = K_.default_row_chunks(B, V, second_mma=True, Kp=self.Kp)
         K_.dec_sweep(K_.ROW_GRAD2, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=self.beta_s,

@@ -68,7 +68,8 @@ def dec_sweep(mode: int, *, B: int, V: int, K: int, theta_bf: torch.Tensor, beta
               doc_const=None, dtheta=None, colc=None, theta_mean=None, running_mean=None, running_var=None,
               bn_eps: float = 1e-5, bn_momentum: float = 0.1, use_running: bool = False, asp=None,
               csp=None, dbeta=None, corr=None, colptr=None, theta_cols: int = 0, beta_cols: int = 0,
-              ext_col0: int = 0, betaT_bf=None, beta3=None, fed: int = 0, fed_ctas: int = 0) -> None:
+              ext_col0: int = 0, betaT_bf=None, beta3=None, fed: int = 0, fed_ctas: int = 0, fed_tmaps: int = 0,
+              dbeta_bf=None) -> None:
     lib = _lib.load()
     Kp = beta_bf.shape[0]
     assert theta_bf.dtype == torch.bfloat16 and beta_bf.dtype == torch.bfloat16
@@ -91,7 +92,9 @@ def dec_sweep(mode: int, *, B: int, V: int, K: int, theta_bf: torch.Tensor, beta
     a.betaT_bf, a.beta3 = _ptr(betaT_bf), _ptr(beta3)
     a.ld_beta3 = beta3.stride(0) if beta3 is not None else 0
     a.ld_corr = corr.stride(0) if corr is not None else 0
-    a.fed, a.fed_ctas = (fed or None), fed_ctas
+    a.fed, a.fed_ctas, a.fed_tmaps = (fed or None), fed_ctas, (fed_tmaps or None)
+    a.dbeta_bf = _ptr(dbeta_bf)
+    a.ld_dbeta_bf = dbeta_bf.stride(0) if dbeta_bf is not None else 0
     check(lib.gf_dec_sweep(C.byref(a), _stream()), "gf_dec_sweep")
 
 

@@ -22,7 +22,7 @@ from typing import Dict, List, Optional, Sequence
 import torch
 
 from ..ops import _lib
-from ..ops._lib import GF_MAX_RANKS, GfFedArgs, check
+from ..ops._lib import GF_FED_FLAG_BYTES, GF_FED_MAX_RANGES, GF_MAX_RANKS, GfFedArgs, check
 
 
 def _align(n: int, a: int = 256) -> int:
@@ -133,13 +133,18 @@ class EmulatedArena(_ArenaBase):
         torch.cuda.synchronize()
 
 
-FLAG_BYTES = 2 * GF_MAX_RANKS * 4
+FLAG_BYTES = GF_FED_FLAG_BYTES  # uint32 [GF_FED_FLAG_SLOTS][GF_MAX_RANKS] per rank (include/gfedntm_kernels.h)
 
 
 def fill_rank_ctx(ctx, arena, rank: int, *, M: torch.Tensor, V2: torch.Tensor, done_counter: torch.Tensor,
-                  has_shadows: bool) -> None:
-    """Peer pointer tables of one rank (names: P, G, S, beta_bf, betaT_bf, flags)."""
+                  has_shadows: bool, agg_counter: Optional[torch.Tensor] = None, ld_gb: int = 0) -> None:
+    """Peer pointer tables of one rank (names: P, G, S, beta_bf, betaT_bf, Gb, flags)."""
     ctx.rank = rank
+    has_gb = has_shadows and "Gb" in arena.offsets
+    for c in range(arena.world):
+        ctx.Gb[c] = arena.peer_ptr(c, "Gb") if has_gb else None
+    ctx.ld_gb = ld_gb if has_gb else 0
+    ctx.agg_counter = agg_counter.data_ptr() if agg_counter is not None else None
     for c in range(arena.world):
         ctx.G[c] = arena.peer_ptr(c, "G")
         ctx.P[c] = arena.peer_ptr(c, "P")
@@ -165,10 +170,33 @@ class FusedAggregator:
     """Launches ``gf_fed_aggregate`` for one rank (or for all emulated ranks at once)."""
 
     def __init__(self, *, world: int, weights: Sequence[float], flat_n: int, beta_off: int, s_n: int, K: int,
-                 V: int, Kp: int, ldb: int, lr: float, betas, eps: float = 1e-8, wd: float = 0.0) -> None:
+                 V: int, Kp: int, ldb: int, lr: float, betas, eps: float = 1e-8, wd: float = 0.0,
+                 ranges: Optional[Sequence[tuple]] = None, s_mask: int = 63, beta_shared: bool = True,
+                 local_gscale: float = 1.0) -> None:
+        """``ranges``: optional ``(offset, length, shared)`` pieces covering the flat region ``[0, flat_n)``
+        (grads_to_share of the reference, federated_model.py:98-131): unshared pieces stay client-local.
+        ``s_mask``: bit per BatchNorm statistics block; ``beta_shared``: whether beta takes part."""
         assert 1 <= world <= GF_MAX_RANKS
         self.args = GfFedArgs()
         a = self.args
+        a.n_ranges = 0
+        a.s_mask, a.beta_shared, a.local_gscale = int(s_mask), int(beta_shared), float(local_gscale)
+        if ranges is not None:
+            merged: List[list] = []
+            for off, ln, sh in ranges:
+                if ln <= 0:
+                    continue
+                assert off % 4 == 0 and ln % 4 == 0, "ranges must be 16-byte aligned"
+                if merged and merged[-1][2] == bool(sh) and merged[-1][0] + merged[-1][1] == off:
+                    merged[-1][1] += ln
+                else:
+                    merged.append([off, ln, bool(sh)])
+            all_shared = all(m[2] for m in merged) and (s_mask & 63) == 63 and beta_shared
+            if not all_shared:
+                assert len(merged) <= GF_FED_MAX_RANGES, "too many alternating shared / unshared segments"
+                a.n_ranges = len(merged)
+                for i, (off, ln, sh) in enumerate(merged):
+                    a.ranges[i].off, a.ranges[i].len, a.ranges[i].shared = off, ln, int(sh)
         a.world, a.flat_n, a.beta_off, a.s_n = world, flat_n, beta_off, s_n
         a.K, a.V, a.Kp, a.ldb = K, V, Kp, ldb
         for c in range(world):
@@ -178,12 +206,14 @@ class FusedAggregator:
         self.epoch = 0
         self._keep: List[torch.Tensor] = []
 
-    def add_rank(self, arena, rank: int, *, M, V2, has_shadows: bool) -> None:
+    def add_rank(self, arena, rank: int, *, M, V2, has_shadows: bool, ld_gb: int = 0) -> None:
         i = self.args.n_rank_ctx
-        done = torch.zeros(1, dtype=torch.int32, device=M.device)
+        done = torch.zeros(2, dtype=torch.int32, device=M.device)  # [0] launch-completion, [1] word-tile counter
         self._keep.append(done)
-        fill_rank_ctx(self.args.ranks[i], arena, rank, M=M, V2=V2, done_counter=done, has_shadows=has_shadows)
+        fill_rank_ctx(self.args.ranks[i], arena, rank, M=M, V2=V2, done_counter=done[0:1], has_shadows=has_shadows,
+                      agg_counter=done[1:2], ld_gb=ld_gb)
         self.args.n_rank_ctx = i + 1
+        self._arena = arena
 
     def set_lr(self, lr: float, betas) -> None:
         self.args.lr, self.args.b1, self.args.b2 = lr, betas[0], betas[1]
@@ -194,12 +224,24 @@ class FusedAggregator:
         step are read from ``step_ctr`` on the device) and returns the handle the decoder uses."""
         assert self.args.n_rank_ctx == 1, "the overlapped path runs one rank per process"
         a = self.args
+        assert a.ranks[0].Gb[0], "the arena has no bf16 gradient buffer (Gb)"
         a.mode, a.epoch, a.step, a.parts = 0, 0, 0, 2
         a.step_ctr = step_ctr.data_ptr()
         raw = bytes(memoryview(a).cast("B"))
         dev = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(step_ctr.device)
         self._keep.append(dev)
-        return BetaOverlap(self, dev, step_ctr, ctas)
+        # tensor maps of every rank's bf16 beta gradient (host memory: they travel as a kernel parameter)
+        tm = (C.c_ubyte * (128 * GF_MAX_RANKS + 64))()
+        tm_ptr = (C.addressof(tm) + 63) // 64 * 64
+        check(_lib.load().gf_fed_make_tmaps(C.byref(a), tm_ptr), "gf_fed_make_tmaps")
+        self._keep.append(tm)
+        gb = self._arena.tensor("Gb", torch.bfloat16).view(a.K, a.ranks[0].ld_gb)
+        return BetaOverlap(self, dev, step_ctr, ctas, tm_ptr, gb)
+
+    def gather_beta(self) -> None:
+        """Completes this rank's fp32 copy of beta from the owners' master slices (overlapped path)."""
+        check(_lib.load().gf_fed_gather_beta(C.byref(self.args), torch.cuda.current_stream().cuda_stream),
+              "gf_fed_gather_beta")
 
     def launch(self, *, mode: str, step: int, step_ctr=None, parts: int = 3) -> None:
         """``mode``: 'grad' (weighted gradients + global sharded Adam) or 'param' (weighted mean of the
@@ -223,9 +265,12 @@ class BetaOverlap:
 
     PHASE_BETA_READY = 2
 
-    def __init__(self, agg: FusedAggregator, dev_args: torch.Tensor, step_ctr: torch.Tensor, ctas: int) -> None:
+    def __init__(self, agg: FusedAggregator, dev_args: torch.Tensor, step_ctr: torch.Tensor, ctas: int,
+                 tmaps_ptr: int, gb: torch.Tensor) -> None:
         self.agg, self._dev, self.step_ctr, self.ctas = agg, dev_args, step_ctr, int(ctas)
         self.dev_args = dev_args.data_ptr()
+        self.tmaps_ptr = tmaps_ptr   # host pointer: GF_MAX_RANKS CUtensorMap (gf_fed_make_tmaps)
+        self.gb = gb                 # [K, ld_gb] bf16: this rank's beta gradient in the exchange format
 
     def signal_beta_ready(self) -> None:
         a = self.agg.args

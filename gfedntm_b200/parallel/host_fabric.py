@@ -9,6 +9,9 @@ Same decomposition as the kernel, with collectives as the transport instead of N
 * ``agg="param"``: weighted mean of the locally updated parameters (reference semantics,
   src/federation/server.py:477-487).
 * BatchNorm running statistics are averaged with the client weights in both modes.
+* ``shared`` (optional boolean mask over the flat space = ``grads_to_share`` of the reference,
+  federated_model.py:98-131): unshared elements stay client-local — their own Adam step on the client's
+  unweighted gradient in ``agg="grad"``, untouched by the averaging in ``agg="param"``.
 
 It exists so the *semantics* (slice ownership, sharded optimiser state, weighting) are testable without
 GPUs (``tests/test_cpu_multiproc.py``), and as a slow fallback data plane for hosts without peer access.
@@ -33,7 +36,7 @@ def owner_slice(n: int, world: int, rank: int, granule: int = 4) -> Tuple[int, i
 
 class HostAggregator:
     def __init__(self, n_params: int, weights: Sequence[float], *, lr: float, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 0.0, group=None) -> None:
+                 weight_decay: float = 0.0, group=None, shared: Optional[torch.Tensor] = None) -> None:
         import torch.distributed as dist
 
         self.group = group if group is not None else dist.group.WORLD
@@ -48,6 +51,21 @@ class HostAggregator:
         self.m = torch.zeros(self.hi - self.lo)
         self.v = torch.zeros(self.hi - self.lo)
         self.step = 0
+        self.shared = None
+        if shared is not None and not bool(shared.all()):
+            self.shared = shared.to(torch.bool).clone()
+            # client-local optimiser state of the unshared elements (full length, used where ~shared)
+            self.m_loc = torch.zeros(self.n)
+            self.v_loc = torch.zeros(self.n)
+
+    def _adam(self, p, g, m, v):
+        if self.wd != 0.0:
+            g = g + self.wd * p
+        m.mul_(self.b1).add_(g, alpha=1.0 - self.b1)
+        v.mul_(self.b2).addcmul_(g, g, value=1.0 - self.b2)
+        bc1 = 1.0 - self.b1 ** self.step
+        bc2 = 1.0 - self.b2 ** self.step
+        return p - (self.lr / bc1) * (m / (v.sqrt() / math.sqrt(bc2) + self.eps))
 
     # ------------------------------------------------------------------------------------------
     def _all_gather_slices(self, flat: torch.Tensor, mine: torch.Tensor) -> None:
@@ -74,17 +92,13 @@ class HostAggregator:
         g = weighted_grad.clone()
         dist.all_reduce(g, group=self.group)  # transport of the reduce-scatter; only [lo, hi) is used below
         self.step += 1
-        gs = g[self.lo:self.hi]
-        p = params[self.lo:self.hi].clone()
-        if self.wd != 0.0:
-            gs = gs + self.wd * p
-        self.m.mul_(self.b1).add_(gs, alpha=1.0 - self.b1)
-        self.v.mul_(self.b2).addcmul_(gs, gs, value=1.0 - self.b2)
-        bc1 = 1.0 - self.b1 ** self.step
-        bc2 = 1.0 - self.b2 ** self.step
-        denom = self.v.sqrt() / math.sqrt(bc2) + self.eps
-        p = p - (self.lr / bc1) * (self.m / denom)
+        local_new = None
+        if self.shared is not None:  # client-local step on the unweighted own gradient
+            local_new = self._adam(params.clone(), weighted_grad / self.weights[self.rank], self.m_loc, self.v_loc)
+        p = self._adam(params[self.lo:self.hi].clone(), g[self.lo:self.hi], self.m, self.v)
         self._all_gather_slices(params, p)
+        if local_new is not None:
+            params[~self.shared] = local_new[~self.shared]
         if stats is not None:
             self._average_stats(stats)
 
@@ -93,7 +107,10 @@ class HostAggregator:
 
         w = params * self.weights[self.rank]
         dist.all_reduce(w, group=self.group)
-        params.copy_(w)
+        if self.shared is not None:
+            params[self.shared] = w[self.shared]
+        else:
+            params.copy_(w)
         if stats is not None:
             self._average_stats(stats)
 

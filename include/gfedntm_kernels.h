@@ -85,10 +85,18 @@ typedef struct GfSweepArgs {
   int ld_corr;           /* COL_GRAD2: corr is TRANSPOSED, [Kp, ld_corr] (gf_csc_corr_t)                */
   const void* fed;       /* ROW_GRAD2: DEVICE copy of a GfFedArgs (n_rank_ctx 1, step_ctr set) or null.  The
                             last fed_ctas CTAs of the grid then wait for every peer's
-                            GF_FED_PHASE_BETA_READY flag and run the beta part of the aggregation (P2P
-                            reduce + Adam + P2P pushes) while the other CTAs do the sweep; finish the step
-                            with gf_fed_aggregate(parts = 1).                                            */
+                            GF_FED_PHASE_BETA_READY flag and run the beta part of the aggregation (TMA
+                            pulls of the peers' bf16 gradient tiles + sharded Adam + pushes of the bf16
+                            operand shadows) while the other CTAs do the sweep; a sweep CTA that runs out
+                            of sweep work joins them (word tiles are handed out by an atomic counter).
+                            Finish the step with gf_fed_aggregate(parts = 1).                            */
   int fed_ctas;
+  const void* fed_tmaps; /* ROW_GRAD2 with fed: HOST pointer to the GF_MAX_RANKS tensor maps written by
+                            gf_fed_make_tmaps (one per rank's bf16 beta gradient; passed to the kernel as
+                            a parameter).  They cover plain (non-multicast) loads of peer memory.        */
+  void* dbeta_bf;        /* COL_GRAD2: when non-null the beta gradient is written as bf16 [K, ld_dbeta_bf]
+                            here INSTEAD of fp32 `dbeta` (the federated exchange format)                 */
+  int ld_dbeta_bf;
 } GfSweepArgs;
 
 int gf_dec_sweep(const GfSweepArgs* args, void* stream);
@@ -315,14 +323,30 @@ typedef struct GfFabricRank {
   float* S[GF_MAX_RANKS];         /* flat BatchNorm running statistics of every rank            */
   void* beta_bf[GF_MAX_RANKS];    /* bf16 [Kp, ldb] shadow of every rank (may be null)          */
   void* betaT_bf[GF_MAX_RANKS];   /* bf16 [V, Kp] shadow of every rank (may be null)            */
-  uint32_t* flags[GF_MAX_RANKS];  /* flag array of every rank: uint32 [4][GF_MAX_RANKS], zeroed once:
-                                     slot 0 gradients ready, 1 pushes done, 2 beta gradient ready      */
+  uint32_t* flags[GF_MAX_RANKS];  /* flag array of every rank: uint32 [GF_FED_FLAG_SLOTS][GF_MAX_RANKS]
+                                     (GF_FED_FLAG_BYTES), zeroed once: slot 0 gradients ready, 1 pushes
+                                     done, 2 beta gradient ready                                      */
   float* M; float* V2;            /* this rank's Adam moments (same indexing as P)              */
   unsigned int* done_counter;     /* this rank, zeroed once                                     */
   /* Optional NVLS multicast aliases of the same buffers (one multimem.st reaches every rank, the
      NVSwitch replicates it); null => one P2P store per rank.                                    */
   float* P_mc; float* S_mc; void* beta_bf_mc; void* betaT_bf_mc;
+  /* Overlapped beta aggregation (GF_ROW_GRAD2 with `fed`): every rank's beta gradient as bf16
+     [K, ld_gb] (written by GF_COL_GRAD2 via dbeta_bf) and this rank's word-tile counter.        */
+  void* Gb[GF_MAX_RANKS];
+  int ld_gb;
+  unsigned int* agg_counter;      /* this rank, reset by gf_fed_signal(GF_FED_PHASE_BETA_READY)  */
 } GfFabricRank;
+
+/* A contiguous range of the flat parameter space [0, flat_n) with its sharing rule (grads_to_share of
+ * the reference, federated_model.py:98-131): shared ranges are aggregated, the others stay client-local
+ * (mode 0: local Adam on the client's own unweighted gradient; mode 1: untouched).               */
+#define GF_FED_MAX_RANGES 48
+typedef struct GfFedRange {
+  long long off, len;             /* floats, both multiples of 4                                */
+  int shared;
+  int pad_;
+} GfFedRange;
 
 typedef struct GfFedArgs {
   int world;                      /* number of federated clients (ranks)                        */
@@ -339,14 +363,34 @@ typedef struct GfFedArgs {
   const long long* step_ctr;      /* optional device counters: epoch = step = step_ctr[1]       */
   int parts;                      /* 0 or 3 = everything; bit 0 = flat region + BatchNorm statistics, bit 1 =
                                      beta (which GF_ROW_GRAD2 can run on spare CTAs, see GfSweepArgs.fed) */
+  /* Subset sharing.  n_ranges = 0: all of [0, flat_n), every BatchNorm statistic and beta are shared.  */
+  int n_ranges;
+  GfFedRange ranges[GF_FED_MAX_RANGES];
+  int s_mask;                     /* bit i: block i of the statistics buffer is shared; blocks are
+                                     {mu mean, mu var, sigma mean, sigma var}[K] then {beta mean, beta var}[V] */
+  int beta_shared;                /* 0: beta stays local (the caller runs its own optimiser on it)        */
+  float local_gscale;             /* mode 0, unshared ranges: gradient scale of the local Adam (1 / w[rank],
+                                     undoing the client weight folded into the backward pass)             */
   GfFabricRank ranks[GF_MAX_RANKS];
 } GfFedArgs;
 
 /* One call per rank and step, on every rank of the federation, with the same `epoch`.          */
 int gf_fed_aggregate(const GfFedArgs* args, void* stream);
-/* Raise flag slot `phase` (>= 2) of this rank on every peer with the current epoch.             */
+/* Raise flag slot `phase` (2 <= phase < GF_FED_FLAG_SLOTS) of this rank on every peer with the current
+ * epoch.  GF_FED_PHASE_BETA_READY also resets this rank's word-tile counter (ranks[0].agg_counter).   */
 int gf_fed_signal(const GfFedArgs* args, int phase, void* stream);
 #define GF_FED_PHASE_BETA_READY 2
+#define GF_FED_FLAG_SLOTS 8
+#define GF_FED_FLAG_BYTES (GF_FED_FLAG_SLOTS * GF_MAX_RANKS * 4)
+/* Writes GF_MAX_RANKS CUtensorMap (128 bytes each, 64-byte aligned HOST buffer) describing every rank's
+ * bf16 beta gradient ranks[0].Gb[c] as [K, ld_gb] with 32-topic x 128-word boxes (entries of absent ranks
+ * are zeroed).  The maps are used for plain TMA loads; they are never used with cluster multicast.   */
+int gf_fed_make_tmaps(const GfFedArgs* args, void* out_tmaps_host);
+/* Overlapped aggregation keeps the fp32 master copy of beta on the owner of each word-tile range only;
+ * this copies every range this rank does not own from its owner's parameter buffer (P2P loads) so that
+ * state_dict() / checkpoints see the complete tensor.  Collective in spirit: every rank must be between
+ * steps (host barrier before and after).                                                             */
+int gf_fed_gather_beta(const GfFedArgs* args, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Host-side data loader helpers (no device code).

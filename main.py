@@ -157,7 +157,8 @@ def main(argv=None):
         return run_fabric_federation(n_clients=args.fabric, source=args.source, data_type=args.data_type,
                                      fos=args.fos, model_type=args.model_type, training_params=training_params,
                                      max_iters=args.max_iters, save_client=save_client, save_server=save_server,
-                                     logs_client=logs_client, agg="grad" if agg == "grad" else "param")
+                                     logs_client=logs_client, agg="grad" if agg == "grad" else "param",
+                                     grads_to_share=grads_to_share)
     if args.id == 0:
         print("Starting server with", args.min_clients_federation,
               "as minimum number of clients to start the federation.")

@@ -103,3 +103,68 @@ def test_host_fabric_matches_single_process_adam():
     torch.testing.assert_close(p0, ref.detach(), rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(s0, torch.full((8,), 0.25 * 1 + 0.75 * 2))
     torch.testing.assert_close(pm0, torch.full((n,), 0.25 * 1 + 0.75 * 2))
+
+
+def _subset_worker(rank, world, port, out):
+    import torch
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from gfedntm_b200.parallel.host_fabric import HostAggregator
+
+    n, weights = 64, [0.25, 0.75]
+    shared = torch.zeros(n, dtype=torch.bool)
+    shared[16:40] = True
+    params = torch.randn(n, generator=torch.Generator().manual_seed(0))
+    agg = HostAggregator(n, weights, lr=1e-2, betas=(0.9, 0.99), shared=shared)
+    for step in range(2):
+        gl = torch.randn(n, generator=torch.Generator().manual_seed(10 * step + rank))
+        agg.aggregate_grad(params, gl * weights[rank])
+    pm = torch.full((n,), float(rank + 1))
+    agg.aggregate_param(pm)
+    out.put((rank, params, pm))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_host_fabric_subset_sharing_keeps_unshared_tensors_local():
+    """grads_to_share subset (federated_model.py:98-131): shared elements follow the global Adam on the weighted
+    gradient sum, unshared ones the client's own Adam on its own gradient; parameter mode averages the shared
+    elements only."""
+    import torch
+
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_subset_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(2)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, p0, pm0), (_, p1, pm1) = res
+    n, weights = 64, [0.25, 0.75]
+    shared = torch.zeros(n, dtype=torch.bool)
+    shared[16:40] = True
+    assert torch.equal(p0[shared], p1[shared]) and not torch.equal(p0[~shared], p1[~shared])
+    init = torch.randn(n, generator=torch.Generator().manual_seed(0))
+    refs = []
+    for who in ("global", 0, 1):
+        ref = init.clone().requires_grad_(True)
+        opt = torch.optim.Adam([ref], lr=1e-2, betas=(0.9, 0.99))
+        for step in range(2):
+            gs = [torch.randn(n, generator=torch.Generator().manual_seed(10 * step + r)) for r in range(2)]
+            ref.grad = sum(weights[r] * gs[r] for r in range(2)) if who == "global" else gs[who]
+            opt.step()
+        refs.append(ref.detach())
+    torch.testing.assert_close(p0[shared], refs[0][shared], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(p0[~shared], refs[1][~shared], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(p1[~shared], refs[2][~shared], rtol=1e-5, atol=1e-6)
+    assert torch.equal(pm0[shared], torch.full((24,), 1.75)) and torch.equal(pm0[~shared], torch.full((40,), 1.0))
+    assert torch.equal(pm1[~shared], torch.full((40,), 2.0))

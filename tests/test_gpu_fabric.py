@@ -8,7 +8,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def _setup(world, model_type="prodLDA", V=700, K=12, B=48):
+def _setup(world, model_type="prodLDA", V=700, K=12, B=48, share=None):
     from gfedntm_b200.engine.fused import FusedEngine
     from gfedntm_b200.models.networks import DecoderNetwork
     from gfedntm_b200.ops.decoder import CsrBatch
@@ -33,10 +33,17 @@ def _setup(world, model_type="prodLDA", V=700, K=12, B=48):
     tot = sum(weights)
     weights = [w / tot for w in weights]
     fl = engines[0].flat
+    ranges, s_mask, beta_shared = None, 63, True
+    if share is not None:
+        from gfedntm_b200.federated.trainer import FederatedTrainer
+
+        planner = FederatedTrainer.__new__(FederatedTrainer)
+        planner.grads_to_share = list(share)
+        ranges, s_mask, beta_shared = planner._share_plan(fl)
     agg = FusedAggregator(world=world, weights=weights, flat_n=fl.beta_off, beta_off=fl.beta_off, s_n=fl.s_n,
                           K=K, V=V, Kp=engines[0].Kp,
                           ldb=engines[0].beta_bf.stride(0) if engines[0].is_prod else 0, lr=2e-3,
-                          betas=(0.99, 0.99))
+                          betas=(0.99, 0.99), ranges=ranges, s_mask=s_mask, beta_shared=beta_shared)
     for r, eng in enumerate(engines):
         agg.add_rank(arena.view_as(r) if r else arena, r, M=eng.flat.M, V2=eng.flat.V2, has_shadows=eng.is_prod)
     return engines, batches, weights, agg
@@ -85,3 +92,61 @@ def test_fused_param_aggregation_matches_weighted_mean():
         for eng in engines:
             for n in names:
                 torch.testing.assert_close(eng.flat.view(eng.flat.P, n), want[n], rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize("mode", ["grad", "param"])
+def test_subset_sharing_keeps_unshared_tensors_local(mode):
+    """grads_to_share subset (reference: federated_model.py:98-131, server default server.py:71): shared tensors
+    follow the global update, every other tensor the client's own optimiser; only shared BatchNorm statistics are
+    averaged."""
+    world = 2
+    share = ["prior_mean", "prior_variance", "beta", "inf_net.f_mu.weight", "beta_batchnorm.running_var"]
+    engines, batches, weights, agg = _setup(world, share=share)
+    names = [n for n, _ in engines[0].model.named_parameters()]
+    init = {n: engines[0].flat.view(engines[0].flat.P, n).detach().clone() for n in names}
+    # oracles: one global Adam (shared tensors) + one private Adam per client (unshared tensors)
+    glob = {n: init[n].clone().requires_grad_(True) for n in names}
+    gopt = torch.optim.Adam([glob[n] for n in names], lr=2e-3, betas=(0.99, 0.99))
+    loc = [{n: init[n].clone().requires_grad_(True) for n in names} for _ in range(world)]
+    lopt = [torch.optim.Adam([l[n] for n in names], lr=2e-3, betas=(0.99, 0.99)) for l in loc]
+    for step in range(1, 3):
+        if mode == "grad":
+            for r, eng in enumerate(engines):
+                agg.args.local_gscale = 1.0  # emulation: one argument block for every rank -> unit weights below
+                eng.forward_backward(batches[r], training=True, gscale=1.0)
+            g = [{n: e.flat.view(e.flat.G, n).detach().clone() for n in names} for e in engines]
+            s_before = [e.flat.S.detach().clone() for e in engines]
+            agg.launch(mode="grad", step=step)
+            torch.cuda.synchronize()
+            for n in names:
+                glob[n].grad = sum(gr[n] for gr in g)
+            gopt.step()
+            for r in range(world):
+                for n in names:
+                    loc[r][n].grad = g[r][n]
+                lopt[r].step()
+            for r, eng in enumerate(engines):
+                for n in names:
+                    want = glob[n] if n in share else loc[r][n]
+                    torch.testing.assert_close(eng.flat.view(eng.flat.P, n), want.detach(), rtol=3e-4, atol=3e-6,
+                                               msg=lambda m: f"rank {r} {n} step {step}: {m}")
+                eng.step_count = step
+        else:
+            for r, eng in enumerate(engines):
+                eng.forward_backward(batches[r], training=True)
+                eng.optimizer_step()
+            mine = [{n: e.flat.view(e.flat.P, n).detach().clone() for n in names} for e in engines]
+            s_before = [e.flat.S.detach().clone() for e in engines]
+            agg.launch(mode="param", step=step)
+            torch.cuda.synchronize()
+            for r, eng in enumerate(engines):
+                for n in names:
+                    want = sum(w * m[n] for w, m in zip(weights, mine)) if n in share else mine[r][n]
+                    torch.testing.assert_close(eng.flat.view(eng.flat.P, n), want, rtol=1e-5, atol=1e-7)
+        K, V = engines[0].K, engines[0].V
+        s_mean = sum(w * s for w, s in zip(weights, s_before))
+        for r, eng in enumerate(engines):
+            # only beta_batchnorm.running_var (last block) is shared
+            torch.testing.assert_close(eng.flat.S[4 * K + V:4 * K + 2 * V], s_mean[4 * K + V:4 * K + 2 * V],
+                                       rtol=1e-5, atol=1e-6)
+            torch.testing.assert_close(eng.flat.S[:4 * K + V], s_before[r][:4 * K + V], rtol=0, atol=0)

@@ -10,17 +10,23 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("agg,folded", [("grad", False), ("param", False), ("grad", True)])
-def test_fused_aggregation_across_gpus(agg, folded):
+SUBSET = "prior_mean,prior_variance,beta"  # the reference server's default grads_to_share (server.py:71)
+
+
+@pytest.mark.parametrize("agg,folded,share", [("grad", False, ""), ("param", False, ""), ("grad", True, ""),
+                                              ("grad", False, SUBSET), ("param", False, SUBSET),
+                                              ("grad", True, SUBSET)])
+def test_fused_aggregation_across_gpus(agg, folded, share):
     """``folded=True`` forces the folded decoder, which turns on the overlapped beta aggregation (spare CTAs of
     the d-theta sweep) in grad mode; the check against the NCCL + torch.Adam oracle is the same."""
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs at least 2 GPUs")
     world = 2 if n < 4 else (4 if n < 8 else 8)
-    port = 29600 + (os.getpid() % 300) + (0 if agg == "grad" else 1) + (2 if folded else 0)
+    port = 29600 + (os.getpid() % 300) + (0 if agg == "grad" else 1) + (2 if folded else 0) + (4 if share else 0)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
-           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mp_fed_check.py"), agg]
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mp_fed_check.py"), agg,
+           share]
     env = dict(os.environ, GFEDNTM_DECODER_V1="0" if folded else "1")
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
