@@ -151,6 +151,12 @@ class _Ctx:
         torch.cuda.synchronize()
 
 
+def _trace(ctx, msg: str) -> None:
+    """Progress lines on stderr (GFEDNTM_BENCH_TRACE=1): where a multi-rank run is when it stalls."""
+    if os.environ.get("GFEDNTM_BENCH_TRACE", "0") == "1":
+        print(f"[bench r{ctx.rank} {time.strftime('%H:%M:%S')}] {msg}", file=sys.stderr, flush=True)
+
+
 def build_trainer(ctx: _Ctx, cfg: dict, agg: str):
     from gfedntm_b200.federated.trainer import FederatedTrainer
     from gfedntm_b200.models import AVITM, CTM, BOWDataset, CTMDataset
@@ -198,10 +204,15 @@ def measure_ours(ctx: _Ctx, cfg: dict, steps: int, warmup: int, agg: str, sample
 
     # untimed: the engine captures one CUDA graph per input buffer set (eager warm-up + capture call),
     # so every staged minibatch is visited twice before the W warm-up steps proper
+    _trace(ctx, "trainer built, warm-up")
     for i in range(2 * len(staged) + warmup):
         bow, xc = staged[i % len(staged)]
         trainer.step(bow, xc)
+        if i < 3:
+            torch.cuda.synchronize()
+            _trace(ctx, f"warm-up step {i} done")
     ctx.barrier()
+    _trace(ctx, "timed region")
     if sampler is not None and ctx.rank == 0:
         sampler.start()
     launches0 = lib.gf_launch_count() + eng.replayed_launches
@@ -226,6 +237,7 @@ def measure_ours(ctx: _Ctx, cfg: dict, steps: int, warmup: int, agg: str, sample
     else:
         ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
     ms = allreduce_max(ms, world, device)
+    _trace(ctx, f"device-timed {ms / steps:.3f} ms/step; end-to-end loop")
 
     # ---- end to end through the public API: host assembly + pinned H2D + step + loss D2H.  The loss of
     # step i is copied to pinned host memory right behind the step and read by the host while step i+1
@@ -264,6 +276,7 @@ def measure_ours(ctx: _Ctx, cfg: dict, steps: int, warmup: int, agg: str, sample
     ctx.barrier()
     e2e_s = allreduce_max(time.perf_counter() - t0, world, device)
     assert loss_sum == loss_sum, "NaN loss in the end-to-end loop"
+    it.close()  # stops the loader's staging thread and releases its slots (verification iterates again)
 
     docs = world * B * steps
     out = {"value": docs / (ms / 1e3), "ms_per_step": ms / steps, "steps": steps,
@@ -276,6 +289,7 @@ def measure_ours(ctx: _Ctx, cfg: dict, steps: int, warmup: int, agg: str, sample
            "global_batch": world * B}
     if world > 1:
         out["aggregation"] = trainer.describe_aggregation()
+        _trace(ctx, "verification")
         if verify:
             from gfedntm_b200.federated.verify import verify_against_oracle
 
@@ -283,6 +297,7 @@ def measure_ours(ctx: _Ctx, cfg: dict, steps: int, warmup: int, agg: str, sample
         # exposed cost of the aggregation = federated step - the same step trained locally (N=1 path:
         # local fused Adam instead of the NVLink aggregation).  Runs last: it lets the ranks diverge.
         ctx.barrier()
+        _trace(ctx, "local steps")
         for i in range(2 * len(staged) + 3):
             eng.train_step(*staged[i % len(staged)])
         ctx.barrier()

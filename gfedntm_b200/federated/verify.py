@@ -108,6 +108,8 @@ def verify_against_oracle(trainer, loader, steps: int = 2) -> Dict[str, object]:
         s_err = float((eng.flat.S - grabbed["__S"]).abs().max()) / max(float(grabbed["__S"].abs().max()), 1e-30)
         worst = max(worst, s_err)
         identical = identical and ranks_identical(trainer)
+    if hasattr(it, "close"):
+        it.close()
     t = torch.tensor([worst], dtype=torch.float64, device=eng.device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
     return {"ranks_identical": bool(identical), "oracle_max_rel_err": float(t.item()), "oracle_steps": steps}

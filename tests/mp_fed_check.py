@@ -50,6 +50,7 @@ def main():
         loss = tr.step(mb.bow, None)
         losses.append(float(loss.item()) / mb.size)
     torch.cuda.synchronize()
+    it.close()
     if share is None:
         res = verify_against_oracle(tr, loader, steps=3)
         if not res["ranks_identical"]:
@@ -66,7 +67,8 @@ def main():
     else:
         # subset sharing: shared tensors identical on every rank, unshared ones must have diverged
         tr.materialize()
-        sd = {k: v.detach().clone() for k, v in model.model.state_dict().items() if v.dtype.is_floating_point}
+        sd = {k: v.detach().clone().contiguous() for k, v in model.model.state_dict().items()
+              if v.dtype.is_floating_point}
         res = {"oracle_max_rel_err": float("nan")}
         for k, v in sd.items():
             ref = v.clone()
