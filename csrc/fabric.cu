@@ -63,11 +63,13 @@ __global__ void __launch_bounds__(256) fed_aggregate_kernel(const GfFedArgs a, A
     for (int ri = 0; ri < n_ranges; ++ri) {
       const long long r_off = a.n_ranges > 0 ? a.ranges[ri].off : 0;
       const long long r_len = a.n_ranges > 0 ? a.ranges[ri].len : a.flat_n;
-      const bool shared = a.n_ranges > 0 ? (a.ranges[ri].shared != 0) : true;
+      const int kind = a.n_ranges > 0 ? a.ranges[ri].shared : 1;
+      // kind 2 (replicated): G already holds the global gradient on every rank -> the same local Adam everywhere
+      const bool shared = (kind == 1) || (kind >= 2 && a.mode != 0);
       const long long n4 = (r_len + 3) / 4;
       if (!shared) {
-        if (a.mode != 0) continue;
-        const float gs = a.local_gscale;
+        if (a.mode != 0 || kind == 3) continue;  // kind 3: the caller applies the (replicated) update itself
+        const float gs = (kind == 2) ? 1.0f : a.local_gscale;
         for (long long q = tid; q < n4; q += nthr) {
           const long long i = r_off + q * 4;
           float4 g = *reinterpret_cast<const float4*>(me.G[rank] + i);
@@ -188,6 +190,44 @@ __global__ void fed_signal_kernel(const GfFedArgs a, int phase) {
   }
 }
 
+// One-shot small all-reduce: push x into my slot on every rank, flag, wait, sum the slots in rank order.
+__global__ void __launch_bounds__(256) fed_allreduce_small_kernel(const GfFedArgs a, float* __restrict__ x, long long n) {
+  __shared__ int is_last;
+  const GfFabricRank& me = a.ranks[0];
+  const int world = a.world, rank = me.rank;
+  uint32_t epoch = (uint32_t)a.epoch;
+  if (a.step_ctr != nullptr) epoch = (uint32_t)a.step_ctr[1];
+  const long long n4 = n / 4;
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+  for (long long q = tid; q < n4; q += nthr) {
+    const float4 v = *reinterpret_cast<const float4*>(x + q * 4);
+    for (int c = 0; c < world; ++c) st_peer_f4(me.AR[c] + (long long)rank * me.ar_cap + q * 4, v);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(me.done_counter, 1u);
+    is_last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last) {
+    if (threadIdx.x == 0) *me.done_counter = 0;
+    if (threadIdx.x < (unsigned)world) {
+      __threadfence_system();
+      st_release_sys(me.flags[threadIdx.x] + GF_FED_PHASE_SMALL_AR * GF_MAX_RANKS + rank, epoch);
+    }
+  }
+  wait_peers(me, world, GF_FED_PHASE_SMALL_AR, epoch);
+  for (long long q = tid; q < n4; q += nthr) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int c = 0; c < world; ++c) {
+      const float4 v = ld_peer_f4(me.AR[rank] + (long long)c * me.ar_cap + q * 4);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    *reinterpret_cast<float4*>(x + q * 4) = acc;
+  }
+}
+
 // Collects the fp32 master copy of beta: every word-tile range this rank does not own is read from its
 // owner (the overlapped aggregation updates the master copy on the owner only).
 __global__ void __launch_bounds__(256) fed_gather_beta_kernel(const GfFedArgs a) {
@@ -243,6 +283,21 @@ extern "C" int gf_fed_make_tmaps(const GfFedArgs* a, void* out_) {
       return GF_ERR_DRIVER;
     }
   }
+  return GF_OK;
+}
+
+extern "C" int gf_fed_allreduce_small(const GfFedArgs* a, float* x, long long n, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(a->world >= 1 && a->world <= GF_MAX_RANKS && a->n_rank_ctx == 1, "world / n_rank_ctx");
+  const GfFabricRank& me = a->ranks[0];
+  GF_ARG_CHECK(n > 0 && n % 4 == 0 && n <= me.ar_cap && me.AR[0] != nullptr && me.ar_cap % 4 == 0,
+               "n must be a multiple of 4 and fit the staging area");
+  GF_ARG_CHECK((reinterpret_cast<uintptr_t>(x) & 15) == 0, "x must be 16-byte aligned");
+  if (a->world == 1) return GF_OK;
+  long long blocks = (n / 4 + 255) / 256;
+  if (blocks > 64) blocks = 64;  // every block waits on the peers' flags: all of them must be co-resident
+  fed_allreduce_small_kernel<<<(int)blocks, 256, 0, st>>>(*a, x, n);
+  GF_LAUNCHED();
   return GF_OK;
 }
 

@@ -78,6 +78,10 @@ class FlatParams:
                 if getattr(arena, "world", 1) > 1:
                     # beta gradient in the federated exchange format (bf16 [K, ldb]), pulled by the owners
                     arena.reserve("Gb", 2 * K * ldb)
+            if getattr(arena, "world", 1) > 1 and getattr(model, "infnet", "") == "combined":
+                # staging area of the small all-reduce of CombinedTM's collapsed-weight gradient
+                self.ar_cap = ((model.contextual_size + 1) * model.hidden_sizes[0] + 3) // 4 * 4
+                arena.reserve("AR", 4 * self.ar_cap * arena.world)
             arena.commit(device)
         self.arena = arena
         self.P = arena.tensor("P", torch.float32)
@@ -177,9 +181,28 @@ class FusedEngine:
         self.dlv = torch.zeros(B, K, **f32)
         self.dpre0 = torch.zeros(B, self.hidden[0], **f32)
         # buffers that must start at zero every step, zeroed with one memset each
-        self.zpool = torch.zeros(4 * K + K, **f32)
+        n_dm = K_.round_up((self.C + 1) * self.hidden[0], 4) if self.kind == "combined" else 0
+        off_dm = K_.round_up(5 * K, 4)  # 16-byte aligned: the federated small all-reduce moves float4
+        self.zpool = torch.zeros(off_dm + n_dm, **f32)
         self.bn_bsums = self.zpool[:4 * K]
         self.theta_colsum = self.zpool[4 * K:5 * K]
+        if self.kind == "combined":
+            # Collapsed adapt_bert layer (csrc/ctm_gemm.cu): bf16 hi/lo shadows of A' = [adapt_bert.weight |
+            # adapt_bert.bias] and of W = input_layer.weight[:, V:2V]^T, the collapsed weight M'^T (+ effective
+            # bias in its last row) and the gradient wrt it (+ d b1 in its last row).
+            C_, H0 = self.C, self.hidden[0]
+            self.ctm_Cp = K_.round_up(C_ + 1, 64)
+            self.ctm_Np = K_.round_up(H0, 64)
+            bf = dict(dtype=torch.bfloat16, device=dev)
+            self.ctm_a_hi = torch.zeros(V, self.ctm_Cp, **bf)
+            self.ctm_a_lo = torch.zeros(V, self.ctm_Cp, **bf)
+            self.ctm_w_hi = torch.zeros(V, self.ctm_Np, **bf)
+            self.ctm_w_lo = torch.zeros(V, self.ctm_Np, **bf)
+            self.ctm_d_hi = torch.zeros(C_ + 1, self.ctm_Np, **bf)
+            self.ctm_d_lo = torch.zeros(C_ + 1, self.ctm_Np, **bf)
+            self.ctm_MTx = torch.zeros(C_ + 1, H0, **f32)
+            self.ctm_dM_flat = self.zpool[off_dm:off_dm + n_dm]           # (padded to a multiple of 4 floats)
+            self.ctm_dMx = self.ctm_dM_flat[:(C_ + 1) * H0].view(C_ + 1, H0)
         self.dpool = torch.zeros(4 * K + 1, dtype=torch.float64, device=dev)
         self.bn_sums = self.dpool[:4 * K]
         self.loss = self.dpool[4 * K:]
@@ -236,6 +259,41 @@ class FusedEngine:
         (load_state_dict, federated parameter averaging)."""
         if self.is_prod:
             refresh_beta_shadows(self._p("beta"), self.beta_bf, self.betaT_bf)
+        self._refresh_ctm_shadows()
+
+    def _refresh_ctm_shadows(self) -> None:
+        """bf16 hi/lo operand shadows of the CombinedTM adapt_bert layer and of the contextual half of the first
+        layer (rebuilt after every optimiser step / parameter load)."""
+        if self.kind != "combined":
+            return
+        self.ctm_adam_step(do_update=False)
+
+    def ctm_adam_step(self, gscale: float = 1.0, do_update: bool = True) -> None:
+        """Adam on adapt_bert.{weight,bias} and on the contextual half of the first layer, fused with the refresh of
+        their bf16 hi/lo operand shadows (``do_update=False``: shadows only).  The caller advanced the step counter."""
+        fl, V = self.flat, self.V
+        b1, b2 = self.betas
+        kw = dict(lr=self.lr, b1=b1, b2=b2, eps=self.adam_eps, wd=self.weight_decay, step=max(self.step_count, 1),
+                  gscale=gscale, do_update=do_update, step_ctr=self.ctr if do_update else None)
+        A, ab = "inf_net.adapt_bert.weight", "inf_net.adapt_bert.bias"
+        K_.adam_split(fl.view(fl.P, A), fl.view(fl.G, A), fl.view(fl.M, A), fl.view(fl.V2, A), self.ctm_a_hi,
+                      self.ctm_a_lo, p_col=fl.view(fl.P, ab), g_col=fl.view(fl.G, ab), m_col=fl.view(fl.M, ab),
+                      v_col=fl.view(fl.V2, ab), **kw)
+        W = "inf_net.input_layer.weight"
+        K_.adam_split(fl.storage_view(fl.P, W)[V:2 * V], fl.storage_view(fl.G, W)[V:2 * V],
+                      fl.storage_view(fl.M, W)[V:2 * V], fl.storage_view(fl.V2, W)[V:2 * V], self.ctm_w_hi,
+                      self.ctm_w_lo, **kw)
+
+    def _flat_adam_pieces(self):
+        """Slices of the flat region [0, beta_off) that the plain flat Adam updates (everything except the tensors
+        ``ctm_adam_step`` owns)."""
+        fl = self.flat
+        if self.kind != "combined":
+            return [(0, fl.beta_off)]
+        ab = fl.segments["inf_net.adapt_bert.bias"]
+        w = fl.segments["inf_net.input_layer.weight"]
+        ab_end = (ab.offset + ab.numel + 3) // 4 * 4
+        return [(0, ab.offset), (ab_end, w.offset + self.V * self.hidden[0])]
 
     def _hidden_params(self, flat: torch.Tensor):
         Wh, bh = [], []
@@ -260,18 +318,18 @@ class FusedEngine:
             return st, b1, None, None
         if self.kind == "zeroshot":
             return None, b1, x_ctx, st
-        # combined: collapse adapt_bert into the first layer, M^T = A^T W1b^T  ([C,V] x [V,H0])
-        V = self.V
-        A = self._p("inf_net.adapt_bert.weight")      # [V, C]
-        ab = self._p("inf_net.adapt_bert.bias")       # [V]
-        W1bT = st[V:2 * V]                            # [V, H0]
-        self._MT = A.t() @ W1bT                       # plain library GEMM (cuBLAS), see DESIGN.md
-        self._b1_eff = b1 + ab @ W1bT
-        return st[:V], self._b1_eff, x_ctx, self._MT
+        # combined: collapse adapt_bert into the first layer: [M^T ; b_eff] = [A | ab]^T W (+ b1 in the last
+        # row), a split-V tcgen05 GEMM over the bf16 hi/lo shadows (csrc/ctm_gemm.cu)
+        V, C_ = self.V, self.C
+        K_.ctm_init_out(self.ctm_MTx, bias_row=C_, bias=b1)
+        K_.ctm_vc(self.ctm_a_hi, self.ctm_a_lo, self.ctm_w_hi, self.ctm_w_lo, self.ctm_MTx, m_total=C_ + 1,
+                  n_valid=self.hidden[0])
+        return st[:V], self.ctm_MTx[C_], x_ctx, self.ctm_MTx[:C_]
 
     def forward_backward(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *,
                          training: bool = True, sample: bool = True, gscale: float = 1.0,
-                         need_grad: bool = True, eps_in=None, mask_enc_in=None, mask_theta_in=None, fed=None):
+                         need_grad: bool = True, eps_in=None, mask_enc_in=None, mask_theta_in=None, fed=None,
+                         ctm_reduce_hook=None):
         """Runs forward (and backward when ``need_grad``); returns the device scalar
         ``loss = sum_b (kl_weight*KL_b + RL_b)`` (float64, shape [1])."""
         B, K, V = batch.B, self.K, self.V
@@ -348,8 +406,7 @@ class FusedEngine:
             gst.zero_()
             dWdT = gst
         elif self.kind == "combined":
-            self._dMT = torch.zeros_like(self._MT)
-            dWdT = self._dMT
+            dWdT = self.ctm_dMx[:self.C]  # (zeroed with the step's other accumulators)
         else:
             dWdT = None
         K_.enc_bwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, dmu=self.dmu, dlv=self.dlv, mu=self.mu,
@@ -365,14 +422,17 @@ class FusedEngine:
             K_.csc_spmm(self.csc.colptr, self.csc.row, self.csc.src, batch.counts, self.dpre0, gst[:V],
                         V=V, N=self.hidden[0])
         if self.kind == "combined":
-            st = self.flat.storage_view(self.flat.P, "inf_net.input_layer.weight")
-            A = self._p("inf_net.adapt_bert.weight")
-            ab = self._p("inf_net.adapt_bert.bias")
-            W1bT = st[V:2 * V]
-            dsum = self._g("inf_net.input_layer.bias")        # = sum_b dpre0
-            torch.matmul(W1bT, self._dMT.t(), out=self._g("inf_net.adapt_bert.weight"))
-            torch.addmm(torch.outer(ab, dsum), A, self._dMT, out=gst[V:2 * V])
-            torch.mv(W1bT, dsum, out=self._g("inf_net.adapt_bert.bias"))
+            # gradient wrt the collapsed weight (+ d b1 as its last row) -> exact gradients of adapt_bert and of
+            # the contextual half of the first layer.  Both products are linear in [dM^T ; dsum], so a federated
+            # run sums THAT over the clients (ctm_reduce_hook: 150 KB) instead of the 38 M-element gradients.
+            self.ctm_dMx[self.C].copy_(self._g("inf_net.input_layer.bias"))        # dsum = sum_b dpre0
+            if ctm_reduce_hook is not None:
+                ctm_reduce_hook(self.ctm_dM_flat)
+            K_.ctm_split(self.ctm_dMx[:self.C], self.ctm_d_hi, self.ctm_d_lo, tail_row=self.ctm_dMx[self.C])
+            K_.ctm_rc(self.ctm_a_hi, self.ctm_a_lo, self.ctm_d_hi, self.ctm_d_lo, gst[V:2 * V], k_total=self.C + 1,
+                      n_valid=self.hidden[0])
+            K_.ctm_rr(self.ctm_w_hi, self.ctm_w_lo, self.ctm_d_hi, self.ctm_d_lo,
+                      self._g("inf_net.adapt_bert.weight"), n_valid=self.C, extra=self._g("inf_net.adapt_bert.bias"))
         return self.loss
 
     # ------------------------------------------------------------------------------------------
@@ -385,10 +445,13 @@ class FusedEngine:
         K_.step_begin(self.ctr, 0, 1)
         fl = self.flat
         b1, b2 = self.betas
-        end = fl.beta_off
-        K_.adam_flat(fl.P[:end], fl.G[:end], fl.M[:end], fl.V2[:end], lr=self.lr, b1=b1, b2=b2,
-                     eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
-                     step_ctr=self.ctr)
+        for lo, hi in self._flat_adam_pieces():
+            if hi > lo:
+                K_.adam_flat(fl.P[lo:hi], fl.G[lo:hi], fl.M[lo:hi], fl.V2[lo:hi], lr=self.lr, b1=b1, b2=b2,
+                             eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
+                             step_ctr=self.ctr)
+        if self.kind == "combined":
+            self.ctm_adam_step(gscale=gscale)
         K, V = self.K, self.V
         if self.is_prod:
             K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"),

@@ -91,6 +91,8 @@ class FederatedTrainer:
         # Overlap: the beta part of the aggregation (the bulk of the bytes) runs on a few CTAs of the d-theta
         # sweep, i.e. concurrently with ~1 ms of backward compute that no longer touches beta.
         self._overlap = None
+        if not hasattr(self, "_ctm_trick"):
+            self._ctm_trick = False
         # 40 CTAs measured best with P2P pushes (N=2: 16: 5.40, 24: 4.46, 32: 3.88, 40: 3.55-3.64, 56: 3.76 ms/step);
         # with NVLS multicast pushes the aggregation needs fewer (N=8: 32 CTAs 3.41 ms/step, 40 CTAs 3.50)
         nvls = bool(self.aggregator.args.ranks[0].P_mc)
@@ -100,11 +102,26 @@ class FederatedTrainer:
                 and os.environ.get("GFEDNTM_NO_OVERLAP", "0") != "1"):
             self._overlap = self.aggregator.overlap_handle(eng.ctr, ctas)
 
+    CTM_KEYS = ("inf_net.adapt_bert.weight", "inf_net.adapt_bert.bias", "inf_net.input_layer.weight",
+                "inf_net.input_layer.bias")
+
     def _share_plan(self, fl):
-        """(ranges over the flat region, BatchNorm statistics mask, beta shared?) from ``grads_to_share``."""
-        if not self.grads_to_share:
+        """(ranges over the flat region, BatchNorm statistics mask, beta shared?) from ``grads_to_share``.
+
+        CombinedTM in gradient mode: the gradients of ``adapt_bert`` and of the contextual half of the first layer
+        are linear images of the small gradient wrt the collapsed weight (engine/fused.py), so the clients sum
+        THAT (``allreduce_small``, 150 KB) and every rank applies the identical Adam step itself; those ranges
+        are marked *replicated* and never cross NVLink."""
+        eng = self.model.engine
+        keys = set(self.grads_to_share) if self.grads_to_share else None
+        self._ctm_trick = (eng.kind == "combined" and self.agg == "grad" and self.world > 1
+                           and (keys is None or all(k in keys for k in self.CTM_KEYS))
+                           and (eng.V * eng.hidden[0]) % 4 == 0 and "AR" in self.arena.offsets
+                           and os.environ.get("GFEDNTM_NO_CTM_TRICK", "0") != "1")
+        if keys is None and not self._ctm_trick:
             return None, 63, True
-        keys = set(self.grads_to_share)
+        if keys is None:
+            keys = set(fl.segments) | {"__all_stats__"}
         known = set(fl.segments) | {f"{bn}.{st}" for bn in ("inf_net.f_mu_batchnorm", "inf_net.f_sigma_batchnorm",
                                                             "beta_batchnorm")
                                     for st in ("running_mean", "running_var", "num_batches_tracked")}
@@ -121,7 +138,15 @@ class FederatedTrainer:
             end = (sg.offset + sg.numel + 3) // 4 * 4
             if sg.offset > cur:  # alignment padding: harmless either way
                 ranges.append((cur, sg.offset - cur, True))
-            ranges.append((sg.offset, end - sg.offset, sg.name in keys))
+            kind = int(sg.name in keys)
+            if self._ctm_trick and sg.name.startswith("inf_net.adapt_bert."):
+                kind = 3   # replicated, updated by eng.ctm_adam_step (keeps the operand shadows in step)
+            if self._ctm_trick and sg.name == "inf_net.input_layer.weight":
+                half = eng.V * eng.hidden[0]  # storage is [2V, H0]: BoW half aggregated, contextual half replicated
+                ranges.append((sg.offset, half, 1))
+                ranges.append((sg.offset + half, end - sg.offset - half, 3))
+            else:
+                ranges.append((sg.offset, end - sg.offset, kind))
             cur = end
         if cur < fl.beta_off:
             ranges.append((cur, fl.beta_off - cur, True))
@@ -130,9 +155,16 @@ class FederatedTrainer:
                   ("inf_net.f_sigma_batchnorm", "running_mean"), ("inf_net.f_sigma_batchnorm", "running_var"),
                   ("beta_batchnorm", "running_mean"), ("beta_batchnorm", "running_var")]
         for i, (bn, st) in enumerate(blocks):
-            if f"{bn}.{st}" in keys:
+            if f"{bn}.{st}" in keys or "__all_stats__" in keys:
                 s_mask |= 1 << i
         return ranges, s_mask, ("beta" in keys)
+
+    def replicated_grad_names(self):
+        """Parameters whose gradient buffer already holds the GLOBAL gradient after the backward pass (CombinedTM
+        in gradient mode; of ``inf_net.input_layer.weight`` only the contextual half, columns V..2V)."""
+        if not getattr(self, "_ctm_trick", False):
+            return ()
+        return ("inf_net.adapt_bert.weight", "inf_net.adapt_bert.bias", "inf_net.input_layer.weight")
 
     def materialize(self) -> None:
         """Makes this rank's fp32 parameters complete.  The overlapped aggregation keeps the fp32 master copy
@@ -167,19 +199,29 @@ class FederatedTrainer:
                     after_backward()
                 self._launch("grad", eng.step_count + 1, parts=1)
             elif self.agg == "grad":
-                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank])
+                hook = None
+                if self._ctm_trick:
+                    K_.step_begin(eng.ctr, 0, 1)  # the small all-reduce inside the backward pass uses epoch t
+                    hook = lambda buf: self.aggregator.allreduce_small(buf, eng.ctr)  # noqa: E731
+                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], ctm_reduce_hook=hook)
                 if after_backward is not None:
                     after_backward()
-                K_.step_begin(eng.ctr, 0, 1)
+                if not self._ctm_trick:
+                    K_.step_begin(eng.ctr, 0, 1)
                 if not self.beta_shared:  # beta stays client-local: its own Adam on the unweighted gradient
                     eng.optimizer_step_beta(gscale=1.0 / max(self.weights[self.rank], 1e-30))
                 self._launch("grad", eng.step_count + 1)
+                if self._ctm_trick:
+                    eng.ctm_adam_step(gscale=1.0)   # identical update on every rank from the summed small gradient
+                else:
+                    eng._refresh_ctm_shadows()
             else:
                 eng.forward_backward(bow, x_ctx, training=True)
                 eng.optimizer_step()
                 if after_backward is not None:
                     after_backward()
                 self._launch("param", eng.step_count)
+                eng._refresh_ctm_shadows()
 
         if not eng.use_graphs or after_backward is not None:
             body()

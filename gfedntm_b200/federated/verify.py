@@ -88,7 +88,15 @@ def verify_against_oracle(trainer, loader, steps: int = 2) -> Dict[str, object]:
             grabbed["__S"] = eng.flat.S.detach().clone() * w[rank]
 
         trainer.step(mb.bow, mb.x_ctx, after_backward=grab)
+        repl = trainer.replicated_grad_names() if trainer.agg == "grad" else ()
         for n in names:
+            if n in repl and n != "inf_net.input_layer.weight":
+                continue  # already the global gradient on every rank (summed through the collapsed weight)
+            if n in repl:  # first layer [H0, 2V]: BoW half is local, contextual half already global
+                loc = grabbed[n].clone()
+                dist.all_reduce(loc, group=group)
+                grabbed[n][:, :eng.V] = loc[:, :eng.V]
+                continue
             dist.all_reduce(grabbed[n], group=group)
         dist.all_reduce(grabbed["__S"], group=group)
         if trainer.agg == "grad":

@@ -129,6 +129,7 @@ class GfFabricRank(C.Structure):
         ("M", _p), ("V2", _p), ("done_counter", _p),
         ("P_mc", _p), ("S_mc", _p), ("beta_bf_mc", _p), ("betaT_bf_mc", _p),
         ("Gb", _p * GF_MAX_RANKS), ("ld_gb", _i), ("agg_counter", _p),
+        ("AR", _p * GF_MAX_RANKS), ("ar_cap", C.c_longlong),
     ]
 
 
@@ -189,12 +190,23 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_csc_corr_t.argtypes = [_p, _p, _p, _p, _p, _i, _p, _i, _i, _i, _p]
     for fn in ("gf_theta_center_fold", "gf_scale_beta", "gf_theta_gram", "gf_gram", "gf_gram_finish", "gf_csc_corr_t"):
         getattr(lib, fn).restype = _i
+    lib.gf_ctm_split.argtypes = [_p, ll, _p, _p, _i, _i, _p, _p, _i, _p]
+    lib.gf_ctm_init_out.argtypes = [_p, _i, _i, _i, _i, _p, _p]
+    lib.gf_ctm_vc.argtypes = [_p, _p, _i, _i, _p, _p, _i, _i, _p, _i, _i, _p]
+    lib.gf_ctm_rc.argtypes = [_p, _p, _i, _i, _p, _p, _i, _i, _i, _p, _i, _i, _p]
+    lib.gf_ctm_rr.argtypes = [_p, _p, _p, _p, _i, _i, _i, _p, _i, _i, _p, _p]
+    lib.gf_adam_split.argtypes = [_p, _p, _p, _p, ll, _i, _i, _p, _p, _p, _p, _p, _p, _i, _f, _f, _f, _f, _f, _i, _f, _i,
+                                  _p, _p]
+    for fn in ("gf_ctm_split", "gf_ctm_init_out", "gf_ctm_vc", "gf_ctm_rc", "gf_ctm_rr", "gf_adam_split"):
+        getattr(lib, fn).restype = _i
     lib.gf_fed_signal.argtypes = [C.POINTER(GfFedArgs), _i, _p]
     lib.gf_fed_signal.restype = _i
     lib.gf_fed_make_tmaps.argtypes = [C.POINTER(GfFedArgs), _p]
     lib.gf_fed_make_tmaps.restype = _i
     lib.gf_fed_gather_beta.argtypes = [C.POINTER(GfFedArgs), _p]
     lib.gf_fed_gather_beta.restype = _i
+    lib.gf_fed_allreduce_small.argtypes = [C.POINTER(GfFedArgs), _p, C.c_longlong, _p]
+    lib.gf_fed_allreduce_small.restype = _i
     lib.gf_dec_row_chunks_grid.argtypes = [_i, _i, _i]
     lib.gf_dec_row_chunks_grid.restype = _i
     lib.gf_num_sms.argtypes = []

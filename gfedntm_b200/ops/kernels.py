@@ -349,3 +349,58 @@ def adam_beta(p, g, m, v, beta_bf, betaT_bf, *, K: int, V: int, lr: float = 0.0,
                            (g.stride(0) if g is not None else 0), _ptr(beta_bf), beta_bf.stride(0),
                            _ptr(betaT_bf), betaT_bf.shape[1], lr, b1, b2, eps, wd, step, gscale,
                            int(do_update), _ptr(step_ctr), _stream()), "gf_adam_beta")
+
+
+# ----------------------------------------------------------------------------------------------
+# CombinedTM: collapsed adapt_bert layer (csrc/ctm_gemm.cu)
+# ----------------------------------------------------------------------------------------------
+def ctm_split(src: torch.Tensor, out_hi: torch.Tensor, out_lo: torch.Tensor, *, extra_col=None, tail_row=None) -> None:
+    """bf16 hi / lo shadows of ``src`` [rows, cols] (+ one extra column / row), zero padded to ``out`` width."""
+    assert src.dim() == 2 and src.stride(1) == 1 and out_hi.stride(1) == 1 and out_hi.shape == out_lo.shape
+    rows, cols = src.shape
+    assert out_hi.shape[0] >= rows + (1 if tail_row is not None else 0)
+    check(_lib.load().gf_ctm_split(_ptr(src), src.stride(0), _ptr(extra_col), _ptr(tail_row), rows, cols,
+                                   _ptr(out_hi), _ptr(out_lo), out_hi.stride(0), _stream()), "gf_ctm_split")
+
+
+def ctm_init_out(out: torch.Tensor, *, bias_row: int, bias) -> None:
+    check(_lib.load().gf_ctm_init_out(_ptr(out), out.shape[0], out.shape[1], out.stride(0), bias_row, _ptr(bias),
+                                      _stream()), "gf_ctm_init_out")
+
+
+def ctm_vc(x_hi, x_lo, y_hi, y_lo, out, *, m_total: int, n_valid: int) -> None:
+    """out[m, n] += sum_r x[r, m] y[r, n]  (contraction over the rows of both operands)."""
+    R, ldx = x_hi.shape[0], x_hi.stride(0)
+    nb = y_hi.stride(0) // 64
+    assert y_hi.shape[0] == R and y_hi.stride(0) % 64 == 0
+    check(_lib.load().gf_ctm_vc(_ptr(x_hi), _ptr(x_lo), ldx, m_total, _ptr(y_hi), _ptr(y_lo), nb, R, _ptr(out),
+                                out.stride(0), n_valid, _stream()), "gf_ctm_vc")
+
+
+def ctm_rc(x_hi, x_lo, z_hi, z_lo, out, *, k_total: int, n_valid: int) -> None:
+    """out[r, n] = sum_k x[r, k] z[k, n]."""
+    R, ldx = x_hi.shape[0], x_hi.stride(0)
+    nb = z_hi.stride(0) // 64
+    check(_lib.load().gf_ctm_rc(_ptr(x_hi), _ptr(x_lo), ldx, k_total, _ptr(z_hi), _ptr(z_lo), nb, z_hi.shape[0], R,
+                                _ptr(out), out.stride(0), n_valid, _stream()), "gf_ctm_rc")
+
+
+def ctm_rr(x_hi, x_lo, z_hi, z_lo, out, *, n_valid: int, extra=None) -> None:
+    """out[r, c] = sum_k x[r, k] z[c, k] for c < n_valid; ``extra[r]`` receives column ``n_valid``."""
+    R = x_hi.shape[0]
+    nb = x_hi.stride(0) // 64
+    assert z_hi.stride(0) == x_hi.stride(0)
+    check(_lib.load().gf_ctm_rr(_ptr(x_hi), _ptr(x_lo), _ptr(z_hi), _ptr(z_lo), nb, z_hi.shape[0], R, _ptr(out),
+                                out.stride(0), n_valid, _ptr(extra), _stream()), "gf_ctm_rr")
+
+
+def adam_split(p, g, m, v, out_hi, out_lo, *, p_col=None, g_col=None, m_col=None, v_col=None, lr: float = 0.0,
+               b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8, wd: float = 0.0, step: int = 1, gscale: float = 1.0,
+               do_update: bool = True, step_ctr=None) -> None:
+    """Adam on a row-major [rows, cols] block (+ per-row scalar ``p_col`` as one more column) fused with the refresh
+    of its bf16 hi / lo shadows; ``do_update=False`` only refreshes the shadows."""
+    assert p.dim() == 2 and p.stride(1) == 1
+    rows, cols = p.shape
+    check(_lib.load().gf_adam_split(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.stride(0), rows, cols, _ptr(p_col), _ptr(g_col),
+                                    _ptr(m_col), _ptr(v_col), _ptr(out_hi), _ptr(out_lo), out_hi.stride(0), lr, b1, b2, eps,
+                                    wd, step, gscale, int(do_update), _ptr(step_ctr), _stream()), "gf_adam_split")

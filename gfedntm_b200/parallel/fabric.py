@@ -145,6 +145,10 @@ def fill_rank_ctx(ctx, arena, rank: int, *, M: torch.Tensor, V2: torch.Tensor, d
         ctx.Gb[c] = arena.peer_ptr(c, "Gb") if has_gb else None
     ctx.ld_gb = ld_gb if has_gb else 0
     ctx.agg_counter = agg_counter.data_ptr() if agg_counter is not None else None
+    has_ar = "AR" in arena.offsets
+    for c in range(arena.world):
+        ctx.AR[c] = arena.peer_ptr(c, "AR") if has_ar else None
+    ctx.ar_cap = (arena.sizes["AR"] // (4 * arena.world)) if has_ar else 0
     for c in range(arena.world):
         ctx.G[c] = arena.peer_ptr(c, "G")
         ctx.P[c] = arena.peer_ptr(c, "P")
@@ -187,11 +191,12 @@ class FusedAggregator:
                 if ln <= 0:
                     continue
                 assert off % 4 == 0 and ln % 4 == 0, "ranges must be 16-byte aligned"
-                if merged and merged[-1][2] == bool(sh) and merged[-1][0] + merged[-1][1] == off:
+                kind = int(sh)  # 0 client-local, 1 aggregated, 2 replicated (see GfFedRange)
+                if merged and merged[-1][2] == kind and merged[-1][0] + merged[-1][1] == off:
                     merged[-1][1] += ln
                 else:
-                    merged.append([off, ln, bool(sh)])
-            all_shared = all(m[2] for m in merged) and (s_mask & 63) == 63 and beta_shared
+                    merged.append([off, ln, kind])
+            all_shared = all(m[2] == 1 for m in merged) and (s_mask & 63) == 63 and beta_shared
             if not all_shared:
                 assert len(merged) <= GF_FED_MAX_RANGES, "too many alternating shared / unshared segments"
                 a.n_ranges = len(merged)
@@ -237,6 +242,16 @@ class FusedAggregator:
         self._keep.append(tm)
         gb = self._arena.tensor("Gb", torch.bfloat16).view(a.K, a.ranks[0].ld_gb)
         return BetaOverlap(self, dev, step_ctr, ctas, tm_ptr, gb)
+
+    def allreduce_small(self, x: torch.Tensor, step_ctr: torch.Tensor) -> None:
+        """In-place sum of a small fp32 buffer over the ranks (one-shot all-reduce through peer memory); the
+        flag epoch is the device step counter, so the launch replays from a CUDA graph."""
+        a = self.args
+        a.step_ctr = step_ctr.data_ptr()
+        n = x.numel()
+        assert n % 4 == 0 and x.is_contiguous()
+        check(_lib.load().gf_fed_allreduce_small(C.byref(a), x.data_ptr(), n, torch.cuda.current_stream().cuda_stream),
+              "gf_fed_allreduce_small")
 
     def gather_beta(self) -> None:
         """Completes this rank's fp32 copy of beta from the owners' master slices (overlapped path)."""

@@ -310,6 +310,37 @@ int gf_adam_beta(float* p, const float* g, float* m, float* v, int K, int V, int
                  float wd, int step, float gscale, int do_update, const long long* step_ctr, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Skinny tcgen05 GEMMs of the CombinedTM encoder (csrc/ctm_gemm.cu): the adapt_bert layer collapsed into the
+ * first encoder layer, M^T = A^T W, and its exact gradients dW = A dM^T + ab (x) dsum, dA = W dM, d ab = W dsum.
+ * Ref: ctm_network/inference_network.py:160-193 and its autograd.  Operands are bf16 hi + lo shadows
+ * (gf_ctm_split); every product is three MMAs (hi.hi + lo.hi + hi.lo) accumulated in fp32.
+ * ---------------------------------------------------------------------------------------- */
+/* hi = bf16(x), lo = bf16(x - hi) of src [rows, cols] (row pitch ld_src floats) into [rows_out, ldo] bf16;
+ * column `cols` <- extra_col[row] (may be null), row `rows` <- tail_row[0..cols) (may be null; rows_out = rows+1
+ * then), everything else zero.                                                                             */
+int gf_ctm_split(const float* src, long long ld_src, const float* extra_col, const float* tail_row, int rows, int cols,
+                 void* out_hi, void* out_lo, int ldo, void* stream);
+/* Adam on a row-major [rows, cols] block (+ an optional per-row scalar p_col, folded in as column `cols`) fused with
+ * the refresh of its bf16 hi / lo shadows [rows, ldo] (ldo % 8 == 0, padding columns zeroed); do_update = 0 only
+ * refreshes the shadows.  step_ctr as in gf_adam_flat.  Ref: optimizer.step(), federated_ctm.py:76-78.       */
+int gf_adam_split(float* p, const float* g, float* m, float* v, long long ld, int rows, int cols, float* p_col,
+                  const float* g_col, float* m_col, float* v_col, void* out_hi, void* out_lo, int ldo, float lr, float b1,
+                  float b2, float eps, float wd, int step, float gscale, int do_update, const long long* step_ctr,
+                  void* stream);
+/* out [rows, ld] <- 0, except row bias_row <- bias[0..cols)  (accumulation target of gf_ctm_vc).            */
+int gf_ctm_init_out(float* out, int rows, int cols, int ld, int bias_row, const float* bias, void* stream);
+/* out[m, n] += sum_r X[r, m] Y[r, n]   X hi/lo [R, ldx] (m_total valid columns), Y hi/lo [R, 64 nb]         */
+int gf_ctm_vc(const void* x_hi, const void* x_lo, int ldx, int m_total, const void* y_hi, const void* y_lo, int nb,
+              int R, float* out, int ldo, int n_valid, void* stream);
+/* out[r, n] = sum_k X[r, k] Z[k, n]    X hi/lo [R, ldx] (k_total valid columns), Z hi/lo [z_rows, 64 nb]    */
+int gf_ctm_rc(const void* x_hi, const void* x_lo, int ldx, int k_total, const void* z_hi, const void* z_lo, int nb,
+              int z_rows, int R, float* out, int ldo, int n_valid, void* stream);
+/* out[r, c] = sum_k X[r, k] Z[c, k] (c < n_valid), extra[r] = column n_valid (may be null)
+ * X hi/lo [R, 64 nb], Z hi/lo [z_rows, 64 nb]                                                               */
+int gf_ctm_rr(const void* x_hi, const void* x_lo, const void* z_hi, const void* z_lo, int nb, int z_rows, int R,
+              float* out, int ldo, int n_valid, float* extra, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Fused federated aggregation over NVLink peer memory (no NCCL on this path).
  * Ref: src/federation/server.py:442-521 (gather / weighted mean / broadcast over gRPC) and the
  *      clients' optimizer.step() + load_state_dict (federated_avitm.py:78, federated_model.py:117-131).
@@ -336,6 +367,9 @@ typedef struct GfFabricRank {
   void* Gb[GF_MAX_RANKS];
   int ld_gb;
   unsigned int* agg_counter;      /* this rank, reset by gf_fed_signal(GF_FED_PHASE_BETA_READY)  */
+  /* One-shot small all-reduce (gf_fed_allreduce_small): every rank's staging area, float [world][ar_cap] */
+  float* AR[GF_MAX_RANKS];
+  long long ar_cap;
 } GfFabricRank;
 
 /* A contiguous range of the flat parameter space [0, flat_n) with its sharing rule (grads_to_share of
@@ -344,7 +378,10 @@ typedef struct GfFabricRank {
 #define GF_FED_MAX_RANGES 48
 typedef struct GfFedRange {
   long long off, len;             /* floats, both multiples of 4                                */
-  int shared;
+  int shared;                     /* 0 client-local, 1 aggregated, 2 replicated: the gradient in G already is the
+                                     global one on every rank (mode 0: local Adam with unit gradient scale; mode 1:
+                                     aggregated like 1); 3 = like 2 but the caller runs the optimiser on it
+                                     itself (gf_adam_split keeps the operand shadows in step)                    */
   int pad_;
 } GfFedRange;
 
@@ -380,12 +417,19 @@ int gf_fed_aggregate(const GfFedArgs* args, void* stream);
  * epoch.  GF_FED_PHASE_BETA_READY also resets this rank's word-tile counter (ranks[0].agg_counter).   */
 int gf_fed_signal(const GfFedArgs* args, int phase, void* stream);
 #define GF_FED_PHASE_BETA_READY 2
+#define GF_FED_PHASE_SMALL_AR 3
 #define GF_FED_FLAG_SLOTS 8
 #define GF_FED_FLAG_BYTES (GF_FED_FLAG_SLOTS * GF_MAX_RANKS * 4)
 /* Writes GF_MAX_RANKS CUtensorMap (128 bytes each, 64-byte aligned HOST buffer) describing every rank's
  * bf16 beta gradient ranks[0].Gb[c] as [K, ld_gb] with 32-topic x 128-word boxes (entries of absent ranks
  * are zeroed).  The maps are used for plain TMA loads; they are never used with cluster multicast.   */
 int gf_fed_make_tmaps(const GfFedArgs* args, void* out_tmaps_host);
+/* One-shot all-reduce (sum) of a small fp32 buffer x[0..n) (n <= ranks[0].ar_cap, x 16-byte aligned, n % 4 == 0)
+ * over peer memory: every rank stores its x into its slot of every rank's staging area, raises flag slot
+ * GF_FED_PHASE_SMALL_AR, waits for all ranks and sums the slots in rank order (bit-identical result everywhere).
+ * Used for the gradient of CombinedTM's collapsed weight (150 KB instead of the 38 M-element adapt_bert
+ * gradient).  Every rank calls it once per step, before gf_fed_aggregate of the same step.                  */
+int gf_fed_allreduce_small(const GfFedArgs* args, float* x, long long n, void* stream);
 /* Overlapped aggregation keeps the fp32 master copy of beta on the owner of each word-tile range only;
  * this copies every range this rank does not own from its owner's parameter buffer (P2P loads) so that
  * state_dict() / checkpoints see the complete tensor.  Collective in spirit: every rank must be between

@@ -25,14 +25,23 @@ def main():
     dist.init_process_group("nccl", device_id=device)
     agg = sys.argv[1] if len(sys.argv) > 1 else "grad"
     share = sys.argv[2].split(",") if len(sys.argv) > 2 and sys.argv[2] else None
+    kind = sys.argv[3] if len(sys.argv) > 3 else "avitm"   # avitm | combined | zeroshot
     V, K, B = 3000, 20, 64
     rng = np.random.default_rng(100 + rank)
     n_docs = B * (3 + rank)  # different corpus sizes -> non-uniform client weights
     X = rng.poisson(0.02, (n_docs, V)).astype(np.float32)
     X[X.sum(1) == 0, 0] = 1
-    ds = BOWDataset(X, None)
-    model = AVITM(input_size=V, n_components=K, hidden_sizes=(32, 32), batch_size=B, num_epochs=1, verbose=False,
-                  device=device, seed=3)
+    if kind == "avitm":
+        ds = BOWDataset(X, None)
+        model = AVITM(input_size=V, n_components=K, hidden_sizes=(32, 32), batch_size=B, num_epochs=1, verbose=False,
+                      device=device, seed=3)
+    else:
+        from gfedntm_b200.models import CTM, CTMDataset
+
+        ctx = rng.standard_normal((n_docs, 96)).astype(np.float32)
+        ds = CTMDataset(ctx, X, None)
+        model = CTM(input_size=V, contextual_size=96, inference_type=kind, n_components=K, hidden_sizes=(32, 32),
+                    batch_size=B, num_epochs=1, verbose=False, device=device, seed=3)
     tr = FederatedTrainer(model, n_samples=n_docs, world_size=world, rank=rank, agg=agg, grads_to_share=share)
     loader = model.make_loader(ds, shuffle=True)
     tr.prepare(loader)
@@ -47,7 +56,7 @@ def main():
         except StopIteration:
             it = iter(loader)
             mb = next(it)
-        loss = tr.step(mb.bow, None)
+        loss = tr.step(mb.bow, mb.x_ctx)
         losses.append(float(loss.item()) / mb.size)
     torch.cuda.synchronize()
     it.close()

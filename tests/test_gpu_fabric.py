@@ -37,8 +37,11 @@ def _setup(world, model_type="prodLDA", V=700, K=12, B=48, share=None):
     if share is not None:
         from gfedntm_b200.federated.trainer import FederatedTrainer
 
+        import types
+
         planner = FederatedTrainer.__new__(FederatedTrainer)
         planner.grads_to_share = list(share)
+        planner.model, planner.agg, planner.world, planner.arena = types.SimpleNamespace(engine=engines[0]), "grad", 1, arena
         ranges, s_mask, beta_shared = planner._share_plan(fl)
     agg = FusedAggregator(world=world, weights=weights, flat_n=fl.beta_off, beta_off=fl.beta_off, s_n=fl.s_n,
                           K=K, V=V, Kp=engines[0].Kp,
