@@ -111,7 +111,14 @@ enc_fwd_kernel(const GfEncArgs a_) {
         }
       }
     }
-    if (a.xdense != nullptr) {
+    if (a.pre0_ext != nullptr) {
+      // dense part (contextual embedding) already contracted on the tensor cores (gf_ctm_rc)
+#pragma unroll
+      for (int c = 0; c < kMaxH / 32; ++c) {
+        const int j = c * 32 + lane;
+        if (j < H0) acc[c] += __ldg(a.pre0_ext + (size_t)b * H0 + j);
+      }
+    } else if (a.xdense != nullptr) {
       // dense part (contextual embedding): 32 inputs per round (one per lane), weight rows of 8 inputs in
       // flight at a time -- a one-input-at-a-time loop was a serial chain of C dependent L2 round trips
       const float* xr = a.xdense + (size_t)b * a.C;
@@ -620,6 +627,78 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// theta_mc: Monte-Carlo document-topic inference in ONE launch.  Ref: avitm.py:470-523 (n_samples full passes of
+// get_theta, averaged) + federated_model.py:170-173 (entries < thr zeroed, rows L1-renormalised).  The encoder
+// pass does not depend on the draw, so only the reparameterised soft-max is repeated: one warp per document
+// keeps mu / sigma in registers, loops over the draws and applies the threshold / renormalisation epilogue.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+theta_mc_kernel(const float* __restrict__ mu_pre, const float* __restrict__ ls_pre, const float* __restrict__ mu_rm,
+                const float* __restrict__ mu_rv, const float* __restrict__ ls_rm, const float* __restrict__ ls_rv,
+                float bn_eps, int B, int K, int n_samples, unsigned long long seed, float thr, float* __restrict__ out) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 8 + warp;
+  if (b >= B) return;
+  float mu[kMaxH / 32], sd[kMaxH / 32], acc[kMaxH / 32];
+#pragma unroll
+  for (int c = 0; c < kMaxH / 32; ++c) {
+    const int k = c * 32 + lane;
+    mu[c] = 0.f; sd[c] = 0.f; acc[c] = 0.f;
+    if (k < K) {
+      mu[c] = (mu_pre[(size_t)b * K + k] - mu_rm[k]) * rsqrtf(mu_rv[k] + bn_eps);
+      const float lv = (ls_pre[(size_t)b * K + k] - ls_rm[k]) * rsqrtf(ls_rv[k] + bn_eps);
+      sd[c] = __expf(0.5f * lv);
+    }
+  }
+  Philox ph(seed);
+  for (int s = 0; s < n_samples; ++s) {
+    float z[kMaxH / 32];
+    float zmax = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < kMaxH / 32; ++c) {
+      const int k = c * 32 + lane;
+      z[c] = -INFINITY;
+      if (k < K) {
+        const uint4 rr = ph((uint64_t)b * K + k, 0x4d430000ull + (uint64_t)s);
+        z[c] = fmaf(box_muller(rr.x, rr.y).x, sd[c], mu[c]);
+        zmax = fmaxf(zmax, z[c]);
+      }
+    }
+    zmax = warp_max(zmax);
+    float zs = 0.f;
+#pragma unroll
+    for (int c = 0; c < kMaxH / 32; ++c) {
+      const int k = c * 32 + lane;
+      if (k < K) { z[c] = __expf(z[c] - zmax); zs += z[c]; }
+    }
+    zs = warp_sum(zs);
+    const float inv = 1.f / zs;
+#pragma unroll
+    for (int c = 0; c < kMaxH / 32; ++c)
+      if (c * 32 + lane < K) acc[c] = fmaf(z[c], inv, acc[c]);
+  }
+  const float inv_n = 1.f / (float)n_samples;
+  float tot = 0.f;
+#pragma unroll
+  for (int c = 0; c < kMaxH / 32; ++c) {
+    acc[c] *= inv_n;
+    if (thr > 0.f && acc[c] < thr) acc[c] = 0.f;
+    if (c * 32 + lane < K) tot += acc[c];
+  }
+  if (thr > 0.f) {
+    tot = warp_sum(tot);
+    const float r = tot > 0.f ? 1.f / tot : 1.f;
+#pragma unroll
+    for (int c = 0; c < kMaxH / 32; ++c) acc[c] *= r;
+  }
+#pragma unroll
+  for (int c = 0; c < kMaxH / 32; ++c) {
+    const int k = c * 32 + lane;
+    if (k < K) out[(size_t)b * K + k] = acc[c];
+  }
+}
+
 // ctr[0] += inc_rng (every forward pass), ctr[1] += inc_opt (every optimiser step)
 __global__ void step_begin_kernel(long long* ctr, int inc_rng, int inc_opt) {
   if (threadIdx.x == 0 && blockIdx.x == 0) {
@@ -688,6 +767,17 @@ extern "C" int gf_enc_bwd(const GfEncBwdArgs* a, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   const int grid = (a->B + kDocsPerBlock - 1) / kDocsPerBlock;
   enc_bwd_kernel<<<grid, kDocsPerBlock * 32, 0, st>>>(*a);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_theta_mc(const float* mu_pre, const float* ls_pre, const float* mu_rm, const float* mu_rv,
+                           const float* ls_rm, const float* ls_rv, float bn_eps, int B, int K, int n_samples,
+                           unsigned long long seed, float thr, float* out, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(K >= 1 && K <= kMaxH && B >= 1 && n_samples >= 1, "shapes");
+  theta_mc_kernel<<<(B + 7) / 8, 256, 0, st>>>(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, bn_eps, B, K, n_samples, seed,
+                                               thr, out);
   GF_LAUNCHED();
   return GF_OK;
 }

@@ -186,6 +186,19 @@ class FusedEngine:
         self.zpool = torch.zeros(off_dm + n_dm, **f32)
         self.bn_bsums = self.zpool[:4 * K]
         self.theta_colsum = self.zpool[4 * K:5 * K]
+        if self.kind in ("combined", "zeroshot"):
+            # Dense contextual input on the tensor cores (csrc/ctm_gemm.cu): x_ctx [B,C] . W^T [C,H0] forward
+            # (gf_ctm_rc) and d W^T = x_ctx^T . d pre0 backward (gf_ctm_vc), on bf16 hi/lo shadows.
+            C_, H0 = self.C, self.hidden[0]
+            bf = dict(dtype=torch.bfloat16, device=dev)
+            self.ctx_Cp, self.ctx_Np = K_.round_up(C_, 64), K_.round_up(H0, 64)
+            self.ctx_x_hi = torch.zeros(B, self.ctx_Cp, **bf)
+            self.ctx_x_lo = torch.zeros(B, self.ctx_Cp, **bf)
+            self.ctx_z_hi = torch.zeros(C_, self.ctx_Np, **bf)     # shadows of the dense first-layer weight [C, H0]
+            self.ctx_z_lo = torch.zeros(C_, self.ctx_Np, **bf)
+            self.ctx_g_hi = torch.zeros(B, self.ctx_Np, **bf)      # shadows of d pre0 [B, H0]
+            self.ctx_g_lo = torch.zeros(B, self.ctx_Np, **bf)
+            self.ctx_pre0 = torch.zeros(B, H0, **f32)
         if self.kind == "combined":
             # Collapsed adapt_bert layer (csrc/ctm_gemm.cu): bf16 hi/lo shadows of A' = [adapt_bert.weight |
             # adapt_bert.bias] and of W = input_layer.weight[:, V:2V]^T, the collapsed weight M'^T (+ effective
@@ -260,6 +273,14 @@ class FusedEngine:
         if self.is_prod:
             refresh_beta_shadows(self._p("beta"), self.beta_bf, self.betaT_bf)
         self._refresh_ctm_shadows()
+        self._refresh_ctx_shadows()
+
+    def _refresh_ctx_shadows(self) -> None:
+        """ZeroShotTM: bf16 hi/lo shadows of the dense first-layer weight [C, H0] (CombinedTM rebuilds them from the
+        collapsed weight every step)."""
+        if self.kind == "zeroshot":
+            st = self.flat.storage_view(self.flat.P, "inf_net.input_layer.weight")
+            K_.ctm_split(st, self.ctx_z_hi, self.ctx_z_lo)
 
     def _refresh_ctm_shadows(self) -> None:
         """bf16 hi/lo operand shadows of the CombinedTM adapt_bert layer and of the contextual half of the first
@@ -310,21 +331,28 @@ class FusedEngine:
     # ------------------------------------------------------------------------------------------
     # forward (+ backward) of one minibatch
     # ------------------------------------------------------------------------------------------
-    def _first_layer(self, x_ctx: Optional[torch.Tensor]):
-        """Returns (W1T or None, b1, xdense, WdT) for enc_fwd according to the encoder kind."""
+    def _first_layer(self, x_ctx: Optional[torch.Tensor], B: int):
+        """Returns (W1T or None, b1, pre0_ext or None) for enc_fwd according to the encoder kind.  The dense
+        contextual input is contracted on the tensor cores here; enc_fwd only adds the result."""
         st = self.flat.storage_view(self.flat.P, "inf_net.input_layer.weight")  # [fan_in, H0]
         b1 = self._p("inf_net.input_layer.bias")
         if self.kind == "bow":
-            return st, b1, None, None
+            return st, b1, None
+        H0, C_ = self.hidden[0], self.C
+        K_.ctm_split(x_ctx[:B], self.ctx_x_hi, self.ctx_x_lo)
         if self.kind == "zeroshot":
-            return None, b1, x_ctx, st
-        # combined: collapse adapt_bert into the first layer: [M^T ; b_eff] = [A | ab]^T W (+ b1 in the last
-        # row), a split-V tcgen05 GEMM over the bf16 hi/lo shadows (csrc/ctm_gemm.cu)
-        V, C_ = self.V, self.C
-        K_.ctm_init_out(self.ctm_MTx, bias_row=C_, bias=b1)
-        K_.ctm_vc(self.ctm_a_hi, self.ctm_a_lo, self.ctm_w_hi, self.ctm_w_lo, self.ctm_MTx, m_total=C_ + 1,
-                  n_valid=self.hidden[0])
-        return st[:V], self.ctm_MTx[C_], x_ctx, self.ctm_MTx[:C_]
+            W1T = None   # (weight shadows ctx_z_* follow the optimiser, see _refresh_ctx_shadows)
+        else:
+            # combined: collapse adapt_bert into the first layer: [M^T ; b_eff] = [A | ab]^T W (+ b1 in the last
+            # row), a split-V tcgen05 GEMM over the bf16 hi/lo shadows (csrc/ctm_gemm.cu)
+            K_.ctm_init_out(self.ctm_MTx, bias_row=C_, bias=b1)
+            K_.ctm_vc(self.ctm_a_hi, self.ctm_a_lo, self.ctm_w_hi, self.ctm_w_lo, self.ctm_MTx, m_total=C_ + 1,
+                      n_valid=H0)
+            K_.ctm_split(self.ctm_MTx[:C_], self.ctx_z_hi, self.ctx_z_lo)
+            W1T, b1 = st[:self.V], self.ctm_MTx[C_]
+        K_.ctm_rc(self.ctx_x_hi[:B], self.ctx_x_lo[:B], self.ctx_z_hi, self.ctx_z_lo, self.ctx_pre0[:B], k_total=C_,
+                  n_valid=H0)
+        return W1T, b1, self.ctx_pre0
 
     def forward_backward(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *,
                          training: bool = True, sample: bool = True, gscale: float = 1.0,
@@ -344,13 +372,14 @@ class FusedEngine:
             self.flat.G[:self.flat.small_end].zero_()
             self.csc.build(batch, dynamic_nnz=True)
 
-        W1T, b1, xdense, WdT = self._first_layer(x_ctx)
+        W1T, b1, pre0_ext = self._first_layer(x_ctx, B)
         Wh, bh = self._hidden_params(self.flat.P)
         use_bow = self.kind in ("bow", "combined")
         pad = [None] * (K_.GF_MAX_HIDDEN - len(self.hidden))
         K_.enc_fwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, training=training,
                    indptr=batch.indptr if use_bow else None, indices=batch.indices if use_bow else None,
-                   counts=batch.counts if use_bow else None, W1T=W1T, b1=b1, xdense=xdense, WdT=WdT,
+                   counts=batch.counts if use_bow else None, W1T=W1T, b1=b1, xdense=None, WdT=None,
+                   pre0_ext=pre0_ext,
                    Wh=Wh, bh=bh, Wmu=self._p("inf_net.f_mu.weight"), bmu=self._p("inf_net.f_mu.bias"),
                    Wsig=self._p("inf_net.f_sigma.weight"), bsig=self._p("inf_net.f_sigma.bias"),
                    pre=self.pre + pad, enc_drop_p=self.enc_drop, mask_enc_in=mask_enc_in,
@@ -402,21 +431,24 @@ class FusedEngine:
                       d_prior_var=self._g("prior_variance") if learn else None)
         dWh, dbh = self._hidden_params(self.flat.G)
         gst = self.flat.storage_view(self.flat.G, "inf_net.input_layer.weight")
-        if self.kind == "zeroshot":
-            gst.zero_()
-            dWdT = gst
-        elif self.kind == "combined":
-            dWdT = self.ctm_dMx[:self.C]  # (zeroed with the step's other accumulators)
-        else:
-            dWdT = None
         K_.enc_bwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, dmu=self.dmu, dlv=self.dlv, mu=self.mu,
                    logvar=self.logvar, bn_sums=self.bn_sums, bn_bsums=self.bn_bsums, bn_eps=BN_EPS,
                    pre=self.pre + pad, mask_enc=self.mask_enc, Wh=Wh, Wmu=self._p("inf_net.f_mu.weight"),
                    Wsig=self._p("inf_net.f_sigma.weight"), dWh=dWh, dbh=dbh,
                    dWmu=self._g("inf_net.f_mu.weight"), dbmu=self._g("inf_net.f_mu.bias"),
                    dWsig=self._g("inf_net.f_sigma.weight"), dbsig=self._g("inf_net.f_sigma.bias"),
-                   db1=self._g("inf_net.input_layer.bias"), dpre0=self.dpre0, xdense=xdense, dWdT=dWdT,
+                   db1=self._g("inf_net.input_layer.bias"), dpre0=self.dpre0, xdense=None, dWdT=None,
                    seed=seed, step_ctr=self.ctr)
+        if self.kind in ("zeroshot", "combined"):
+            # d W^T [C,H0] = x_ctx^T . d pre0 on the tensor cores (accumulates into a zeroed target)
+            if self.kind == "zeroshot":
+                dWdT = gst
+                K_.ctm_init_out(dWdT, bias_row=-1, bias=None)
+            else:
+                dWdT = self.ctm_dMx[:self.C]  # (zeroed with the step's other accumulators)
+            K_.ctm_split(self.dpre0[:B], self.ctx_g_hi, self.ctx_g_lo)
+            K_.ctm_vc(self.ctx_x_hi[:B], self.ctx_x_lo[:B], self.ctx_g_hi[:B], self.ctx_g_lo[:B], dWdT, m_total=self.C,
+                      n_valid=self.hidden[0])
         if use_bow:
             # d W1a^T[v,:] = sum_b x[b,v] * dpre0[b,:]  (all V rows written, zeros for unused words)
             K_.csc_spmm(self.csc.colptr, self.csc.row, self.csc.src, batch.counts, self.dpre0, gst[:V],
@@ -452,6 +484,7 @@ class FusedEngine:
                              step_ctr=self.ctr)
         if self.kind == "combined":
             self.ctm_adam_step(gscale=gscale)
+        self._refresh_ctx_shadows()
         K, V = self.K, self.V
         if self.is_prod:
             K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"),
@@ -520,34 +553,29 @@ class FusedEngine:
     # ------------------------------------------------------------------------------------------
     # inference
     # ------------------------------------------------------------------------------------------
-    def sample_theta(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, n_samples: int = 1
-                     ) -> torch.Tensor:
-        """Mean of ``n_samples`` stochastic draws of theta in eval mode (running BN statistics, no
-        dropout).  Ref: avitm.py:470-523 (get_doc_topic_distribution)."""
+    def sample_theta(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, n_samples: int = 1,
+                     thr: float = 0.0) -> torch.Tensor:
+        """Mean of ``n_samples`` stochastic draws of theta in eval mode (running BN statistics, no dropout): ONE
+        encoder pass and ONE Monte-Carlo kernel for all draws; ``thr > 0`` also applies the result extraction's
+        threshold + L1 renormalisation on the device.  Ref: avitm.py:470-523, federated_model.py:170-173."""
         B, K, V = batch.B, self.K, self.V
-        acc = torch.zeros(B, K, dtype=torch.float32, device=self.device)
-        W1T, b1, xdense, WdT = self._first_layer(x_ctx)
+        acc = torch.empty(B, K, dtype=torch.float32, device=self.device)
+        W1T, b1, pre0_ext = self._first_layer(x_ctx, B)
         Wh, bh = self._hidden_params(self.flat.P)
         use_bow = self.kind in ("bow", "combined")
         pad = [None] * (K_.GF_MAX_HIDDEN - len(self.hidden))
         K_.enc_fwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, training=False,
                    indptr=batch.indptr if use_bow else None, indices=batch.indices if use_bow else None,
-                   counts=batch.counts if use_bow else None, W1T=W1T, b1=b1, xdense=xdense, WdT=WdT,
+                   counts=batch.counts if use_bow else None, W1T=W1T, b1=b1, xdense=None, WdT=None,
+                   pre0_ext=pre0_ext,
                    Wh=Wh, bh=bh, Wmu=self._p("inf_net.f_mu.weight"), bmu=self._p("inf_net.f_mu.bias"),
                    Wsig=self._p("inf_net.f_sigma.weight"), bsig=self._p("inf_net.f_sigma.bias"),
                    pre=self.pre + pad, enc_drop_p=0.0, mask_enc_in=None, mask_enc=None,
                    mu_pre=self.mu_pre, ls_pre=self.ls_pre, bn_sums=None, seed=0)
         mu_rm, mu_rv, _ = self._bn("f_mu_batchnorm")
         ls_rm, ls_rv, _ = self._bn("f_sigma_batchnorm")
-        for _ in range(n_samples):
-            seed = (self.seed * 0x9E3779B97F4A7C15 + self.rng_calls * 0xD1B54A32D192ED03 + 7) & ((1 << 64) - 1)
-            self.rng_calls += 1
-            K_.latent_fwd(B=B, K=K, training=False, sample=True, mu_pre=self.mu_pre, ls_pre=self.ls_pre,
-                          bn_sums=self.bn_sums, mu_rm=mu_rm, mu_rv=mu_rv, ls_rm=ls_rm, ls_rv=ls_rv,
-                          bn_eps=BN_EPS, bn_momentum=BN_MOMENTUM, prior_mean=self.model.prior_mean,
-                          prior_var=self.model.prior_variance, eps_in=None, mask_theta_in=None,
-                          theta_drop_p=0.0, mu=self.mu, logvar=self.logvar, eps=self.eps,
-                          theta_s=self.theta_s, mask_theta=self.mask_theta, theta=self.theta,
-                          theta_colsum=None, kl=self.kl, loss=None, kl_weight=self.kl_weight, seed=seed)
-            acc += self.theta[:B]
-        return acc / float(n_samples)
+        seed = (self.seed * 0x9E3779B97F4A7C15 + self.rng_calls * 0xD1B54A32D192ED03 + 7) & ((1 << 64) - 1)
+        self.rng_calls += n_samples
+        K_.theta_mc(self.mu_pre, self.ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, acc, B=B, K=K, n_samples=n_samples, seed=seed,
+                    bn_eps=BN_EPS, thr=thr)
+        return acc

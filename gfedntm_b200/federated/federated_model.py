@@ -176,8 +176,8 @@ class FederatedModel:
         if self.best_components is None:
             self.best_components = self.model.beta
         self.topics = self.get_topics()
-        thetas = np.asarray(self.get_doc_topic_distribution(self.train_data))
-        self.thetas = thresholded_thetas(thetas, 3e-3)
+        thetas = np.asarray(self.get_doc_topic_distribution(self.train_data, thr=3e-3))
+        self.thetas = thresholded_thetas(thetas, 3e-3)   # (idempotent: exact float64 normalisation of the rows)
         self.betas = self.get_topic_word_distribution()
         self.logger.info(f"-- -- Saving model at {save_dir} ")
         save_model_as_npz(save_dir, self)

@@ -215,6 +215,7 @@ class FederatedTrainer:
                     eng.ctm_adam_step(gscale=1.0)   # identical update on every rank from the summed small gradient
                 else:
                     eng._refresh_ctm_shadows()
+                eng._refresh_ctx_shadows()
             else:
                 eng.forward_backward(bow, x_ctx, training=True)
                 eng.optimizer_step()
@@ -222,6 +223,7 @@ class FederatedTrainer:
                     after_backward()
                 self._launch("param", eng.step_count)
                 eng._refresh_ctm_shadows()
+                eng._refresh_ctx_shadows()
 
         if not eng.use_graphs or after_backward is not None:
             body()

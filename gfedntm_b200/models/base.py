@@ -162,6 +162,14 @@ class NeuralTopicModel:
                     and len(hidden_sizes) <= 8 and not reduce_on_plateau)
         if backend == "auto":
             backend = "fused" if fused_ok else "eager"
+            if not fused_ok and self.device.type == "cuda":
+                why = [msg for cond, msg in (
+                    (solver != "adam", f"solver='{solver}'"), (label_size != 0, "label_size>0"),
+                    (activation == "swish", "activation='swish'"), (n_components > 236, "n_components>236"),
+                    (max(hidden_sizes) > 256, "hidden size>256"), (len(hidden_sizes) > 8, "more than 8 hidden layers"),
+                    (reduce_on_plateau, "reduce_on_plateau=True")) if cond]
+                self.logger.warning("this configuration (%s) is outside the fused sm_100a engine and runs on the eager "
+                                    "PyTorch backend, typically 10-70x slower per step", ", ".join(why))
         if backend == "fused" and not fused_ok:
             raise ValueError("the fused backend needs CUDA, solver='adam', label_size=0, n_components<=236, "
                              "hidden sizes<=256 and reduce_on_plateau=False")
@@ -350,8 +358,10 @@ class NeuralTopicModel:
     # ------------------------------------------------------------------------------------------
     # inference / results
     # ------------------------------------------------------------------------------------------
-    def get_doc_topic_distribution(self, dataset, n_samples=20):
-        """Mean of ``n_samples`` stochastic theta draws per document, ``[n_docs, K]`` numpy array."""
+    def get_doc_topic_distribution(self, dataset, n_samples=20, thr: float = 0.0):
+        """Mean of ``n_samples`` stochastic theta draws per document, ``[n_docs, K]`` numpy array.  ``thr > 0``:
+        entries below it are zeroed and the rows L1-renormalised (federated_model.py:170-173), on the device for
+        the fused backend."""
         self.model.eval()
         loader = self.make_loader(dataset, shuffle=False)
         self._ensure_engine(loader)
@@ -359,7 +369,7 @@ class NeuralTopicModel:
         with torch.no_grad():
             for mb in loader:
                 if self.backend == "fused":
-                    th = self.engine.sample_theta(mb.bow, mb.x_ctx, n_samples=n_samples)
+                    th = self.engine.sample_theta(mb.bow, mb.x_ctx, n_samples=n_samples, thr=thr)
                 else:
                     x = mb.bow.to_dense()
                     th = torch.zeros(mb.size, self.n_components, device=self.device)
@@ -367,6 +377,10 @@ class NeuralTopicModel:
                         th += self.model.get_theta(x, mb.x_ctx, mb.labels)
                     th /= n_samples
                 out[mb.index] = th.double().cpu().numpy()
+        if thr > 0 and self.backend != "fused":
+            from ..utils.metrics import thresholded_thetas
+
+            out = thresholded_thetas(out, thr)
         return out
 
     def get_thetas(self, dataset, n_samples=20):

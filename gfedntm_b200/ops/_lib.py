@@ -55,6 +55,7 @@ class GfEncArgs(C.Structure):
         ("seed", _u64),
         ("step_ctr", _p),
         ("w_smem", _i),
+        ("pre0_ext", _p),
     ]
 
 
@@ -199,6 +200,8 @@ def _declare(lib: C.CDLL) -> None:
                                   _p, _p]
     for fn in ("gf_ctm_split", "gf_ctm_init_out", "gf_ctm_vc", "gf_ctm_rc", "gf_ctm_rr", "gf_adam_split"):
         getattr(lib, fn).restype = _i
+    lib.gf_theta_mc.argtypes = [_p, _p, _p, _p, _p, _p, _f, _i, _i, _i, _u64, _f, _p, _p]
+    lib.gf_theta_mc.restype = _i
     lib.gf_fed_signal.argtypes = [C.POINTER(GfFedArgs), _i, _p]
     lib.gf_fed_signal.restype = _i
     lib.gf_fed_make_tmaps.argtypes = [C.POINTER(GfFedArgs), _p]

@@ -108,7 +108,8 @@ def _fill_ptr_array(arr, tensors: Sequence[Optional[torch.Tensor]]) -> None:
 
 def enc_fwd(*, B: int, V: int, K: int, hidden: Sequence[int], act: int, training: bool,
             indptr, indices, counts, W1T, b1, xdense, WdT, Wh, bh, Wmu, bmu, Wsig, bsig, pre,
-            enc_drop_p: float, mask_enc_in, mask_enc, mu_pre, ls_pre, bn_sums, seed: int, step_ctr=None) -> None:
+            enc_drop_p: float, mask_enc_in, mask_enc, mu_pre, ls_pre, bn_sums, seed: int, step_ctr=None,
+            pre0_ext=None) -> None:
     lib = _lib.load()
     a = GfEncArgs()
     a.B, a.V, a.K, a.L = B, V, K, len(hidden)
@@ -127,6 +128,7 @@ def enc_fwd(*, B: int, V: int, K: int, hidden: Sequence[int], act: int, training
     a.mu_pre, a.ls_pre, a.bn_sums = _ptr(mu_pre), _ptr(ls_pre), _ptr(bn_sums)
     a.seed = seed & 0xFFFFFFFFFFFFFFFF
     a.step_ctr = _ptr(step_ctr)
+    a.pre0_ext = _ptr(pre0_ext)
     check(lib.gf_enc_fwd(C.byref(a), _stream()), "gf_enc_fwd")
 
 
@@ -404,3 +406,12 @@ def adam_split(p, g, m, v, out_hi, out_lo, *, p_col=None, g_col=None, m_col=None
     check(_lib.load().gf_adam_split(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.stride(0), rows, cols, _ptr(p_col), _ptr(g_col),
                                     _ptr(m_col), _ptr(v_col), _ptr(out_hi), _ptr(out_lo), out_hi.stride(0), lr, b1, b2, eps,
                                     wd, step, gscale, int(do_update), _ptr(step_ctr), _stream()), "gf_adam_split")
+
+
+def theta_mc(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, out, *, B: int, K: int, n_samples: int, seed: int,
+             bn_eps: float = 1e-5, thr: float = 0.0) -> None:
+    """Mean of ``n_samples`` reparameterised soft-max draws (eval-mode BatchNorm) in one launch, with the
+    ``thr`` threshold + L1 renormalisation epilogue of the reference's result extraction (``thr <= 0``: off)."""
+    check(_lib.load().gf_theta_mc(_ptr(mu_pre), _ptr(ls_pre), _ptr(mu_rm), _ptr(mu_rv), _ptr(ls_rm), _ptr(ls_rv), bn_eps,
+                                  B, K, n_samples, seed & 0xFFFFFFFFFFFFFFFF, float(thr), _ptr(out), _stream()),
+          "gf_theta_mc")

@@ -140,12 +140,21 @@ typedef struct GfEncArgs {
   unsigned long long seed;
   const long long* step_ctr; /* optional device counters (gf_step_begin): seed advances by ctr[0]    */
   int w_smem;                /* set by gf_enc_fwd (callers leave 0): head weights staged in shared memory */
+  const float* pre0_ext;     /* optional [B, H0]: first-layer contribution computed elsewhere (the dense contextual
+                                input on the tensor cores, gf_ctm_rc); added to the pre-activation, xdense unused */
 } GfEncArgs;
 /* Device-side step counters, so that a whole training step can be replayed from a CUDA graph:
  * ctr[0] counts forward passes (advances the dropout / reparameterisation seeds), ctr[1] counts
  * optimiser steps (Adam bias correction, federated epoch flag).                                  */
 int gf_step_begin(long long* ctr, int inc_rng, int inc_opt, void* stream);
 int gf_enc_fwd(const GfEncArgs* args, void* stream);
+
+/* Monte-Carlo document-topic inference in one launch: mean over n_samples reparameterised soft-max draws from the
+ * eval-mode encoder outputs (gf_enc_fwd with training = 0), then entries < thr zeroed and rows L1-renormalised
+ * (thr <= 0: plain mean).  Ref: avitm.py:470-523 + federated_model.py:170-173.                              */
+int gf_theta_mc(const float* mu_pre, const float* ls_pre, const float* mu_rm, const float* mu_rv, const float* ls_rm,
+                const float* ls_rv, float bn_eps, int B, int K, int n_samples, unsigned long long seed, float thr,
+                float* out, void* stream);
 
 typedef struct GfLatentArgs {
   int B, K, training, sample;   /* sample: draw eps ~ N(0,1) (else eps = 0 unless eps_in)     */

@@ -137,3 +137,42 @@ def test_engine_loss_decreases_and_theta_inference():
     torch.testing.assert_close(theta.sum(1), torch.ones(B, device="cuda"), rtol=1e-4, atol=1e-4)
     val = eng.forward_backward(batch, training=False, sample=True, need_grad=False)
     assert torch.isfinite(val).all()
+
+
+def test_theta_mc_matches_per_draw_softmax_statistics():
+    """gf_theta_mc (all Monte-Carlo draws + threshold / renormalisation in one launch) against the same
+    computation in PyTorch: the draws are random, so the mean over many draws must match the analytic
+    expectation estimated with an independent large sample; the epilogue must match exactly."""
+    from gfedntm_b200.ops import kernels as K_
+
+    torch.manual_seed(0)
+    B, K = 37, 50
+    dd = dict(dtype=torch.float32, device="cuda")
+    mu_pre, ls_pre = torch.randn(B, K, **dd), torch.randn(B, K, **dd) * 0.3 - 1.0
+    mu_rm, ls_rm = torch.randn(K, **dd) * 0.1, torch.randn(K, **dd) * 0.1
+    mu_rv, ls_rv = torch.rand(K, **dd) + 0.5, torch.rand(K, **dd) + 0.5
+    mu = (mu_pre - mu_rm) * torch.rsqrt(mu_rv + 1e-5)
+    sd = torch.exp(0.5 * (ls_pre - ls_rm) * torch.rsqrt(ls_rv + 1e-5))
+    n = 4000
+    out = torch.empty(B, K, **dd)
+    K_.theta_mc(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, out, B=B, K=K, n_samples=n, seed=123, thr=0.0)
+    ref = torch.zeros(B, K, **dd)
+    for _ in range(40):
+        ref += torch.softmax(mu + torch.randn(100, B, K, **dd) * sd, dim=-1).sum(0)
+    ref /= 4000
+    torch.testing.assert_close(out.sum(1), torch.ones(B, **dd), rtol=1e-4, atol=1e-4)
+    assert float((out - ref).abs().max()) < 0.02  # two independent 4000-draw estimates of a value in [0,1]
+    # different seeds give different draws, the same seed the same result
+    out2, out3 = torch.empty_like(out), torch.empty_like(out)
+    K_.theta_mc(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, out2, B=B, K=K, n_samples=20, seed=1, thr=0.0)
+    K_.theta_mc(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, out3, B=B, K=K, n_samples=20, seed=1, thr=0.0)
+    assert torch.equal(out2, out3)
+    K_.theta_mc(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, out3, B=B, K=K, n_samples=20, seed=2, thr=0.0)
+    assert not torch.equal(out2, out3)
+    # threshold + L1 renormalisation epilogue (federated_model.py:170-173) on the same draws
+    thr = 3e-3
+    K_.theta_mc(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, out3, B=B, K=K, n_samples=20, seed=1, thr=thr)
+    want = out2.clone()
+    want[want < thr] = 0
+    want = want / want.sum(1, keepdim=True)
+    torch.testing.assert_close(out3, want, rtol=1e-5, atol=1e-7)
