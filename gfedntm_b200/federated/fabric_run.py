@@ -92,9 +92,17 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
     dist.all_reduce(steps, op=dist.ReduceOp.MAX)
     steps_per_epoch = int(steps.item())
     total = min(kw["max_iters"], steps_per_epoch * int(params["num_epochs"]))
+    start = 0
+    ckpt_dir, ckpt_every = kw.get("checkpoint_dir"), int(kw.get("checkpoint_every") or 0)
+    if kw.get("resume") and ckpt_dir:
+        from ..utils.checkpoint import fabric_checkpoint_path, load_fabric_checkpoint
+
+        if os.path.exists(fabric_checkpoint_path(ckpt_dir, rank)):
+            start = int(load_fabric_checkpoint(ckpt_dir, trainer, loader)["global_step"])
+            log.info("resumed from %s at global step %d", ckpt_dir, start)
     it = iter(loader)
     model.model.train()
-    for step in range(total):
+    for step in range(start, total):
         try:
             mb = next(it)
         except StopIteration:
@@ -104,6 +112,10 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
         if rank == 0 and (step % 100 == 0 or step == total - 1):
             log.info("global step %d/%d  client-1 minibatch loss/doc %.3f", step + 1, total,
                      float(loss.item()) / mb.size)
+        if ckpt_dir and ckpt_every > 0 and (step + 1) % ckpt_every == 0 and step + 1 < total:
+            from ..utils.checkpoint import save_fabric_checkpoint
+
+            save_fabric_checkpoint(ckpt_dir, trainer, loader, global_step=step + 1)
     torch.cuda.synchronize()
     dist.barrier()
     trainer.materialize()  # complete fp32 parameters on every rank (the master copy of beta is sharded by owner)
@@ -126,7 +138,8 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
 def run_fabric_federation(*, n_clients: int, source: str, data_type: str, fos: str, model_type: str,
                           training_params: dict, max_iters: int, save_client: str, save_server: str,
                           logs_client: str, agg: str = "grad", port: Optional[int] = None,
-                          grads_to_share: Optional[list] = None) -> None:
+                          grads_to_share: Optional[list] = None, checkpoint_dir: Optional[str] = None,
+                          checkpoint_every: int = 0, resume: bool = False) -> None:
     import torch
     import torch.multiprocessing as mp
 
@@ -135,5 +148,6 @@ def run_fabric_federation(*, n_clients: int, source: str, data_type: str, fos: s
     port = port or (29400 + os.getpid() % 500)
     kw = dict(source=source, data_type=data_type, fos=fos, model_type=model_type,
               training_params=training_params, max_iters=max_iters, save_client=save_client,
-              save_server=save_server, logs_client=logs_client, agg=agg, grads_to_share=grads_to_share)
+              save_server=save_server, logs_client=logs_client, agg=agg, grads_to_share=grads_to_share,
+              checkpoint_dir=checkpoint_dir, checkpoint_every=checkpoint_every, resume=resume)
     mp.spawn(_worker, args=(n_clients, port, kw), nprocs=n_clients, join=True)

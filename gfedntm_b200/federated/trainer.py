@@ -46,6 +46,14 @@ class FederatedTrainer:
         self.aggregator: Optional[FusedAggregator] = None
         self._agg_events: List = []
         self.global_step = 0
+        # observability (utils/observability.py): NVTX range per global step, CUDA-event step timer and a JSON-lines
+        # sink, switched on by GFEDNTM_METRICS_JSONL=<path> (or by assigning .metrics / .timer)
+        from ..utils.observability import JsonlMetrics, StepTimer
+
+        path = os.environ.get("GFEDNTM_METRICS_JSONL")
+        self.metrics = JsonlMetrics(f"{path}.rank{rank}" if path and world_size > 1 else path)
+        self.timer = StepTimer(enabled=bool(path))
+        self.metrics_every = int(os.environ.get("GFEDNTM_METRICS_EVERY", "100"))
 
     # ------------------------------------------------------------------------------------------
     def prepare(self, loader) -> None:
@@ -182,6 +190,18 @@ class FederatedTrainer:
         """One synchronous global step (local minibatch + aggregation).  Returns this client's summed
         minibatch loss (device tensor).  ``after_backward`` (verification hook): called between the local
         backward pass and the closing aggregation launch; forces the eager (non-graph) path."""
+        from ..utils.observability import nvtx_range
+
+        with nvtx_range("gfedntm.global_step"), self.timer.region("global_step"):
+            loss = self._step(bow, x_ctx, after_backward)
+        if self.metrics.path and self.global_step % self.metrics_every == 0:
+            t = self.timer.summary()  # (one synchronisation per logging interval)
+            self.metrics.log(step=self.global_step, rank=self.rank, world=self.world, agg=self.agg,
+                             loss_per_doc=float(loss.item()) / max(bow.B, 1), ms_per_step=t.get("global_step"),
+                             docs_per_s=(1e3 * bow.B * self.world / t["global_step"]) if t.get("global_step") else None)
+        return loss
+
+    def _step(self, bow: CsrBatch, x_ctx, after_backward) -> torch.Tensor:
         eng = self.model.engine
         self.global_step += 1
         if self.world == 1:

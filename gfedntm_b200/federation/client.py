@@ -9,6 +9,7 @@ are ignored; the client wakes up when the server's STOP arrives instead of sleep
 from __future__ import annotations
 
 import logging
+import os
 import threading
 import time
 from concurrent import futures
@@ -32,7 +33,8 @@ class FederatedClientServer(federated_pb2_grpc.FederationServerServicer):
     """Serves ``getGradient`` / ``sendAggregatedTensor`` for one client."""
 
     def __init__(self, local_model: Union[FederatedAVITM, FederatedCTM], train_data, id: int,
-                 save_client: str, logger=None) -> None:
+                 save_client: str, logger=None, checkpoint_path: str = None, checkpoint_every: int = 0,
+                 resume: bool = False) -> None:
         self._local_model = local_model
         self.id = id
         self._save_client = save_client
@@ -41,10 +43,23 @@ class FederatedClientServer(federated_pb2_grpc.FederationServerServicer):
         self._lock = threading.Lock()
         self._logger = logger if logger else make_logger("ClientServer", None)
         self._local_model.preFit(train_data)
+        # mid-training checkpoints (utils/checkpoint.py): every `checkpoint_every` aggregated updates; `resume`
+        # restores model, optimiser, bookkeeping and RNG state before the first pull
+        self._ckpt_path, self._ckpt_every, self._n_updates = checkpoint_path, int(checkpoint_every or 0), 0
+        if resume and checkpoint_path and os.path.exists(checkpoint_path):
+            from ..utils.checkpoint import load_training_checkpoint
+
+            load_training_checkpoint(checkpoint_path, self._local_model, getattr(self._local_model, "train_loader", None))
+            self._logger.info("-- -- Client %s resumed from %s", str(self.id), checkpoint_path)
+        self._last_iter, self._last_reply = None, None
         self._logger.info("FederatedClientServer object initialized")
 
     def getGradient(self, request, context):
         with self._lock:
+            # Idempotent per global iteration: a server-side retry of a timed-out pull must not train a second
+            # time on the same minibatch (the optimiser would advance twice while the counters advance once).
+            if self._last_reply is not None and request.iter == self._last_iter:
+                return self._last_reply
             self.global_epoch = request.iter
             gr_upt = self._local_model.train_mb_delta()
             header = federated_pb2.MessageHeader(
@@ -57,7 +72,9 @@ class FederatedClientServer(federated_pb2_grpc.FederationServerServicer):
                        for k, v in gr_upt.items() if k not in ("current_mb", "current_epoch", "num_epochs")]
             self._logger.info("-- -- Client %s sent gradient update for global epoch %s", str(self.id),
                               self.global_epoch)
-            return federated_pb2.ClientTensorRequest(header=header, metadata=metadata, updates=updates)
+            reply = federated_pb2.ClientTensorRequest(header=header, metadata=metadata, updates=updates)
+            self._last_iter, self._last_reply = request.iter, reply
+            return reply
 
     def sendAggregatedTensor(self, request, context):
         mt = request.header.message_type
@@ -67,7 +84,18 @@ class FederatedClientServer(federated_pb2_grpc.FederationServerServicer):
                                   str(self.id), self.global_epoch)
                 state = proto_to_modelStateDict(request.nndata.modelUpdate)
                 self._local_model.deltaUpdateFit(modelStateDict=state, save_dir=self._save_client)
-            header = federated_pb2.MessageHeader(id_request=str(self.global_epoch),
+                self._n_updates += 1
+                if self._ckpt_path and self._ckpt_every > 0 and self._n_updates % self._ckpt_every == 0 \
+                        and not self._local_model.finished:
+                    from ..utils.checkpoint import save_training_checkpoint
+
+                    save_training_checkpoint(self._ckpt_path, self._local_model,
+                                             getattr(self._local_model, "train_loader", None),
+                                             extra={"updates": self._n_updates, "global_epoch": int(self.global_epoch)})
+            # the ack tells the server whether this client has just reached num_epochs (it rolls its epoch counter
+            # and saves its results while installing the aggregate), so that it is not pulled again
+            done = ";finished" if self._local_model.finished else ""
+            header = federated_pb2.MessageHeader(id_request=str(self.global_epoch) + done,
                                                  message_type=federated_pb2.MessageType.CLIENT_CONFIRM_RECEIVED)
             return federated_pb2.ClientReceivedResponse(header=header)
         if mt == federated_pb2.MessageType.SERVER_STOP_TRAINING_REQUEST:
@@ -88,8 +116,10 @@ class Client:
     def __init__(self, id: int, stub, local_corpus, data_type: str, opts_server: list, save_client: str,
                  logs_client: str, sleep_time: int, base_port: int,
                  grads_to_share=["prior_mean", "prior_variance", "beta"], logger=None, share: str = "param",
-                 backend: str = "auto", device=None) -> None:
+                 backend: str = "auto", device=None, checkpoint_path: str = None, checkpoint_every: int = 0,
+                 resume: bool = False) -> None:
         self.id = id
+        self._ckpt = (checkpoint_path, checkpoint_every, resume)
         self._stub = stub
         self._save_client = save_client
         self._sleep_time = sleep_time
@@ -189,7 +219,8 @@ class Client:
     def __start_client_server(self, opts_server: list, save_client: str) -> None:
         self.client_server = grpc.server(futures.ThreadPoolExecutor(max_workers=4), options=opts_server)
         self.federated_server = FederatedClientServer(self.local_model, self.train_data, self.id, save_client,
-                                                      self._logger)
+                                                      self._logger, checkpoint_path=self._ckpt[0],
+                                                      checkpoint_every=self._ckpt[1], resume=self._ckpt[2])
         federated_pb2_grpc.add_FederationServerServicer_to_server(self.federated_server, self.client_server)
         self.client_server.add_insecure_port("[::]:" + str(self._base_port + self.id))
         self.client_server.start()

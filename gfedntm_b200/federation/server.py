@@ -361,8 +361,8 @@ class FederatedServer(federated_pb2_grpc.FederationServicer):
                 # ---- push (concurrently)
                 acks = list(pool.map(lambda c: self._call(c, "sendAggregatedTensor", agg_request), alive))
                 for c, ack in zip(alive, acks):
-                    if ack is None:
-                        c.finished = True
+                    if ack is None or ack.header.id_request.endswith(";finished"):
+                        c.finished = True   # unreachable, or reached num_epochs while installing this aggregate
                 # a client rolls its epoch counter while installing the aggregate; its next pull reports it
                 for c in alive:
                     if c.num_max_epochs > 0 and c.current_epoch >= c.num_max_epochs:

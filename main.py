@@ -76,7 +76,8 @@ def load_client_corpus(data_type: str, source: str, id_client: int, fos: str):
 
 
 def start_client(id_client, data_type, fos, source, address, opts_client, opts_server, save_client, logs_client,
-                 client_sleep_time, grads_to_share, base_port=50051, agg="param", backend="auto"):
+                 client_sleep_time, grads_to_share, base_port=50051, agg="param", backend="auto", checkpoint_dir=None,
+                 checkpoint_every=0, resume=False):
     import grpc
 
     from gfedntm_b200.federation.client import Client
@@ -94,7 +95,9 @@ def start_client(id_client, data_type, fos, source, address, opts_client, opts_s
         return Client(id=id_client, stub=stub, local_corpus=corpus, data_type=data_type, opts_server=opts_server,
                       save_client=save_path, logs_client=logs_path, sleep_time=client_sleep_time,
                       base_port=base_port, grads_to_share=grads_to_share,
-                      share="grad" if agg == "grad" else "param", backend=backend)
+                      share="grad" if agg == "grad" else "param", backend=backend,
+                      checkpoint_path=(os.path.join(checkpoint_dir, f"client{id_client}.ckpt") if checkpoint_dir else None),
+                      checkpoint_every=checkpoint_every, resume=resume)
 
 
 def main(argv=None):
@@ -118,6 +121,11 @@ def main(argv=None):
                         help="Run an in-box federation with this many clients, one per GPU, aggregated by the "
                              "fused NVLink kernel (no gRPC data plane).")
     parser.add_argument("--local", action="store_true", help="Use the [addresses] local entry (no Docker DNS).")
+    parser.add_argument("--checkpoint_every", type=int, default=0,
+                        help="Write a mid-training checkpoint every N global steps (clients and --fabric ranks).")
+    parser.add_argument("--checkpoint_dir", type=str, default=os.path.join(WORKDIR, "static/checkpoints"),
+                        help="Directory of the mid-training checkpoints.")
+    parser.add_argument("--resume", action="store_true", help="Continue from the checkpoint in --checkpoint_dir.")
     args = parser.parse_args(argv)
 
     from gfedntm_b200.utils.auxiliary_functions import read_config_experiments
@@ -158,7 +166,8 @@ def main(argv=None):
                                      fos=args.fos, model_type=args.model_type, training_params=training_params,
                                      max_iters=args.max_iters, save_client=save_client, save_server=save_server,
                                      logs_client=logs_client, agg="grad" if agg == "grad" else "param",
-                                     grads_to_share=grads_to_share)
+                                     grads_to_share=grads_to_share, checkpoint_dir=args.checkpoint_dir,
+                                     checkpoint_every=args.checkpoint_every, resume=args.resume)
     if args.id == 0:
         print("Starting server with", args.min_clients_federation,
               "as minimum number of clients to start the federation.")
@@ -174,7 +183,8 @@ def main(argv=None):
                         address=address, opts_client=opts_client, opts_server=opts_server,
                         save_client=save_client, logs_client=logs_client,
                         client_sleep_time=int(config.get("federation", "client_sleep_time")),
-                        grads_to_share=grads_to_share, base_port=base_port, agg=agg, backend=backend)
+                        grads_to_share=grads_to_share, base_port=base_port, agg=agg, backend=backend,
+                        checkpoint_dir=args.checkpoint_dir, checkpoint_every=args.checkpoint_every, resume=args.resume)
 
 
 if __name__ == "__main__":

@@ -132,3 +132,53 @@ def test_ctm_federation_stops_at_num_epochs(tmp_path):
         assert os.path.exists(str(out / f"client{cid}" / f"model_{cid}_epoch_1.npz"))  # CTM per-epoch snapshot
         assert os.path.exists(str(out / f"client{cid}" / f"model_{cid}.npz"))
         assert clients[cid].local_model.model.state_dict()["inf_net.adapt_bert.weight"].shape[1] == 8
+
+
+def test_pull_is_idempotent_per_iteration_and_clients_checkpoint(tmp_path):
+    """A retried ``getGradient`` for the same global iteration returns the cached payload instead of training a
+    second time (server.py's ``_call`` retries pulls), and a client servicer writes / restores mid-training
+    checkpoints."""
+    import torch
+
+    from gfedntm_b200.federated.federated_avitm import FederatedAVITM
+    from gfedntm_b200.federation.client import FederatedClientServer
+    from gfedntm_b200.models import BOWDataset
+    from gfedntm_b200.protos import federated_pb2
+    from gfedntm_b200.utils.auxiliary_functions import modelStateDict_to_proto
+
+    def make(resume=False):
+        torch.manual_seed(0)
+        rng = np.random.default_rng(0)
+        X = rng.poisson(0.3, (40, 60)).astype(np.float32)
+        X[X.sum(1) == 0, 0] = 1
+        params = dict(input_size=60, n_components=4, model_type="prodLDA", hidden_sizes=(8, 8), activation="softplus",
+                      dropout=0.2, learn_priors=True, batch_size=16, lr=2e-3, momentum=0.99, solver="adam", num_epochs=5,
+                      reduce_on_plateau=False, num_samples=2, verbose=False, seed=1, topic_prior_mean=0.0,
+                      topic_prior_variance=None, num_data_loader_workers=0)
+        import logging
+
+        m = FederatedAVITM(params, ["beta", "prior_mean"], logging.getLogger("t"), backend="eager", device="cpu")
+        srv = FederatedClientServer(m, BOWDataset(X, [f"w{i}" for i in range(60)]), 1, str(tmp_path / "model_1"),
+                                    checkpoint_path=str(tmp_path / "client1.ckpt"), checkpoint_every=2, resume=resume)
+        return m, srv
+
+    m, srv = make()
+    r1 = srv.getGradient(federated_pb2.ServerGetGradientRequest(iter=0), None)
+    steps_after_first = int(m.optimizer.state_dict()["state"][0]["step"])
+    r2 = srv.getGradient(federated_pb2.ServerGetGradientRequest(iter=0), None)
+    assert r2 is r1 and int(m.optimizer.state_dict()["state"][0]["step"]) == steps_after_first
+    # two aggregated updates -> a checkpoint exists; a fresh client restores the same weights and bookkeeping
+    for it in range(2):
+        if it:
+            srv.getGradient(federated_pb2.ServerGetGradientRequest(iter=it), None)
+        sd = {k: v for k, v in m.model.state_dict().items() if k in ("beta", "prior_mean")}
+        req = federated_pb2.ServerAggregatedTensorRequest(
+            header=federated_pb2.MessageHeader(message_type=federated_pb2.MessageType.SERVER_AGGREGATED_TENSOR_SEND),
+            nndata=federated_pb2.NNUpdate(modelUpdate=modelStateDict_to_proto(sd, -1, "avitm")))
+        ack = srv.sendAggregatedTensor(req, None)
+        assert not ack.header.id_request.endswith(";finished")
+    assert os.path.exists(tmp_path / "client1.ckpt")
+    m2, srv2 = make(resume=True)
+    assert m2.current_mb == m.current_mb and m2.samples_processed == m.samples_processed
+    for k, v in m.model.state_dict().items():
+        assert torch.equal(v, m2.model.state_dict()[k]), k
