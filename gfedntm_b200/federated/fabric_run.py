@@ -39,6 +39,8 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
     device = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
     cid = rank + 1
+    logging.basicConfig(level=logging.INFO,
+                        format="%(asctime)s [%(name)-14.14s] [%(levelname)-5.5s] %(message)s")
     log = logging.getLogger(f"fabric-client{cid}")
     log.setLevel(logging.INFO)
 
