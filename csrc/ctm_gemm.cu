@@ -21,6 +21,7 @@
 // shadows: [rows, 64-element 128-byte swizzled boxes]; the same global layout serves as K-major or MN-major
 // operand (the byte image is identical, only the descriptor differs), so A' and W each have ONE shadow layout.
 #include "ptx.cuh"
+#include "opt_math.cuh"
 #include "tmap.h"
 #include "../include/gfedntm_kernels.h"
 
@@ -439,14 +440,14 @@ __global__ void ctm_init_out_kernel(float* __restrict__ out, int rows, int cols,
 // refreshes the shadows.  One thread per 8 consecutive shadow columns (16-byte hi / lo stores).
 struct AdamS {
   float lr, b1, b2, eps, bc1, bc2_sqrt, wd, gscale;
+  int solver;
   const long long* step_ctr;
 };
 __device__ __forceinline__ float adam_s(float p, float g, float& m, float& v, const AdamS& h) {
-  g *= h.gscale;
-  if (h.wd != 0.f) g = fmaf(h.wd, p, g);
-  m = fmaf(h.b1, m, (1.f - h.b1) * g);
-  v = fmaf(h.b2, v, (1.f - h.b2) * g * g);
-  return p - (h.lr / h.bc1) * (m / (sqrtf(v) / h.bc2_sqrt + h.eps));
+  OptH o;
+  o.lr = h.lr; o.b1 = h.b1; o.b2 = h.b2; o.eps = h.eps; o.bc1 = h.bc1; o.bc2_sqrt = h.bc2_sqrt; o.wd = h.wd;
+  o.solver = h.solver;
+  return opt_update(p, g * h.gscale, m, v, o);
 }
 __global__ void __launch_bounds__(256)
 adam_split_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
@@ -657,7 +658,7 @@ extern "C" int gf_ctm_rr(const void* x_hi, const void* x_lo, const void* z_hi, c
 extern "C" int gf_adam_split(float* p, const float* g, float* m, float* v, long long ld, int rows, int cols, float* p_col,
                              const float* g_col, float* m_col, float* v_col, void* out_hi, void* out_lo, int ldo, float lr,
                              float b1, float b2, float eps, float wd, int step, float gscale, int do_update,
-                             const long long* step_ctr, void* stream_) {
+                             const long long* step_ctr, int solver, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(rows > 0 && ldo % 8 == 0 && ldo >= cols + (p_col != nullptr ? 1 : 0), "ldo");
   GF_ARG_CHECK(!do_update || (g != nullptr && m != nullptr && v != nullptr), "gradient / moments");
@@ -665,7 +666,7 @@ extern "C" int gf_adam_split(float* p, const float* g, float* m, float* v, long 
                "gradient / moments of the extra column");
   GF_ARG_CHECK(!do_update || step >= 1 || step_ctr != nullptr, "Adam step must be >= 1");
   AdamS h;
-  h.lr = lr; h.b1 = b1; h.b2 = b2; h.eps = eps; h.wd = wd; h.gscale = gscale; h.step_ctr = step_ctr;
+  h.lr = lr; h.b1 = b1; h.b2 = b2; h.eps = eps; h.wd = wd; h.gscale = gscale; h.step_ctr = step_ctr; h.solver = solver;
   const int t = step >= 1 ? step : 1;
   h.bc1 = 1.f - powf(b1, (float)t);
   h.bc2_sqrt = sqrtf(1.f - powf(b2, (float)t));

@@ -325,7 +325,7 @@ extern "C" int gf_fed_aggregate(const GfFedArgs* a, void* stream_) {
                      a->ranges[i].off + a->ranges[i].len <= a->flat_n,
                  "ranges must be 16-byte aligned pieces of [0, flat_n)");
   AdamF h;
-  h.lr = a->lr; h.b1 = a->b1; h.b2 = a->b2; h.eps = a->eps; h.wd = a->wd;
+  h.lr = a->lr; h.b1 = a->b1; h.b2 = a->b2; h.eps = a->eps; h.wd = a->wd; h.solver = a->solver;
   const int step = a->step >= 1 ? a->step : 1;
   h.bc1 = 1.f - powf(a->b1, (float)step);
   h.bc2_sqrt = sqrtf(1.f - powf(a->b2, (float)step));

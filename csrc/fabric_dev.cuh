@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <cuda.h>
 #include "ptx.cuh"
+#include "opt_math.cuh"
 #include "../include/gfedntm_kernels.h"
 
 namespace gf {
@@ -68,15 +69,9 @@ __device__ __forceinline__ void fed_push_b128(void* const* per_rank, void* mc, s
     if (per_rank[c] != nullptr) *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(per_rank[c]) + elem_off_bf16) = v;
 }
 
-struct AdamF {
-  float lr, b1, b2, eps, bc1, bc2_sqrt, wd;
-};
+typedef OptH AdamF;  // (name kept from when Adam was the only solver; see opt_math.cuh)
 __device__ __forceinline__ float adam_upd(float p, float g, float& m, float& v, const AdamF& h) {
-  if (h.wd != 0.f) g = fmaf(h.wd, p, g);
-  m = fmaf(h.b1, m, (1.f - h.b1) * g);
-  v = fmaf(h.b2, v, (1.f - h.b2) * g * g);
-  const float denom = sqrtf(v) / h.bc2_sqrt + h.eps;
-  return p - (h.lr / h.bc1) * (m / denom);
+  return opt_update(p, g, m, v, h);
 }
 
 // A peer that died (out of memory, crashed process) would otherwise leave every other rank spinning on its
@@ -115,7 +110,7 @@ __device__ __forceinline__ void fed_sync256() { asm volatile("bar.sync 2, 256;" 
 // Adam constants for step `t` (bias corrections on the device: graph replays read t from a counter)
 __device__ __forceinline__ AdamF fed_adam_consts(const GfFedArgs& a, long long t) {
   AdamF h;
-  h.lr = a.lr; h.b1 = a.b1; h.b2 = a.b2; h.eps = a.eps; h.wd = a.wd;
+  h.lr = a.lr; h.b1 = a.b1; h.b2 = a.b2; h.eps = a.eps; h.wd = a.wd; h.solver = a.solver;
   h.bc1 = 1.f - powf(h.b1, (float)t);
   h.bc2_sqrt = sqrtf(1.f - powf(h.b2, (float)t));
   return h;

@@ -1,0 +1,55 @@
+// One parameter update of the supported solvers, shared by every kernel that steps parameters (flat Adam, the beta
+// kernels, the fused Adam + shadow refresh and the federated aggregation).  Two state buffers per parameter (m, v)
+// hold whatever the solver needs.  Ref: the optimiser factory of the reference, avitm.py:141-153 -- torch.optim
+// Adam(betas=(momentum, 0.99)), SGD(momentum), Adagrad, Adadelta, RMSprop(momentum) with torch's defaults.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace gf {
+
+enum : int { GF_SOLVER_ADAM = 0, GF_SOLVER_SGD = 1, GF_SOLVER_ADAGRAD = 2, GF_SOLVER_ADADELTA = 3, GF_SOLVER_RMSPROP = 4 };
+
+struct OptH {
+  float lr, b1, b2, eps, bc1, bc2_sqrt, wd;  // adam: bc1 = 1-b1^t, bc2_sqrt = sqrt(1-b2^t); others: unused
+  int solver;
+};
+
+//   adam      m = b1 m + (1-b1) g,  v = b2 v + (1-b2) g^2,  p -= lr/bc1 * m / (sqrt(v)/bc2_sqrt + eps)
+//   sgd       m = b1 m + g                                   p -= lr m                (b1 = momentum)
+//   adagrad   v += g^2                                       p -= lr g / (sqrt(v) + eps)
+//   adadelta  v = b2 v + (1-b2) g^2, d = sqrt(m+eps)/sqrt(v+eps) g, m = b2 m + (1-b2) d^2,  p -= lr d   (b2 = rho)
+//   rmsprop   v = b2 v + (1-b2) g^2, a = g / (sqrt(v)+eps);  b1 > 0: m = b1 m + a, p -= lr m;  else p -= lr a
+__device__ __forceinline__ float opt_update(float p, float g, float& m, float& v, const OptH& h) {
+  if (h.wd != 0.f) g = fmaf(h.wd, p, g);
+  switch (h.solver) {
+    case GF_SOLVER_SGD:
+      m = fmaf(h.b1, m, g);
+      return p - h.lr * m;
+    case GF_SOLVER_ADAGRAD:
+      v = fmaf(g, g, v);
+      return p - h.lr * g / (sqrtf(v) + h.eps);
+    case GF_SOLVER_ADADELTA: {
+      v = fmaf(h.b2, v, (1.f - h.b2) * g * g);
+      const float d = sqrtf(m + h.eps) / sqrtf(v + h.eps) * g;
+      m = fmaf(h.b2, m, (1.f - h.b2) * d * d);
+      return p - h.lr * d;
+    }
+    case GF_SOLVER_RMSPROP: {
+      v = fmaf(h.b2, v, (1.f - h.b2) * g * g);
+      const float a = g / (sqrtf(v) + h.eps);
+      if (h.b1 > 0.f) {
+        m = fmaf(h.b1, m, a);
+        return p - h.lr * m;
+      }
+      return p - h.lr * a;
+    }
+    default: {
+      m = fmaf(h.b1, m, (1.f - h.b1) * g);
+      v = fmaf(h.b2, v, (1.f - h.b2) * g * g);
+      const float denom = sqrtf(v) / h.bc2_sqrt + h.eps;
+      return p - (h.lr / h.bc1) * (m / denom);
+    }
+  }
+}
+
+}  // namespace gf

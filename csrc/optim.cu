@@ -2,6 +2,7 @@
 // (torch.optim.Adam, betas=(momentum, 0.99)), plus the bf16 operand shadows the tensor-core
 // decoder sweeps read (beta [Kp,ldb] and beta^T [V,Kp]).
 #include "ptx.cuh"
+#include "opt_math.cuh"
 #include "tmap.h"
 #include "../include/gfedntm_kernels.h"
 
@@ -9,6 +10,7 @@ namespace gf {
 
 struct AdamH {
   float lr, b1, b2, eps, bc1, bc2_sqrt, wd;  // bc1 = 1-b1^t, bc2_sqrt = sqrt(1-b2^t)
+  int solver;                               // GfSolver (opt_math.cuh)
   const long long* step_ctr;                // optional: t = step_ctr[1] read on the device
 };
 __device__ __forceinline__ AdamH resolve_step(AdamH h) {
@@ -21,11 +23,10 @@ __device__ __forceinline__ AdamH resolve_step(AdamH h) {
 }
 
 __device__ __forceinline__ float adam_one(float p, float g, float& m, float& v, const AdamH& h) {
-  if (h.wd != 0.f) g = fmaf(h.wd, p, g);
-  m = fmaf(h.b1, m, (1.f - h.b1) * g);
-  v = fmaf(h.b2, v, (1.f - h.b2) * g * g);
-  const float denom = sqrtf(v) / h.bc2_sqrt + h.eps;
-  return p - (h.lr / h.bc1) * (m / denom);
+  OptH o;
+  o.lr = h.lr; o.b1 = h.b1; o.b2 = h.b2; o.eps = h.eps; o.bc1 = h.bc1; o.bc2_sqrt = h.bc2_sqrt; o.wd = h.wd;
+  o.solver = h.solver;
+  return opt_update(p, g, m, v, o);
 }
 
 __global__ void __launch_bounds__(256) adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g,
@@ -147,29 +148,31 @@ __global__ void __launch_bounds__(256) adam_beta_vec_kernel(float* __restrict__ 
 
 using namespace gf;
 
-static AdamH make_h(float lr, float b1, float b2, float eps, float wd, int step, const long long* step_ctr) {
+static AdamH make_h(float lr, float b1, float b2, float eps, float wd, int step, const long long* step_ctr, int solver = 0) {
   AdamH h;
   h.lr = lr; h.b1 = b1; h.b2 = b2; h.eps = eps; h.wd = wd; h.step_ctr = step_ctr;
   h.bc1 = 1.f - powf(b1, (float)step);
   h.bc2_sqrt = sqrtf(1.f - powf(b2, (float)step));
+  h.solver = solver;
   return h;
 }
 
 extern "C" int gf_adam_flat(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
-                            float eps, float wd, int step, float gscale, const long long* step_ctr, void* stream_) {
+                            float eps, float wd, int step, float gscale, const long long* step_ctr, int solver, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   if (n <= 0) return GF_OK;
+  GF_ARG_CHECK(solver >= 0 && solver <= 4, "solver");
   GF_ARG_CHECK(step >= 1 || step_ctr != nullptr, "Adam step must be >= 1");
   if (step < 1) step = 1;
   const long long thr = (n + 3) / 4;
-  adam_flat_kernel<<<(unsigned)((thr + 255) / 256), 256, 0, st>>>(p, g, m, v, n, make_h(lr, b1, b2, eps, wd, step, step_ctr), gscale);
+  adam_flat_kernel<<<(unsigned)((thr + 255) / 256), 256, 0, st>>>(p, g, m, v, n, make_h(lr, b1, b2, eps, wd, step, step_ctr, solver), gscale);
   GF_LAUNCHED();
   return GF_OK;
 }
 
 extern "C" int gf_adam_beta(float* p, const float* g, float* m, float* v, int K, int V, int ldp, int ldg,
                             void* beta_bf, int ldb, void* betaT_bf, int Kp, float lr, float b1, float b2, float eps,
-                            float wd, int step, float gscale, int do_update, const long long* step_ctr,
+                            float wd, int step, float gscale, int do_update, const long long* step_ctr, int solver,
                             void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(!do_update || step >= 1 || step_ctr != nullptr, "Adam step must be >= 1");
@@ -178,7 +181,7 @@ extern "C" int gf_adam_beta(float* p, const float* g, float* m, float* v, int K,
     dim3 gridv((V + 127) / 128, (K + 31) / 32);
     adam_beta_vec_kernel<<<gridv, 256, 0, st>>>(p, g, m, v, K, V, ldp, ldg, reinterpret_cast<__nv_bfloat16*>(beta_bf), ldb,
                                                 reinterpret_cast<__nv_bfloat16*>(betaT_bf), Kp,
-                                                make_h(lr, b1, b2, eps, wd, do_update ? step : 1, do_update ? step_ctr : nullptr),
+                                                make_h(lr, b1, b2, eps, wd, do_update ? step : 1, do_update ? step_ctr : nullptr, solver),
                                                 gscale, do_update);
     GF_LAUNCHED();
     return GF_OK;
@@ -186,7 +189,7 @@ extern "C" int gf_adam_beta(float* p, const float* g, float* m, float* v, int K,
   dim3 grid((V + 31) / 32, (K + 31) / 32);
   adam_beta_kernel<<<grid, 256, 0, st>>>(p, g, m, v, K, V, ldp, ldg, reinterpret_cast<__nv_bfloat16*>(beta_bf), ldb,
                                          reinterpret_cast<__nv_bfloat16*>(betaT_bf), Kp,
-                                         make_h(lr, b1, b2, eps, wd, do_update ? step : 1, do_update ? step_ctr : nullptr), gscale,
+                                         make_h(lr, b1, b2, eps, wd, do_update ? step : 1, do_update ? step_ctr : nullptr, solver), gscale,
                                          do_update);
   GF_LAUNCHED();
   return GF_OK;

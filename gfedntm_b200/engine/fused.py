@@ -132,7 +132,7 @@ class FusedEngine:
     def __init__(self, model: DecoderNetwork, *, max_batch: int, max_nnz: int, lr: float = 2e-3,
                  betas: Tuple[float, float] = (0.99, 0.99), adam_eps: float = 1e-8,
                  weight_decay: float = 0.0, kl_weight: float = 1.0, seed: int = 0, device=None,
-                 arena=None) -> None:
+                 arena=None, solver: str = "adam") -> None:
         if not torch.cuda.is_available():
             raise RuntimeError("FusedEngine needs a CUDA device (sm_100a); use the eager backend on CPU")
         if model.label_size:
@@ -149,6 +149,11 @@ class FusedEngine:
         self.enc_drop = float(model.inf_net.dropout)
         self.kl_weight = float(kl_weight)
         self.lr, self.betas, self.adam_eps, self.weight_decay = lr, betas, adam_eps, weight_decay
+        self.solver_name = solver
+        self.solver = 0
+        if solver != "adam":  # (momentum travels as betas[0], like Adam's first beta in the reference's factory)
+            self.solver, b1_, b2_, eps_ = K_.solver_constants(solver, betas[0])
+            self.betas, self.adam_eps = (b1_, b2_), eps_
         self.seed = int(seed)
         self.step_count = 0       # optimiser steps taken
         self.rng_calls = 0        # forward passes (advances the Philox seed)
@@ -253,6 +258,14 @@ class FusedEngine:
                 bn.num_batches_tracked += self._nbt_pending
             self._nbt_pending = 0
 
+    def set_lr(self, lr: float) -> None:
+        """New learning rate (plateau scheduler): the captured step graphs carry the old value, so they are dropped."""
+        if float(lr) != self.lr:
+            self.lr = float(lr)
+            self._graphs.clear()
+            self._graph_launches.clear()
+            self._warm.clear()
+
     def set_step_count(self, n: int) -> None:
         """Optimiser step counter (host mirror + device counter used by the Adam kernels)."""
         self.step_count = int(n)
@@ -295,7 +308,7 @@ class FusedEngine:
         fl, V = self.flat, self.V
         b1, b2 = self.betas
         kw = dict(lr=self.lr, b1=b1, b2=b2, eps=self.adam_eps, wd=self.weight_decay, step=max(self.step_count, 1),
-                  gscale=gscale, do_update=do_update, step_ctr=self.ctr if do_update else None)
+                  gscale=gscale, do_update=do_update, step_ctr=self.ctr if do_update else None, solver=self.solver)
         A, ab = "inf_net.adapt_bert.weight", "inf_net.adapt_bert.bias"
         K_.adam_split(fl.view(fl.P, A), fl.view(fl.G, A), fl.view(fl.M, A), fl.view(fl.V2, A), self.ctm_a_hi,
                       self.ctm_a_lo, p_col=fl.view(fl.P, ab), g_col=fl.view(fl.G, ab), m_col=fl.view(fl.M, ab),
@@ -481,7 +494,7 @@ class FusedEngine:
             if hi > lo:
                 K_.adam_flat(fl.P[lo:hi], fl.G[lo:hi], fl.M[lo:hi], fl.V2[lo:hi], lr=self.lr, b1=b1, b2=b2,
                              eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
-                             step_ctr=self.ctr)
+                             step_ctr=self.ctr, solver=self.solver)
         if self.kind == "combined":
             self.ctm_adam_step(gscale=gscale)
         self._refresh_ctx_shadows()
@@ -490,13 +503,13 @@ class FusedEngine:
             K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"),
                          fl.view(fl.V2, "beta"), self.beta_bf, self.betaT_bf, K=K, V=V, lr=self.lr, b1=b1,
                          b2=b2, eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
-                         step_ctr=self.ctr)
+                         step_ctr=self.ctr, solver=self.solver)
         else:
             s = fl.segments["beta"]
             sl = slice(s.offset, s.offset + s.numel)
             K_.adam_flat(fl.P[sl], fl.G[sl], fl.M[sl], fl.V2[sl], lr=self.lr, b1=b1, b2=b2,
                          eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
-                         step_ctr=self.ctr)
+                         step_ctr=self.ctr, solver=self.solver)
 
     def optimizer_step_beta(self, gscale: float = 1.0) -> None:
         """Adam on beta alone (federated runs that do not share beta); the caller advanced the step counter."""
@@ -506,12 +519,12 @@ class FusedEngine:
             K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"),
                          fl.view(fl.V2, "beta"), self.beta_bf, self.betaT_bf, K=self.K, V=self.V, lr=self.lr, b1=b1,
                          b2=b2, eps=self.adam_eps, wd=self.weight_decay, step=self.step_count + 1, gscale=gscale,
-                         step_ctr=self.ctr)
+                         step_ctr=self.ctr, solver=self.solver)
         else:
             sg = fl.segments["beta"]
             sl = slice(sg.offset, sg.offset + sg.numel)
             K_.adam_flat(fl.P[sl], fl.G[sl], fl.M[sl], fl.V2[sl], lr=self.lr, b1=b1, b2=b2, eps=self.adam_eps,
-                         wd=self.weight_decay, step=self.step_count + 1, gscale=gscale, step_ctr=self.ctr)
+                         wd=self.weight_decay, step=self.step_count + 1, gscale=gscale, step_ctr=self.ctr, solver=self.solver)
 
     def train_step(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, **kw) -> torch.Tensor:
         """Forward + backward + Adam on one minibatch.  The kernel sequence is captured into a CUDA

@@ -41,7 +41,7 @@ class EmulatedFederation:
                 raise RuntimeError("EmulatedFederation drives the fused engine")
             t.engine = FusedEngine(t.model, max_batch=ld.batch_size, max_nnz=max(ld.max_nnz, 1), lr=t.lr,
                                    betas=(t.momentum, 0.99), kl_weight=float(t.weights["beta"]), seed=t.seed + r,
-                                   device=t.device, arena=arena if r == 0 else arena.view_as(r))
+                                   device=t.device, arena=arena if r == 0 else arena.view_as(r), solver=t.solver)
             if r == 0:
                 arena = t.engine.flat.arena
             self.engines.append(t.engine)
@@ -59,7 +59,7 @@ class EmulatedFederation:
         self.aggregator = FusedAggregator(world=n, weights=self.weights, flat_n=fl.beta_off, beta_off=fl.beta_off,
                                           s_n=fl.s_n, K=e0.K, V=e0.V, Kp=e0.Kp,
                                           ldb=(e0.beta_bf.stride(0) if e0.is_prod else 0), lr=t0.lr,
-                                          betas=(t0.momentum, 0.99), ranges=ranges, s_mask=s_mask,
+                                          betas=e0.betas, eps=e0.adam_eps, solver=e0.solver, ranges=ranges, s_mask=s_mask,
                                           beta_shared=self.beta_shared, local_gscale=1.0)
         for r, e in enumerate(self.engines):
             self.aggregator.add_rank(arena.view_as(r) if r else arena, r, M=e.flat.M, V2=e.flat.V2, has_shadows=e.is_prod)

@@ -68,7 +68,7 @@ class FederatedTrainer:
             self.arena = SymmetricArena(self.group) if self.world > 1 else LocalArena()
         m.engine = FusedEngine(m.model, max_batch=loader.batch_size, max_nnz=max(loader.max_nnz, 1), lr=m.lr,
                                betas=(m.momentum, 0.99), kl_weight=float(m.weights["beta"]), seed=m.seed + self.rank,
-                               device=m.device, arena=self.arena)
+                               device=m.device, arena=self.arena, solver=getattr(m, "solver", "adam"))
         eng = m.engine
         if self.world > 1 and isinstance(self.arena, SymmetricArena):
             import torch.distributed as dist
@@ -90,7 +90,8 @@ class FederatedTrainer:
         self.aggregator = FusedAggregator(world=self.world, weights=self.weights, flat_n=fl.beta_off,
                                           beta_off=fl.beta_off, s_n=fl.s_n, K=eng.K, V=eng.V, Kp=eng.Kp,
                                           ldb=(eng.beta_bf.stride(0) if eng.is_prod else 0), lr=m.lr,
-                                          betas=(m.momentum, 0.99), ranges=ranges, s_mask=s_mask,
+                                          betas=eng.betas, eps=eng.adam_eps, solver=eng.solver, ranges=ranges,
+                                          s_mask=s_mask,
                                           beta_shared=self.beta_shared,
                                           local_gscale=1.0 / max(self.weights[self.rank], 1e-30))
         self.aggregator.add_rank(self.arena, self.rank, M=fl.M, V2=fl.V2, has_shadows=eng.is_prod,

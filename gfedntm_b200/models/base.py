@@ -32,6 +32,30 @@ from .networks import ACTIVATION_NAMES, DecoderNetwork, elbo_terms
 SOLVERS = ("adagrad", "adam", "sgd", "adadelta", "rmsprop")
 
 
+class PlateauLR:
+    """``ReduceLROnPlateau(mode='min', factor=0.1, patience, threshold=1e-4 rel)`` for the fused engine, whose learning
+    rate is a kernel argument rather than a ``torch.optim`` param group.  Ref: avitm.py:156-157, 418-419."""
+
+    def __init__(self, trainer, patience: int = 10, factor: float = 0.1, threshold: float = 1e-4, min_lr: float = 0.0):
+        self.trainer, self.patience, self.factor, self.threshold, self.min_lr = trainer, patience, factor, threshold, min_lr
+        self.best, self.num_bad = float("inf"), 0
+
+    def step(self, metric: float) -> None:
+        metric = float(metric)
+        if metric < self.best * (1.0 - self.threshold):
+            self.best, self.num_bad = metric, 0
+        else:
+            self.num_bad += 1
+        if self.num_bad > self.patience:
+            new_lr = max(self.trainer.lr * self.factor, self.min_lr)
+            if self.trainer.lr - new_lr > 1e-8:
+                self.trainer.lr = new_lr
+                if self.trainer.engine is not None:
+                    self.trainer.engine.set_lr(new_lr)
+                self.trainer.logger.info("reducing learning rate to %g", new_lr)
+            self.num_bad = 0
+
+
 class FusedAdamHandle:
     """``torch.optim.Adam``-shaped view (``state_dict`` / ``load_state_dict`` / ``param_groups``) of
     the fused engine's flat Adam state, so code that ships or restores optimiser state (the gRPC
@@ -157,22 +181,21 @@ class NeuralTopicModel:
         self.model = self.model.to(self.device)
         self.early_stopping = EarlyStopping(patience=5, verbose=False)
 
-        fused_ok = (self.device.type == "cuda" and solver == "adam" and label_size == 0
+        fused_ok = (self.device.type == "cuda" and label_size == 0
                     and activation != "swish" and n_components <= 236 and max(hidden_sizes) <= 256
-                    and len(hidden_sizes) <= 8 and not reduce_on_plateau)
+                    and len(hidden_sizes) <= 8)
         if backend == "auto":
             backend = "fused" if fused_ok else "eager"
             if not fused_ok and self.device.type == "cuda":
                 why = [msg for cond, msg in (
-                    (solver != "adam", f"solver='{solver}'"), (label_size != 0, "label_size>0"),
+                    (label_size != 0, "label_size>0"),
                     (activation == "swish", "activation='swish'"), (n_components > 236, "n_components>236"),
-                    (max(hidden_sizes) > 256, "hidden size>256"), (len(hidden_sizes) > 8, "more than 8 hidden layers"),
-                    (reduce_on_plateau, "reduce_on_plateau=True")) if cond]
+                    (max(hidden_sizes) > 256, "hidden size>256"), (len(hidden_sizes) > 8, "more than 8 hidden layers"))
+                       if cond]
                 self.logger.warning("this configuration (%s) is outside the fused sm_100a engine and runs on the eager "
                                     "PyTorch backend, typically 10-70x slower per step", ", ".join(why))
         if backend == "fused" and not fused_ok:
-            raise ValueError("the fused backend needs CUDA, solver='adam', label_size=0, n_components<=236, "
-                             "hidden sizes<=256 and reduce_on_plateau=False")
+            raise ValueError("the fused backend needs CUDA, label_size=0, n_components<=236 and hidden sizes<=256")
         self.backend = backend
         self.engine = None
         self._pending_opt_state = None
@@ -182,7 +205,9 @@ class NeuralTopicModel:
         else:
             self.optimizer = self._make_torch_optimizer()
         if self.reduce_on_plateau:
-            self.scheduler = ReduceLROnPlateau(self.optimizer, patience=10)
+            # fused backend: the same rule (torch defaults: factor 0.1, relative threshold 1e-4) on the engine's lr
+            self.scheduler = (PlateauLR(self, patience=10) if backend == "fused"
+                              else ReduceLROnPlateau(self.optimizer, patience=10))
 
     # ------------------------------------------------------------------------------------------
     def _make_torch_optimizer(self):
@@ -209,7 +234,7 @@ class NeuralTopicModel:
         old = self.engine
         self.engine = FusedEngine(self.model, max_batch=loader.batch_size, max_nnz=max(loader.max_nnz, 1),
                                   lr=self.lr, betas=(self.momentum, 0.99), kl_weight=float(self.weights["beta"]),
-                                  seed=self.seed, device=self.device)
+                                  seed=self.seed, device=self.device, solver=self.solver)
         if old is not None:  # keep optimiser state across a workspace re-allocation
             self.engine.flat.M.copy_(old.flat.M)
             self.engine.flat.V2.copy_(old.flat.V2)

@@ -155,7 +155,7 @@ class GfFedArgs(C.Structure):
         ("parts", _i),
         ("n_ranges", _i),
         ("ranges", GfFedRange * GF_FED_MAX_RANGES),
-        ("s_mask", _i), ("beta_shared", _i), ("local_gscale", _f),
+        ("s_mask", _i), ("beta_shared", _i), ("local_gscale", _f), ("solver", _i),
         ("ranks", GfFabricRank * GF_MAX_RANKS),
     ]
 
@@ -197,7 +197,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_ctm_rc.argtypes = [_p, _p, _i, _i, _p, _p, _i, _i, _i, _p, _i, _i, _p]
     lib.gf_ctm_rr.argtypes = [_p, _p, _p, _p, _i, _i, _i, _p, _i, _i, _p, _p]
     lib.gf_adam_split.argtypes = [_p, _p, _p, _p, ll, _i, _i, _p, _p, _p, _p, _p, _p, _i, _f, _f, _f, _f, _f, _i, _f, _i,
-                                  _p, _p]
+                                  _p, _i, _p]
     for fn in ("gf_ctm_split", "gf_ctm_init_out", "gf_ctm_vc", "gf_ctm_rc", "gf_ctm_rr", "gf_adam_split"):
         getattr(lib, fn).restype = _i
     lib.gf_theta_mc.argtypes = [_p, _p, _p, _p, _p, _p, _f, _i, _i, _i, _u64, _f, _p, _p]
@@ -232,9 +232,9 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_lda_doc.argtypes = [_p, _p, _p, _p, _p, _i, _i, _i, _f, _p, _p, _p, _i, _p, _p]
     lib.gf_lda_beta_bwd.argtypes = [_p, _p, _i, _p, _p, _p, _p, _i, _i, _i, _i, _p]
     lib.gf_row_topk.argtypes = [_p, _i, _i, _i, _i, _p, _p, _p]
-    lib.gf_adam_flat.argtypes = [_p, _p, _p, _p, ll, _f, _f, _f, _f, _f, _i, _f, _p, _p]
+    lib.gf_adam_flat.argtypes = [_p, _p, _p, _p, ll, _f, _f, _f, _f, _f, _i, _f, _p, _i, _p]
     lib.gf_adam_beta.argtypes = [_p, _p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i,
-                                 _f, _f, _f, _f, _f, _i, _f, _i, _p, _p]
+                                 _f, _f, _f, _f, _f, _i, _f, _i, _p, _i, _p]
     lib.gf_fed_aggregate.argtypes = [C.POINTER(GfFedArgs), _p]
     lib.gf_fed_aggregate.restype = _i
     lib.gf_host_gather_csr.argtypes = [_p, _p, _p, _p, _i, _p, _p, _p, ll, _i]

@@ -22,6 +22,17 @@ TILE = 128
 LOG2E = 1.4426950408889634
 LN2 = 0.6931471805599453
 
+# solver -> (GfSolver id, b1 = momentum?, b2, eps): torch defaults of the reference's optimiser factory (avitm.py:141-153)
+SOLVERS = {"adam": 0, "sgd": 1, "adagrad": 2, "adadelta": 3, "rmsprop": 4}
+
+
+def solver_constants(solver: str, momentum: float):
+    """(id, b1, b2, eps) of a solver: Adam(betas=(momentum, 0.99)), SGD(momentum), Adagrad(eps 1e-10), Adadelta(rho 0.9,
+    eps 1e-6), RMSprop(alpha 0.99, eps 1e-8, momentum)."""
+    return {"adam": (0, momentum, 0.99, 1e-8), "sgd": (1, momentum, 0.0, 0.0), "adagrad": (2, 0.0, 0.0, 1e-10),
+            "adadelta": (3, 0.0, 0.9, 1e-6), "rmsprop": (4, momentum, 0.99, 1e-8)}[solver]
+
+
 ACTIVATIONS = {"softplus": 0, "relu": 1, "sigmoid": 2, "tanh": 3, "leakyrelu": 4, "rrelu": 5,
                "elu": 6, "selu": 7}
 
@@ -335,22 +346,22 @@ def row_topk(mat: torch.Tensor, k: int):
 # optimiser
 # ----------------------------------------------------------------------------------------------
 def adam_flat(p, g, m, v, *, lr: float, b1: float, b2: float, eps: float, wd: float, step: int,
-              gscale: float = 1.0, step_ctr=None) -> None:
+              gscale: float = 1.0, step_ctr=None, solver: int = 0) -> None:
     lib = _lib.load()
     n = p.numel()
     assert g.numel() == n and m.numel() == n and v.numel() == n
     check(lib.gf_adam_flat(_ptr(p), _ptr(g), _ptr(m), _ptr(v), n, lr, b1, b2, eps, wd, step, gscale,
-                           _ptr(step_ctr), _stream()), "gf_adam_flat")
+                           _ptr(step_ctr), solver, _stream()), "gf_adam_flat")
 
 
 def adam_beta(p, g, m, v, beta_bf, betaT_bf, *, K: int, V: int, lr: float = 0.0, b1: float = 0.9,
               b2: float = 0.999, eps: float = 1e-8, wd: float = 0.0, step: int = 1, gscale: float = 1.0,
-              do_update: bool = True, step_ctr=None) -> None:
+              do_update: bool = True, step_ctr=None, solver: int = 0) -> None:
     lib = _lib.load()
     check(lib.gf_adam_beta(_ptr(p), _ptr(g), _ptr(m), _ptr(v), K, V, p.stride(0),
                            (g.stride(0) if g is not None else 0), _ptr(beta_bf), beta_bf.stride(0),
                            _ptr(betaT_bf), betaT_bf.shape[1], lr, b1, b2, eps, wd, step, gscale,
-                           int(do_update), _ptr(step_ctr), _stream()), "gf_adam_beta")
+                           int(do_update), _ptr(step_ctr), solver, _stream()), "gf_adam_beta")
 
 
 # ----------------------------------------------------------------------------------------------
@@ -398,14 +409,14 @@ def ctm_rr(x_hi, x_lo, z_hi, z_lo, out, *, n_valid: int, extra=None) -> None:
 
 def adam_split(p, g, m, v, out_hi, out_lo, *, p_col=None, g_col=None, m_col=None, v_col=None, lr: float = 0.0,
                b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8, wd: float = 0.0, step: int = 1, gscale: float = 1.0,
-               do_update: bool = True, step_ctr=None) -> None:
+               do_update: bool = True, step_ctr=None, solver: int = 0) -> None:
     """Adam on a row-major [rows, cols] block (+ per-row scalar ``p_col`` as one more column) fused with the refresh
     of its bf16 hi / lo shadows; ``do_update=False`` only refreshes the shadows."""
     assert p.dim() == 2 and p.stride(1) == 1
     rows, cols = p.shape
     check(_lib.load().gf_adam_split(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.stride(0), rows, cols, _ptr(p_col), _ptr(g_col),
                                     _ptr(m_col), _ptr(v_col), _ptr(out_hi), _ptr(out_lo), out_hi.stride(0), lr, b1, b2, eps,
-                                    wd, step, gscale, int(do_update), _ptr(step_ctr), _stream()), "gf_adam_split")
+                                    wd, step, gscale, int(do_update), _ptr(step_ctr), solver, _stream()), "gf_adam_split")
 
 
 def theta_mc(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, out, *, B: int, K: int, n_samples: int, seed: int,

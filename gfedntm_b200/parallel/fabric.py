@@ -176,7 +176,7 @@ class FusedAggregator:
     def __init__(self, *, world: int, weights: Sequence[float], flat_n: int, beta_off: int, s_n: int, K: int,
                  V: int, Kp: int, ldb: int, lr: float, betas, eps: float = 1e-8, wd: float = 0.0,
                  ranges: Optional[Sequence[tuple]] = None, s_mask: int = 63, beta_shared: bool = True,
-                 local_gscale: float = 1.0) -> None:
+                 local_gscale: float = 1.0, solver: int = 0) -> None:
         """``ranges``: optional ``(offset, length, shared)`` pieces covering the flat region ``[0, flat_n)``
         (grads_to_share of the reference, federated_model.py:98-131): unshared pieces stay client-local.
         ``s_mask``: bit per BatchNorm statistics block; ``beta_shared``: whether beta takes part."""
@@ -185,6 +185,7 @@ class FusedAggregator:
         a = self.args
         a.n_ranges = 0
         a.s_mask, a.beta_shared, a.local_gscale = int(s_mask), int(beta_shared), float(local_gscale)
+        a.solver = int(solver)  # GfSolver of the global update (b1 = momentum, b2 = rho / alpha, see opt_math.cuh)
         if ranges is not None:
             merged: List[list] = []
             for off, ln, sh in ranges:

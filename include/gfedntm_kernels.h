@@ -308,15 +308,19 @@ int gf_row_topk(const float* mat, int ld, int rows, int V, int topk, int* out_id
 /* ------------------------------------------------------------------------------------------
  * Optimiser.  Ref: torch.optim.Adam in avitm.py:141-143 / federated_avitm.py:78.
  * ---------------------------------------------------------------------------------------- */
+/* Solvers of the reference's optimiser factory (avitm.py:141-153), torch defaults.  Two state buffers per
+ * parameter (m, v): adam (exp_avg, exp_avg_sq), sgd (momentum buffer, -), adagrad (-, sum), adadelta (acc_delta,
+ * square_avg), rmsprop (momentum buffer, square_avg).  b1 = momentum, b2 = 0.99 (adam / rmsprop alpha) or rho.   */
+enum GfSolver { GF_ADAM = 0, GF_SGD = 1, GF_ADAGRAD = 2, GF_ADADELTA = 3, GF_RMSPROP = 4 };
 /* `step_ctr` (optional, device): when non-null the step number is read from step_ctr[1] on the
  * device instead of the `step` argument.                                                        */
 int gf_adam_flat(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
-                 float eps, float wd, int step, float gscale, const long long* step_ctr, void* stream);
+                 float eps, float wd, int step, float gscale, const long long* step_ctr, int solver, void* stream);
 /* Adam on beta [K,ldp] plus the bf16 operand shadows beta_bf [Kp,ldb] and betaT_bf [V,Kp];
  * do_update = 0 only refreshes the shadows.                                                  */
 int gf_adam_beta(float* p, const float* g, float* m, float* v, int K, int V, int ldp, int ldg,
                  void* beta_bf, int ldb, void* betaT_bf, int Kp, float lr, float b1, float b2, float eps,
-                 float wd, int step, float gscale, int do_update, const long long* step_ctr, void* stream);
+                 float wd, int step, float gscale, int do_update, const long long* step_ctr, int solver, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Skinny tcgen05 GEMMs of the CombinedTM encoder (csrc/ctm_gemm.cu): the adapt_bert layer collapsed into the
@@ -335,7 +339,7 @@ int gf_ctm_split(const float* src, long long ld_src, const float* extra_col, con
 int gf_adam_split(float* p, const float* g, float* m, float* v, long long ld, int rows, int cols, float* p_col,
                   const float* g_col, float* m_col, float* v_col, void* out_hi, void* out_lo, int ldo, float lr, float b1,
                   float b2, float eps, float wd, int step, float gscale, int do_update, const long long* step_ctr,
-                  void* stream);
+                  int solver, void* stream);
 /* out [rows, ld] <- 0, except row bias_row <- bias[0..cols)  (accumulation target of gf_ctm_vc).            */
 int gf_ctm_init_out(float* out, int rows, int cols, int ld, int bias_row, const float* bias, void* stream);
 /* out[m, n] += sum_r X[r, m] Y[r, n]   X hi/lo [R, ldx] (m_total valid columns), Y hi/lo [R, 64 nb]         */
@@ -417,6 +421,7 @@ typedef struct GfFedArgs {
   int beta_shared;                /* 0: beta stays local (the caller runs its own optimiser on it)        */
   float local_gscale;             /* mode 0, unshared ranges: gradient scale of the local Adam (1 / w[rank],
                                      undoing the client weight folded into the backward pass)             */
+  int solver;                     /* GfSolver of the global / local update (b1 = momentum, b2 = rho / alpha)  */
   GfFabricRank ranks[GF_MAX_RANKS];
 } GfFedArgs;
 

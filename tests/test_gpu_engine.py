@@ -176,3 +176,58 @@ def test_theta_mc_matches_per_draw_softmax_statistics():
     want[want < thr] = 0
     want = want / want.sum(1, keepdim=True)
     torch.testing.assert_close(out3, want, rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize("solver", ["sgd", "adagrad", "adadelta", "rmsprop"])
+def test_engine_other_solvers_match_torch(solver):
+    """The non-Adam solvers of the reference's optimiser factory (avitm.py:141-153) on the fused path: three steps of
+    the engine's fused update against torch.optim with torch's defaults on the same gradients."""
+    from gfedntm_b200.engine.fused import FusedEngine
+    from gfedntm_b200.models.networks import DecoderNetwork
+    from gfedntm_b200.ops.decoder import CsrBatch
+
+    torch.manual_seed(1)
+    B, V, K = 64, 800, 10
+    lr, mom = 2e-3, 0.9
+    model = DecoderNetwork(V, K, "prodLDA", (32, 32), "softplus", 0.2, True)
+    eng = FusedEngine(model, max_batch=B, max_nnz=B * 30, lr=lr, betas=(mom, 0.99), seed=3, solver=solver)
+    x = torch.zeros(B, V, device="cuda")
+    x.scatter_add_(1, torch.randint(0, V, (B, 30), device="cuda"), torch.ones(B, 30, device="cuda"))
+    batch = CsrBatch.from_dense(x)
+    params = {n: p.detach().clone().requires_grad_(True) for n, p in model.named_parameters()}
+    ps = list(params.values())
+    opt = {"sgd": lambda: torch.optim.SGD(ps, lr=lr, momentum=mom), "adagrad": lambda: torch.optim.Adagrad(ps, lr=lr),
+           "adadelta": lambda: torch.optim.Adadelta(ps, lr=lr),
+           "rmsprop": lambda: torch.optim.RMSprop(ps, lr=lr, momentum=mom)}[solver]()
+    for _ in range(3):
+        eng.forward_backward(batch, training=True)
+        for n, p in params.items():
+            p.grad = eng.flat.view(eng.flat.G, n).detach().clone()
+        eng.optimizer_step()
+        opt.step()
+    torch.cuda.synchronize()
+    for n, p in params.items():
+        torch.testing.assert_close(eng.flat.view(eng.flat.P, n), p.detach(), rtol=2e-4, atol=2e-6, msg=lambda m: f"{n}: {m}")
+    torch.testing.assert_close(eng.beta_bf[:K, :V].float(), model.beta.detach().to(torch.bfloat16).float())
+
+
+def test_non_adam_solver_and_plateau_run_on_the_fused_backend():
+    """AVITM(solver='rmsprop', reduce_on_plateau=True) no longer falls back to eager PyTorch; the plateau rule lowers
+    the engine's learning rate and drops the captured graphs."""
+    import numpy as np
+
+    from gfedntm_b200.models import AVITM, BOWDataset
+    from gfedntm_b200.models.base import PlateauLR
+
+    rng = np.random.default_rng(0)
+    X = rng.poisson(0.05, (256, 900)).astype(np.float32)
+    X[X.sum(1) == 0, 0] = 1
+    m = AVITM(input_size=900, n_components=8, hidden_sizes=(16, 16), batch_size=64, num_epochs=2, solver="rmsprop",
+              reduce_on_plateau=True, verbose=False, device="cuda:0", seed=0)
+    assert m.backend == "fused" and isinstance(m.scheduler, PlateauLR)
+    m.fit(BOWDataset(X, None))
+    assert m.engine.solver_name == "rmsprop" and m.engine.solver == 4
+    lr0 = m.lr
+    for _ in range(12):
+        m.scheduler.step(1.0)   # no improvement for more than `patience` calls
+    assert abs(m.lr - 0.1 * lr0) < 1e-12 and abs(m.engine.lr - 0.1 * lr0) < 1e-12 and not m.engine._graphs
