@@ -23,6 +23,15 @@ def main():
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=device)
+    # stage 1 on the box: vocabulary consensus through the symmetric heap (peer-mapped reads, host merge)
+    from gfedntm_b200.parallel import consensus
+
+    toks = [f"tok{j}" for j in range(rank, 40 + 3 * rank)] + ["ünïcode", f"only{rank}"]
+    vocab, cw = consensus.consensus_vocabulary(toks, 10 * (rank + 1))
+    want = sorted(set(t for r in range(world) for t in [f"tok{j}" for j in range(r, 40 + 3 * r)] + ["ünïcode", f"only{r}"]))
+    assert list(vocab) == want and [vocab[t] for t in want] == list(range(len(want))), "vocabulary consensus mismatch"
+    assert abs(sum(cw) - 1.0) < 1e-9 and abs(cw[rank] - 10 * (rank + 1) / sum(10 * (r + 1) for r in range(world))) < 1e-9
+    assert consensus.LAST_TRANSPORT == "symmetric_heap", consensus.LAST_TRANSPORT
     agg = sys.argv[1] if len(sys.argv) > 1 else "grad"
     share = sys.argv[2].split(",") if len(sys.argv) > 2 and sys.argv[2] else None
     kind = sys.argv[3] if len(sys.argv) > 3 else "avitm"   # avitm | combined | zeroshot

@@ -84,3 +84,27 @@ def test_scalability_grid_tiny(tmp_path):
     rows = list(csv.DictReader(open(out)))
     assert len(rows) == 2 and {r["n_topics"] for r in rows} == {"2", "3"}
     assert all(float(r["train_s"]) > 0 and int(r["peak_rss"]) > 0 for r in rows)
+
+
+def test_exact_word_movers_distance():
+    """aux_scripts/evaluation/wmd.py: the exact transport distance is symmetric, zero on identical lists, never below
+    the relaxed nearest-neighbour bound, and equals the closed form when both lists have one word."""
+    import importlib.util
+    import os
+
+    import numpy as np
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("wmd_script", os.path.join(root, "aux_scripts", "evaluation", "wmd.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    rng = np.random.default_rng(0)
+    vec = {f"w{i}": rng.standard_normal(6) for i in range(12)}
+    a, b = [f"w{i}" for i in range(5)], [f"w{i}" for i in range(4, 11)]
+    assert mod.wmd(a, a, vec) < 1e-9
+    assert abs(mod.wmd(a, b, vec) - mod.wmd(b, a, vec)) < 1e-9
+    assert mod.wmd(a, b, vec) >= mod.relaxed_wmd(a, b, vec) - 1e-9
+    assert abs(mod.wmd(["w1"], ["w2"], vec) - np.linalg.norm(vec["w1"] - vec["w2"])) < 1e-9
+    # moving half of the mass: {w1, w2} -> {w1, w3} costs 0.5 * |w2 - w3| at most
+    assert mod.wmd(["w1", "w2"], ["w1", "w3"], vec) <= 0.5 * np.linalg.norm(vec["w2"] - vec["w3"]) + 1e-9
+    assert np.isnan(mod.wmd(["zz"], a, vec))
