@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) 
   GfLatentArgs a = a_;
   a.seed = step_seed(a_.seed, a_.step_ctr);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.x * 8 + warp;
+  const int b = blockIdx.x * (blockDim.x >> 5) + warp;
   const int K = a.K;
   const double invB = 1.0 / (double)a.B;
 
@@ -628,6 +628,70 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// bow_gather: first-layer contribution of the sparse bag of words, out[b,:] (+)= sum_e x_e * W1T[v_e,:].
+// The gather is a chain of dependent DRAM round trips per warp (indices, then the rows); with one warp per
+// document it dominated the encoder at every batch size.  Here `wpd` warps share a document (rounds of 32
+// non-zeros dealt round-robin), each keeps kRows weight rows in flight, and the partial sums meet in shared
+// memory in a fixed order.  Ref: inference_network.py:78 (x . W_in^T for the BoW part of the input).
+// ---------------------------------------------------------------------------------------------
+template <int kNC>
+__global__ void __launch_bounds__(256)
+bow_gather_kernel(const int* __restrict__ indptr, const int* __restrict__ indices, const float* __restrict__ counts,
+                  const float* __restrict__ W1T, int H0, int B, float* __restrict__ out, int accumulate, int wpd) {
+  constexpr int kRows = kNC <= 2 ? 16 : (kNC <= 4 ? 8 : 4);
+  __shared__ float red[8][kNC * 32];
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int dpb = 8 / wpd, dslot = wib / wpd, sub = wib - dslot * wpd;
+  const int b = blockIdx.x * dpb + dslot;
+  float acc[kNC];
+#pragma unroll
+  for (int c = 0; c < kNC; ++c) acc[c] = 0.f;
+  if (b < B) {
+    const int e0 = indptr[b], e1 = indptr[b + 1];
+    for (int base = e0 + 32 * sub; base < e1; base += 32 * wpd) {
+      const int e = base + lane;
+      const int v_l = (e < e1) ? indices[e] : 0;
+      const float x_l = (e < e1) ? counts[e] : 0.f;
+      const int n = min(32, e1 - base);
+      for (int i0 = 0; i0 < n; i0 += kRows) {
+        float w[kRows][kNC];
+        float xs[kRows];
+#pragma unroll
+        for (int u = 0; u < kRows; ++u) {
+          const int vi = __shfl_sync(0xffffffffu, v_l, (i0 + u) & 31);
+          xs[u] = (i0 + u < n) ? __shfl_sync(0xffffffffu, x_l, (i0 + u) & 31) : 0.f;
+          const float* wr = W1T + (size_t)vi * H0;
+#pragma unroll
+          for (int c = 0; c < kNC; ++c) {
+            const int j = c * 32 + lane;
+            w[u][c] = (j < H0) ? __ldg(wr + j) : 0.f;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kRows; ++u)
+#pragma unroll
+          for (int c = 0; c < kNC; ++c) acc[c] = fmaf(xs[u], w[u][c], acc[c]);
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < kNC; ++c) red[wib][c * 32 + lane] = acc[c];
+  __syncthreads();
+  if (b < B && sub == 0) {
+#pragma unroll
+    for (int c = 0; c < kNC; ++c) {
+      const int j = c * 32 + lane;
+      if (j < H0) {
+        float t = 0.f;
+        for (int u = 0; u < wpd; ++u) t += red[wib + u][j];
+        float* o = out + (size_t)b * H0 + j;
+        *o = accumulate ? *o + t : t;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // theta_mc: Monte-Carlo document-topic inference in ONE launch.  Ref: avitm.py:470-523 (n_samples full passes of
 // get_theta, averaged) + federated_model.py:170-173 (entries < thr zeroed, rows L1-renormalised).  The encoder
 // pass does not depend on the draw, so only the reparameterised soft-max is repeated: one warp per document
@@ -738,8 +802,10 @@ extern "C" int gf_latent_fwd(const GfLatentArgs* a, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(a->K >= 1 && a->K <= kMaxH, "n_components must be <= 256");
   GF_ARG_CHECK(!a->training || a->B >= 2, "training-mode BatchNorm needs at least 2 documents");
-  const int grid = (a->B + 7) / 8;
-  latent_fwd_kernel<<<grid, 256, 0, st>>>(*a);
+  // four documents per block: 78 registers per thread allow 3 x 256 threads per SM, so 8-document blocks left
+  // the second wave of a 4096-document batch mostly empty (1.15 waves)
+  const int grid = (a->B + 3) / 4;
+  latent_fwd_kernel<<<grid, 128, 0, st>>>(*a);
   GF_LAUNCHED();
   return GF_OK;
 }
@@ -778,6 +844,21 @@ extern "C" int gf_theta_mc(const float* mu_pre, const float* ls_pre, const float
   GF_ARG_CHECK(K >= 1 && K <= kMaxH && B >= 1 && n_samples >= 1, "shapes");
   theta_mc_kernel<<<(B + 7) / 8, 256, 0, st>>>(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, bn_eps, B, K, n_samples, seed,
                                                thr, out);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_bow_gather(const int* indptr, const int* indices, const float* counts, const float* W1T, int H0, int B,
+                             float* out, int accumulate, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(H0 >= 1 && H0 <= kMaxH && B >= 1, "shapes");
+  const int wpd = B <= 512 ? 8 : 4;
+  const int grid = (B * wpd + 7) / 8;
+  const int nc = (H0 + 31) / 32;
+  if (nc <= 1) bow_gather_kernel<1><<<grid, 256, 0, st>>>(indptr, indices, counts, W1T, H0, B, out, accumulate, wpd);
+  else if (nc <= 2) bow_gather_kernel<2><<<grid, 256, 0, st>>>(indptr, indices, counts, W1T, H0, B, out, accumulate, wpd);
+  else if (nc <= 4) bow_gather_kernel<4><<<grid, 256, 0, st>>>(indptr, indices, counts, W1T, H0, B, out, accumulate, wpd);
+  else bow_gather_kernel<8><<<grid, 256, 0, st>>>(indptr, indices, counts, W1T, H0, B, out, accumulate, wpd);
   GF_LAUNCHED();
   return GF_OK;
 }

@@ -126,10 +126,17 @@ __global__ void csc_scatter_kernel(const int* __restrict__ indptr, const int* __
 //   S_b = sum t; asp[v] += t; csp[v] += t*y; tnnz[e] = rstd_v * t;
 //   dtheta[b,:] = -sum rstd_v t beta[:,v]   (plain store: initialises the d theta buffer)
 // ---------------------------------------------------------------------------------------------
+// kWpd warps per document (8 warps per block, 8 / kWpd documents per block): the non-zeros of a document are
+// dealt to its warps in rounds of 32, so a document's dependent gather chain is kWpd times shorter and the
+// small-batch configurations (64 documents) still put a few hundred warps on the machine.  Partial RL / S /
+// d theta of a document's warps are combined in shared memory (fixed order: deterministic).
+template <int kWpd>
 __global__ void __launch_bounds__(256) dec_sparse_doc_kernel(const GfDecSparseArgs a) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  const int b = warp;
-  if (b >= a.B) return;
+  constexpr int kDpb = 8 / kWpd;
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int dslot = wib / kWpd, sub = wib % kWpd;
+  const int b = blockIdx.x * kDpb + dslot;
+  const bool live = b < a.B;
   const int Kp = a.Kp;
   const float2* lse_part = reinterpret_cast<const float2*>(a.lse_part);
   const __nv_bfloat16* theta_bf = reinterpret_cast<const __nv_bfloat16*>(a.theta_bf);
@@ -137,81 +144,114 @@ __global__ void __launch_bounds__(256) dec_sparse_doc_kernel(const GfDecSparseAr
   const float4* colc = reinterpret_cast<const float4*>(a.colc);
   float2* doc_const = reinterpret_cast<float2*>(a.doc_const);
   float4* sb_doc = reinterpret_cast<float4*>(a.sb_doc);
-  // combine log-sum-exp partials
-  float m = -INFINITY;
-  for (int c = lane; c < a.n_chunks; c += 32) m = fmaxf(m, lse_part[(size_t)b * a.n_chunks + c].x);
-  m = warp_max(m);
-  float ssum = 0.f;
-  for (int c = lane; c < a.n_chunks; c += 32) {
-    const float2 pr = lse_part[(size_t)b * a.n_chunks + c];
-    if (pr.x > -INFINITY) ssum += pr.y * exp2f(pr.x - m);
+  __shared__ float th_s[kDpb][kMaxKp];
+  __shared__ float dred[8][kMaxKp];
+  __shared__ float2 sred[8];
+  // combine log-sum-exp partials (every warp of the document: cheap, avoids a broadcast)
+  float lse2 = 0.f;
+  if (live) {
+    float m = -INFINITY;
+    for (int c = lane; c < a.n_chunks; c += 32) m = fmaxf(m, lse_part[(size_t)b * a.n_chunks + c].x);
+    m = warp_max(m);
+    float ssum = 0.f;
+    for (int c = lane; c < a.n_chunks; c += 32) {
+      const float2 pr = lse_part[(size_t)b * a.n_chunks + c];
+      if (pr.x > -INFINITY) ssum += pr.y * exp2f(pr.x - m);
+    }
+    ssum = warp_sum(ssum);
+    lse2 = m + log2f(ssum);
+    // theta_c row of this document in shared memory (read by every lane in phase 1)
+    for (int k = sub * 32 + lane; k < Kp; k += 32 * kWpd) th_s[dslot][k] = __bfloat162float(theta_bf[(size_t)b * a.ld_theta + k]);
   }
-  ssum = warp_sum(ssum);
-  const float lse2 = m + log2f(ssum);
-
-  // theta_c row of this document in shared memory (read by every lane in phase 1)
-  __shared__ float th_s[8][kMaxKp];
-  const int wslot = threadIdx.x >> 5;
-  for (int k = lane; k < Kp; k += 32) th_s[wslot][k] = __bfloat162float(theta_bf[(size_t)b * a.ld_theta + k]);
-  __syncwarp();
+  __syncthreads();
   float dth[kMaxKp / 32];
 #pragma unroll
   for (int c = 0; c < kMaxKp / 32; ++c) dth[c] = 0.f;
   float rl = 0.f, S = 0.f;
-  const int e0 = a.indptr[b], e1 = a.indptr[b + 1];
-  for (int base = e0; base < e1; base += 32) {
-    // ---- phase 1: one non-zero per lane (32 independent row gathers in flight)
-    const int e = base + lane;
-    const bool valid = e < e1;
-    const int v = valid ? a.indices[e] : 0;
-    const float x = valid ? a.counts[e] : 0.f;
-    const uint4* br = reinterpret_cast<const uint4*>(betaT_bf + (size_t)v * Kp);
-    float dot = 0.f;
-    for (int k8 = 0; k8 < (Kp >> 3); ++k8) {
-      const uint4 q = __ldg(br + k8);
-      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
-      const float* t = &th_s[wslot][k8 * 8];
+  if (live) {
+    const int e0 = a.indptr[b], e1 = a.indptr[b + 1];
+    for (int base = e0 + 32 * sub; base < e1; base += 32 * kWpd) {
+      // ---- phase 1: one non-zero per lane (32 independent row gathers in flight)
+      const int e = base + lane;
+      const bool valid = e < e1;
+      const int v = valid ? a.indices[e] : 0;
+      const float x = valid ? a.counts[e] : 0.f;
+      const uint4* br = reinterpret_cast<const uint4*>(betaT_bf + (size_t)v * Kp);
+      float dot = 0.f;
+#pragma unroll 4
+      for (int k8 = 0; k8 < (Kp >> 3); ++k8) {
+        const uint4 q = __ldg(br + k8);
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
+        const float* t = &th_s[dslot][k8 * 8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const float2 f = __bfloat1622float2(h2[u]);
-        dot = fmaf(t[2 * u], f.x, dot);
-        dot = fmaf(t[2 * u + 1], f.y, dot);
+        for (int u = 0; u < 4; ++u) {
+          const float2 f = __bfloat1622float2(h2[u]);
+          dot = fmaf(t[2 * u], f.x, dot);
+          dot = fmaf(t[2 * u + 1], f.y, dot);
+        }
       }
-    }
-    const float4 cc = colc[v];
-    const float t2 = fmaf(dot, cc.x, cc.y);
-    const float p = exp2f(t2 - lse2);
-    const float y = t2 * kLn2_s;
-    const float rstd = cc.x * kLn2_s;
-    float w = 0.f;
-    if (valid) {
-      rl -= x * __logf(p + 1e-10f);
-      const float t = a.gscale * x * p / (p + 1e-10f);
-      S += t;
-      w = rstd * t;
-      if (a.asp != nullptr) {
-        atomicAdd(&a.asp[v], t);
-        atomicAdd(&a.csp[v], t * y);
-        a.tnnz[e] = w;
+      const float4 cc = colc[v];
+      const float t2 = fmaf(dot, cc.x, cc.y);
+      const float p = exp2f(t2 - lse2);
+      const float y = t2 * kLn2_s;
+      const float rstd = cc.x * kLn2_s;
+      float w = 0.f;
+      if (valid) {
+        rl -= x * __logf(p + 1e-10f);
+        const float t = a.gscale * x * p / (p + 1e-10f);
+        S += t;
+        w = rstd * t;
+        if (a.asp != nullptr) {
+          atomicAdd(&a.asp[v], t);
+          atomicAdd(&a.csp[v], t * y);
+          a.tnnz[e] = w;
+        }
       }
-    }
-    // ---- phase 2: d theta[b,:] -= sum_e w_e * beta[:, v_e]   (lanes over topics, rows now cached)
-    if (a.dtheta != nullptr) {
-      const int n = min(32, e1 - base);
-      for (int i = 0; i < n; ++i) {
-        const int vi = __shfl_sync(0xffffffffu, v, i);
-        const float wi = __shfl_sync(0xffffffffu, w, i);
-        const __nv_bfloat16* bri = betaT_bf + (size_t)vi * Kp;
+      // ---- phase 2: d theta[b,:] -= sum_e w_e * beta[:, v_e]   (lanes over topics, rows now cached)
+      if (a.dtheta != nullptr) {
+        const int n = min(32, e1 - base);
+        for (int i = 0; i < n; ++i) {
+          const int vi = __shfl_sync(0xffffffffu, v, i);
+          const float wi = __shfl_sync(0xffffffffu, w, i);
+          const __nv_bfloat16* bri = betaT_bf + (size_t)vi * Kp;
 #pragma unroll
-        for (int c = 0; c < kMaxKp / 32; ++c) {
-          const int k = c * 32 + lane;
-          if (k < Kp) dth[c] = fmaf(-wi, __bfloat162float(bri[k]), dth[c]);
+          for (int c = 0; c < kMaxKp / 32; ++c) {
+            const int k = c * 32 + lane;
+            if (k < Kp) dth[c] = fmaf(-wi, __bfloat162float(bri[k]), dth[c]);
+          }
         }
       }
     }
   }
   rl = warp_sum(rl);
   S = warp_sum(S);
+  if (kWpd > 1) {
+    if (lane == 0) sred[wib] = make_float2(rl, S);
+    if (a.dtheta != nullptr) {
+#pragma unroll
+      for (int c = 0; c < kMaxKp / 32; ++c) {
+        const int k = c * 32 + lane;
+        if (k < Kp) dred[wib][k] = dth[c];
+      }
+    }
+    __syncthreads();
+    if (sub == 0) {
+      rl = 0.f; S = 0.f;
+#pragma unroll
+      for (int u = 0; u < kWpd; ++u) { rl += sred[wib + u].x; S += sred[wib + u].y; }
+      if (a.dtheta != nullptr) {
+#pragma unroll
+        for (int c = 0; c < kMaxKp / 32; ++c) {
+          const int k = c * 32 + lane;
+          float acc = 0.f;
+          if (k < Kp)
+            for (int u = 0; u < kWpd; ++u) acc += dred[wib + u][k];
+          dth[c] = acc;
+        }
+      }
+    }
+  }
+  if (!live || sub != 0) return;
   if (a.dtheta != nullptr) {
 #pragma unroll
     for (int c = 0; c < kMaxKp / 32; ++c) {
@@ -591,7 +631,9 @@ extern "C" int gf_csr_to_csc_dyn(const int* indptr, const int* indices, int B, i
 extern "C" int gf_dec_sparse_doc(const GfDecSparseArgs* a, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(a->Kp <= kMaxKp && a->Kp % 16 == 0, "Kp");
-  dec_sparse_doc_kernel<<<(a->B * 32 + 255) / 256, 256, 0, st>>>(*a);
+  // warps per document: enough of them to cover the machine at small batches, 4 at the large ones
+  if (a->B <= 512) dec_sparse_doc_kernel<8><<<a->B, 256, 0, st>>>(*a);
+  else dec_sparse_doc_kernel<4><<<(a->B + 1) / 2, 256, 0, st>>>(*a);
   GF_LAUNCHED();
   return GF_OK;
 }

@@ -191,6 +191,8 @@ class FusedEngine:
         self.zpool = torch.zeros(off_dm + n_dm, **f32)
         self.bn_bsums = self.zpool[:4 * K]
         self.theta_colsum = self.zpool[4 * K:5 * K]
+        if self.kind == "bow":
+            self.bow_pre0 = torch.zeros(B, self.hidden[0], **f32)   # first-layer BoW contribution (gf_bow_gather)
         if self.kind in ("combined", "zeroshot"):
             # Dense contextual input on the tensor cores (csrc/ctm_gemm.cu): x_ctx [B,C] . W^T [C,H0] forward
             # (gf_ctm_rc) and d W^T = x_ctx^T . d pre0 backward (gf_ctm_vc), on bf16 hi/lo shadows.
@@ -388,10 +390,16 @@ class FusedEngine:
         W1T, b1, pre0_ext = self._first_layer(x_ctx, B)
         Wh, bh = self._hidden_params(self.flat.P)
         use_bow = self.kind in ("bow", "combined")
+        if use_bow:
+            # sparse BoW part of the first layer: several warps per document, added to the contextual part
+            if pre0_ext is None:
+                pre0_ext = self.bow_pre0
+            K_.bow_gather(batch.indptr, batch.indices, batch.counts, W1T, pre0_ext, B=B,
+                          accumulate=self.kind == "combined")
+            W1T = None   # (enc_fwd gets no CSR input any more: everything of layer 0 arrives through pre0_ext)
         pad = [None] * (K_.GF_MAX_HIDDEN - len(self.hidden))
         K_.enc_fwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, training=training,
-                   indptr=batch.indptr if use_bow else None, indices=batch.indices if use_bow else None,
-                   counts=batch.counts if use_bow else None, W1T=W1T, b1=b1, xdense=None, WdT=None,
+                   indptr=None, indices=None, counts=None, W1T=W1T, b1=b1, xdense=None, WdT=None,
                    pre0_ext=pre0_ext,
                    Wh=Wh, bh=bh, Wmu=self._p("inf_net.f_mu.weight"), bmu=self._p("inf_net.f_mu.bias"),
                    Wsig=self._p("inf_net.f_sigma.weight"), bsig=self._p("inf_net.f_sigma.bias"),
@@ -576,10 +584,16 @@ class FusedEngine:
         W1T, b1, pre0_ext = self._first_layer(x_ctx, B)
         Wh, bh = self._hidden_params(self.flat.P)
         use_bow = self.kind in ("bow", "combined")
+        if use_bow:
+            # sparse BoW part of the first layer: several warps per document, added to the contextual part
+            if pre0_ext is None:
+                pre0_ext = self.bow_pre0
+            K_.bow_gather(batch.indptr, batch.indices, batch.counts, W1T, pre0_ext, B=B,
+                          accumulate=self.kind == "combined")
+            W1T = None   # (enc_fwd gets no CSR input any more: everything of layer 0 arrives through pre0_ext)
         pad = [None] * (K_.GF_MAX_HIDDEN - len(self.hidden))
         K_.enc_fwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, training=False,
-                   indptr=batch.indptr if use_bow else None, indices=batch.indices if use_bow else None,
-                   counts=batch.counts if use_bow else None, W1T=W1T, b1=b1, xdense=None, WdT=None,
+                   indptr=None, indices=None, counts=None, W1T=W1T, b1=b1, xdense=None, WdT=None,
                    pre0_ext=pre0_ext,
                    Wh=Wh, bh=bh, Wmu=self._p("inf_net.f_mu.weight"), bmu=self._p("inf_net.f_mu.bias"),
                    Wsig=self._p("inf_net.f_sigma.weight"), bsig=self._p("inf_net.f_sigma.bias"),

@@ -200,6 +200,8 @@ def _declare(lib: C.CDLL) -> None:
                                   _p, _i, _p]
     for fn in ("gf_ctm_split", "gf_ctm_init_out", "gf_ctm_vc", "gf_ctm_rc", "gf_ctm_rr", "gf_adam_split"):
         getattr(lib, fn).restype = _i
+    lib.gf_bow_gather.argtypes = [_p, _p, _p, _p, _i, _i, _p, _i, _p]
+    lib.gf_bow_gather.restype = _i
     lib.gf_theta_mc.argtypes = [_p, _p, _p, _p, _p, _p, _f, _i, _i, _i, _u64, _f, _p, _p]
     lib.gf_theta_mc.restype = _i
     lib.gf_fed_signal.argtypes = [C.POINTER(GfFedArgs), _i, _p]

@@ -426,3 +426,10 @@ def theta_mc(mu_pre, ls_pre, mu_rm, mu_rv, ls_rm, ls_rv, out, *, B: int, K: int,
     check(_lib.load().gf_theta_mc(_ptr(mu_pre), _ptr(ls_pre), _ptr(mu_rm), _ptr(mu_rv), _ptr(ls_rm), _ptr(ls_rv), bn_eps,
                                   B, K, n_samples, seed & 0xFFFFFFFFFFFFFFFF, float(thr), _ptr(out), _stream()),
           "gf_theta_mc")
+
+
+def bow_gather(indptr, indices, counts, W1T, out, *, B: int, accumulate: bool = False) -> None:
+    """out[b,:] (+)= sum_e counts[e] * W1T[indices[e],:] over the non-zeros of document b (first encoder layer)."""
+    assert W1T.stride(1) == 1 and W1T.stride(0) == W1T.shape[1] and out.stride(0) == W1T.shape[1]
+    check(_lib.load().gf_bow_gather(_ptr(indptr), _ptr(indices), _ptr(counts), _ptr(W1T), W1T.shape[1], B, _ptr(out),
+                                    int(accumulate), _stream()), "gf_bow_gather")

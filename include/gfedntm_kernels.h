@@ -149,6 +149,11 @@ typedef struct GfEncArgs {
 int gf_step_begin(long long* ctr, int inc_rng, int inc_opt, void* stream);
 int gf_enc_fwd(const GfEncArgs* args, void* stream);
 
+/* First-layer contribution of the sparse BoW input: out[b,:] (+)= sum over the document's non-zeros of
+ * count * W1T[word,:]  (several warps per document, rows kept in flight; feed the result to gf_enc_fwd through
+ * GfEncArgs.pre0_ext with indptr = null).  Ref: inference_network.py:78.                                    */
+int gf_bow_gather(const int* indptr, const int* indices, const float* counts, const float* W1T, int H0, int B,
+                  float* out, int accumulate, void* stream);
 /* Monte-Carlo document-topic inference in one launch: mean over n_samples reparameterised soft-max draws from the
  * eval-mode encoder outputs (gf_enc_fwd with training = 0), then entries < thr zeroed and rows L1-renormalised
  * (thr <= 0: plain mean).  Ref: avitm.py:470-523 + federated_model.py:170-173.                              */
