@@ -273,13 +273,29 @@ extern "C" int gf_fed_make_tmaps(const GfFedArgs* a, void* out_) {
     if (me.Gb[c] == nullptr) continue;
     cuuint64_t dims[2] = {(cuuint64_t)a->V, (cuuint64_t)a->K};
     cuuint64_t strides[1] = {(cuuint64_t)me.ld_gb * 2};
-    cuuint32_t box[2] = {128, 32};
+    cuuint32_t box[2] = {128, (cuuint32_t)kFedRows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(&out->m[c], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, me.Gb[c], dims, strides, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
       fprintf(stderr, "[gfedntm] cuTensorMapEncodeTiled failed (%d) for the beta gradient of rank %d\n", (int)r, c);
+      return GF_ERR_DRIVER;
+    }
+  }
+  // this rank's fp32 master copy of beta and its two optimiser moments ([K, V] inside the flat buffers)
+  GF_ARG_CHECK(a->V % 4 == 0 && a->beta_off % 4 == 0, "V and beta_off must be multiples of 4");
+  float* loc[3] = {me.P[me.rank] + a->beta_off, me.M + a->beta_off, me.V2 + a->beta_off};
+  for (int i = 0; i < 3; ++i) {
+    cuuint64_t dims[2] = {(cuuint64_t)a->V, (cuuint64_t)a->K};
+    cuuint64_t strides[1] = {(cuuint64_t)a->V * 4};
+    cuuint32_t box[2] = {128, (cuuint32_t)kFedRows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(&out->loc[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, loc[i], dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+      fprintf(stderr, "[gfedntm] cuTensorMapEncodeTiled failed (%d) for the local beta state %d\n", (int)r, i);
       return GF_ERR_DRIVER;
     }
   }

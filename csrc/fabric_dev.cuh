@@ -276,23 +276,31 @@ __device__ __forceinline__ void fed_beta_phase(const GfFedArgs& a, const GfFabri
 // [stages x n_remote x 8 KB][item table][mbarriers].  Requires V % 8 == 0, ldb % 4 == 0, Kp % 16 == 0.
 // ---------------------------------------------------------------------------------------------------
 struct FedTmaps {
-  CUtensorMap m[GF_MAX_RANKS];
+  CUtensorMap m[GF_MAX_RANKS];  // every rank's bf16 beta gradient [K, ld_gb], boxes of kFedRows topics x 128 words
+  CUtensorMap loc[3];           // this rank's fp32 beta, first and second optimiser moment [K, V], same boxes
 };
-constexpr int kFedTileBytes = 32 * 128 * 2;  // one peer's 32-topic x 128-word bf16 tile
+constexpr int kFedRows = 16;                            // topics per work item
+constexpr int kFedGradBytes = kFedRows * 128 * 2;       // one rank's bf16 gradient tile (4 KB)
+constexpr int kFedStateBytes = kFedRows * 128 * 4;      // one fp32 state tile (8 KB)
 constexpr int kFedMaxStages = 8;
 
+// Shared-memory stage of one work item (kFedRows topics x 128 words): [P][M][V2] fp32, own gradient, the peers'
+// gradients.  EVERY operand arrives by TMA, issued stages ahead by the producer thread, so the 256 consumer
+// threads never wait on a global load: with the operands loaded into registers by the consumers themselves the
+// loop ran at ~0.5 element/ns per SM (one exposed HBM round trip per item and no second CTA on the SM to hide
+// it), which is what the exposed part of the aggregation was made of.
 __device__ __forceinline__ void fed_beta_phase_tma(const GfFedArgs& a, const GfFabricRank& me, const AdamF& h,
                                                    const FedTmaps& tm, uint8_t* smem, uint32_t smem_bytes) {
   const int world = a.world, rank = me.rank, n_remote = world - 1;
   float* tile_v = reinterpret_cast<float*>(smem);
-  float(*tv)[132] = reinterpret_cast<float(*)[132]>(tile_v);
+  float(*tv)[132] = reinterpret_cast<float(*)[132]>(tile_v);  // kFedRows x 128 (+4 pad): transposition buffer
   // transposed-shadow staging: 128 words x Kp topics bf16 (rows padded by 8), flushed as whole rows
   const int ldt = a.Kp + 8;
-  __nv_bfloat16* tT = reinterpret_cast<__nv_bfloat16*>(smem + 17408);  // 32*132*4 = 16896, rounded up to 1 KB
+  __nv_bfloat16* tT = reinterpret_cast<__nv_bfloat16*>(smem + 9216);  // 16*132*4 = 8448, rounded up to 1 KB
   const uint32_t tT_bytes = ((uint32_t)(128 * ldt * 2) + 1023u) & ~1023u;
-  uint8_t* ring = smem + 17408 + tT_bytes;
-  const uint32_t stage_bytes = (uint32_t)n_remote * kFedTileBytes;
-  int stages = (int)((smem_bytes - 17408 - tT_bytes - 512) / stage_bytes);
+  uint8_t* ring = smem + 9216 + tT_bytes;
+  const uint32_t stage_bytes = 3u * kFedStateBytes + (uint32_t)world * kFedGradBytes;
+  int stages = (int)((smem_bytes - 9216 - tT_bytes - 512) / stage_bytes);
   if (stages > kFedMaxStages) stages = kFedMaxStages;
   if (stages < 1) stages = 1;  // (the launcher sizes the shared memory so that this never triggers)
   int* item_wt = reinterpret_cast<int*>(ring + (size_t)stages * stage_bytes);
@@ -309,7 +317,7 @@ __device__ __forceinline__ void fed_beta_phase_tma(const GfFedArgs& a, const GfF
   for (int i = threadIdx.x; i < 128 * ldt / 2; i += blockDim.x) reinterpret_cast<uint32_t*>(tT)[i] = 0u;
   __syncthreads();  // all threads of the CTA call this function
 
-  const int vt = (a.V + 127) / 128, kt = (a.K + 31) / 32;
+  const int vt = (a.V + 127) / 128, kt = (a.K + kFedRows - 1) / kFedRows;
   const int per = (vt + world - 1) / world;
   const int t_lo = rank * per, t_hi = (t_lo + per < vt) ? t_lo + per : vt;
   const int n_wt = t_hi > t_lo ? t_hi - t_lo : 0;  // word tiles owned by this rank; a CTA takes whole word tiles
@@ -326,14 +334,20 @@ __device__ __forceinline__ void fed_beta_phase_tma(const GfFedArgs& a, const GfF
         mbar_wait(&empty[st], ((it / stages) & 1) ^ 1);
         item_wt[st] = done ? -1 : wt;
         item_k[st] = kti;
-        if (done || n_remote == 0) {
+        if (done) {
           mbar_arrive(&full[st]);
         } else {
+          uint8_t* sb = ring + (size_t)st * stage_bytes;
           mbar_arrive_expect_tx(&full[st], stage_bytes);  // out-of-range rows / words are zero-filled and counted
-          int slot = 0;
+          const int k0 = kti * kFedRows;
+          tma_load_2d(sb, &tm.loc[0], &full[st], v0, k0);
+          tma_load_2d(sb + kFedStateBytes, &tm.loc[1], &full[st], v0, k0);
+          tma_load_2d(sb + 2 * kFedStateBytes, &tm.loc[2], &full[st], v0, k0);
+          tma_load_2d(sb + 3 * kFedStateBytes, &tm.m[rank], &full[st], v0, k0);
+          int slot = 1;
           for (int c = 0; c < world; ++c) {
             if (c == rank) continue;
-            tma_load_2d(ring + (size_t)st * stage_bytes + (size_t)slot * kFedTileBytes, &tm.m[c], &full[st], v0, kti * 32);
+            tma_load_2d(sb + 3 * kFedStateBytes + (size_t)slot * kFedGradBytes, &tm.m[c], &full[st], v0, k0);
             ++slot;
           }
         }
@@ -341,90 +355,63 @@ __device__ __forceinline__ void fed_beta_phase_tma(const GfFedArgs& a, const GfF
       if (done) break;
     }
   } else if (threadIdx.x < 256) {
-    // ---------------- consumers
+    // ---------------- consumers: thread (ty, tx) owns words 4 tx .. 4 tx + 3 of topics ty and ty + 8 of the item
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const __nv_bfloat16* gb_own = reinterpret_cast<const __nv_bfloat16*>(me.Gb[rank]);
-    int wt = -1, kti = 0;
-    bool known = false;  // (wt, kti) of this item already known (second and later topic slabs of a word tile)
     for (uint32_t it = 0;; ++it) {
       const int st = it % stages;
-      if (!known) {
-        mbar_wait(&full[st], (it / stages) & 1);
-        wt = item_wt[st];
-        kti = item_k[st];
-        if (wt < 0) break;
-      }
+      mbar_wait(&full[st], (it / stages) & 1);
+      const int wt = item_wt[st], kti = item_k[st];
+      if (wt < 0) break;
       const int v0 = (t_lo + wt) * 128;
       const int vv = v0 + tx * 4;
-      const int k0 = kti * 32;
-      // local operands (their latency overlaps the wait for the peers' tile when the item was known)
-      float4 pp[4], mm[4], v2[4];
-      uint2 gl[4];
-      bool live[4];
-#pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int k = k0 + ty + r * 8;
-        live[r] = (k < a.K) && (vv < a.V);
-        if (live[r]) {
-          const long long ip = a.beta_off + (long long)k * a.V + vv;
-          gl[r] = *reinterpret_cast<const uint2*>(gb_own + (size_t)k * me.ld_gb + vv);
-          pp[r] = *reinterpret_cast<const float4*>(me.P[rank] + ip);
-          mm[r] = *reinterpret_cast<const float4*>(me.M + ip);
-          v2[r] = *reinterpret_cast<const float4*>(me.V2 + ip);
-        }
-      }
-      if (known) mbar_wait(&full[st], (it / stages) & 1);
+      const int k0 = kti * kFedRows;
       const uint8_t* sb = ring + (size_t)st * stage_bytes;
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int k = k0 + ty + r * 8;
+      for (int r = 0; r < kFedRows / 8; ++r) {
+        const int row = ty + r * 8, k = k0 + row;
         float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (live[r]) {
-          const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&gl[r]);
-          float2 lo = __bfloat1622float2(o2[0]), hi = __bfloat1622float2(o2[1]);
-          float4 g = make_float4(lo.x, lo.y, hi.x, hi.y);
-          for (int c = 0; c < n_remote; ++c) {
-            const uint2 x = *reinterpret_cast<const uint2*>(sb + (size_t)c * kFedTileBytes + (ty + r * 8) * 256 + tx * 8);
+        if (k < a.K && vv < a.V) {
+          const uint32_t o4 = (uint32_t)row * 512u + (uint32_t)tx * 16u;  // fp32 tiles: 512-byte rows
+          const uint32_t o2 = (uint32_t)row * 256u + (uint32_t)tx * 8u;   // bf16 tiles: 256-byte rows
+          val = *reinterpret_cast<const float4*>(sb + o4);
+          float4 mm = *reinterpret_cast<const float4*>(sb + kFedStateBytes + o4);
+          float4 v2 = *reinterpret_cast<const float4*>(sb + 2 * kFedStateBytes + o4);
+          float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int c = 0; c < world; ++c) {  // own tile first, then the peers' in rank order
+            const uint2 x = *reinterpret_cast<const uint2*>(sb + 3 * kFedStateBytes + (size_t)c * kFedGradBytes + o2);
             const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&x);
-            lo = __bfloat1622float2(x2[0]);
-            hi = __bfloat1622float2(x2[1]);
+            const float2 lo = __bfloat1622float2(x2[0]), hi = __bfloat1622float2(x2[1]);
             g.x += lo.x; g.y += lo.y; g.z += hi.x; g.w += hi.y;
           }
           const long long ip = a.beta_off + (long long)k * a.V + vv;
-          val = pp[r];
-          val.x = adam_upd(val.x, g.x, mm[r].x, v2[r].x, h);
-          val.y = adam_upd(val.y, g.y, mm[r].y, v2[r].y, h);
-          val.z = adam_upd(val.z, g.z, mm[r].z, v2[r].z, h);
-          val.w = adam_upd(val.w, g.w, mm[r].w, v2[r].w, h);
+          val.x = adam_upd(val.x, g.x, mm.x, v2.x, h);
+          val.y = adam_upd(val.y, g.y, mm.y, v2.y, h);
+          val.z = adam_upd(val.z, g.z, mm.z, v2.z, h);
+          val.w = adam_upd(val.w, g.w, mm.w, v2.w, h);
           *reinterpret_cast<float4*>(me.P[rank] + ip) = val;  // master copy: owner only
-          *reinterpret_cast<float4*>(me.M + ip) = mm[r];
-          *reinterpret_cast<float4*>(me.V2 + ip) = v2[r];
+          *reinterpret_cast<float4*>(me.M + ip) = mm;
+          *reinterpret_cast<float4*>(me.V2 + ip) = v2;
           __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
                                             __float2bfloat16(val.z), __float2bfloat16(val.w)};
           fed_push_b64(me.beta_bf, me.beta_bf_mc, (size_t)k * a.ldb + vv, *reinterpret_cast<const uint2*>(o), world);
         }
-        *reinterpret_cast<float4*>(&tv[ty + r * 8][tx * 4]) = val;
+        *reinterpret_cast<float4*>(&tv[row][tx * 4]) = val;
       }
       fed_sync256();
       if (threadIdx.x == 0) mbar_arrive(&empty[st]);  // every consumer has read the stage and its item entry
-      // transpose this 32-topic slab into the row-major [word][topic] staging tile
+      // transpose this 16-topic slab into the row-major [word][topic] staging tile: thread = (word, 8 topics)
       const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
-      const int kb = k0 + half * 16;
+      const int kb = k0 + half * 8;
       if (kb < a.Kp) {
-        __align__(16) __nv_bfloat16 o[16];
+        __align__(16) __nv_bfloat16 o[8];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) o[j] = __float2bfloat16(tv[half * 16 + j][wv]);
-        uint4* dst = reinterpret_cast<uint4*>(tT + (size_t)wv * ldt + kb);
-        dst[0] = reinterpret_cast<const uint4*>(o)[0];
-        dst[1] = reinterpret_cast<const uint4*>(o)[1];
+        for (int j = 0; j < 8; ++j) o[j] = __float2bfloat16(tv[half * 8 + j][wv]);
+        *reinterpret_cast<uint4*>(tT + (size_t)wv * ldt + kb) = *reinterpret_cast<const uint4*>(o);
       }
       fed_sync256();
-      known = (kti + 1 < kt);
-      if (known) {
-        ++kti;
-      } else {
+      if (kti + 1 == kt) {
         // flush the transposed shadow of this word tile: whole rows of Kp bf16, 16-byte pieces, consecutive
-        // threads -> consecutive addresses (large NVLink packets instead of one 32-byte store per topic slab)
+        // threads -> consecutive addresses (large NVLink packets instead of one 16-byte store per topic slab)
         const int cpr = a.Kp >> 3;  // 16-byte chunks per row
         for (int idx = threadIdx.x; idx < 128 * cpr; idx += 256) {
           const int rw = idx / cpr, ch = idx - rw * cpr;

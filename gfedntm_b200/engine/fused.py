@@ -75,9 +75,9 @@ class FlatParams:
             if self.has_shadows:
                 arena.reserve("beta_bf", 2 * Kp * ldb)
                 arena.reserve("betaT_bf", 2 * V * Kp)
-                if getattr(arena, "world", 1) > 1:
-                    # beta gradient in the federated exchange format (bf16 [K, ldb]), pulled by the owners
-                    arena.reserve("Gb", 2 * K * ldb)
+                # beta gradient in the exchange format of the overlapped update (bf16 [K, ldb]): pulled by the owners
+                # in a federation, read by this GPU's own update CTAs otherwise
+                arena.reserve("Gb", 2 * K * ldb)
             if getattr(arena, "world", 1) > 1 and getattr(model, "infnet", "") == "combined":
                 # staging area of the small all-reduce of CombinedTM's collapsed-weight gradient
                 self.ar_cap = ((model.contextual_size + 1) * model.hidden_sizes[0] + 3) // 4 * 4
@@ -251,6 +251,29 @@ class FusedEngine:
         self._nbt_pending = 0
         self.model.register_state_dict_pre_hook(lambda *a, **k: self.flush_counters())
         self.sync_shadows()
+        self._self_overlap = None
+        self._init_self_overlap(arena)
+
+    def _init_self_overlap(self, arena) -> None:
+        """Single-GPU training, OPT-IN (``GFEDNTM_SELF_OVERLAP=1``): the beta part of the optimiser step runs on CTAs of
+        the d-theta sweep -- the overlapped federated aggregation with a world of one; the gradient travels as bf16
+        [K, ldb].  Measured at V=200k, K=200, B=4096: 3.52 ms/step against 3.32 with the separate ``adam_beta``
+        kernel (235 us at 5.3 TB/s): a sweep CTA owns its SM (registers and shared memory), so the update cannot
+        share an SM with the sweep, and as the tail after the sweep it moves ~3 TB/s.  Kept because it exercises the
+        aggregation role of the sweep kernel on one GPU (profiling with ncu, tests)."""
+        from ..parallel.fabric import FusedAggregator, LocalArena
+
+        if not (self.is_prod and self.decoder.folded and isinstance(arena, LocalArena) and self.V % 8 == 0
+                and "Gb" in arena.offsets and os.environ.get("GFEDNTM_SELF_OVERLAP", "0") == "1"):
+            return
+        fl = self.flat
+        agg = FusedAggregator(world=1, weights=[1.0], flat_n=fl.beta_off, beta_off=fl.beta_off, s_n=fl.s_n, K=self.K,
+                              V=self.V, Kp=self.Kp, ldb=self.beta_bf.stride(0), lr=self.lr, betas=self.betas,
+                              eps=self.adam_eps, wd=self.weight_decay, solver=self.solver)
+        agg.add_rank(arena, 0, M=fl.M, V2=fl.V2, has_shadows=True, ld_gb=self.beta_bf.stride(0))
+        ctas = int(os.environ.get("GFEDNTM_SELF_AGG_CTAS", "16"))
+        self._self_agg = agg
+        self._self_overlap = agg.overlap_handle(self.ctr, ctas)
 
     def flush_counters(self) -> None:
         """Apply the pending ``num_batches_tracked`` increments of the three BatchNorm layers."""
@@ -264,6 +287,9 @@ class FusedEngine:
         """New learning rate (plateau scheduler): the captured step graphs carry the old value, so they are dropped."""
         if float(lr) != self.lr:
             self.lr = float(lr)
+            if self._self_overlap is not None:  # the update CTAs read lr from a device copy of the arguments
+                self._self_agg.set_lr(self.lr, self.betas)
+                self._self_overlap = self._self_agg.overlap_handle(self.ctr, self._self_overlap.ctas)
             self._graphs.clear()
             self._graph_launches.clear()
             self._warm.clear()
@@ -491,11 +517,13 @@ class FusedEngine:
     # ------------------------------------------------------------------------------------------
     # optimiser
     # ------------------------------------------------------------------------------------------
-    def optimizer_step(self, gscale: float = 1.0) -> None:
-        """Fused Adam over the flat buffers; refreshes the bf16 shadows of beta."""
+    def optimizer_step(self, gscale: float = 1.0, beta_done: bool = False) -> None:
+        """Fused Adam over the flat buffers; refreshes the bf16 shadows of beta.  ``beta_done``: the step counter was
+        advanced and beta updated already (overlapped with the d-theta sweep, see ``train_step``)."""
         if not torch.cuda.is_current_stream_capturing():
             self.step_count += 1
-        K_.step_begin(self.ctr, 0, 1)
+        if not beta_done:
+            K_.step_begin(self.ctr, 0, 1)
         fl = self.flat
         b1, b2 = self.betas
         for lo, hi in self._flat_adam_pieces():
@@ -507,7 +535,9 @@ class FusedEngine:
             self.ctm_adam_step(gscale=gscale)
         self._refresh_ctx_shadows()
         K, V = self.K, self.V
-        if self.is_prod:
+        if beta_done:
+            pass
+        elif self.is_prod:
             K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"),
                          fl.view(fl.V2, "beta"), self.beta_bf, self.betaT_bf, K=K, V=V, lr=self.lr, b1=b1,
                          b2=b2, eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
@@ -539,8 +569,13 @@ class FusedEngine:
         graph per (input buffers, batch size) and replayed: the first call on a new key runs eagerly
         (warm-up), the second captures, later ones replay.  Injected noise/masks force the eager path."""
         def body():
-            self.forward_backward(batch, x_ctx, training=True, **kw)
-            self.optimizer_step()
+            if self._self_overlap is not None:
+                K_.step_begin(self.ctr, 0, 1)  # step t first: the update CTAs inside the d-theta sweep read it
+                self.forward_backward(batch, x_ctx, training=True, fed=self._self_overlap, **kw)
+                self.optimizer_step(beta_done=True)
+            else:
+                self.forward_backward(batch, x_ctx, training=True, **kw)
+                self.optimizer_step()
 
         if kw or not self.use_graphs:
             body()

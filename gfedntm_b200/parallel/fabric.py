@@ -237,7 +237,7 @@ class FusedAggregator:
         dev = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(step_ctr.device)
         self._keep.append(dev)
         # tensor maps of every rank's bf16 beta gradient (host memory: they travel as a kernel parameter)
-        tm = (C.c_ubyte * (128 * GF_MAX_RANKS + 64))()
+        tm = (C.c_ubyte * (128 * (GF_MAX_RANKS + 3) + 64))()  # GF_FED_TMAPS
         tm_ptr = (C.addressof(tm) + 63) // 64 * 64
         check(_lib.load().gf_fed_make_tmaps(C.byref(a), tm_ptr), "gf_fed_make_tmaps")
         self._keep.append(tm)

@@ -439,9 +439,11 @@ int gf_fed_signal(const GfFedArgs* args, int phase, void* stream);
 #define GF_FED_PHASE_SMALL_AR 3
 #define GF_FED_FLAG_SLOTS 8
 #define GF_FED_FLAG_BYTES (GF_FED_FLAG_SLOTS * GF_MAX_RANKS * 4)
-/* Writes GF_MAX_RANKS CUtensorMap (128 bytes each, 64-byte aligned HOST buffer) describing every rank's
- * bf16 beta gradient ranks[0].Gb[c] as [K, ld_gb] with 32-topic x 128-word boxes (entries of absent ranks
- * are zeroed).  The maps are used for plain TMA loads; they are never used with cluster multicast.   */
+/* Writes GF_FED_TMAPS CUtensorMap (128 bytes each, 64-byte aligned HOST buffer): GF_MAX_RANKS maps of every
+ * rank's bf16 beta gradient ranks[0].Gb[c] as [K, ld_gb] (entries of absent ranks are zeroed), then three maps of
+ * this rank's fp32 beta / first / second moment [K, V]; boxes of 16 topics x 128 words.  The maps are used for
+ * plain TMA loads; they are never used with cluster multicast.                                        */
+#define GF_FED_TMAPS (GF_MAX_RANKS + 3)
 int gf_fed_make_tmaps(const GfFedArgs* args, void* out_tmaps_host);
 /* One-shot all-reduce (sum) of a small fp32 buffer x[0..n) (n <= ranks[0].ar_cap, x 16-byte aligned, n % 4 == 0)
  * over peer memory: every rank stores its x into its slot of every rank's staging area, raises flag slot

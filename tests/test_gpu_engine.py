@@ -231,3 +231,41 @@ def test_non_adam_solver_and_plateau_run_on_the_fused_backend():
     for _ in range(12):
         m.scheduler.step(1.0)   # no improvement for more than `patience` calls
     assert abs(m.lr - 0.1 * lr0) < 1e-12 and abs(m.engine.lr - 0.1 * lr0) < 1e-12 and not m.engine._graphs
+
+
+def test_single_gpu_overlapped_beta_update_matches_separate_kernel(monkeypatch):
+    """GFEDNTM_SELF_OVERLAP=1 runs the aggregation role of the d-theta sweep with a world of one (TMA-fed update
+    loop, bf16 gradient): three training steps must track the default path (separate fused Adam on fp32 gradients)."""
+    import numpy as np
+
+    from gfedntm_b200.engine.fused import FusedEngine
+    from gfedntm_b200.models.networks import DecoderNetwork
+    from gfedntm_b200.ops.decoder import CsrBatch
+
+    monkeypatch.setenv("GFEDNTM_DECODER_V1", "0")   # folded sweeps at a small shape
+    B, V, K = 192, 2048, 24
+    g = torch.Generator(device="cuda").manual_seed(2)
+    x = torch.zeros(B, V, device="cuda")
+    x.scatter_add_(1, torch.randint(0, V, (B, 50), device="cuda", generator=g), torch.ones(B, 50, device="cuda"))
+    batch = CsrBatch.from_dense(x)
+    eps = torch.randn(B, K, device="cuda", generator=g)
+    me, mt = torch.ones(B, 32, device="cuda"), torch.ones(B, K, device="cuda")
+    res = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("GFEDNTM_SELF_OVERLAP", flag)
+        torch.manual_seed(0)
+        model = DecoderNetwork(V, K, "prodLDA", (32, 32), "softplus", 0.2, True)
+        with torch.no_grad():
+            model.beta.mul_(10.0)
+        eng = FusedEngine(model, max_batch=B, max_nnz=batch.nnz, lr=2e-3, betas=(0.99, 0.99), seed=1)
+        assert (eng._self_overlap is not None) == (flag == "1")
+        losses = [float(eng.train_step(batch, eps_in=eps, mask_enc_in=me, mask_theta_in=mt).item()) for _ in range(3)]
+        torch.cuda.synchronize()
+        res[flag] = (losses, model.beta.detach().clone(), eng.beta_bf.detach().clone(), eng.betaT_bf.detach().clone())
+    np.testing.assert_allclose(res["1"][0], res["0"][0], rtol=2e-5)
+    # Adam's first steps move every weight by ~lr whatever the gradient magnitude: a bf16-rounded gradient may flip
+    # the direction of weights whose gradient is ~0, so compare in units of the step size
+    diff = (res["1"][1] - res["0"][1]).abs()
+    assert float(diff.mean()) < 0.05 * 2e-3 * 3 and float((diff > 2e-3).float().mean()) < 0.02
+    assert torch.equal(res["1"][2][:K, :V].float(), res["1"][1].to(torch.bfloat16).float())
+    assert torch.equal(res["1"][3][:, :K].float(), res["1"][1].t().to(torch.bfloat16).float())

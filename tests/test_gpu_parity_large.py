@@ -170,8 +170,8 @@ def test_fused_training_tracks_eager_fp32_for_50_steps_at_benchmark_shape():
         me = (torch.rand(B, 50, device="cuda", generator=g) > 0.2).float() / 0.8
         mt = (torch.rand(B, K, device="cuda", generator=g) > 0.2).float() / 0.8
         batch, _ = batches[step % n_mb]
-        loss = eng.forward_backward(batch, training=True, eps_in=eps, mask_enc_in=me, mask_theta_in=mt)
-        eng.optimizer_step()
+        # the path the benchmark runs: beta's gradient as bf16, its optimiser step overlapped with the d-theta sweep
+        loss = eng.train_step(batch, eps_in=eps, mask_enc_in=me, mask_theta_in=mt)
         fused.append(float(loss.item()) / B)
         opt.zero_grad(set_to_none=True)
         ref_loss = _eager_loss(ref, dense[step % n_mb], eps, me, mt)
