@@ -102,10 +102,10 @@ class FederatedTrainer:
         self._overlap = None
         if not hasattr(self, "_ctm_trick"):
             self._ctm_trick = False
-        # 40 CTAs measured best with P2P pushes (N=2: 16: 5.40, 24: 4.46, 32: 3.88, 40: 3.55-3.64, 56: 3.76 ms/step);
-        # with NVLS multicast pushes the aggregation needs fewer (N=8: 32 CTAs 3.41 ms/step, 40 CTAs 3.50)
+        # CTAs that aggregate from the start of the d-theta sweep; every sweep CTA joins once it runs out of sweep work
+        # (measured at N=2, large config: 16 -> 3.42 ms/step, 40 -> 3.49; the same step trained locally 3.32)
         nvls = bool(self.aggregator.args.ranks[0].P_mc)
-        ctas = int(os.environ.get("GFEDNTM_AGG_CTAS", "32" if (nvls and self.world >= 8) else "40"))
+        ctas = int(os.environ.get("GFEDNTM_AGG_CTAS", "16"))
         if (self.world > 1 and self.agg == "grad" and ctas >= 0 and eng.is_prod and eng.decoder.folded
                 and isinstance(self.arena, SymmetricArena) and self.beta_shared and eng.V % 8 == 0
                 and os.environ.get("GFEDNTM_NO_OVERLAP", "0") != "1"):
