@@ -692,6 +692,86 @@ bow_gather_kernel(const int* __restrict__ indptr, const int* __restrict__ indice
 }
 
 // ---------------------------------------------------------------------------------------------
+// Supervised CTM (label_size > 0).  Ref: the one-hot labels are concatenated to the encoder input
+// (ctm_network/inference_network.py:79-94,178-183), a Linear(K -> L) head classifies theta and the mean
+// cross-entropy joins the loss (decoding_network.py:84-85,156-159, ctm.py:292-296).
+//   small_linear_fwd    out[b,:] (+)= sum_l x[b,l] W[l,:]          label rows of the first layer
+//   small_linear_wgrad  dW[l,:]   = sum_b x[b,l] g[b,:]
+//   label_head          logits = theta Wc^T + bc, loss += CE / B, d theta += ..., d Wc, d bc (one warp per document)
+// ---------------------------------------------------------------------------------------------
+__global__ void small_linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ W, float* __restrict__ out,
+                                        int B, int L, int H, int accumulate) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * H) return;
+  const int b = idx / H, h = idx - b * H;
+  float s = 0.f;
+  for (int l = 0; l < L; ++l) s = fmaf(x[(size_t)b * L + l], __ldg(W + (size_t)l * H + h), s);
+  out[idx] = accumulate ? out[idx] + s : s;
+}
+__global__ void small_linear_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ g, float* __restrict__ dW,
+                                          int B, int L, int H) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= L * H) return;
+  const int l = idx / H, h = idx - l * H;
+  float s = 0.f;
+  for (int b = 0; b < B; ++b) s = fmaf(x[(size_t)b * L + l], g[(size_t)b * H + h], s);
+  dW[idx] = s;
+}
+constexpr int kMaxLabels = 256;
+__global__ void __launch_bounds__(256)
+label_head_kernel(const float* __restrict__ theta, const float* __restrict__ Wc, const float* __restrict__ bc,
+                  const float* __restrict__ labels, int B, int K, int L, float gscale, double* __restrict__ loss,
+                  float* __restrict__ dtheta, int ld_dtheta, float* __restrict__ dWc, float* __restrict__ dbc) {
+  __shared__ float dl_s[8][kMaxLabels];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 8 + warp;
+  if (b >= B) return;
+  const float* th = theta + (size_t)b * K;
+  // logits (lanes over labels), arg-max of the one-hot target row
+  float mx = -INFINITY, tgt_val = -INFINITY;
+  int tgt = 0;
+  for (int l = lane; l < L; l += 32) {
+    float s = bc[l];
+    for (int k = 0; k < K; ++k) s = fmaf(th[k], __ldg(Wc + (size_t)l * K + k), s);
+    dl_s[warp][l] = s;
+    mx = fmaxf(mx, s);
+    const float y = labels[(size_t)b * L + l];
+    if (y > tgt_val) { tgt_val = y; tgt = l; }
+  }
+  mx = warp_max(mx);
+  for (int o = 16; o > 0; o >>= 1) {  // arg-max across lanes (first maximum wins, like torch.argmax)
+    const float ov = __shfl_xor_sync(0xffffffffu, tgt_val, o);
+    const int ot = __shfl_xor_sync(0xffffffffu, tgt, o);
+    if (ov > tgt_val || (ov == tgt_val && ot < tgt)) { tgt_val = ov; tgt = ot; }
+  }
+  float se = 0.f;
+  for (int l = lane; l < L; l += 32) se += __expf(dl_s[warp][l] - mx);
+  se = warp_sum(se);
+  __syncwarp();
+  const float lse = mx + __logf(se);
+  if (lane == 0 && loss != nullptr) atomicAdd(loss, (double)((lse - dl_s[warp][tgt]) / (float)B));
+  if (dtheta == nullptr) return;
+  const float sc = gscale / (float)B;
+  __syncwarp();
+  for (int l = lane; l < L; l += 32) {
+    const float d = (__expf(dl_s[warp][l] - lse) - (l == tgt ? 1.f : 0.f)) * sc;
+    dl_s[warp][l] = d;
+    atomicAdd(&dbc[l], d);
+  }
+  __syncwarp();
+  for (int k = lane; k < K; k += 32) {
+    float acc = 0.f;
+    const float t = th[k];
+    for (int l = 0; l < L; ++l) {
+      const float d = dl_s[warp][l];
+      acc = fmaf(d, __ldg(Wc + (size_t)l * K + k), acc);
+      atomicAdd(&dWc[(size_t)l * K + k], d * t);
+    }
+    dtheta[(size_t)b * ld_dtheta + k] += acc;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // theta_mc: Monte-Carlo document-topic inference in ONE launch.  Ref: avitm.py:470-523 (n_samples full passes of
 // get_theta, averaged) + federated_model.py:170-173 (entries < thr zeroed, rows L1-renormalised).  The encoder
 // pass does not depend on the draw, so only the reparameterised soft-max is repeated: one warp per document
@@ -859,6 +939,32 @@ extern "C" int gf_bow_gather(const int* indptr, const int* indices, const float*
   else if (nc <= 2) bow_gather_kernel<2><<<grid, 256, 0, st>>>(indptr, indices, counts, W1T, H0, B, out, accumulate, wpd);
   else if (nc <= 4) bow_gather_kernel<4><<<grid, 256, 0, st>>>(indptr, indices, counts, W1T, H0, B, out, accumulate, wpd);
   else bow_gather_kernel<8><<<grid, 256, 0, st>>>(indptr, indices, counts, W1T, H0, B, out, accumulate, wpd);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+
+extern "C" int gf_small_linear_fwd(const float* x, const float* W, float* out, int B, int L, int H, int accumulate,
+                                   void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(B >= 1 && L >= 1 && H >= 1, "shapes");
+  small_linear_fwd_kernel<<<(B * H + 255) / 256, 256, 0, st>>>(x, W, out, B, L, H, accumulate);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+extern "C" int gf_small_linear_wgrad(const float* x, const float* g, float* dW, int B, int L, int H, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(B >= 1 && L >= 1 && H >= 1, "shapes");
+  small_linear_wgrad_kernel<<<(L * H + 255) / 256, 256, 0, st>>>(x, g, dW, B, L, H);
+  GF_LAUNCHED();
+  return GF_OK;
+}
+extern "C" int gf_label_head(const float* theta, const float* Wc, const float* bc, const float* labels, int B, int K, int L,
+                             float gscale, double* loss, float* dtheta, int ld_dtheta, float* dWc, float* dbc,
+                             void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  GF_ARG_CHECK(B >= 1 && K >= 1 && L >= 1 && L <= kMaxLabels, "label_size must be <= 256");
+  GF_ARG_CHECK(dtheta == nullptr || (dWc != nullptr && dbc != nullptr), "gradient outputs");
+  label_head_kernel<<<(B + 7) / 8, 256, 0, st>>>(theta, Wc, bc, labels, B, K, L, gscale, loss, dtheta, ld_dtheta, dWc, dbc);
   GF_LAUNCHED();
   return GF_OK;
 }

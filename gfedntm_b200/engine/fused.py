@@ -135,8 +135,9 @@ class FusedEngine:
                  arena=None, solver: str = "adam") -> None:
         if not torch.cuda.is_available():
             raise RuntimeError("FusedEngine needs a CUDA device (sm_100a); use the eager backend on CPU")
-        if model.label_size:
-            raise NotImplementedError("label_size > 0 runs on the eager backend")
+        self.L = int(model.label_size or 0)
+        if self.L and model.infnet == "bow":
+            raise NotImplementedError("labels belong to the contextualized models")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.model = model.to(self.device)
         self.kind = model.infnet
@@ -321,7 +322,7 @@ class FusedEngine:
         collapsed weight every step)."""
         if self.kind == "zeroshot":
             st = self.flat.storage_view(self.flat.P, "inf_net.input_layer.weight")
-            K_.ctm_split(st, self.ctx_z_hi, self.ctx_z_lo)
+            K_.ctm_split(st[:self.C], self.ctx_z_hi, self.ctx_z_lo)
 
     def _refresh_ctm_shadows(self) -> None:
         """bf16 hi/lo operand shadows of the CombinedTM adapt_bert layer and of the contextual half of the first
@@ -355,7 +356,11 @@ class FusedEngine:
         ab = fl.segments["inf_net.adapt_bert.bias"]
         w = fl.segments["inf_net.input_layer.weight"]
         ab_end = (ab.offset + ab.numel + 3) // 4 * 4
-        return [(0, ab.offset), (ab_end, w.offset + self.V * self.hidden[0])]
+        half = self.V * self.hidden[0]
+        pieces = [(0, ab.offset), (ab_end, w.offset + half)]
+        if w.numel > 2 * half:  # label rows of the first layer (supervised CTM) follow the contextual half
+            pieces.append((w.offset + 2 * half, (w.offset + w.numel + 3) // 4 * 4))
+        return pieces
 
     def _hidden_params(self, flat: torch.Tensor):
         Wh, bh = [], []
@@ -398,7 +403,7 @@ class FusedEngine:
     def forward_backward(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *,
                          training: bool = True, sample: bool = True, gscale: float = 1.0,
                          need_grad: bool = True, eps_in=None, mask_enc_in=None, mask_theta_in=None, fed=None,
-                         ctm_reduce_hook=None):
+                         ctm_reduce_hook=None, labels: Optional[torch.Tensor] = None):
         """Runs forward (and backward when ``need_grad``); returns the device scalar
         ``loss = sum_b (kl_weight*KL_b + RL_b)`` (float64, shape [1])."""
         B, K, V = batch.B, self.K, self.V
@@ -423,6 +428,10 @@ class FusedEngine:
             K_.bow_gather(batch.indptr, batch.indices, batch.counts, W1T, pre0_ext, B=B,
                           accumulate=self.kind == "combined")
             W1T = None   # (enc_fwd gets no CSR input any more: everything of layer 0 arrives through pre0_ext)
+        if self.L and labels is not None:
+            # supervised CTM: the one-hot labels are the last label_size inputs of the first layer
+            st_all = self.flat.storage_view(self.flat.P, "inf_net.input_layer.weight")
+            K_.small_linear_fwd(labels[:B].contiguous(), st_all[st_all.shape[0] - self.L:], pre0_ext, accumulate=True)
         pad = [None] * (K_.GF_MAX_HIDDEN - len(self.hidden))
         K_.enc_fwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, training=training,
                    indptr=None, indices=None, counts=None, W1T=W1T, b1=b1, xdense=None, WdT=None,
@@ -466,6 +475,12 @@ class FusedEngine:
                             V=V, N=K)
                 K_.lda_beta_bwd(self.bp, self.dbpT, self.xhat, self.col_rstd, self.dxhat, self._g("beta"),
                                 K=K, V=V, training=training)
+        if self.L and labels is not None:
+            # classification head on theta: mean cross-entropy joins the loss, its gradient joins d theta
+            wc, bcl = "label_classification.weight", "label_classification.bias"
+            K_.label_head(self.theta, self._p(wc), self._p(bcl), labels[:B].contiguous(), B=B, gscale=gscale,
+                          loss=self.loss, dtheta=dtheta if grad else None, dWc=self._g(wc) if grad else None,
+                          dbc=self._g(bcl) if grad else None)
         if not grad:
             return self.loss
 
@@ -486,10 +501,12 @@ class FusedEngine:
                    dWsig=self._g("inf_net.f_sigma.weight"), dbsig=self._g("inf_net.f_sigma.bias"),
                    db1=self._g("inf_net.input_layer.bias"), dpre0=self.dpre0, xdense=None, dWdT=None,
                    seed=seed, step_ctr=self.ctr)
+        if self.L and labels is not None:
+            K_.small_linear_wgrad(labels[:B].contiguous(), self.dpre0[:B], gst[gst.shape[0] - self.L:])
         if self.kind in ("zeroshot", "combined"):
             # d W^T [C,H0] = x_ctx^T . d pre0 on the tensor cores (accumulates into a zeroed target)
             if self.kind == "zeroshot":
-                dWdT = gst
+                dWdT = gst[:self.C]
                 K_.ctm_init_out(dWdT, bias_row=-1, bias=None)
             else:
                 dWdT = self.ctm_dMx[:self.C]  # (zeroed with the step's other accumulators)
@@ -564,24 +581,26 @@ class FusedEngine:
             K_.adam_flat(fl.P[sl], fl.G[sl], fl.M[sl], fl.V2[sl], lr=self.lr, b1=b1, b2=b2, eps=self.adam_eps,
                          wd=self.weight_decay, step=self.step_count + 1, gscale=gscale, step_ctr=self.ctr, solver=self.solver)
 
-    def train_step(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, **kw) -> torch.Tensor:
+    def train_step(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, labels: Optional[torch.Tensor] = None,
+                   **kw) -> torch.Tensor:
         """Forward + backward + Adam on one minibatch.  The kernel sequence is captured into a CUDA
         graph per (input buffers, batch size) and replayed: the first call on a new key runs eagerly
         (warm-up), the second captures, later ones replay.  Injected noise/masks force the eager path."""
         def body():
             if self._self_overlap is not None:
                 K_.step_begin(self.ctr, 0, 1)  # step t first: the update CTAs inside the d-theta sweep read it
-                self.forward_backward(batch, x_ctx, training=True, fed=self._self_overlap, **kw)
+                self.forward_backward(batch, x_ctx, training=True, fed=self._self_overlap, labels=labels, **kw)
                 self.optimizer_step(beta_done=True)
             else:
-                self.forward_backward(batch, x_ctx, training=True, **kw)
+                self.forward_backward(batch, x_ctx, training=True, labels=labels, **kw)
                 self.optimizer_step()
 
         if kw or not self.use_graphs:
             body()
             return self.loss
         return self.run_graphed(("train", batch.indptr.data_ptr(), batch.indices.data_ptr(), batch.B,
-                                 x_ctx.data_ptr() if x_ctx is not None else 0), body)
+                                 x_ctx.data_ptr() if x_ctx is not None else 0,
+                                 labels.data_ptr() if labels is not None else 0), body)
 
     def run_graphed(self, key, body, n_opt_steps: int = 1) -> torch.Tensor:
         """Runs ``body`` (a pure sequence of launches on static buffers) through a cached CUDA graph."""
@@ -610,7 +629,7 @@ class FusedEngine:
     # inference
     # ------------------------------------------------------------------------------------------
     def sample_theta(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, n_samples: int = 1,
-                     thr: float = 0.0) -> torch.Tensor:
+                     thr: float = 0.0, labels: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Mean of ``n_samples`` stochastic draws of theta in eval mode (running BN statistics, no dropout): ONE
         encoder pass and ONE Monte-Carlo kernel for all draws; ``thr > 0`` also applies the result extraction's
         threshold + L1 renormalisation on the device.  Ref: avitm.py:470-523, federated_model.py:170-173."""
@@ -626,6 +645,10 @@ class FusedEngine:
             K_.bow_gather(batch.indptr, batch.indices, batch.counts, W1T, pre0_ext, B=B,
                           accumulate=self.kind == "combined")
             W1T = None   # (enc_fwd gets no CSR input any more: everything of layer 0 arrives through pre0_ext)
+        if self.L and labels is not None:
+            # supervised CTM: the one-hot labels are the last label_size inputs of the first layer
+            st_all = self.flat.storage_view(self.flat.P, "inf_net.input_layer.weight")
+            K_.small_linear_fwd(labels[:B].contiguous(), st_all[st_all.shape[0] - self.L:], pre0_ext, accumulate=True)
         pad = [None] * (K_.GF_MAX_HIDDEN - len(self.hidden))
         K_.enc_fwd(B=B, V=V, K=K, hidden=self.hidden, act=self.act, training=False,
                    indptr=None, indices=None, counts=None, W1T=W1T, b1=b1, xdense=None, WdT=None,

@@ -119,7 +119,7 @@ class FederatedModel:
         local optimiser step.  The step only matters for tensors that are NOT shared (they keep training
         locally); shared tensors are overwritten by the server's result in ``deltaUpdateFit``."""
         if self.backend == "fused":
-            loss = self.engine.forward_backward(mb.bow, mb.x_ctx, training=True).clone()
+            loss = self.engine.forward_backward(mb.bow, mb.x_ctx, training=True, labels=mb.labels).clone()
             self._grad_payload = {n: p.grad.detach().clone() for n, p in self.model.named_parameters()
                                   if n in self.grads_to_share}
             self.engine.optimizer_step()

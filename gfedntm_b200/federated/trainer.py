@@ -153,7 +153,9 @@ class FederatedTrainer:
             if self._ctm_trick and sg.name == "inf_net.input_layer.weight":
                 half = eng.V * eng.hidden[0]  # storage is [2V, H0]: BoW half aggregated, contextual half replicated
                 ranges.append((sg.offset, half, 1))
-                ranges.append((sg.offset + half, end - sg.offset - half, 3))
+                ranges.append((sg.offset + half, half, 3))
+                if end - sg.offset > 2 * half:   # label rows (supervised CTM): aggregated like the BoW half
+                    ranges.append((sg.offset + 2 * half, end - sg.offset - 2 * half, 1))
             else:
                 ranges.append((sg.offset, end - sg.offset, kind))
             cur = end
@@ -187,14 +189,15 @@ class FederatedTrainer:
             self._beta_master_partial = False
 
     # ------------------------------------------------------------------------------------------
-    def step(self, bow: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *, after_backward=None) -> torch.Tensor:
+    def step(self, bow: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *, after_backward=None,
+             labels: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One synchronous global step (local minibatch + aggregation).  Returns this client's summed
         minibatch loss (device tensor).  ``after_backward`` (verification hook): called between the local
         backward pass and the closing aggregation launch; forces the eager (non-graph) path."""
         from ..utils.observability import nvtx_range
 
         with nvtx_range("gfedntm.global_step"), self.timer.region("global_step"):
-            loss = self._step(bow, x_ctx, after_backward)
+            loss = self._step(bow, x_ctx, after_backward, labels)
         if self.metrics.path and self.global_step % self.metrics_every == 0:
             t = self.timer.summary()  # (one synchronisation per logging interval)
             self.metrics.log(step=self.global_step, rank=self.rank, world=self.world, agg=self.agg,
@@ -202,11 +205,11 @@ class FederatedTrainer:
                              docs_per_s=(1e3 * bow.B * self.world / t["global_step"]) if t.get("global_step") else None)
         return loss
 
-    def _step(self, bow: CsrBatch, x_ctx, after_backward) -> torch.Tensor:
+    def _step(self, bow: CsrBatch, x_ctx, after_backward, labels=None) -> torch.Tensor:
         eng = self.model.engine
         self.global_step += 1
         if self.world == 1:
-            return eng.train_step(bow, x_ctx)
+            return eng.train_step(bow, x_ctx, labels=labels)
         from ..ops import kernels as K_
 
         if self._overlap is not None and self.agg == "grad":
@@ -215,7 +218,7 @@ class FederatedTrainer:
         def body():
             if self.agg == "grad" and self._overlap is not None:
                 K_.step_begin(eng.ctr, 0, 1)  # epoch / Adam step t first: the overlapped part reads it too
-                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], fed=self._overlap)
+                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], fed=self._overlap, labels=labels)
                 if after_backward is not None:
                     after_backward()
                 self._launch("grad", eng.step_count + 1, parts=1)
@@ -224,7 +227,7 @@ class FederatedTrainer:
                 if self._ctm_trick:
                     K_.step_begin(eng.ctr, 0, 1)  # the small all-reduce inside the backward pass uses epoch t
                     hook = lambda buf: self.aggregator.allreduce_small(buf, eng.ctr)  # noqa: E731
-                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], ctm_reduce_hook=hook)
+                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], ctm_reduce_hook=hook, labels=labels)
                 if after_backward is not None:
                     after_backward()
                 if not self._ctm_trick:
@@ -238,7 +241,7 @@ class FederatedTrainer:
                     eng._refresh_ctm_shadows()
                 eng._refresh_ctx_shadows()
             else:
-                eng.forward_backward(bow, x_ctx, training=True)
+                eng.forward_backward(bow, x_ctx, training=True, labels=labels)
                 eng.optimizer_step()
                 if after_backward is not None:
                     after_backward()
@@ -252,7 +255,7 @@ class FederatedTrainer:
                 eng.step_count += 1
             return eng.loss
         key = ("fed", self.agg, bow.indptr.data_ptr(), bow.indices.data_ptr(), bow.B,
-               x_ctx.data_ptr() if x_ctx is not None else 0)
+               x_ctx.data_ptr() if x_ctx is not None else 0, labels.data_ptr() if labels is not None else 0)
         eager_warmup = key not in eng._warm
         loss = eng.run_graphed(key, body, n_opt_steps=1)
         if eager_warmup and self.agg == "grad":

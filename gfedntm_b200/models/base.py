@@ -181,21 +181,21 @@ class NeuralTopicModel:
         self.model = self.model.to(self.device)
         self.early_stopping = EarlyStopping(patience=5, verbose=False)
 
-        fused_ok = (self.device.type == "cuda" and label_size == 0
+        fused_ok = (self.device.type == "cuda" and label_size <= 256
                     and activation != "swish" and n_components <= 236 and max(hidden_sizes) <= 256
                     and len(hidden_sizes) <= 8)
         if backend == "auto":
             backend = "fused" if fused_ok else "eager"
             if not fused_ok and self.device.type == "cuda":
                 why = [msg for cond, msg in (
-                    (label_size != 0, "label_size>0"),
+                    (label_size > 256, "label_size>256"),
                     (activation == "swish", "activation='swish'"), (n_components > 236, "n_components>236"),
                     (max(hidden_sizes) > 256, "hidden size>256"), (len(hidden_sizes) > 8, "more than 8 hidden layers"))
                        if cond]
                 self.logger.warning("this configuration (%s) is outside the fused sm_100a engine and runs on the eager "
                                     "PyTorch backend, typically 10-70x slower per step", ", ".join(why))
         if backend == "fused" and not fused_ok:
-            raise ValueError("the fused backend needs CUDA, label_size=0, n_components<=236 and hidden sizes<=256")
+            raise ValueError("the fused backend needs CUDA, label_size<=256, n_components<=236 and hidden sizes<=256")
         self.backend = backend
         self.engine = None
         self._pending_opt_state = None
@@ -293,7 +293,7 @@ class NeuralTopicModel:
         """One optimisation step on a staged minibatch; returns the summed loss (0-d/1-d tensor,
         still on the device)."""
         if self.backend == "fused":
-            return self.engine.train_step(mb.bow, mb.x_ctx).clone()
+            return self.engine.train_step(mb.bow, mb.x_ctx, labels=mb.labels).clone()
         self.model.zero_grad()
         loss = self._eager_forward_loss(mb)
         loss.backward()
@@ -320,7 +320,7 @@ class NeuralTopicModel:
         with torch.no_grad():
             for mb in loader:
                 if self.backend == "fused":
-                    loss = self.engine.forward_backward(mb.bow, mb.x_ctx, training=False, need_grad=False)
+                    loss = self.engine.forward_backward(mb.bow, mb.x_ctx, training=False, need_grad=False, labels=mb.labels)
                     total += float(loss.item())
                 else:
                     total += float(self._eager_forward_loss(mb).item())
@@ -394,7 +394,7 @@ class NeuralTopicModel:
         with torch.no_grad():
             for mb in loader:
                 if self.backend == "fused":
-                    th = self.engine.sample_theta(mb.bow, mb.x_ctx, n_samples=n_samples, thr=thr)
+                    th = self.engine.sample_theta(mb.bow, mb.x_ctx, n_samples=n_samples, thr=thr, labels=mb.labels)
                 else:
                     x = mb.bow.to_dense()
                     th = torch.zeros(mb.size, self.n_components, device=self.device)

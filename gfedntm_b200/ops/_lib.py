@@ -200,6 +200,11 @@ def _declare(lib: C.CDLL) -> None:
                                   _p, _i, _p]
     for fn in ("gf_ctm_split", "gf_ctm_init_out", "gf_ctm_vc", "gf_ctm_rc", "gf_ctm_rr", "gf_adam_split"):
         getattr(lib, fn).restype = _i
+    lib.gf_small_linear_fwd.argtypes = [_p, _p, _p, _i, _i, _i, _i, _p]
+    lib.gf_small_linear_wgrad.argtypes = [_p, _p, _p, _i, _i, _i, _p]
+    lib.gf_label_head.argtypes = [_p, _p, _p, _p, _i, _i, _i, _f, _p, _p, _i, _p, _p, _p]
+    for fn in ("gf_small_linear_fwd", "gf_small_linear_wgrad", "gf_label_head"):
+        getattr(lib, fn).restype = _i
     lib.gf_bow_gather.argtypes = [_p, _p, _p, _p, _i, _i, _p, _i, _p]
     lib.gf_bow_gather.restype = _i
     lib.gf_theta_mc.argtypes = [_p, _p, _p, _p, _p, _p, _f, _i, _i, _i, _u64, _f, _p, _p]

@@ -433,3 +433,28 @@ def bow_gather(indptr, indices, counts, W1T, out, *, B: int, accumulate: bool = 
     assert W1T.stride(1) == 1 and W1T.stride(0) == W1T.shape[1] and out.stride(0) == W1T.shape[1]
     check(_lib.load().gf_bow_gather(_ptr(indptr), _ptr(indices), _ptr(counts), _ptr(W1T), W1T.shape[1], B, _ptr(out),
                                     int(accumulate), _stream()), "gf_bow_gather")
+
+
+def small_linear_fwd(x, W, out, *, accumulate: bool) -> None:
+    """out[b,:] (+)= x[b,:] @ W  with x [B,L], W [L,H] (label rows of the first encoder layer)."""
+    B, L = x.shape
+    assert W.shape[0] == L and W.stride(1) == 1 and W.stride(0) == W.shape[1] and x.is_contiguous()
+    check(_lib.load().gf_small_linear_fwd(_ptr(x), _ptr(W), _ptr(out), B, L, W.shape[1], int(accumulate), _stream()),
+          "gf_small_linear_fwd")
+
+
+def small_linear_wgrad(x, g, dW) -> None:
+    """dW [L,H] = x^T g  with x [B,L], g [B,H]."""
+    B, L = x.shape
+    assert x.is_contiguous() and g.is_contiguous() and dW.stride(1) == 1 and dW.stride(0) == g.shape[1]
+    check(_lib.load().gf_small_linear_wgrad(_ptr(x), _ptr(g), _ptr(dW), B, L, g.shape[1], _stream()),
+          "gf_small_linear_wgrad")
+
+
+def label_head(theta, Wc, bc, labels, *, B: int, gscale: float, loss, dtheta=None, dWc=None, dbc=None) -> None:
+    """Classification head of the supervised CTM: mean cross-entropy into ``loss`` and (optionally) its gradients."""
+    L, K = Wc.shape
+    assert theta.stride(0) == K and labels.is_contiguous() and labels.shape[1] == L and Wc.is_contiguous()
+    check(_lib.load().gf_label_head(_ptr(theta), _ptr(Wc), _ptr(bc), _ptr(labels), B, K, L, gscale, _ptr(loss),
+                                    _ptr(dtheta), dtheta.stride(0) if dtheta is not None else 0, _ptr(dWc), _ptr(dbc),
+                                    _stream()), "gf_label_head")

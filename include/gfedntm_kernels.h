@@ -149,6 +149,15 @@ typedef struct GfEncArgs {
 int gf_step_begin(long long* ctr, int inc_rng, int inc_opt, void* stream);
 int gf_enc_fwd(const GfEncArgs* args, void* stream);
 
+/* Supervised CTM (label_size > 0; ref: ctm_network/inference_network.py:79-94,178-183, decoding_network.py:84-85,
+ * 156-159, ctm.py:292-296).  gf_small_linear_fwd: out[b,:] (+)= x[b,:] W (the one-hot labels' rows of the first
+ * layer); gf_small_linear_wgrad: dW = x^T g; gf_label_head: logits = theta Wc^T + bc, loss += mean cross-entropy
+ * against argmax(labels), and with dtheta != null: dtheta[b,:K] += d/d theta, dWc / dbc += (atomics, zeroed by the
+ * caller); gradients carry gscale / B.                                                                        */
+int gf_small_linear_fwd(const float* x, const float* W, float* out, int B, int L, int H, int accumulate, void* stream);
+int gf_small_linear_wgrad(const float* x, const float* g, float* dW, int B, int L, int H, void* stream);
+int gf_label_head(const float* theta, const float* Wc, const float* bc, const float* labels, int B, int K, int L,
+                  float gscale, double* loss, float* dtheta, int ld_dtheta, float* dWc, float* dbc, void* stream);
 /* First-layer contribution of the sparse BoW input: out[b,:] (+)= sum over the document's non-zeros of
  * count * W1T[word,:]  (several warps per document, rows kept in flight; feed the result to gf_enc_fwd through
  * GfEncArgs.pre0_ext with indptr = null).  Ref: inference_network.py:78.                                    */

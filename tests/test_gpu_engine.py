@@ -269,3 +269,60 @@ def test_single_gpu_overlapped_beta_update_matches_separate_kernel(monkeypatch):
     assert float(diff.mean()) < 0.05 * 2e-3 * 3 and float((diff > 2e-3).float().mean()) < 0.02
     assert torch.equal(res["1"][2][:K, :V].float(), res["1"][1].to(torch.bfloat16).float())
     assert torch.equal(res["1"][3][:, :K].float(), res["1"][1].t().to(torch.bfloat16).float())
+
+
+@pytest.mark.parametrize("kind", ["combined", "zeroshot"])
+def test_engine_supervised_head_matches_autograd(kind):
+    """label_size > 0 on the fused path: labels as extra first-layer inputs, Linear(K -> L) head on theta with the mean
+    cross-entropy added to the loss (decoding_network.py:84-85,156-159, ctm.py:292-296) -- against eager autograd."""
+    from gfedntm_b200.engine.fused import FusedEngine
+    from gfedntm_b200.models.networks import DecoderNetwork, elbo_terms
+    from gfedntm_b200.ops.decoder import CsrBatch
+
+    torch.manual_seed(0)
+    B, V, K, C, L = 64, 1200, 16, 40, 7
+    g = torch.Generator(device="cuda").manual_seed(5)
+    model = DecoderNetwork(V, K, "prodLDA", (32, 32), "softplus", 0.2, True, infnet=kind, contextual_size=C, label_size=L)
+    with torch.no_grad():
+        model.beta.mul_(20.0)
+    ref = copy.deepcopy(model).cuda().train()
+    x = torch.zeros(B, V, device="cuda")
+    x.scatter_add_(1, torch.randint(0, V, (B, 50), device="cuda", generator=g), torch.ones(B, 50, device="cuda"))
+    x_ctx = torch.randn(B, C, device="cuda", generator=g)
+    labels = F.one_hot(torch.randint(0, L, (B,), device="cuda", generator=g), L).float()
+    eps = torch.randn(B, K, device="cuda", generator=g)
+    me, mt = _masks(B, 32, K, 0.2, 0.2, g)
+    eng = FusedEngine(model, max_batch=B, max_nnz=B * 50, lr=2e-3, seed=1)
+    loss = eng.forward_backward(CsrBatch.from_dense(x), x_ctx, training=True, eps_in=eps, mask_enc_in=me,
+                                mask_theta_in=mt, labels=labels)
+    torch.cuda.synchronize()
+    inf = ref.inf_net
+    h = inf.hiddens(inf.activation(inf.input_layer(inf.first_layer_input(x, x_ctx, labels)))) * me
+    mu = inf.f_mu_batchnorm(inf.f_mu(h))
+    logvar = inf.f_sigma_batchnorm(inf.f_sigma(h))
+    theta = F.softmax(mu + eps * torch.exp(0.5 * logvar), dim=1) * mt
+    kl, rl = elbo_terms(x, ref.decode(theta), ref.prior_mean, ref.prior_variance, mu, torch.exp(logvar), logvar)
+    ref_loss = (kl + rl).sum() + torch.nn.CrossEntropyLoss()(ref.label_classification(theta), torch.argmax(labels, 1))
+    ref_loss.backward()
+    assert abs(loss.item() - ref_loss.item()) <= 3e-3 * abs(ref_loss.item()), (loss.item(), ref_loss.item())
+    bad = []
+    for name, p in ref.named_parameters():
+        got = eng.flat.view(eng.flat.G, name)
+        scale = p.grad.abs().max().item()
+        err = (got - p.grad).abs().max().item()
+        if err > 3e-2 * scale + 2e-3:
+            bad.append(f"{name}: err {err:.3e} scale {scale:.3e}")
+    assert not bad, "\n".join(bad)
+    # the head's own gradients are exact fp32 work: tighter
+    for name in ("label_classification.weight", "label_classification.bias"):
+        torch.testing.assert_close(eng.flat.view(eng.flat.G, name), dict(ref.named_parameters())[name].grad, rtol=2e-3, atol=1e-6)
+    # one optimiser step moves every tensor, label rows of the first layer included
+    before = eng.flat.P.clone()
+    eng.optimizer_step()
+    torch.cuda.synchronize()
+    w = eng.flat.segments["inf_net.input_layer.weight"]
+    lab = slice(w.offset + w.numel - L * 32, w.offset + w.numel)          # storage [fan_in, H0]: the last L rows
+    assert float((eng.flat.P[lab] - before[lab]).abs().min()) > 0
+    ctx_rows = slice(w.offset + w.numel - (L + C) * 32, w.offset + w.numel - L * 32) if kind == "zeroshot" else \
+        slice(w.offset + V * 32, w.offset + 2 * V * 32)
+    assert float((eng.flat.P[ctx_rows] - before[ctx_rows]).abs().max()) > 0
