@@ -136,6 +136,46 @@ class TMWrapper:
         m.fit(ds)
         return m, ds, keep, time.perf_counter() - t0
 
+    # -- the reference's calling convention: a model folder with config.json, a CLI run as a subprocess ----------
+    def create_model_folder(self, path: str, name: str, trainer: str, training_set: str, tm_params: Optional[dict] = None,
+                            preproc: Optional[dict] = None, description: str = "", **extra) -> str:
+        """Writes ``<path>/<name>/config.json`` in the layout ``topicmodeling.py`` reads (ref:
+        tm_wrapper.py:60-121: ``_get_model_config`` / ``_do_preproc`` build the same file).  ``training_set``: json
+        describing the parquet sources (``{"Dtsets": [{"parquet", "idfld", "lemmasfld"}]}``)."""
+        folder = Path(path) / name
+        folder.mkdir(parents=True, exist_ok=True)
+        cfg = {"name": name, "description": description, "trainer": trainer, "TrDtSet": str(training_set),
+               "Preproc": {**dict(min_lemas=3, no_below=1, no_above=1.0, keep_n=100000, stopwords=[], equivalences=[]),
+                           **(preproc or {})},
+               "TMparam": dict(tm_params or {}), "hierarchy-level": 0}
+        cfg.update(extra)
+        with open(folder / "config.json", "w", encoding="utf-8") as f:
+            json.dump(cfg, f, indent=1)
+        return str(folder / "config.json")
+
+    def _run_cli(self, *args: str) -> float:
+        """Runs the CLI in a subprocess (like the reference, tm_wrapper.py:123-169) and returns its wall time."""
+        import subprocess
+        import sys
+
+        cmd = [sys.executable, "-m", "gfedntm_b200.aux_modules.topicmodeling", *args]
+        self._logger.info("running %s", " ".join(cmd))
+        t0 = time.perf_counter()
+        res = subprocess.run(cmd, capture_output=True, text=True, cwd=str(Path(__file__).resolve().parents[2]))
+        dt = time.perf_counter() - t0
+        if res.returncode != 0:
+            raise RuntimeError(f"topicmodeling CLI failed ({res.returncode}):\n{res.stdout[-2000:]}\n{res.stderr[-2000:]}")
+        return dt
+
+    def preproc_corpus_cli(self, config_file: str, nw: int = 0) -> float:
+        return self._run_cli("--preproc", "--config", config_file, "--nw", str(nw))
+
+    def train_model_cli(self, config_file: str) -> float:
+        return self._run_cli("--train", "--config", config_file)
+
+    def train_htm_submodel_cli(self, config_father: str, config_child: str) -> float:
+        return self._run_cli("--hierarchical", "--config", config_father, "--config_child", config_child)
+
     # -- evaluation ------------------------------------------------------------------------------
     @staticmethod
     def calculate_cohr_vs_ref(model, reference_bow, k: int = 10) -> float:

@@ -108,3 +108,44 @@ def test_exact_word_movers_distance():
     # moving half of the mass: {w1, w2} -> {w1, w3} costs 0.5 * |w2 - w3| at most
     assert mod.wmd(["w1", "w2"], ["w1", "w3"], vec) <= 0.5 * np.linalg.norm(vec["w2"] - vec["w3"]) + 1e-9
     assert np.isnan(mod.wmd(["zz"], a, vec))
+
+
+def test_tmwrapper_cli_preproc_train_and_child_model(tmp_path):
+    """The reference's calling convention (tm_wrapper.py:123-169,345): a model folder with config.json, the
+    preprocessing / training / hierarchical CLI run as a SUBPROCESS, on the shipped sample parquet."""
+    import json
+    import os
+
+    import numpy as np
+
+    from gfedntm_b200.aux_modules.tm_wrapper import TMWrapper
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    trset = tmp_path / "trset.json"
+    trset.write_text(json.dumps({"name": "t", "Dtsets": [{"parquet": os.path.join(root, "static/datasets/s2cs_tiny.parquet"),
+                                                          "source": "s2cs_tiny", "idfld": "id", "lemmasfld": ["lemmas"],
+                                                          "filter": ""}]}))
+    w = TMWrapper()
+    cfg = w.create_model_folder(str(tmp_path), "root", "prodLDA", str(trset),
+                                tm_params=dict(ntopics=5, num_epochs=3, batch_size=64, hidden_sizes=[16, 16], num_samples=2),
+                                preproc=dict(min_lemas=10, stopwords=["english_generic", "S2_stopwords"],
+                                             equivalences=["S2_equivalences"]))
+    t_pre = w.preproc_corpus_cli(cfg)
+    assert t_pre > 0 and (tmp_path / "root" / "corpus.parquet").exists() and (tmp_path / "root" / "vocabulary.txt").exists()
+    vocab = (tmp_path / "root" / "vocabulary.txt").read_text().split()
+    assert "the" not in vocab and "tumour" not in vocab and len(vocab) > 50
+    t_tr = w.train_model_cli(cfg)
+    assert t_tr > 0 and (tmp_path / "root" / "TMmodel").is_dir() and (tmp_path / "root" / "model.pth").exists()
+    rep = json.loads((tmp_path / "root" / "train_report.json").read_text())
+    assert rep["ntopics"] == 5 and rep["documents"] > 300
+    child = w.create_model_folder(str(tmp_path), "child", "prodLDA", str(trset),
+                                  tm_params=dict(ntopics=3, num_epochs=2), **{"hierarchy-level": 1, "htm-version": "htm-ds",
+                                                                              "expansion_tpc": 0, "thr": 0.05})
+    w.train_htm_submodel_cli(cfg, child)
+    assert (tmp_path / "child" / "TMmodel").is_dir()
+    # unavailable third-party trainers are refused with a clear message
+    bad = w.create_model_folder(str(tmp_path), "bad", "mallet", str(trset))
+    import pytest
+
+    with pytest.raises(RuntimeError, match="unavailable"):
+        w.train_model_cli(bad)
