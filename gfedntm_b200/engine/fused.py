@@ -254,6 +254,11 @@ class FusedEngine:
         self.sync_shadows()
         self._self_overlap = None
         self._init_self_overlap(arena)
+        # Side stream of the training step: the per-step CSC transpose (needed only by the backward pass) runs under
+        # the encoder forward, and the optimiser step of beta (pure HBM traffic) starts as soon as d beta is final and
+        # runs under the tail of the d-theta sweep and the small latency-bound kernels of the encoder backward.
+        self._side = torch.cuda.Stream(self.device) if os.environ.get("GFEDNTM_SIDE_STREAM", "1") != "0" else None
+        self._side_beta = False
 
     def _init_self_overlap(self, arena) -> None:
         """Single-GPU training, OPT-IN (``GFEDNTM_SELF_OVERLAP=1``): the beta part of the optimiser step runs on CTAs of
@@ -403,7 +408,7 @@ class FusedEngine:
     def forward_backward(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *,
                          training: bool = True, sample: bool = True, gscale: float = 1.0,
                          need_grad: bool = True, eps_in=None, mask_enc_in=None, mask_theta_in=None, fed=None,
-                         ctm_reduce_hook=None, labels: Optional[torch.Tensor] = None):
+                         ctm_reduce_hook=None, labels: Optional[torch.Tensor] = None, side_stream: bool = False):
         """Runs forward (and backward when ``need_grad``); returns the device scalar
         ``loss = sum_b (kl_weight*KL_b + RL_b)`` (float64, shape [1])."""
         B, K, V = batch.B, self.K, self.V
@@ -414,9 +419,15 @@ class FusedEngine:
         K_.step_begin(self.ctr, 1, 0)
         self.zpool.zero_()
         self.dpool.zero_()
+        side = self._side if (grad and side_stream and self.is_prod and self.decoder.folded) else None
         if grad:
             self.flat.G[:self.flat.small_end].zero_()
-            self.csc.build(batch, dynamic_nnz=True)
+            if side is not None:
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    self.csc.build(batch, dynamic_nnz=True)
+            else:
+                self.csc.build(batch, dynamic_nnz=True)
 
         W1T, b1, pre0_ext = self._first_layer(x_ctx, B)
         Wh, bh = self._hidden_params(self.flat.P)
@@ -456,11 +467,20 @@ class FusedEngine:
             self._nbt_pending += 1  # BatchNorm step counters are flushed lazily (state_dict hook)
 
         if self.is_prod:
+            hook = None
+            if side is not None:
+                torch.cuda.current_stream().wait_stream(side)   # the CSC transpose is needed from here on
+                if fed is None:
+                    def hook():  # optimiser step of beta on the side stream (joined in optimizer_step)
+                        side.wait_stream(torch.cuda.current_stream())
+                        with torch.cuda.stream(side):
+                            self._adam_beta_now(gscale=1.0)
+                        self._side_beta = True
             _, dtheta = self.decoder.forward_backward(
                 self.theta, self.theta_colsum, self.beta_bf, self.betaT_bf, batch, self.csc,
                 training=training, running_mean=bbn.running_mean, running_var=bbn.running_var,
                 dbeta=self._g("beta") if grad else None, loss=self.loss, gscale=gscale, need_grad=grad,
-                fed=fed if (grad and self.decoder.folded) else None)
+                fed=fed if (grad and self.decoder.folded) else None, on_dbeta_final=hook)
         else:
             beta = self._p("beta")
             K_.lda_beta_fwd(beta, K=K, V=V, eps=BN_EPS, momentum=BN_MOMENTUM, training=training,
@@ -552,7 +572,10 @@ class FusedEngine:
             self.ctm_adam_step(gscale=gscale)
         self._refresh_ctx_shadows()
         K, V = self.K, self.V
-        if beta_done:
+        if self._side_beta:   # beta was stepped on the side stream during the backward pass: join it
+            torch.cuda.current_stream().wait_stream(self._side)
+            self._side_beta = False
+        elif beta_done:
             pass
         elif self.is_prod:
             K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"),
@@ -565,6 +588,14 @@ class FusedEngine:
             K_.adam_flat(fl.P[sl], fl.G[sl], fl.M[sl], fl.V2[sl], lr=self.lr, b1=b1, b2=b2,
                          eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
                          step_ctr=self.ctr, solver=self.solver)
+
+    def _adam_beta_now(self, gscale: float = 1.0) -> None:
+        """The fused optimiser step of beta + shadows; the device step counter must already hold step t."""
+        fl = self.flat
+        b1, b2 = self.betas
+        K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"), fl.view(fl.V2, "beta"),
+                     self.beta_bf, self.betaT_bf, K=self.K, V=self.V, lr=self.lr, b1=b1, b2=b2, eps=self.adam_eps,
+                     wd=self.weight_decay, step=self.step_count + 1, gscale=gscale, step_ctr=self.ctr, solver=self.solver)
 
     def optimizer_step_beta(self, gscale: float = 1.0) -> None:
         """Adam on beta alone (federated runs that do not share beta); the caller advanced the step counter."""
@@ -590,6 +621,10 @@ class FusedEngine:
             if self._self_overlap is not None:
                 K_.step_begin(self.ctr, 0, 1)  # step t first: the update CTAs inside the d-theta sweep read it
                 self.forward_backward(batch, x_ctx, training=True, fed=self._self_overlap, labels=labels, **kw)
+                self.optimizer_step(beta_done=True)
+            elif self._side is not None and self.is_prod and self.decoder.folded:
+                K_.step_begin(self.ctr, 0, 1)  # step t first: beta is stepped on the side stream during the backward
+                self.forward_backward(batch, x_ctx, training=True, labels=labels, side_stream=True, **kw)
                 self.optimizer_step(beta_done=True)
             else:
                 self.forward_backward(batch, x_ctx, training=True, labels=labels, **kw)

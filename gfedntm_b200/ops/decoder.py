@@ -134,7 +134,8 @@ class ProdLDADecoder:
                          betaT_bf: torch.Tensor, batch: CsrBatch, csc: Optional[CscWorkspace], *,
                          training: bool, running_mean: Optional[torch.Tensor],
                          running_var: Optional[torch.Tensor], dbeta: Optional[torch.Tensor],
-                         loss: Optional[torch.Tensor], gscale: float = 1.0, need_grad: bool = True, fed=None):
+                         loss: Optional[torch.Tensor], gscale: float = 1.0, need_grad: bool = True, fed=None,
+                         on_dbeta_final=None):
         """Runs the sweeps.  Returns (rl[B], dtheta[B,Kp] or None).  ``dbeta`` [K,ld] is overwritten.
 
         ``fed`` (folded formulation only): an object with ``signal_beta_ready()``, ``dev_args`` (device
@@ -183,6 +184,10 @@ class ProdLDADecoder:
         K_.gram(self.beta3, beta_bf, self.gram_partial, V=V)
         K_.gram_finish(self.gram_partial, self.gram_parts, self.beta_s, K=Kt, col_hi=self.Vpad,
                        col_lo=self.Vpad + self.n_ext * TILE)
+        if on_dbeta_final is not None:
+            # d beta is final and the unscaled beta shadows are no longer read by this step (ROW_GRAD2 reads the scaled
+            # copy): the caller may start the optimiser step of beta now (engine: side stream)
+            on_dbeta_final()
         if fed is not None:
             # d beta is final and this rank no longer reads its unscaled beta shadows: peers may push
             fed.signal_beta_ready()
