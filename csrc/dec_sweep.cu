@@ -121,9 +121,13 @@ __host__ __device__ constexpr int mode_sb_stages(int m) { return mode_has_sb(m) 
 
 struct Smem {
   uint8_t* a;
-  uint8_t* b[kMaxStages];
-  float4* sb[kSbStagesMax];
-  uint8_t* p[2];
+  uint8_t* b0;         // operand stages: b0 + i * bstride   (address arithmetic, not a pointer table: a table
+  uint32_t bstride;    //  indexed at run time lives in local memory and costs the single MMA thread a load per use)
+  float4* sb0;         // side-band ring: sb0 + i * kBN
+  uint8_t* p0;         // P tiles: p0 + i * 32 KB
+  __device__ __forceinline__ uint8_t* b(int i) const { return b0 + (uint32_t)i * bstride; }
+  __device__ __forceinline__ float4* sb(int i) const { return sb0 + i * kBN; }
+  __device__ __forceinline__ uint8_t* p(int i) const { return p0 + (uint32_t)i * (kBN * 256u); }
   uint64_t* a_full;
   uint64_t* a_empty;
   uint64_t* b_full;    // [kMaxStages]  operand tile landed
@@ -146,7 +150,7 @@ struct Smem {
 // so a 128-wide tile of either is two TMA boxes of {64 columns x Kp rows} (Kp*128 bytes each,
 // 128B-swizzled rows).  For MMA1 both tiles are MN-major operands (rows = contraction index);
 // for MMA2 the streamed tile's very same bytes are a K-major B operand (rows = N index = topics).
-template <int kMode>
+template <int kMode, bool kFed = false>
 __global__ void __launch_bounds__(kThreads, 1)
 sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant__ CUtensorMap tm_beta,
              const __grid_constant__ FedTmaps fed_tm, const SweepParams p) {
@@ -169,17 +173,13 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   Smem s;
   s.a = base;
   uint8_t* cur = base + tile_bytes;
-  for (int i = 0; i < kMaxStages; ++i) {
-    s.b[i] = cur;
-    if (i < stages) cur += stile_bytes;
-  }
-  s.p[0] = cur;
-  s.p[1] = cur + kPBytes;
+  s.b0 = cur;
+  s.bstride = stile_bytes;
+  cur += (uint32_t)stages * stile_bytes;
+  s.p0 = cur;
   if (kHasMMA2) cur += kPBytes * p.p_bufs;  // double-buffered when it fits: epilogue(t+1) overlaps MMA2(t)
-  for (int i = 0; i < kSbStagesMax; ++i) {
-    s.sb[i] = reinterpret_cast<float4*>(cur);
-    if (i < kSbStages) cur += kSbBytes;
-  }
+  s.sb0 = reinterpret_cast<float4*>(cur);
+  cur += kSbBytes * kSbStages;
   uint64_t* bars = reinterpret_cast<uint64_t*>(cur);
   s.a_full = bars + 0;
   s.a_empty = bars + 1;
@@ -244,12 +244,12 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   // federated aggregation (NVLink peer loads / stores) with the sweep the other CTAs are running.
   int n_sweep = (int)gridDim.x;
   bool agg_role = false;
-  if (kMode == ROW_GRAD2 && p.fed != nullptr) {
+  if (kFed) {
     n_sweep = (int)gridDim.x - p.fed_ctas;
     agg_role = (int)blockIdx.x >= n_sweep;
   }
 
-  if (kMode == ROW_GRAD2 && agg_role) {
+  if (kFed && agg_role) {
     // (runs the aggregation after the role dispatch below, together with the sweep CTAs that are done)
   } else if (warp == 0) {
     // ============================ TMA producer ============================
@@ -270,8 +270,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
             mbar_wait(&s.b_empty[st], ((b_it / stages) & 1) ^ 1);
             mbar_arrive_expect_tx(&s.b_full[st], stile_bytes);
             const int tc = (kMode == COL_STATS2) ? (p.ext_tile0 + t) : t;
-            tma_load_2d(s.b[st], tm_strm, &s.b_full[st], tc * kBN, 0);
-            tma_load_2d(s.b[st] + blk, tm_strm, &s.b_full[st], tc * kBN + 64, 0);
+            tma_load_2d(s.b(st), tm_strm, &s.b_full[st], tc * kBN, 0);
+            tma_load_2d(s.b(st) + blk, tm_strm, &s.b_full[st], tc * kBN + 64, 0);
             if (kSb) {
               // side band: 128 float4 = 2 KB, plain bulk copy with its own full/empty pair (its ring
               // slot is only reused after the epilogue released it, so the parity can never alias)
@@ -280,7 +280,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
               mbar_arrive_expect_tx(&s.sb_full[sbs], kSbBytes);
               asm volatile(
                   "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::
-                      "r"(smem_u32(s.sb[sbs])),
+                      "r"(smem_u32(s.sb(sbs))),
                   "l"(reinterpret_cast<uint64_t>(p.sb_stream + (size_t)t * kBN)), "r"(kSbBytes),
                   "r"(smem_u32(&s.sb_full[sbs]))
                   : "memory");
@@ -296,8 +296,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
               const int st = b_it % stages;
               mbar_wait(&s.b_empty[st], ((b_it / stages) & 1) ^ 1);
               mbar_arrive_expect_tx(&s.b_full[st], stile_bytes);
-              tma_load_2d(s.b[st], tm_strm, &s.b_full[st], (p.ext_tile0 + i) * kBN, 0);
-              tma_load_2d(s.b[st] + blk, tm_strm, &s.b_full[st], (p.ext_tile0 + i) * kBN + 64, 0);
+              tma_load_2d(s.b(st), tm_strm, &s.b_full[st], (p.ext_tile0 + i) * kBN, 0);
+              tma_load_2d(s.b(st) + blk, tm_strm, &s.b_full[st], (p.ext_tile0 + i) * kBN + 64, 0);
               ++b_it;
             }
           }
@@ -315,8 +315,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
       auto issue_mma2 = [&](int st, bool first) {
         const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;  // caller observed p_full[pb]
         tc_fence_after();
-        const uint32_t p_base = smem_u32(s.p[pb]);
-        const uint32_t b_base = smem_u32(s.b[st]);
+        const uint32_t p_base = smem_u32(s.p(pb));
+        const uint32_t b_base = smem_u32(s.b(st));
 #pragma unroll
         for (int j = 0; j < kBN / 16; ++j) {  // contraction over the 128 streamed columns, 16 per step
           const uint64_t da = umma_smem_desc(p_base + (j >> 2) * 16384u + (j & 3) * 32u, 16, 1024);
@@ -361,7 +361,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
               if (mbar_test_wait(&s.b_full[st], (bi / stages) & 1) &&
                   mbar_test_wait(&s.d1_empty[buf], ((d1_it >> 1) & 1) ^ 1)) {
                 tc_fence_after();
-                const uint32_t b_base = smem_u32(s.b[st]);
+                const uint32_t b_base = smem_u32(s.b(st));
                 const uint32_t d_addr = tmem + buf * kBN;
 #pragma unroll
                 for (int j = 0; j < 15; ++j) {
@@ -385,7 +385,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         umma_commit(s.a_empty);
         ++a_it;
       }
-      if (kMode == ROW_GRAD2 && p.fed != nullptr) {
+      if (kFed) {
         // This CTA goes on to the aggregation and reuses its shared memory: wait for the asynchronous
         // arrivals of the commits nobody else waits for (the last operand stages, P tiles and stationary tile).
         const uint32_t nb = b_it < (uint32_t)stages ? b_it : (uint32_t)stages;
@@ -440,9 +440,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
           mbar_wait(&s.d1_full[buf], (d1_it >> 1) & 1);
           tc_fence_after();
           const uint32_t pb = (p.p_bufs == 2) ? (p_it & 1) : 0;
-          const uint32_t pbuf = smem_u32(s.p[pb]);
+          const uint32_t pbuf = smem_u32(s.p(pb));
           if (m2) mbar_wait(&s.p_empty[pb], (((p.p_bufs == 2) ? (p_it >> 1) : p_it) & 1) ^ 1);
-          const uint32_t sb = smem_u32(s.sb[sbs]);  // shared-space address of this tile's side band
+          const uint32_t sb = smem_u32(s.sb(sbs));  // shared-space address of this tile's side band
           const uint32_t taddr = lane_addr + buf * kBN;
 
           // consume one 32-column chunk `c` of the accumulator held in v[]
@@ -834,7 +834,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
   // straight here; a sweep CTA arrives once its share of the sweep is done (every MMA it issued has completed
   // and every tile it loaded has been consumed, so its shared memory is free) and takes the word tiles the
   // atomic counter still has.
-  if (kMode == ROW_GRAD2 && p.fed != nullptr) {
+  if constexpr (kFed) {
     tc_fence_before();
     __syncthreads();
     if (threadIdx.x == 0) {  // the sweep's mbarriers die here: the aggregation lays its own over the same bytes
@@ -896,7 +896,8 @@ static int launch_sweep(const CUtensorMap& tm_theta, const CUtensorMap& tm_beta,
   // aggregation CTAs stage (world-1) peer tiles of 16 KB per pipeline stage: give them the whole SM
   if (kMode == ROW_GRAD2 && p.fed != nullptr) plan.bytes = (size_t)max_smem;
   p.smem_bytes = (uint32_t)plan.bytes;
-  auto kern = sweep_kernel<kMode>;
+  // the aggregation role is a separate instantiation: its code in the same kernel costs the plain sweep ~25 %
+  auto kern = (kMode == ROW_GRAD2 && p.fed != nullptr) ? sweep_kernel<kMode, kMode == ROW_GRAD2> : sweep_kernel<kMode, false>;
   GF_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.bytes));
   const int total = p.n_stat * p.n_chunks;
   const int fed_ctas = (kMode == ROW_GRAD2 && p.fed != nullptr) ? p.fed_ctas : 0;

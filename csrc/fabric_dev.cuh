@@ -289,7 +289,7 @@ constexpr int kFedMaxStages = 8;
 // threads never wait on a global load: with the operands loaded into registers by the consumers themselves the
 // loop ran at ~0.5 element/ns per SM (one exposed HBM round trip per item and no second CTA on the SM to hide
 // it), which is what the exposed part of the aggregation was made of.
-__device__ __forceinline__ void fed_beta_phase_tma(const GfFedArgs& a, const GfFabricRank& me, const AdamF& h,
+static __device__ __noinline__ void fed_beta_phase_tma(const GfFedArgs& a, const GfFabricRank& me, const AdamF& h,
                                                    const FedTmaps& tm, uint8_t* smem, uint32_t smem_bytes) {
   const int world = a.world, rank = me.rank, n_remote = world - 1;
   float* tile_v = reinterpret_cast<float*>(smem);
