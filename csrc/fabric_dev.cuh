@@ -272,7 +272,7 @@ __device__ __forceinline__ void fed_beta_phase(const GfFedArgs& a, const GfFabri
 // and latecomers simply take what is left.
 //   threads 0..255   consumers
 //   thread  256      producer (claims word tiles, issues the TMA loads)
-// `smem` must be 1024-byte aligned; layout: [tile 32x132 f32][transposed staging 128 x (Kp+8) bf16]
+// `smem` must be 1024-byte aligned; layout: [2 x tile 16x132 f32][pointer table][transposed staging 128 x (Kp+8) bf16]
 // [stages x n_remote x 8 KB][item table][mbarriers].  Requires V % 8 == 0, ldb % 4 == 0, Kp % 16 == 0.
 // ---------------------------------------------------------------------------------------------------
 struct FedTmaps {
@@ -296,11 +296,14 @@ static __device__ __noinline__ void fed_beta_phase_tma(const GfFedArgs& a, const
   float(*tv)[132] = reinterpret_cast<float(*)[132]>(tile_v);  // kFedRows x 128 (+4 pad): transposition buffer
   // transposed-shadow staging: 128 words x Kp topics bf16 (rows padded by 8), flushed as whole rows
   const int ldt = a.Kp + 8;
-  __nv_bfloat16* tT = reinterpret_cast<__nv_bfloat16*>(smem + 9216);  // 16*132*4 = 8448, rounded up to 1 KB
+  // [0, 16896): two transposition buffers of 16 x 132 floats; [16896, 17408): the peers' shadow pointers
+  void** psh = reinterpret_cast<void**>(smem + 16896);
+  constexpr uint32_t kHead = 17408;
+  __nv_bfloat16* tT = reinterpret_cast<__nv_bfloat16*>(smem + kHead);
   const uint32_t tT_bytes = ((uint32_t)(128 * ldt * 2) + 1023u) & ~1023u;
-  uint8_t* ring = smem + 9216 + tT_bytes;
+  uint8_t* ring = smem + kHead + tT_bytes;
   const uint32_t stage_bytes = 3u * kFedStateBytes + (uint32_t)world * kFedGradBytes;
-  int stages = (int)((smem_bytes - 9216 - tT_bytes - 512) / stage_bytes);
+  int stages = (int)((smem_bytes - kHead - tT_bytes - 512) / stage_bytes);
   if (stages > kFedMaxStages) stages = kFedMaxStages;
   if (stages < 1) stages = 1;  // (the launcher sizes the shared memory so that this never triggers)
   int* item_wt = reinterpret_cast<int*>(ring + (size_t)stages * stage_bytes);
@@ -315,6 +318,10 @@ static __device__ __noinline__ void fed_beta_phase_tma(const GfFedArgs& a, const
     mbar_fence_init();
   }
   for (int i = threadIdx.x; i < 128 * ldt / 2; i += blockDim.x) reinterpret_cast<uint32_t*>(tT)[i] = 0u;
+  if (threadIdx.x < GF_MAX_RANKS) {
+    psh[threadIdx.x] = me.beta_bf[threadIdx.x];
+    psh[GF_MAX_RANKS + threadIdx.x] = me.betaT_bf[threadIdx.x];
+  }
   __syncthreads();  // all threads of the CTA call this function
 
   const int vt = (a.V + 127) / 128, kt = (a.K + kFedRows - 1) / kFedRows;
@@ -357,6 +364,39 @@ static __device__ __noinline__ void fed_beta_phase_tma(const GfFedArgs& a, const
   } else if (threadIdx.x < 256) {
     // ---------------- consumers: thread (ty, tx) owns words 4 tx .. 4 tx + 3 of topics ty and ty + 8 of the item
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    // Everything the loop needs from the argument blocks is copied into registers / shared memory first: both
+    // live in global memory, and with stores to global memory in the loop the compiler has to reload every field
+    // (sizes, strides, the pointer tables) in front of each use otherwise.
+    const int K = a.K, V = a.V, Kp = a.Kp, ldb = a.ldb;
+    const long long beta_off = a.beta_off;
+    float* const Pm = me.P[rank];
+    float* const Mm = me.M;
+    float* const Vm = me.V2;
+    void* const bf_mc = me.beta_bf_mc;
+    void* const bT_mc = me.betaT_bf_mc;
+    void* const* bf_tab = psh;
+    void* const* bT_tab = psh + GF_MAX_RANKS;
+    const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
+    // optimiser constants in registers (`h` is a reference into the caller's frame); Adam without weight decay, the
+    // usual case, gets a path with the two constant divisions hoisted and no solver dispatch per element.  With
+    // eight consumer warps per SM this loop is bound by instruction issue, so every instruction per element counts.
+    const AdamF hl = h;
+    const bool fast = hl.solver == GF_SOLVER_ADAM && hl.wd == 0.f;
+    const float c_b1 = hl.b1, c_b2 = hl.b2, c_omb1 = 1.f - hl.b1, c_omb2 = 1.f - hl.b2, c_eps = hl.eps;
+    const float c_inv_bc2 = __fdividef(1.f, hl.bc2_sqrt), c_nlr = -__fdividef(hl.lr, hl.bc1);
+    auto upd = [&](float p, float g, float& m, float& v) -> float {
+      if (fast) {  // same operations, in the same order, as the Adam branch of opt_update
+        m = fmaf(c_b1, m, c_omb1 * g);
+        v = fmaf(c_b2, v, c_omb2 * g * g);
+        float sq;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(v));
+        return fmaf(c_nlr, __fdividef(m, fmaf(sq, c_inv_bc2, c_eps)), p);
+      }
+      return opt_update(p, g, m, v, hl);
+    };
+    const uint32_t ring_s = smem_u32(ring), tv_s = smem_u32(tile_v), tT_s = smem_u32(tT);
+    const int cpr = Kp >> 3;  // 16-byte chunks per row of the transposed shadow
+    const int rw0 = (int)threadIdx.x / cpr, ch0 = (int)threadIdx.x % cpr, dq = 256 / cpr, dr = 256 % cpr;
     for (uint32_t it = 0;; ++it) {
       const int st = it % stages;
       mbar_wait(&full[st], (it / stages) & 1);
@@ -365,60 +405,75 @@ static __device__ __noinline__ void fed_beta_phase_tma(const GfFedArgs& a, const
       const int v0 = (t_lo + wt) * 128;
       const int vv = v0 + tx * 4;
       const int k0 = kti * kFedRows;
-      const uint8_t* sb = ring + (size_t)st * stage_bytes;
+      const uint32_t sb = ring_s + (uint32_t)st * stage_bytes;                    // shared-space addresses: LDS / STS,
+      const uint32_t tvb = tv_s + (it & 1) * (uint32_t)(kFedRows * 132 * 4);     // not generic loads and stores
 #pragma unroll
       for (int r = 0; r < kFedRows / 8; ++r) {
         const int row = ty + r * 8, k = k0 + row;
         float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (k < a.K && vv < a.V) {
+        if (k < K && vv < V) {
           const uint32_t o4 = (uint32_t)row * 512u + (uint32_t)tx * 16u;  // fp32 tiles: 512-byte rows
           const uint32_t o2 = (uint32_t)row * 256u + (uint32_t)tx * 8u;   // bf16 tiles: 256-byte rows
-          val = *reinterpret_cast<const float4*>(sb + o4);
-          float4 mm = *reinterpret_cast<const float4*>(sb + kFedStateBytes + o4);
-          float4 v2 = *reinterpret_cast<const float4*>(sb + 2 * kFedStateBytes + o4);
+          val = lds_f4(sb + o4);
+          float4 mm = lds_f4(sb + kFedStateBytes + o4);
+          float4 v2 = lds_f4(sb + 2 * kFedStateBytes + o4);
           float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
           for (int c = 0; c < world; ++c) {  // own tile first, then the peers' in rank order
-            const uint2 x = *reinterpret_cast<const uint2*>(sb + 3 * kFedStateBytes + (size_t)c * kFedGradBytes + o2);
-            const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&x);
-            const float2 lo = __bfloat1622float2(x2[0]), hi = __bfloat1622float2(x2[1]);
-            g.x += lo.x; g.y += lo.y; g.z += hi.x; g.w += hi.y;
+            const float2 xr = lds_f2(sb + 3 * kFedStateBytes + (uint32_t)c * kFedGradBytes + o2);
+            const uint32_t x0 = __float_as_uint(xr.x), x1 = __float_as_uint(xr.y);  // 4 bf16: widen by shifting
+            g.x += __uint_as_float(x0 << 16); g.y += __uint_as_float(x0 & 0xffff0000u);
+            g.z += __uint_as_float(x1 << 16); g.w += __uint_as_float(x1 & 0xffff0000u);
           }
-          const long long ip = a.beta_off + (long long)k * a.V + vv;
-          val.x = adam_upd(val.x, g.x, mm.x, v2.x, h);
-          val.y = adam_upd(val.y, g.y, mm.y, v2.y, h);
-          val.z = adam_upd(val.z, g.z, mm.z, v2.z, h);
-          val.w = adam_upd(val.w, g.w, mm.w, v2.w, h);
-          *reinterpret_cast<float4*>(me.P[rank] + ip) = val;  // master copy: owner only
-          *reinterpret_cast<float4*>(me.M + ip) = mm;
-          *reinterpret_cast<float4*>(me.V2 + ip) = v2;
-          __align__(8) __nv_bfloat16 o[4] = {__float2bfloat16(val.x), __float2bfloat16(val.y),
-                                            __float2bfloat16(val.z), __float2bfloat16(val.w)};
-          fed_push_b64(me.beta_bf, me.beta_bf_mc, (size_t)k * a.ldb + vv, *reinterpret_cast<const uint2*>(o), world);
+          const long long ip = beta_off + (long long)k * V + vv;
+          val.x = upd(val.x, g.x, mm.x, v2.x);
+          val.y = upd(val.y, g.y, mm.y, v2.y);
+          val.z = upd(val.z, g.z, mm.z, v2.z);
+          val.w = upd(val.w, g.w, mm.w, v2.w);
+          *reinterpret_cast<float4*>(Pm + ip) = val;  // master copy: owner only
+          *reinterpret_cast<float4*>(Mm + ip) = mm;
+          *reinterpret_cast<float4*>(Vm + ip) = v2;
+          uint2 o;
+          o.x = pack_bf16(val.x, val.y);
+          o.y = pack_bf16(val.z, val.w);
+          fed_push_b64(bf_tab, bf_mc, (size_t)k * ldb + vv, o, world);
         }
-        *reinterpret_cast<float4*>(&tv[row][tx * 4]) = val;
+        sts_u4(tvb + (uint32_t)(row * 132 + tx * 4) * 4u, __float_as_uint(val.x), __float_as_uint(val.y),
+               __float_as_uint(val.z), __float_as_uint(val.w));
       }
-      fed_sync256();
-      if (threadIdx.x == 0) mbar_arrive(&empty[st]);  // every consumer has read the stage and its item entry
-      // transpose this 16-topic slab into the row-major [word][topic] staging tile: thread = (word, 8 topics)
-      const int wv = threadIdx.x >> 1, half = threadIdx.x & 1;
+      fed_sync256();  // the item's values are in tvb; every consumer is done with the stage and its item entry
+      if (threadIdx.x == 0) mbar_arrive(&empty[st]);
+      // transpose this 16-topic slab into the row-major [word][topic] staging tile: thread = (word, 8 topics).
+      // (tvb is rewritten two items later, i.e. after the next item's barrier, which every thread reaches only
+      // after this read.)
       const int kb = k0 + half * 8;
-      if (kb < a.Kp) {
-        __align__(16) __nv_bfloat16 o[8];
+      if (kb < Kp) {
+        uint32_t o[4];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = __float2bfloat16(tv[half * 8 + j][wv]);
-        *reinterpret_cast<uint4*>(tT + (size_t)wv * ldt + kb) = *reinterpret_cast<const uint4*>(o);
+        for (int j = 0; j < 8; j += 2) {
+          float lo, hi;
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(lo) : "r"(tvb + (uint32_t)((half * 8 + j) * 132 + wv) * 4u));
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(hi) : "r"(tvb + (uint32_t)((half * 8 + j + 1) * 132 + wv) * 4u));
+          o[j >> 1] = pack_bf16(lo, hi);
+        }
+        sts_u4(tT_s + (uint32_t)(wv * ldt + kb) * 2u, o[0], o[1], o[2], o[3]);
       }
-      fed_sync256();
       if (kti + 1 == kt) {
+        fed_sync256();
         // flush the transposed shadow of this word tile: whole rows of Kp bf16, 16-byte pieces, consecutive
         // threads -> consecutive addresses (large NVLink packets instead of one 16-byte store per topic slab)
-        const int cpr = a.Kp >> 3;  // 16-byte chunks per row
+        // (global offsets are linear in idx; the padded staging rows need (row, chunk), stepped without a division)
+        int rw = rw0, ch = ch0;
         for (int idx = threadIdx.x; idx < 128 * cpr; idx += 256) {
-          const int rw = idx / cpr, ch = idx - rw * cpr;
-          if (v0 + rw < a.V) {
-            const uint4 q = *reinterpret_cast<const uint4*>(tT + (size_t)rw * ldt + ch * 8);
-            fed_push_b128(me.betaT_bf, me.betaT_bf_mc, (size_t)(v0 + rw) * a.Kp + ch * 8, q, world);
+          if (v0 + rw < V) {
+            uint4 q;
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w)
+                         : "r"(tT_s + (uint32_t)(rw * ldt + ch * 8) * 2u));
+            fed_push_b128(bT_tab, bT_mc, (size_t)v0 * Kp + (size_t)idx * 8, q, world);
           }
+          rw += dq;
+          ch += dr;
+          if (ch >= cpr) { ch -= cpr; ++rw; }
         }
         fed_sync256();
       }
