@@ -134,7 +134,7 @@ class FederatedTrainer:
         known = set(fl.segments) | {f"{bn}.{st}" for bn in ("inf_net.f_mu_batchnorm", "inf_net.f_sigma_batchnorm",
                                                             "beta_batchnorm")
                                     for st in ("running_mean", "running_var", "num_batches_tracked")}
-        unknown = sorted(keys - known)
+        unknown = sorted(keys - known - {"__all_stats__"})
         if unknown:
             # (the reference raises KeyError in get_gradients for such keys)
             import logging
