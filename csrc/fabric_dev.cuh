@@ -381,18 +381,9 @@ static __device__ __noinline__ void fed_beta_phase_tma(const GfFedArgs& a, const
     // usual case, gets a path with the two constant divisions hoisted and no solver dispatch per element.  With
     // eight consumer warps per SM this loop is bound by instruction issue, so every instruction per element counts.
     const AdamF hl = h;
-    const bool fast = hl.solver == GF_SOLVER_ADAM && hl.wd == 0.f;
-    const float c_b1 = hl.b1, c_b2 = hl.b2, c_omb1 = 1.f - hl.b1, c_omb2 = 1.f - hl.b2, c_eps = hl.eps;
-    const float c_inv_bc2 = __fdividef(1.f, hl.bc2_sqrt), c_nlr = -__fdividef(hl.lr, hl.bc1);
+    const OptFast hf = opt_fast(hl);
     auto upd = [&](float p, float g, float& m, float& v) -> float {
-      if (fast) {  // same operations, in the same order, as the Adam branch of opt_update
-        m = fmaf(c_b1, m, c_omb1 * g);
-        v = fmaf(c_b2, v, c_omb2 * g * g);
-        float sq;
-        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(v));
-        return fmaf(c_nlr, __fdividef(m, fmaf(sq, c_inv_bc2, c_eps)), p);
-      }
-      return opt_update(p, g, m, v, hl);
+      return hf.on ? opt_update_fast(p, g, m, v, hf) : opt_update(p, g, m, v, hl);
     };
     const uint32_t ring_s = smem_u32(ring), tv_s = smem_u32(tile_v), tT_s = smem_u32(tT);
     const int cpr = Kp >> 3;  // 16-byte chunks per row of the transposed shadow

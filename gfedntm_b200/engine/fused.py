@@ -474,7 +474,7 @@ class FusedEngine:
                     def hook():  # optimiser step of beta on the side stream (joined in optimizer_step)
                         side.wait_stream(torch.cuda.current_stream())
                         with torch.cuda.stream(side):
-                            self._adam_beta_now(gscale=1.0)
+                            self._adam_beta_now(gscale=1.0, background=os.environ.get("GFEDNTM_BG_ADAM", "1") != "0")
                         self._side_beta = True
             _, dtheta = self.decoder.forward_backward(
                 self.theta, self.theta_colsum, self.beta_bf, self.betaT_bf, batch, self.csc,
@@ -589,10 +589,17 @@ class FusedEngine:
                          eps=self.adam_eps, wd=self.weight_decay, step=self.step_count, gscale=gscale,
                          step_ctr=self.ctr, solver=self.solver)
 
-    def _adam_beta_now(self, gscale: float = 1.0) -> None:
-        """The fused optimiser step of beta + shadows; the device step counter must already hold step t."""
+    def _adam_beta_now(self, gscale: float = 1.0, background: bool = False) -> None:
+        """The fused optimiser step of beta + shadows; the device step counter must already hold step t.
+        ``background``: the variant that fits on the SMs beside the d-theta sweep (side stream)."""
         fl = self.flat
         b1, b2 = self.betas
+        if background and self.betaT_bf.shape[1] % 16 == 0:
+            K_.adam_beta_bg(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"), fl.view(fl.V2, "beta"),
+                            self.beta_bf, self.betaT_bf, K=self.K, V=self.V, lr=self.lr, b1=b1, b2=b2, eps=self.adam_eps,
+                            wd=self.weight_decay, step=self.step_count + 1, gscale=gscale, step_ctr=self.ctr,
+                            solver=self.solver, blocks_per_sm=int(os.environ.get("GFEDNTM_BG_BLOCKS", "2")))
+            return
         K_.adam_beta(fl.view(fl.P, "beta"), fl.view(fl.G, "beta"), fl.view(fl.M, "beta"), fl.view(fl.V2, "beta"),
                      self.beta_bf, self.betaT_bf, K=self.K, V=self.V, lr=self.lr, b1=b1, b2=b2, eps=self.adam_eps,
                      wd=self.weight_decay, step=self.step_count + 1, gscale=gscale, step_ctr=self.ctr, solver=self.solver)

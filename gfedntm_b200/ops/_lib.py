@@ -242,6 +242,9 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_adam_flat.argtypes = [_p, _p, _p, _p, ll, _f, _f, _f, _f, _f, _i, _f, _p, _i, _p]
     lib.gf_adam_beta.argtypes = [_p, _p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i,
                                  _f, _f, _f, _f, _f, _i, _f, _i, _p, _i, _p]
+    lib.gf_adam_beta_bg.argtypes = [_p, _p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i,
+                                    _f, _f, _f, _f, _f, _i, _f, _p, _i, _i, _p]
+    lib.gf_adam_beta_bg.restype = _i
     lib.gf_fed_aggregate.argtypes = [C.POINTER(GfFedArgs), _p]
     lib.gf_fed_aggregate.restype = _i
     lib.gf_host_gather_csr.argtypes = [_p, _p, _p, _p, _i, _p, _p, _p, ll, _i]

@@ -364,6 +364,15 @@ def adam_beta(p, g, m, v, beta_bf, betaT_bf, *, K: int, V: int, lr: float = 0.0,
                            int(do_update), _ptr(step_ctr), solver, _stream()), "gf_adam_beta")
 
 
+def adam_beta_bg(p, g, m, v, beta_bf, betaT_bf, *, K: int, V: int, lr: float, b1: float, b2: float, eps: float,
+                 wd: float = 0.0, step: int = 1, gscale: float = 1.0, step_ctr=None, solver: int = 0,
+                 blocks_per_sm: int = 2) -> None:
+    """``adam_beta`` for the stream that runs next to the d-theta sweep (no shared memory, small register footprint)."""
+    check(_lib.load().gf_adam_beta_bg(_ptr(p), _ptr(g), _ptr(m), _ptr(v), K, V, p.stride(0), g.stride(0), _ptr(beta_bf),
+                                      beta_bf.stride(0), _ptr(betaT_bf), betaT_bf.shape[1], lr, b1, b2, eps, wd, step,
+                                      gscale, _ptr(step_ctr), solver, blocks_per_sm, _stream()), "gf_adam_beta_bg")
+
+
 # ----------------------------------------------------------------------------------------------
 # CombinedTM: collapsed adapt_bert layer (csrc/ctm_gemm.cu)
 # ----------------------------------------------------------------------------------------------

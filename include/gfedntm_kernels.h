@@ -335,6 +335,12 @@ int gf_adam_flat(float* p, const float* g, float* m, float* v, long long n, floa
 int gf_adam_beta(float* p, const float* g, float* m, float* v, int K, int V, int ldp, int ldg,
                  void* beta_bf, int ldb, void* betaT_bf, int Kp, float lr, float b1, float b2, float eps,
                  float wd, int step, float gscale, int do_update, const long long* step_ctr, int solver, void* stream);
+/* The same update for a caller that runs it on a second stream NEXT TO GF_ROW_GRAD2: no shared memory, <= 64
+ * registers x 128 threads, `blocks_per_sm` (default 2) persistent blocks per SM, streaming cache hints. */
+int gf_adam_beta_bg(float* p, const float* g, float* m, float* v, int K, int V, int ldp, int ldg,
+                    void* beta_bf, int ldb, void* betaT_bf, int Kp, float lr, float b1, float b2, float eps,
+                    float wd, int step, float gscale, const long long* step_ctr, int solver, int blocks_per_sm,
+                    void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Skinny tcgen05 GEMMs of the CombinedTM encoder (csrc/ctm_gemm.cu): the adapt_bert layer collapsed into the
