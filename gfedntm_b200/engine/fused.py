@@ -408,7 +408,8 @@ class FusedEngine:
     def forward_backward(self, batch: CsrBatch, x_ctx: Optional[torch.Tensor] = None, *,
                          training: bool = True, sample: bool = True, gscale: float = 1.0,
                          need_grad: bool = True, eps_in=None, mask_enc_in=None, mask_theta_in=None, fed=None,
-                         ctm_reduce_hook=None, labels: Optional[torch.Tensor] = None, side_stream: bool = False):
+                         ctm_reduce_hook=None, labels: Optional[torch.Tensor] = None, side_stream: bool = False,
+                         inc_opt: int = 0):
         """Runs forward (and backward when ``need_grad``); returns the device scalar
         ``loss = sum_b (kl_weight*KL_b + RL_b)`` (float64, shape [1])."""
         B, K, V = batch.B, self.K, self.V
@@ -416,12 +417,16 @@ class FusedEngine:
             raise ValueError("minibatch exceeds the engine workspace (max_batch / max_nnz)")
         grad = need_grad and training
         seed = (self.seed * 0x9E3779B97F4A7C15 + 1) & ((1 << 64) - 1)
-        K_.step_begin(self.ctr, 1, 0)
-        self.zpool.zero_()
-        self.dpool.zero_()
+        # step counter + every zero fill of the step in one launch (the column sums of the decoder included)
+        zero = [self.zpool, self.dpool]
+        if grad:
+            zero.append(self.flat.G[:self.flat.small_end])
+            if self.is_prod:
+                zero.append(self.decoder.asp_csp)
+        # (inc_opt = 1: the caller wants the optimiser-step counter advanced here too, see train_step)
+        K_.step_begin_zero(self.ctr, 1, inc_opt, zero)
         side = self._side if (grad and side_stream and self.is_prod and self.decoder.folded) else None
         if grad:
-            self.flat.G[:self.flat.small_end].zero_()
             if side is not None:
                 side.wait_stream(torch.cuda.current_stream())
                 with torch.cuda.stream(side):
@@ -480,7 +485,7 @@ class FusedEngine:
                 self.theta, self.theta_colsum, self.beta_bf, self.betaT_bf, batch, self.csc,
                 training=training, running_mean=bbn.running_mean, running_var=bbn.running_var,
                 dbeta=self._g("beta") if grad else None, loss=self.loss, gscale=gscale, need_grad=grad,
-                fed=fed if (grad and self.decoder.folded) else None, on_dbeta_final=hook)
+                fed=fed if (grad and self.decoder.folded) else None, on_dbeta_final=hook, sums_zeroed=grad)
         else:
             beta = self._p("beta")
             K_.lda_beta_fwd(beta, K=K, V=V, eps=BN_EPS, momentum=BN_MOMENTUM, training=training,
@@ -554,12 +559,12 @@ class FusedEngine:
     # ------------------------------------------------------------------------------------------
     # optimiser
     # ------------------------------------------------------------------------------------------
-    def optimizer_step(self, gscale: float = 1.0, beta_done: bool = False) -> None:
+    def optimizer_step(self, gscale: float = 1.0, beta_done: bool = False, ctr_done: bool = False) -> None:
         """Fused Adam over the flat buffers; refreshes the bf16 shadows of beta.  ``beta_done``: the step counter was
         advanced and beta updated already (overlapped with the d-theta sweep, see ``train_step``)."""
         if not torch.cuda.is_current_stream_capturing():
             self.step_count += 1
-        if not beta_done:
+        if not (beta_done or ctr_done):
             K_.step_begin(self.ctr, 0, 1)
         fl = self.flat
         b1, b2 = self.betas
@@ -625,17 +630,17 @@ class FusedEngine:
         graph per (input buffers, batch size) and replayed: the first call on a new key runs eagerly
         (warm-up), the second captures, later ones replay.  Injected noise/masks force the eager path."""
         def body():
+            # the optimiser-step counter advances with the first launch of the step (inc_opt=1): the update of beta
+            # inside / beside the d-theta sweep reads step t, and the step saves a launch
             if self._self_overlap is not None:
-                K_.step_begin(self.ctr, 0, 1)  # step t first: the update CTAs inside the d-theta sweep read it
-                self.forward_backward(batch, x_ctx, training=True, fed=self._self_overlap, labels=labels, **kw)
-                self.optimizer_step(beta_done=True)
+                self.forward_backward(batch, x_ctx, training=True, fed=self._self_overlap, labels=labels, inc_opt=1, **kw)
+                self.optimizer_step(beta_done=True, ctr_done=True)
             elif self._side is not None and self.is_prod and self.decoder.folded:
-                K_.step_begin(self.ctr, 0, 1)  # step t first: beta is stepped on the side stream during the backward
-                self.forward_backward(batch, x_ctx, training=True, labels=labels, side_stream=True, **kw)
-                self.optimizer_step(beta_done=True)
+                self.forward_backward(batch, x_ctx, training=True, labels=labels, side_stream=True, inc_opt=1, **kw)
+                self.optimizer_step(beta_done=True, ctr_done=True)
             else:
-                self.forward_backward(batch, x_ctx, training=True, labels=labels, **kw)
-                self.optimizer_step()
+                self.forward_backward(batch, x_ctx, training=True, labels=labels, inc_opt=1, **kw)
+                self.optimizer_step(ctr_done=True)
 
         if kw or not self.use_graphs:
             body()

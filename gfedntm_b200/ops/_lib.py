@@ -228,6 +228,8 @@ def _declare(lib: C.CDLL) -> None:
     lib.gf_csr_to_csc.argtypes = [_p, _p, _i, _i, _i, _p, _p, _p, _p, _p]
     lib.gf_step_begin.argtypes = [_p, _i, _i, _p]
     lib.gf_step_begin.restype = _i
+    lib.gf_step_begin_zero.argtypes = [_p, _i, _i, C.POINTER(C.c_void_p), C.POINTER(C.c_longlong), _i, _p]
+    lib.gf_step_begin_zero.restype = _i
     lib.gf_csr_to_csc_dyn.argtypes = [_p, _p, _i, _i, _i, _p, _p, _p, _p, _p]
     lib.gf_csr_to_csc_dyn.restype = _i
     lib.gf_csr_to_csc_static.argtypes = [_p, _p, _i, _i, _i, _p, _p, _p, _p]

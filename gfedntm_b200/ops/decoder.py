@@ -135,7 +135,7 @@ class ProdLDADecoder:
                          training: bool, running_mean: Optional[torch.Tensor],
                          running_var: Optional[torch.Tensor], dbeta: Optional[torch.Tensor],
                          loss: Optional[torch.Tensor], gscale: float = 1.0, need_grad: bool = True, fed=None,
-                         on_dbeta_final=None):
+                         on_dbeta_final=None, sums_zeroed: bool = False):
         """Runs the sweeps.  Returns (rl[B], dtheta[B,Kp] or None).  ``dbeta`` [K,ld] is overwritten.
 
         ``fed`` (folded formulation only): an object with ``signal_beta_ready()``, ``dev_args`` (device
@@ -147,7 +147,7 @@ class ProdLDADecoder:
         if not self.folded:
             return self._forward_backward_v1(theta, theta_colsum, beta_bf, betaT_bf, batch, csc, training=training,
                                              running_mean=running_mean, running_var=running_var, dbeta=dbeta,
-                                             loss=loss, gscale=gscale, need_grad=need_grad)
+                                             loss=loss, gscale=gscale, need_grad=need_grad, sums_zeroed=sums_zeroed)
         tcols = self.thetaT_bf.shape[1]
         K_.theta_center_fold(theta, theta_colsum, self.theta_bf, self.thetaT_bf, self.theta_mean, B=B, K=Kt,
                              Bpad=round_up(B, TILE), center=training)
@@ -164,7 +164,7 @@ class ProdLDADecoder:
                      n_chunks=n_chunks, lse_part=self.lse_part, theta_cols=tcols, beta_cols=self.Vpad)
         bcols = self.beta_s.shape[1]
         grad = need_grad and training
-        if grad:
+        if grad and not sums_zeroed:  # (the engine zeroes the column sums with its other fills)
             self.asp_csp.zero_()
         K_.dec_sparse_doc(B=B, n_chunks=n_chunks, indptr=batch.indptr, indices=batch.indices,
                           counts=batch.counts, theta_bf=self.theta_bf, betaT_bf=betaT_bf, colc=self.colc,
@@ -203,7 +203,7 @@ class ProdLDADecoder:
         return self.rl[:B], self.dtheta[:B]
 
     def _forward_backward_v1(self, theta, theta_colsum, beta_bf, betaT_bf, batch, csc, *, training,
-                             running_mean, running_var, dbeta, loss, gscale, need_grad):
+                             running_mean, running_var, dbeta, loss, gscale, need_grad, sums_zeroed=False):
         """Earlier formulation: epilogue constants through the float4 side bands."""
         B, V, Kt = batch.B, self.V, self.K
         K_.theta_center(theta, theta_colsum, self.theta_bf, self.thetaT_bf, self.theta_mean, B=B, K=Kt,
@@ -217,7 +217,7 @@ class ProdLDADecoder:
         K_.dec_sweep(K_.ROW_LSE, B=B, V=V, K=Kt, theta_bf=self.thetaT_bf, beta_bf=beta_bf,
                      sb_stream=self.colc, n_chunks=n_chunks, lse_part=self.lse_part)
         grad = need_grad and training
-        if grad:
+        if grad and not sums_zeroed:  # (the engine zeroes the column sums with its other fills)
             self.asp_csp.zero_()
         K_.dec_sparse_doc(B=B, n_chunks=n_chunks, indptr=batch.indptr, indices=batch.indices,
                           counts=batch.counts, theta_bf=self.theta_bf, betaT_bf=betaT_bf, colc=self.colc,

@@ -264,6 +264,18 @@ def csr_to_csc(indptr, indices, *, B: int, V: int, nnz: int, colptr, cursor, csc
              _stream()), "gf_csr_to_csc")
 
 
+def step_begin_zero(ctr, inc_rng: int, inc_opt: int, buffers) -> None:
+    """``step_begin`` and the zero fill of ``buffers`` (contiguous tensors, at most 6) in one launch."""
+    import ctypes as C
+
+    bufs = [b for b in buffers if b is not None and b.numel() > 0]
+    assert len(bufs) <= 6 and all(b.is_contiguous() for b in bufs)
+    ptrs = (C.c_void_p * max(len(bufs), 1))(*[b.data_ptr() for b in bufs])
+    nbytes = (C.c_longlong * max(len(bufs), 1))(*[b.numel() * b.element_size() for b in bufs])
+    check(_lib.load().gf_step_begin_zero(_ptr(ctr), inc_rng, inc_opt, ptrs, nbytes, len(bufs), _stream()),
+          "gf_step_begin_zero")
+
+
 def step_begin(ctr: torch.Tensor, inc_rng: int = 1, inc_opt: int = 0) -> None:
     lib = _lib.load()
     check(lib.gf_step_begin(_ptr(ctr), inc_rng, inc_opt, _stream()), "gf_step_begin")

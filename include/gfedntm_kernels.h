@@ -147,6 +147,11 @@ typedef struct GfEncArgs {
  * ctr[0] counts forward passes (advances the dropout / reparameterisation seeds), ctr[1] counts
  * optimiser steps (Adam bias correction, federated epoch flag).                                  */
 int gf_step_begin(long long* ctr, int inc_rng, int inc_opt, void* stream);
+/* gf_step_begin (ctr may be null) and the zero fill of up to GF_ZERO_MAX buffers (16-byte aligned, sizes % 4 == 0;
+ * `ptrs` / `bytes` are HOST arrays) in one launch. */
+#define GF_ZERO_MAX 6
+int gf_step_begin_zero(long long* ctr, int inc_rng, int inc_opt, void* const* ptrs, const long long* bytes, int n,
+                       void* stream);
 int gf_enc_fwd(const GfEncArgs* args, void* stream);
 
 /* Supervised CTM (label_size > 0; ref: ctm_network/inference_network.py:79-94,178-183, decoding_network.py:84-85,
