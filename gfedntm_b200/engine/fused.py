@@ -409,7 +409,7 @@ class FusedEngine:
                          training: bool = True, sample: bool = True, gscale: float = 1.0,
                          need_grad: bool = True, eps_in=None, mask_enc_in=None, mask_theta_in=None, fed=None,
                          ctm_reduce_hook=None, labels: Optional[torch.Tensor] = None, side_stream: bool = False,
-                         inc_opt: int = 0):
+                         inc_opt: int = 0, beta_on_side: bool = False):
         """Runs forward (and backward when ``need_grad``); returns the device scalar
         ``loss = sum_b (kl_weight*KL_b + RL_b)`` (float64, shape [1])."""
         B, K, V = batch.B, self.K, self.V
@@ -425,7 +425,9 @@ class FusedEngine:
                 zero.append(self.decoder.asp_csp)
         # (inc_opt = 1: the caller wants the optimiser-step counter advanced here too, see train_step)
         K_.step_begin_zero(self.ctr, 1, inc_opt, zero)
-        side = self._side if (grad and side_stream and self.is_prod and self.decoder.folded) else None
+        # side stream: the CSC transpose of the batch (needed by the backward pass only) runs next to the encoder
+        # forward; with beta_on_side also beta's optimiser step, beside the d-theta sweep (folded decoder)
+        side = self._side if (grad and side_stream) else None
         if grad:
             if side is not None:
                 side.wait_stream(torch.cuda.current_stream())
@@ -471,11 +473,12 @@ class FusedEngine:
         if training and not torch.cuda.is_current_stream_capturing():
             self._nbt_pending += 1  # BatchNorm step counters are flushed lazily (state_dict hook)
 
+        if side is not None:
+            torch.cuda.current_stream().wait_stream(side)   # the CSC transpose is needed from here on
         if self.is_prod:
             hook = None
             if side is not None:
-                torch.cuda.current_stream().wait_stream(side)   # the CSC transpose is needed from here on
-                if fed is None:
+                if fed is None and beta_on_side and self.decoder.folded:
                     def hook():  # optimiser step of beta on the side stream (joined in optimizer_step)
                         side.wait_stream(torch.cuda.current_stream())
                         with torch.cuda.stream(side):
@@ -636,10 +639,12 @@ class FusedEngine:
                 self.forward_backward(batch, x_ctx, training=True, fed=self._self_overlap, labels=labels, inc_opt=1, **kw)
                 self.optimizer_step(beta_done=True, ctr_done=True)
             elif self._side is not None and self.is_prod and self.decoder.folded:
-                self.forward_backward(batch, x_ctx, training=True, labels=labels, side_stream=True, inc_opt=1, **kw)
+                self.forward_backward(batch, x_ctx, training=True, labels=labels, side_stream=True, inc_opt=1,
+                                      beta_on_side=True, **kw)
                 self.optimizer_step(beta_done=True, ctr_done=True)
             else:
-                self.forward_backward(batch, x_ctx, training=True, labels=labels, inc_opt=1, **kw)
+                self.forward_backward(batch, x_ctx, training=True, labels=labels, inc_opt=1,
+                                      side_stream=self._side is not None, **kw)
                 self.optimizer_step(ctr_done=True)
 
         if kw or not self.use_graphs:

@@ -215,23 +215,24 @@ class FederatedTrainer:
         if self._overlap is not None and self.agg == "grad":
             self._beta_master_partial = True
 
+        side = eng._side is not None   # CSC transpose of the batch on the engine's side stream
+
         def body():
             if self.agg == "grad" and self._overlap is not None:
-                K_.step_begin(eng.ctr, 0, 1)  # epoch / Adam step t first: the overlapped part reads it too
-                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], fed=self._overlap, labels=labels)
+                # (inc_opt=1: epoch / Adam step t is set by the first launch of the step; the overlapped part reads it)
+                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], fed=self._overlap,
+                                     labels=labels, inc_opt=1, side_stream=side)
                 if after_backward is not None:
                     after_backward()
                 self._launch("grad", eng.step_count + 1, parts=1)
             elif self.agg == "grad":
                 hook = None
-                if self._ctm_trick:
-                    K_.step_begin(eng.ctr, 0, 1)  # the small all-reduce inside the backward pass uses epoch t
+                if self._ctm_trick:  # (the small all-reduce inside the backward pass uses epoch t)
                     hook = lambda buf: self.aggregator.allreduce_small(buf, eng.ctr)  # noqa: E731
-                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], ctm_reduce_hook=hook, labels=labels)
+                eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], ctm_reduce_hook=hook,
+                                     labels=labels, inc_opt=1, side_stream=side)
                 if after_backward is not None:
                     after_backward()
-                if not self._ctm_trick:
-                    K_.step_begin(eng.ctr, 0, 1)
                 if not self.beta_shared:  # beta stays client-local: its own Adam on the unweighted gradient
                     eng.optimizer_step_beta(gscale=1.0 / max(self.weights[self.rank], 1e-30))
                 self._launch("grad", eng.step_count + 1)
@@ -241,8 +242,8 @@ class FederatedTrainer:
                     eng._refresh_ctm_shadows()
                 eng._refresh_ctx_shadows()
             else:
-                eng.forward_backward(bow, x_ctx, training=True, labels=labels)
-                eng.optimizer_step()
+                eng.forward_backward(bow, x_ctx, training=True, labels=labels, inc_opt=1, side_stream=side)
+                eng.optimizer_step(ctr_done=True)
                 if after_backward is not None:
                     after_backward()
                 self._launch("param", eng.step_count)
