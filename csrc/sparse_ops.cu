@@ -454,44 +454,92 @@ __global__ void __launch_bounds__(1024) lda_row_softmax_kernel(const float* __re
   const float inv = 1.f / s;
   for (int v = threadIdx.x; v < V; v += blockDim.x) bp[(size_t)k * V + v] = __expf(x[v] - m) * inv;
 }
-// Stage 3 (one warp per document): wd = theta . beta'[:,v] at the non-zeros; RL; d theta;
-// g[e] = -gscale * x / (wd + 1e-10) kept for the d beta' scatter.
+// Stage 3: wd = theta . beta'[:,v] at the non-zeros; RL; d theta; g[e] = -gscale * x / (wd + 1e-10) kept for the
+// d beta' scatter.  kWpd warps per document (8 at small batches, where one warp per document left most SMs idle),
+// four non-zeros in flight per warp: a column of beta' [K,V] is K different cache lines, and one non-zero at a
+// time was a chain of nnz dependent L2 round trips (118 us at B=64, K=50, V=20k).
+template <int kWpd>
 __global__ void __launch_bounds__(256) lda_doc_kernel(const int* __restrict__ indptr, const int* __restrict__ indices,
                                                       const float* __restrict__ counts, const float* __restrict__ theta,
                                                       const float* __restrict__ bp /*[K,V]*/, int B, int K, int V,
                                                       float gscale, float* __restrict__ rl, double* __restrict__ loss,
                                                       float* __restrict__ dtheta, int ld_dtheta,
                                                       float* __restrict__ gnnz) {
-  const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (b >= B) return;
-  float th[kMaxKp / 32], dth[kMaxKp / 32];
+  constexpr int kDpb = 8 / kWpd;
+  constexpr int kC = kMaxKp / 32;
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int dslot = wib / kWpd, sub = wib % kWpd;
+  const int b = blockIdx.x * kDpb + dslot;
+  const bool live = b < B;
+  __shared__ float dred[8][kMaxKp];
+  __shared__ float rred[8];
+  float th[kC], dth[kC];
 #pragma unroll
-  for (int c = 0; c < kMaxKp / 32; ++c) {
+  for (int c = 0; c < kC; ++c) {
     const int k = c * 32 + lane;
-    th[c] = (k < K) ? theta[(size_t)b * K + k] : 0.f;
+    th[c] = (live && k < K) ? theta[(size_t)b * K + k] : 0.f;
     dth[c] = 0.f;
   }
   float r = 0.f;
-  for (int e = indptr[b]; e < indptr[b + 1]; ++e) {
-    const int v = indices[e];
-    const float x = counts[e];
-    float bv[kMaxKp / 32], dot = 0.f;
+  if (live) {
+    const int e0 = indptr[b], e1 = indptr[b + 1];
+    for (int base = e0 + sub * 4; base < e1; base += 4 * kWpd) {
+      int v[4];
+      float x[4], bv[4][kC], dot[4];
 #pragma unroll
-    for (int c = 0; c < kMaxKp / 32; ++c) {
-      const int k = c * 32 + lane;
-      bv[c] = (k < K) ? __ldg(bp + (size_t)k * V + v) : 0.f;
-      dot = fmaf(th[c], bv[c], dot);
+      for (int u = 0; u < 4; ++u) {
+        const bool ok = base + u < e1;
+        v[u] = ok ? indices[base + u] : 0;
+        x[u] = ok ? counts[base + u] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int c = 0; c < kC; ++c) {
+          const int k = c * 32 + lane;
+          bv[u][c] = (k < K) ? __ldg(bp + (size_t)k * V + v[u]) : 0.f;
+        }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float d = 0.f;
+#pragma unroll
+        for (int c = 0; c < kC; ++c) d = fmaf(th[c], bv[u][c], d);
+        dot[u] = warp_sum(d);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (base + u < e1) {
+          r -= x[u] * __logf(dot[u] + 1e-10f);
+          const float g = -gscale * x[u] / (dot[u] + 1e-10f);
+          if (lane == 0 && gnnz != nullptr) gnnz[base + u] = g;
+#pragma unroll
+          for (int c = 0; c < kC; ++c) dth[c] = fmaf(g, bv[u][c], dth[c]);
+        }
+      }
     }
-    dot = warp_sum(dot);
-    r -= x * __logf(dot + 1e-10f);
-    const float g = -gscale * x / (dot + 1e-10f);
-    if (lane == 0 && gnnz != nullptr) gnnz[e] = g;
-#pragma unroll
-    for (int c = 0; c < kMaxKp / 32; ++c) dth[c] = fmaf(g, bv[c], dth[c]);
   }
+  if (kWpd > 1) {
+    if (lane == 0) rred[wib] = r;
+#pragma unroll
+    for (int c = 0; c < kC; ++c) dred[wib][c * 32 + lane] = dth[c];
+    __syncthreads();
+    if (sub == 0) {
+      r = 0.f;
+#pragma unroll
+      for (int u = 0; u < kWpd; ++u) r += rred[wib + u];
+#pragma unroll
+      for (int c = 0; c < kC; ++c) {
+        float acc = 0.f;
+#pragma unroll
+        for (int u = 0; u < kWpd; ++u) acc += dred[wib + u][c * 32 + lane];
+        dth[c] = acc;
+      }
+    }
+  }
+  if (!live || sub != 0) return;
   if (dtheta != nullptr) {
 #pragma unroll
-    for (int c = 0; c < kMaxKp / 32; ++c) {
+    for (int c = 0; c < kC; ++c) {
       const int k = c * 32 + lane;
       if (k < ld_dtheta) dtheta[(size_t)b * ld_dtheta + k] = (k < K) ? dth[c] : 0.f;
     }
@@ -689,7 +737,11 @@ extern "C" int gf_lda_doc(const int* indptr, const int* indices, const float* co
                           int ld_dtheta, float* gnnz, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   GF_ARG_CHECK(K <= kMaxKp && ld_dtheta <= kMaxKp, "K");
-  lda_doc_kernel<<<(B * 32 + 255) / 256, 256, 0, st>>>(indptr, indices, counts, theta, bp, B, K, V, gscale, rl, loss,
+  if (B <= 512)
+    lda_doc_kernel<8><<<B, 256, 0, st>>>(indptr, indices, counts, theta, bp, B, K, V, gscale, rl, loss,
+                                        dtheta, ld_dtheta, gnnz);
+  else
+    lda_doc_kernel<1><<<(B + 7) / 8, 256, 0, st>>>(indptr, indices, counts, theta, bp, B, K, V, gscale, rl, loss,
                                                        dtheta, ld_dtheta, gnnz);
   GF_LAUNCHED();
   return GF_OK;
