@@ -216,12 +216,16 @@ class FederatedTrainer:
             self._beta_master_partial = True
 
         side = eng._side is not None   # CSC transpose of the batch on the engine's side stream
+        key = ("fed", self.agg, bow.indptr.data_ptr(), bow.indices.data_ptr(), bow.B,
+               x_ctx.data_ptr() if x_ctx is not None else 0, labels.data_ptr() if labels is not None else 0)
+        # the step's graph also copies the loss to a pinned host slot (engine.loss_slot), behind the forward pass
+        eng.loss_slot = slot = eng.loss_slot_for(key if after_backward is None else "eager")
 
         def body():
             if self.agg == "grad" and self._overlap is not None:
                 # (inc_opt=1: epoch / Adam step t is set by the first launch of the step; the overlapped part reads it)
                 eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], fed=self._overlap,
-                                     labels=labels, inc_opt=1, side_stream=side)
+                                     labels=labels, inc_opt=1, side_stream=side, loss_host=slot)
                 if after_backward is not None:
                     after_backward()
                 self._launch("grad", eng.step_count + 1, parts=1)
@@ -230,7 +234,7 @@ class FederatedTrainer:
                 if self._ctm_trick:  # (the small all-reduce inside the backward pass uses epoch t)
                     hook = lambda buf: self.aggregator.allreduce_small(buf, eng.ctr)  # noqa: E731
                 eng.forward_backward(bow, x_ctx, training=True, gscale=self.weights[self.rank], ctm_reduce_hook=hook,
-                                     labels=labels, inc_opt=1, side_stream=side)
+                                     labels=labels, inc_opt=1, side_stream=side, loss_host=slot)
                 if after_backward is not None:
                     after_backward()
                 if not self.beta_shared:  # beta stays client-local: its own Adam on the unweighted gradient
@@ -242,21 +246,20 @@ class FederatedTrainer:
                     eng._refresh_ctm_shadows()
                 eng._refresh_ctx_shadows()
             else:
-                eng.forward_backward(bow, x_ctx, training=True, labels=labels, inc_opt=1, side_stream=side)
+                eng.forward_backward(bow, x_ctx, training=True, labels=labels, inc_opt=1, side_stream=side, loss_host=slot)
                 eng.optimizer_step(ctr_done=True)
                 if after_backward is not None:
                     after_backward()
                 self._launch("param", eng.step_count)
                 eng._refresh_ctm_shadows()
                 eng._refresh_ctx_shadows()
+            eng.join_side()
 
         if not eng.use_graphs or after_backward is not None:
             body()
             if self.agg == "grad":
                 eng.step_count += 1
             return eng.loss
-        key = ("fed", self.agg, bow.indptr.data_ptr(), bow.indices.data_ptr(), bow.B,
-               x_ctx.data_ptr() if x_ctx is not None else 0, labels.data_ptr() if labels is not None else 0)
         eager_warmup = key not in eng._warm
         loss = eng.run_graphed(key, body, n_opt_steps=1)
         if eager_warmup and self.agg == "grad":

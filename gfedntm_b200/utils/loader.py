@@ -158,21 +158,39 @@ class CsrMinibatchLoader:
             lab = slot.lab_h[:n].clone() if slot.lab_h is not None else None
         return Minibatch(bow, ctx, lab, rows64, h2d)
 
-    def __iter__(self) -> Iterator[Minibatch]:
+    def _epoch_rows(self) -> Iterator[np.ndarray]:
         order = self.rng.permutation(self.N) if self.shuffle else np.arange(self.N)
         starts = list(range(0, self.N, self.batch_size))
         if self.drop_last and starts and self.N - starts[-1] < self.batch_size:
             starts.pop()
+        for s in starts:
+            yield order[s:s + self.batch_size]
+
+    def _rows(self, endless: bool) -> Iterator[np.ndarray]:
+        while True:
+            yield from self._epoch_rows()
+            if not endless:
+                return
+
+    def __iter__(self) -> Iterator[Minibatch]:
+        return self._iterate(self._rows(False))
+
+    def cycle(self) -> Iterator[Minibatch]:
+        """Endless iteration, a new permutation per epoch: the staging pipeline (worker thread, H2D copies two batches
+        ahead) keeps running across epoch boundaries instead of draining and restarting at every epoch."""
+        return self._iterate(self._rows(True))
+
+    def _iterate(self, rows_iter: Iterator[np.ndarray]) -> Iterator[Minibatch]:
         if self.prefetch:
-            yield from self._iter_prefetch(order, starts)
+            yield from self._iter_prefetch(rows_iter)
             return
         pending = None
-        for i, s in enumerate(starts):
+        for i, rows in enumerate(rows_iter):
             slot = self.slots[i & 1]
             if self.device.type == "cuda":
                 # the slot's device buffers were last read by the step two batches ago
                 self.copy_stream.wait_stream(torch.cuda.current_stream(self.device))
-            mb = self._stage(slot, order[s:s + self.batch_size])
+            mb = self._stage(slot, rows)
             if pending is not None:
                 yield pending
             if self.device.type == "cuda":
@@ -182,7 +200,7 @@ class CsrMinibatchLoader:
             yield pending
 
     # -- background staging: the worker is at most two batches ahead (one queued, one being assembled)
-    def _iter_prefetch(self, order: np.ndarray, starts) -> Iterator[Minibatch]:
+    def _iter_prefetch(self, rows_iter: Iterator[np.ndarray]) -> Iterator[Minibatch]:
         q: "queue.Queue" = queue.Queue(maxsize=1)
         stop = threading.Event()
         dev = self.device
@@ -190,14 +208,14 @@ class CsrMinibatchLoader:
         def worker() -> None:
             try:
                 torch.cuda.set_device(dev)
-                for i, s in enumerate(starts):
+                for i, rows in enumerate(rows_iter):
                     slot = self.slots[i % 3]
                     while not slot.free.wait(0.05):
                         if stop.is_set():
                             return
                     if slot.consumed is not None:
                         self.copy_stream.wait_event(slot.consumed)  # the step that read this slot is queued
-                    mb = self._stage(slot, order[s:s + self.batch_size])
+                    mb = self._stage(slot, rows)
                     while True:
                         if stop.is_set():
                             return

@@ -150,6 +150,16 @@ def test_loader_batches_cover_corpus_and_match_dense():
     assert sorted(seen) == list(range(101))
     assert len(CsrMinibatchLoader(ds, 32, drop_last=True)) == 3
     np.testing.assert_array_equal(ds[5]["X"].numpy(), X[5])
+    # endless iteration: every epoch is a permutation of the corpus, the iterator never ends
+    it = CsrMinibatchLoader(ds, 32, shuffle=True, seed=3).cycle()
+    epochs = [[], []]
+    for b in range(8):           # 4 batches per epoch (32 + 32 + 32 + 5)
+        mb = next(it)
+        np.testing.assert_array_equal(mb.bow.to_dense().numpy(), X[mb.index])
+        epochs[b // 4].extend(mb.index.tolist())
+    it.close()
+    assert sorted(epochs[0]) == list(range(101)) and sorted(epochs[1]) == list(range(101))
+    assert epochs[0] != epochs[1]
 
 
 def test_tensor_and_model_serialisation_roundtrip():
