@@ -270,7 +270,31 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) 
       rv[kk] = (1.f - a.bn_momentum) * rv[kk] + a.bn_momentum * (float)unb;
     }
   }
-  if (b >= a.B) return;
+  // BatchNorm constants of both heads once per block (shared memory) instead of four fp64 loads and the fp64
+  // arithmetic per element; column sums of theta are combined per block before they go to global memory
+  // (one atomic per topic and block instead of one per element on only K addresses).
+  __shared__ float s_stat[4][kMaxH];
+  __shared__ float s_cs[kMaxH];
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    float mmean, mrstd, smean, srstd;
+    if (a.training) {
+      const double m1 = a.bn_sums[k] * invB;
+      double v1 = a.bn_sums[K + k] * invB - m1 * m1;
+      const double m2 = a.bn_sums[2 * K + k] * invB;
+      double v2 = a.bn_sums[3 * K + k] * invB - m2 * m2;
+      if (v1 < 0) v1 = 0;
+      if (v2 < 0) v2 = 0;
+      mmean = (float)m1; mrstd = rsqrtf((float)v1 + a.bn_eps);
+      smean = (float)m2; srstd = rsqrtf((float)v2 + a.bn_eps);
+    } else {
+      mmean = a.mu_rm[k]; mrstd = rsqrtf(a.mu_rv[k] + a.bn_eps);
+      smean = a.ls_rm[k]; srstd = rsqrtf(a.ls_rv[k] + a.bn_eps);
+    }
+    s_stat[0][k] = mmean; s_stat[1][k] = mrstd; s_stat[2][k] = smean; s_stat[3][k] = srstd;
+    s_cs[k] = 0.f;
+  }
+  __syncthreads();
+  const bool live = b < a.B;
 
   float z[kMaxH / 32], mu[kMaxH / 32], lv[kMaxH / 32], ep[kMaxH / 32];
   float zmax = -INFINITY;
@@ -278,23 +302,9 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) 
   for (int c = 0; c < kMaxH / 32; ++c) {
     const int k = c * 32 + lane;
     z[c] = -INFINITY; mu[c] = 0.f; lv[c] = 0.f; ep[c] = 0.f;
-    if (k < K) {
-      float mmean, mrstd, smean, srstd;
-      if (a.training) {
-        const double m1 = a.bn_sums[k] * invB;
-        double v1 = a.bn_sums[K + k] * invB - m1 * m1;
-        const double m2 = a.bn_sums[2 * K + k] * invB;
-        double v2 = a.bn_sums[3 * K + k] * invB - m2 * m2;
-        if (v1 < 0) v1 = 0;
-        if (v2 < 0) v2 = 0;
-        mmean = (float)m1; mrstd = rsqrtf((float)v1 + a.bn_eps);
-        smean = (float)m2; srstd = rsqrtf((float)v2 + a.bn_eps);
-      } else {
-        mmean = a.mu_rm[k]; mrstd = rsqrtf(a.mu_rv[k] + a.bn_eps);
-        smean = a.ls_rm[k]; srstd = rsqrtf(a.ls_rv[k] + a.bn_eps);
-      }
-      mu[c] = (a.mu_pre[(size_t)b * K + k] - mmean) * mrstd;
-      lv[c] = (a.ls_pre[(size_t)b * K + k] - smean) * srstd;
+    if (live && k < K) {
+      mu[c] = (a.mu_pre[(size_t)b * K + k] - s_stat[0][k]) * s_stat[1][k];
+      lv[c] = (a.ls_pre[(size_t)b * K + k] - s_stat[2][k]) * s_stat[3][k];
       float e;
       if (a.eps_in != nullptr) {
         e = a.eps_in[(size_t)b * K + k];
@@ -315,7 +325,7 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) 
 #pragma unroll
   for (int c = 0; c < kMaxH / 32; ++c) {
     const int k = c * 32 + lane;
-    if (k < K) { z[c] = __expf(z[c] - zmax); zs += z[c]; }
+    if (live && k < K) { z[c] = __expf(z[c] - zmax); zs += z[c]; }
   }
   zs = warp_sum(zs);
   const float inv = 1.f / zs;
@@ -323,7 +333,7 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) 
 #pragma unroll
   for (int c = 0; c < kMaxH / 32; ++c) {
     const int k = c * 32 + lane;
-    if (k < K) {
+    if (live && k < K) {
       const float th = z[c] * inv;
       float m = 1.f;
       if (a.training && a.theta_drop_p > 0.f) {
@@ -343,7 +353,7 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) 
       a.mask_theta[o] = m;
       const float thd = th * m;
       a.theta[o] = thd;
-      if (a.theta_colsum != nullptr) atomicAdd(&a.theta_colsum[k], thd);
+      if (a.theta_colsum != nullptr) atomicAdd(&s_cs[k], thd);
       const float pv = a.prior_var[k], pm = a.prior_mean[k];
       const float var = __expf(lv[c]);
       const float d = pm - mu[c];
@@ -351,9 +361,13 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) 
     }
   }
   kl = 0.5f * warp_sum(kl);
-  if (lane == 0) {
+  if (live && lane == 0) {
     a.kl[b] = kl;
     if (a.loss != nullptr) atomicAdd(a.loss, (double)(kl * a.kl_weight));
+  }
+  if (a.theta_colsum != nullptr) {
+    __syncthreads();
+    for (int k = threadIdx.x; k < K; k += blockDim.x) atomicAdd(&a.theta_colsum[k], s_cs[k]);
   }
 }
 
