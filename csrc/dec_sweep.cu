@@ -396,6 +396,31 @@ sweep_kernel(const __grid_constant__ CUtensorMap tm_theta, const __grid_constant
         if (a_it > 0) mbar_wait(s.a_empty, (a_it - 1) & 1);
       }
     }
+  } else if (kMode == COL_GRAD2 && warp == 3) {
+    // ============================ drain prefetch (otherwise idle warp) ============================
+    // The drain of a word slab reads the slab's sparse correction (Kp rows x 512 bytes of a 166 MB array written
+    // just before this kernel, mostly out of L2 by now) and a few per-word scalars, in dependent steps with the
+    // tensor pipe idle.  Pull those lines into L2 while the slab's main loop runs.
+    uint32_t pf_it = 0;
+    for (int w = blockIdx.x; w < total_work; w += n_sweep, ++pf_it) {
+      // pace with the producer: slab n is fetched when the drain of slab n-1 has ended (same wait as the TMA warp)
+      mbar_wait(s.a_empty, (pf_it & 1) ^ 1);
+      const int stat = w / p.n_chunks;
+      const size_t w0 = (size_t)stat * kTile;
+      if (p.corr != nullptr) {
+        for (int i = (int)lane; i < p.K * 4; i += 32) {
+          const size_t col = w0 + (size_t)(i & 3) * 32;
+          if (col < (size_t)p.V)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.corr + (size_t)(i >> 2) * p.ldc + col));
+        }
+      }
+      if (lane < 4 && w0 + lane * 32 < (size_t)p.V) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p.asp + w0 + lane * 32));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p.csp + w0 + lane * 32));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p.colc + w0 + lane * 32));
+        if (p.colptr != nullptr) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.colptr + w0 + lane * 32));
+      }
+    }
   } else if (warp >= 4) {
     // ============================ epilogue ============================
     // Two warps per TMEM lane quarter (a warp may only touch lanes 32*(warp%4)..+31): warps 4..7 take
