@@ -103,7 +103,8 @@ class FederatedTrainer:
         if not hasattr(self, "_ctm_trick"):
             self._ctm_trick = False
         # CTAs that aggregate from the start of the d-theta sweep; every sweep CTA joins once it runs out of sweep work
-        # (measured at N=2, large config: 16 -> 3.42 ms/step, 40 -> 3.49; the same step trained locally 3.32)
+        # (measured, large config: N=2 4 / 8 / 16 CTAs -> 3.33 / 3.30 / 3.26 ms/step; N=8 2 / 4 / 8 / 16 -> 3.25 / 3.28 /
+        # 3.27 / 3.27, i.e. flat)
         nvls = bool(self.aggregator.args.ranks[0].P_mc)
         ctas = int(os.environ.get("GFEDNTM_AGG_CTAS", "16"))
         if (self.world > 1 and self.agg == "grad" and ctas >= 0 and eng.is_prod and eng.decoder.folded
