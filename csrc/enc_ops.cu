@@ -62,6 +62,42 @@ __device__ __forceinline__ unsigned long long step_seed(unsigned long long seed,
   return ctr != nullptr ? seed + (unsigned long long)ctr[0] * 0x9E3779B97F4A7C15ull : seed;
 }
 
+// Block-wide small product for the kDocsPerBlock documents of a block:
+//   out[r][m] += sum_{k < Kred} w(k, m) * in[r][k]        (out zeroed by the caller, shared memory)
+// Thread = (output m, slice of the reduction): every weight element is loaded ONCE for all documents of the block
+// and the loads of a slice are independent of each other (four in flight), instead of one thread per (document,
+// output) walking the whole reduction with a weight load in front of every FMA -- at batch 64 these chains of
+// dependent L2 round trips were most of enc_fwd / enc_bwd.  Partial sums meet in shared-memory atomics.
+template <typename WFn>
+__device__ __forceinline__ void block_matvec(float* out, int ldo, const float* in, int ldi, int M, int Kred, WFn w) {
+  const int G = max(1, (int)blockDim.x / M);
+  const int g = (int)threadIdx.x / M, m = (int)threadIdx.x - g * M;
+  if (g >= G) return;
+  const int per = (Kred + G - 1) / G;
+  const int k0 = g * per, k1 = min(Kred, k0 + per);
+  float acc[kDocsPerBlock];
+#pragma unroll
+  for (int r = 0; r < kDocsPerBlock; ++r) acc[r] = 0.f;
+  int k = k0;
+  for (; k + 4 <= k1; k += 4) {
+    const float w0 = w(k, m), w1 = w(k + 1, m), w2 = w(k + 2, m), w3 = w(k + 3, m);
+#pragma unroll
+    for (int r = 0; r < kDocsPerBlock; ++r) {
+      const float* x = in + r * ldi + k;
+      acc[r] = fmaf(w3, x[3], fmaf(w2, x[2], fmaf(w1, x[1], fmaf(w0, x[0], acc[r]))));
+    }
+  }
+  for (; k < k1; ++k) {
+    const float w0 = w(k, m);
+#pragma unroll
+    for (int r = 0; r < kDocsPerBlock; ++r) acc[r] = fmaf(w0, in[r * ldi + k], acc[r]);
+  }
+  if (k1 > k0) {
+#pragma unroll
+    for (int r = 0; r < kDocsPerBlock; ++r) atomicAdd(&out[r * ldo + m], acc[r]);
+  }
+}
+
 __global__ void __launch_bounds__(kDocsPerBlock * 32)
 enc_fwd_kernel(const GfEncArgs a_) {
   GfEncArgs a = a_;
@@ -155,24 +191,34 @@ enc_fwd_kernel(const GfEncArgs a_) {
         hbuf[0][warp][j] = act_fwd(a.act, acc[c], sl);
       }
     }
+  } else {
+    for (int j = lane; j < kMaxH; j += 32) hbuf[0][warp][j] = 0.f;  // rows past the batch: defined inputs below
   }
+  for (int idx = threadIdx.x; idx < kDocsPerBlock * kMaxH; idx += blockDim.x) (&hbuf[1][0][0])[idx] = 0.f;
   __syncthreads();
 
-  // ---- hidden layers 1..L-1 (all threads, outputs strided)
+  // ---- hidden layers 1..L-1: block_matvec accumulates W h into the (zeroed) other buffer, then bias + activation
   int cur = 0;
   for (int l = 1; l < a.L; ++l) {
     const int M = a.H[l - 1], N = a.H[l];
     const float* W = a.Wh[l - 1];
     const float* bias = a.bh[l - 1];
-    for (int idx = threadIdx.x; idx < kDocsPerBlock * N; idx += blockDim.x) {
-      const int r = idx / N, n = idx - r * N;
-      if (b0 + r >= a.B) continue;
-      float s = bias[n];
-      const float* wr = W + (size_t)n * M;
-      for (int m = 0; m < M; ++m) s = fmaf(__ldg(wr + m), hbuf[cur][r][m], s);
-      a.pre[l][(size_t)(b0 + r) * N + n] = s;
-      const float sl = rrelu_slope(a.act, a.training, a.seed, l, (uint64_t)(b0 + r) * N + n);
-      hbuf[cur ^ 1][r][n] = act_fwd(a.act, s, sl);
+    block_matvec(&hbuf[cur ^ 1][0][0], kMaxH, &hbuf[cur][0][0], kMaxH, N, M,
+                 [&](int m, int n) { return __ldg(W + (size_t)n * M + m); });
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < kDocsPerBlock * kMaxH; idx += blockDim.x) {
+      const int r = idx / kMaxH, n = idx - r * kMaxH;
+      hbuf[cur][r][n] = 0.f;  // accumulator of the next layer
+      if (n < N) {
+        float h = 0.f;
+        if (b0 + r < a.B) {
+          const float s = hbuf[cur ^ 1][r][n] + bias[n];
+          a.pre[l][(size_t)(b0 + r) * N + n] = s;
+          const float sl = rrelu_slope(a.act, a.training, a.seed, l, (uint64_t)(b0 + r) * N + n);
+          h = act_fwd(a.act, s, sl);
+        }
+        hbuf[cur ^ 1][r][n] = h;
+      }
     }
     __syncthreads();
     cur ^= 1;
@@ -207,9 +253,23 @@ enc_fwd_kernel(const GfEncArgs a_) {
   const int K = a.K;
   const int ldw = HL + 1;
   if (a.w_smem) {
-    for (int idx = threadIdx.x; idx < 2 * K * HL; idx += blockDim.x) {
-      const int n2 = idx / HL, m = idx - n2 * HL;
-      wsm[n2 * ldw + m] = __ldg((n2 >= K ? a.Wsig + (size_t)(n2 - K) * HL : a.Wmu + (size_t)n2 * HL) + m);
+    // (four independent loads in flight per thread: one load -> one store at a time was a chain of L2 round trips)
+    const int n_w = K * HL;  // Wmu and Wsig are contiguous [K, HL] each
+    for (int i0 = threadIdx.x; i0 < 2 * n_w; i0 += 4 * blockDim.x) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * (int)blockDim.x;
+        v[u] = (idx < 2 * n_w) ? __ldg(idx < n_w ? a.Wmu + idx : a.Wsig + (idx - n_w)) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * (int)blockDim.x;
+        if (idx < 2 * n_w) {
+          const int n2 = idx / HL, m = idx - n2 * HL;
+          wsm[n2 * ldw + m] = v[u];
+        }
+      }
     }
     __syncthreads();
   }
@@ -516,6 +576,7 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
       h = act_fwd(a.act, a.pre[L - 1][o], sl) * a.mask_enc[o];
     }
     hact[r][n] = h;
+    dcur[r][n] = 0.f;  // accumulator of the d h_last product below
   }
   __syncthreads();
 
@@ -536,18 +597,14 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
     atomicAdd(&(sg ? a.dbsig : a.dbmu)[sg ? n2 - K : n2], s);
   }
   // ---- d h_last = Wmu^T dmu_pre + Wsig^T dls_pre, then dropout mask
+  block_matvec(&dcur[0][0], kMaxH, &dhead[0][0], 2 * kMaxH, HL, 2 * K, [&](int k, int m) {
+    return __ldg((k < K ? a.Wmu + (size_t)k * HL : a.Wsig + (size_t)(k - K) * HL) + m);
+  });
+  __syncthreads();
   for (int idx = threadIdx.x; idx < kDocsPerBlock * HL; idx += blockDim.x) {
     const int r = idx / HL, m = idx - r * HL;
     const int bb = b0 + r;
-    float s = 0.f;
-    if (bb < a.B) {
-      for (int k = 0; k < K; ++k) {
-        s = fmaf(__ldg(a.Wmu + (size_t)k * HL + m), dhead[r][k], s);
-        s = fmaf(__ldg(a.Wsig + (size_t)k * HL + m), dhead[r][K + k], s);
-      }
-      s *= a.mask_enc[(size_t)bb * HL + m];
-    }
-    dcur[r][m] = s;
+    dcur[r][m] = (bb < a.B) ? dcur[r][m] * a.mask_enc[(size_t)bb * HL + m] : 0.f;
   }
   __syncthreads();
 
@@ -577,6 +634,7 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
         h = act_fwd(a.act, a.pre[l - 1][o], sl);
       }
       hact[r][m] = h;
+      dhead[r][m] = 0.f;  // (dhead is scratch from here on: accumulator of d h_{l-1})
     }
     __syncthreads();
     for (int idx = threadIdx.x; idx < N * M; idx += blockDim.x) {
@@ -593,11 +651,10 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
       atomicAdd(&a.dbh[l - 1][n], s);
     }
     // d h_{l-1} = W_l^T dpre_l  -> stage in dhead (reused as scratch), then copy to dcur
-    for (int idx = threadIdx.x; idx < kDocsPerBlock * M; idx += blockDim.x) {
-      const int r = idx / M, m = idx - r * M;
-      float s = 0.f;
-      for (int n = 0; n < N; ++n) s = fmaf(__ldg(a.Wh[l - 1] + (size_t)n * M + m), dcur[r][n], s);
-      dhead[r][m] = s;
+    {
+      const float* Wl = a.Wh[l - 1];
+      block_matvec(&dhead[0][0], 2 * kMaxH, &dcur[0][0], kMaxH, M, N,
+                   [&](int n, int m) { return __ldg(Wl + (size_t)n * M + m); });
     }
     __syncthreads();
     for (int idx = threadIdx.x; idx < kDocsPerBlock * M; idx += blockDim.x) {
