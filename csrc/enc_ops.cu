@@ -100,8 +100,10 @@ __device__ __forceinline__ void block_matvec(float* out, int ldo, const float* i
 
 __global__ void __launch_bounds__(kDocsPerBlock * 32)
 enc_fwd_kernel(const GfEncArgs a_) {
-  GfEncArgs a = a_;
-  a.seed = step_seed(a_.seed, a_.step_ctr);
+  // (the argument block stays in the constant bank: a modified local copy would live on the stack, and every
+  //  a.H[l] / a.pre[l] / a.Wh[l] with a run-time l would be a local-memory load in front of its use)
+  const GfEncArgs& a = a_;
+  const unsigned long long seed_ = step_seed(a_.seed, a_.step_ctr);
   __shared__ float hbuf[2][kDocsPerBlock][kMaxH];
   extern __shared__ float wsm[];  // optional staging of the head weights, rows padded to HL+1 (a.w_smem)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -187,7 +189,7 @@ enc_fwd_kernel(const GfEncArgs a_) {
       const int j = c * 32 + lane;
       if (j < H0) {
         a.pre[0][(size_t)b * H0 + j] = acc[c];
-        const float sl = rrelu_slope(a.act, a.training, a.seed, 0, (uint64_t)b * H0 + j);
+        const float sl = rrelu_slope(a.act, a.training, seed_, 0, (uint64_t)b * H0 + j);
         hbuf[0][warp][j] = act_fwd(a.act, acc[c], sl);
       }
     }
@@ -214,7 +216,7 @@ enc_fwd_kernel(const GfEncArgs a_) {
         if (b0 + r < a.B) {
           const float s = hbuf[cur ^ 1][r][n] + bias[n];
           a.pre[l][(size_t)(b0 + r) * N + n] = s;
-          const float sl = rrelu_slope(a.act, a.training, a.seed, l, (uint64_t)(b0 + r) * N + n);
+          const float sl = rrelu_slope(a.act, a.training, seed_, l, (uint64_t)(b0 + r) * N + n);
           h = act_fwd(a.act, s, sl);
         }
         hbuf[cur ^ 1][r][n] = h;
@@ -235,7 +237,7 @@ enc_fwd_kernel(const GfEncArgs a_) {
       if (a.mask_enc_in != nullptr) {
         m = a.mask_enc_in[(size_t)bb * HL + n];
       } else {
-        Philox ph(a.seed);
+        Philox ph(seed_);
         const uint4 rr = ph((uint64_t)bb * HL + n, 0x454e4300ull);
         m = (u32_to_unit(rr.x) > a.enc_drop_p) ? 1.f / (1.f - a.enc_drop_p) : 0.f;
       }
@@ -308,8 +310,10 @@ enc_fwd_kernel(const GfEncArgs a_) {
 // One warp per document; lanes stride over topics.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) {
-  GfLatentArgs a = a_;
-  a.seed = step_seed(a_.seed, a_.step_ctr);
+  // (the argument block stays in the constant bank: a modified local copy would live on the stack, and every
+  //  a.H[l] / a.pre[l] / a.Wh[l] with a run-time l would be a local-memory load in front of its use)
+  const GfLatentArgs& a = a_;
+  const unsigned long long seed_ = step_seed(a_.seed, a_.step_ctr);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * (blockDim.x >> 5) + warp;
   const int K = a.K;
@@ -369,7 +373,7 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) 
       if (a.eps_in != nullptr) {
         e = a.eps_in[(size_t)b * K + k];
       } else if (a.sample) {
-        Philox ph(a.seed);
+        Philox ph(seed_);
         const uint4 rr = ph((uint64_t)b * K + k, 0x45505300ull);
         e = box_muller(rr.x, rr.y).x;
       } else {
@@ -400,7 +404,7 @@ __global__ void __launch_bounds__(256) latent_fwd_kernel(const GfLatentArgs a_) 
         if (a.mask_theta_in != nullptr) {
           m = a.mask_theta_in[(size_t)b * K + k];
         } else {
-          Philox ph(a.seed);
+          Philox ph(seed_);
           const uint4 rr = ph((uint64_t)b * K + k, 0x54484500ull);
           m = (u32_to_unit(rr.x) > a.theta_drop_p) ? 1.f / (1.f - a.theta_drop_p) : 0.f;
         }
@@ -534,8 +538,10 @@ __global__ void __launch_bounds__(256) latent_bwd_kernel(const GfLatentBwdArgs a
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kDocsPerBlock * 32)
 enc_bwd_kernel(const GfEncBwdArgs a_) {
-  GfEncBwdArgs a = a_;
-  a.seed = step_seed(a_.seed, a_.step_ctr);
+  // (the argument block stays in the constant bank: a modified local copy would live on the stack, and every
+  //  a.H[l] / a.pre[l] / a.Wh[l] with a run-time l would be a local-memory load in front of its use)
+  const GfEncBwdArgs& a = a_;
+  const unsigned long long seed_ = step_seed(a_.seed, a_.step_ctr);
   __shared__ float hact[kDocsPerBlock][kMaxH];   // forward activation of the layer below
   __shared__ float dcur[kDocsPerBlock][kMaxH];   // gradient w.r.t. current layer output
   __shared__ float dhead[kDocsPerBlock][2 * kMaxH];  // d mu_pre | d ls_pre
@@ -572,7 +578,7 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
     float h = 0.f;
     if (bb < a.B) {
       const size_t o = (size_t)bb * HL + n;
-      const float sl = rrelu_slope(a.act, 1, a.seed, L - 1, o);
+      const float sl = rrelu_slope(a.act, 1, seed_, L - 1, o);
       h = act_fwd(a.act, a.pre[L - 1][o], sl) * a.mask_enc[o];
     }
     hact[r][n] = h;
@@ -618,7 +624,7 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
       float v = 0.f;
       if (bb < a.B) {
         const size_t o = (size_t)bb * N + n;
-        const float sl = rrelu_slope(a.act, 1, a.seed, l, o);
+        const float sl = rrelu_slope(a.act, 1, seed_, l, o);
         v = dcur[r][n] * act_bwd(a.act, a.pre[l][o], sl);
       }
       dcur[r][n] = v;
@@ -630,7 +636,7 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
       float h = 0.f;
       if (bb < a.B) {
         const size_t o = (size_t)bb * M + m;
-        const float sl = rrelu_slope(a.act, 1, a.seed, l - 1, o);
+        const float sl = rrelu_slope(a.act, 1, seed_, l - 1, o);
         h = act_fwd(a.act, a.pre[l - 1][o], sl);
       }
       hact[r][m] = h;
@@ -672,7 +678,7 @@ enc_bwd_kernel(const GfEncBwdArgs a_) {
     float v = 0.f;
     if (bb < a.B) {
       const size_t o = (size_t)bb * H0 + n;
-      const float sl = rrelu_slope(a.act, 1, a.seed, 0, o);
+      const float sl = rrelu_slope(a.act, 1, seed_, 0, o);
       v = dcur[r][n] * act_bwd(a.act, a.pre[0][o], sl);
       a.dpre0[o] = v;
     }
