@@ -137,19 +137,49 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
     dist.destroy_process_group()
 
 
+def supervise(launch, *, max_restarts: int = 0, can_resume: bool = False, log=None) -> int:
+    """Failure recovery of the fabric path: ``launch(resume, attempt)`` runs all ranks to completion and raises
+    when one of them dies (a crashed process, or the device-side trap the other ranks take 120 s after a peer's flag
+    stopped advancing, ``csrc/fabric_dev.cuh``).  The federation is synchronous -- every step needs every rank -- so
+    recovery is a restart of ALL ranks from the last common checkpoint: up to ``max_restarts`` times when the run
+    writes checkpoints.  Returns the number of restarts that were needed.  (The reference has no recovery: a client
+    that dies leaves the server waiting)"""
+    import logging
+
+    log = log or logging.getLogger("gfedntm.fabric")
+    attempt = 0
+    while True:
+        try:
+            launch(attempt > 0, attempt)
+            return attempt
+        except KeyboardInterrupt:
+            raise
+        except BaseException as ex:  # mp.spawn raises ProcessRaisedException / ProcessExitedException
+            if attempt >= max_restarts or not can_resume:
+                raise
+            attempt += 1
+            log.warning("fabric federation failed (%s: %s); restart %d of %d from the last checkpoint",
+                        type(ex).__name__, str(ex).splitlines()[0] if str(ex) else "", attempt, max_restarts)
+
+
 def run_fabric_federation(*, n_clients: int, source: str, data_type: str, fos: str, model_type: str,
                           training_params: dict, max_iters: int, save_client: str, save_server: str,
                           logs_client: str, agg: str = "grad", port: Optional[int] = None,
                           grads_to_share: Optional[list] = None, checkpoint_dir: Optional[str] = None,
-                          checkpoint_every: int = 0, resume: bool = False) -> None:
+                          checkpoint_every: int = 0, resume: bool = False, max_restarts: int = 0) -> None:
     import torch
     import torch.multiprocessing as mp
 
     if torch.cuda.device_count() < n_clients:
         raise RuntimeError(f"--fabric {n_clients} needs {n_clients} GPUs, found {torch.cuda.device_count()}")
     port = port or (29400 + os.getpid() % 500)
-    kw = dict(source=source, data_type=data_type, fos=fos, model_type=model_type,
-              training_params=training_params, max_iters=max_iters, save_client=save_client,
-              save_server=save_server, logs_client=logs_client, agg=agg, grads_to_share=grads_to_share,
-              checkpoint_dir=checkpoint_dir, checkpoint_every=checkpoint_every, resume=resume)
-    mp.spawn(_worker, args=(n_clients, port, kw), nprocs=n_clients, join=True)
+
+    def launch(resume_now: bool, attempt: int) -> None:
+        kw = dict(source=source, data_type=data_type, fos=fos, model_type=model_type,
+                  training_params=training_params, max_iters=max_iters, save_client=save_client,
+                  save_server=save_server, logs_client=logs_client, agg=agg, grads_to_share=grads_to_share,
+                  checkpoint_dir=checkpoint_dir, checkpoint_every=checkpoint_every, resume=resume or resume_now)
+        # (a fresh rendezvous port per attempt: the previous store may still be in TIME_WAIT)
+        mp.spawn(_worker, args=(n_clients, port + attempt, kw), nprocs=n_clients, join=True)
+
+    supervise(launch, max_restarts=max_restarts, can_resume=bool(checkpoint_dir) and checkpoint_every > 0)

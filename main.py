@@ -126,6 +126,9 @@ def main(argv=None):
     parser.add_argument("--checkpoint_dir", type=str, default=os.path.join(WORKDIR, "static/checkpoints"),
                         help="Directory of the mid-training checkpoints.")
     parser.add_argument("--resume", action="store_true", help="Continue from the checkpoint in --checkpoint_dir.")
+    parser.add_argument("--max_restarts", type=int, default=0,
+                        help="--fabric: restart all ranks from the last checkpoint when one of them dies, at most this "
+                             "many times (needs --checkpoint_every).")
     args = parser.parse_args(argv)
 
     from gfedntm_b200.utils.auxiliary_functions import read_config_experiments
@@ -167,7 +170,8 @@ def main(argv=None):
                                      max_iters=args.max_iters, save_client=save_client, save_server=save_server,
                                      logs_client=logs_client, agg="grad" if agg == "grad" else "param",
                                      grads_to_share=grads_to_share, checkpoint_dir=args.checkpoint_dir,
-                                     checkpoint_every=args.checkpoint_every, resume=args.resume)
+                                     checkpoint_every=args.checkpoint_every, resume=args.resume,
+                                     max_restarts=args.max_restarts)
     if args.id == 0:
         print("Starting server with", args.min_clients_federation,
               "as minimum number of clients to start the federation.")

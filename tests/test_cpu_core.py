@@ -517,3 +517,26 @@ def test_prometheus_exporter_counts_iterations():
     text = ex.scrape()
     assert "gfedntm_global_iterations_total 2.0" in text and "gfedntm_active_clients 2.0" in text
     assert "gfedntm_payload_bytes_total 1000.0" in text and "gfedntm_rpc_failures_total 1.0" in text
+
+
+def test_fabric_supervisor_restarts_from_checkpoint_and_gives_up():
+    """Failure recovery of the fabric path: a launch that dies is repeated with resume=True while restarts are left."""
+    from gfedntm_b200.federated.fabric_run import supervise
+
+    calls = []
+
+    def flaky(resume, attempt):
+        calls.append((resume, attempt))
+        if attempt < 2:
+            raise RuntimeError("rank 3 exited with code -6")
+
+    assert supervise(flaky, max_restarts=3, can_resume=True) == 2
+    assert calls == [(False, 0), (True, 1), (True, 2)]
+    calls.clear()
+    with pytest.raises(RuntimeError):          # no checkpoints -> nothing to resume from: fail at once
+        supervise(flaky, max_restarts=3, can_resume=False)
+    assert calls == [(False, 0)]
+    calls.clear()
+    with pytest.raises(RuntimeError):          # restarts exhausted
+        supervise(flaky, max_restarts=1, can_resume=True)
+    assert calls == [(False, 0), (True, 1)]
