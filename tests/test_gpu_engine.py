@@ -147,6 +147,11 @@ def test_engine_loss_decreases_and_theta_inference():
     losses = [eng.train_step(batch).item() for _ in range(150)]
     assert all(l == l for l in losses)
     assert losses[-1] < 0.9 * losses[0], (losses[0], losses[-1])
+    # every step also leaves its loss in a pinned host slot (copied by the step's own CUDA graph on the side stream)
+    for _ in range(3):
+        dev_loss = eng.train_step(batch)
+        torch.cuda.synchronize()
+        assert eng.loss_slot.is_pinned() and float(eng.loss_slot[0]) == float(dev_loss.item())
     theta = eng.sample_theta(batch, n_samples=5)
     torch.testing.assert_close(theta.sum(1), torch.ones(B, device="cuda"), rtol=1e-4, atol=1e-4)
     val = eng.forward_backward(batch, training=False, sample=True, need_grad=False)
