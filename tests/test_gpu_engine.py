@@ -345,3 +345,16 @@ def test_engine_supervised_head_matches_autograd(kind):
     ctx_rows = slice(w.offset + w.numel - (L + C) * 32, w.offset + w.numel - L * 32) if kind == "zeroshot" else \
         slice(w.offset + V * 32, w.offset + 2 * V * 32)
     assert float((eng.flat.P[ctx_rows] - before[ctx_rows]).abs().max()) > 0
+
+
+@pytest.mark.parametrize("rows,V,k", [(7, 1000, 10), (50, 20011, 15), (3, 33, 32)])
+def test_row_topk_matches_torch(rows, V, k):
+    """Top words per topic (get_topics; ref avitm.py:574 torch.topk per row)."""
+    from gfedntm_b200.ops import kernels as K_
+
+    g = torch.Generator(device="cuda").manual_seed(rows * 131 + V)
+    mat = torch.randn(rows, V, device="cuda", generator=g)
+    val, idx = K_.row_topk(mat, k)
+    ref_val, ref_idx = torch.topk(mat, k, dim=1)
+    torch.testing.assert_close(val, ref_val, rtol=0, atol=0)
+    assert torch.equal(idx, ref_idx)
