@@ -14,11 +14,11 @@ from __future__ import annotations
 
 import os
 from dataclasses import dataclass
-from typing import Dict, List, Optional, Tuple
+from typing import Dict, Optional, Tuple
 
 import torch
 
-from ..models.networks import ENCODER_DROPOUT, DecoderNetwork
+from ..models.networks import DecoderNetwork
 from ..ops import kernels as K_
 from ..ops.decoder import (CscWorkspace, CsrBatch, ProdLDADecoder, make_beta_shadows,
                            refresh_beta_shadows)

@@ -28,7 +28,6 @@ def _worker(rank: int, world: int, port: int, kw: dict) -> None:
 
     from ..models.data_preparation import TopicModelDataPreparation
     from ..models.datasets import BOWDataset
-    from ..utils.metrics import thresholded_thetas
     from .federated_avitm import FederatedAVITM
     from .federated_ctm import FederatedCTM
     from .trainer import FederatedTrainer

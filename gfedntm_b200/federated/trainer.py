@@ -211,8 +211,6 @@ class FederatedTrainer:
         self.global_step += 1
         if self.world == 1:
             return eng.train_step(bow, x_ctx, labels=labels)
-        from ..ops import kernels as K_
-
         if self._overlap is not None and self.agg == "grad":
             self._beta_master_partial = True
 

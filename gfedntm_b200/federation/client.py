@@ -8,7 +8,6 @@ are ignored; the client wakes up when the server's STOP arrives instead of sleep
 """
 from __future__ import annotations
 
-import logging
 import os
 import threading
 import time

@@ -16,7 +16,6 @@ from __future__ import annotations
 import datetime
 import logging
 import os
-from collections import defaultdict
 from typing import List, Optional
 
 import numpy as np

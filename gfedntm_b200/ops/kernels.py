@@ -6,7 +6,6 @@ on the current CUDA stream.  There is no CPU or PyTorch fallback in this module.
 from __future__ import annotations
 
 import ctypes as C
-import math
 from typing import Optional, Sequence
 
 import torch

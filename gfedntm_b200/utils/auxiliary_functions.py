@@ -9,8 +9,7 @@ from __future__ import annotations
 
 import configparser
 import pickle
-from collections import OrderedDict
-from typing import Dict, Iterable, Optional
+from typing import Dict, Iterable
 
 import numpy as np
 import torch

@@ -9,11 +9,9 @@ previous checkpoint.
 from __future__ import annotations
 
 import os
-import pickle
 import tempfile
 from typing import Optional
 
-import numpy as np
 import torch
 
 

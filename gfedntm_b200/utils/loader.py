@@ -11,7 +11,6 @@ avitm.py:371-375 (dense rows, default collate, ``.cuda()`` per batch).
 """
 from __future__ import annotations
 
-import ctypes as C
 import queue
 import threading
 from dataclasses import dataclass

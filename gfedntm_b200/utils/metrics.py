@@ -8,7 +8,7 @@
 """
 from __future__ import annotations
 
-from typing import List, Sequence
+from typing import Sequence
 
 import numpy as np
 import scipy.sparse as sp
