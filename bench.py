@@ -10,8 +10,11 @@ aggregate every step (weighted by corpus size) through the fused NVLink collecti
 
 Prints ONE JSON line on rank 0.  ``value`` is the device-timed (CUDA events, max over ranks)
 aggregate docs/s with the minibatches already resident on the device; ``e2e`` is the same metric
-through the public trainer API with every step's minibatch assembled on the host, copied from
-pinned memory, and the loss read back.
+through the public API (``CsrMinibatchLoader.cycle()`` + ``FederatedTrainer.step``), wall clock, max over
+ranks: every step's minibatch is gathered from the host corpus into pinned memory and copied to the
+device (``h2d_bytes_per_step``), and every step's loss reaches the host inside the timed region -- the
+step's own CUDA graph copies it into a pinned slot (``engine.loss_slot``, 8 bytes) which the host reads
+one step behind the GPU.  ``e2e.gpu_ms_per_step`` is the same loop timed with CUDA events.
 """
 from __future__ import annotations
 
